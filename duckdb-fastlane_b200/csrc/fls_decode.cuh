@@ -1,0 +1,297 @@
+// fls_decode.cuh — per-vector decoders for fixed-width columns (one warp = one 1024-value vector).
+//
+// Each decoder is a struct with
+//   SMEM            bytes of per-warp shared scratch it needs (staging slot + tiles)
+//   run(w, ...)     called by ALL lanes of the warp with warp-uniform arguments; per-lane work sits inside
+//                   FLS_LANES(t) { ... } regions (see fls_dev.cuh).
+//
+// Restated FastLanes primitives (upstream source absent):
+//   DecFFOR  = unffor                      DecDELTA = unffor + rsum + untranspose (App. A.3)
+//   DecRLE   = rle_map                     DecDICT  = dict gather
+//   DecALP   = alp decode + patch (twin: duckdb .../alp/algorithm/alp.hpp:129-134,376-404)
+//   DecALPRD = alp_rd decode + patch (twin: duckdb .../alprd/algorithm/alprd.hpp:206-233)
+#pragma once
+#include "fls_dev.cuh"
+
+template <typename T> struct FlsRowGeom {            // thread (q,g): rows g*RPT .. g*RPT+RPT-1, bytes [16q,16q+16)
+  static constexpr uint32_t TB = sizeof(T) * 8u;     // bits per value = rows per vector
+  static constexpr uint32_t RPT = TB / 4u;           // rows per thread
+};
+
+// broadcast a T-sized pattern into 16 bytes
+template <typename T> FLS_DEV fls_u4 fls_splat(uint64_t v) {
+  if (sizeof(T) == 1) v = (v & 0xFFull) * 0x0101010101010101ull;
+  else if (sizeof(T) == 2) v = (v & 0xFFFFull) * 0x0001000100010001ull;
+  else if (sizeof(T) == 4) v = (v & 0xFFFFFFFFull) * 0x0000000100000001ull;
+  fls_u4 o;
+  o.x = (uint32_t)v; o.y = (uint32_t)(v >> 32); o.z = o.x; o.w = o.y;
+  return o;
+}
+
+// one row (16 bytes per thread) of a packed T-vector
+template <typename T> FLS_DEV fls_u4 fls_unpack_row(const uint8_t *sm, uint32_t W, uint32_t row, uint32_t q, uint64_t base) {
+  if (sizeof(T) == 8) {
+    const fls_ul2 v = fls_unpack64_row(sm, W, row, q, base);
+    fls_u4 o;
+    o.x = (uint32_t)v.x; o.y = (uint32_t)(v.x >> 32); o.z = (uint32_t)v.y; o.w = (uint32_t)(v.y >> 32);
+    return o;
+  } else if (sizeof(T) == 4) {
+    return fls_unpack32_row(sm, W, row, q, (uint32_t)base);
+  } else if (sizeof(T) == 2) {
+    return fls_unpack16_row(sm, W, row, q, (uint32_t)base & 0xFFFFu);
+  } else {
+    return fls_unpack8_row(sm, W, row, q, (uint32_t)base & 0xFFu);
+  }
+}
+
+// ===================================================================== FFOR
+// payload: [packed 128*bw]
+template <typename T> struct DecFFOR {
+  static constexpr uint32_t SMEM = 128u * sizeof(T) * 8u;
+  FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
+    constexpr uint32_t RPT = FlsRowGeom<T>::RPT;
+    if (bw == 0) {
+      const fls_u4 pat = fls_splat<T>(base);
+      FLS_LANES(t) {
+        const uint32_t q = t & 7u, g = t >> 3;
+#pragma unroll 4
+        for (uint32_t j = 0; j < RPT; ++j) fls_st128((uint8_t *)out + (g * RPT + j) * 128u + q * 16u, pat);
+      }
+      return;
+    }
+    w.stage(0, in, 128u * bw);
+    w.wait();
+    FLS_LANES(t) {
+      const uint32_t q = t & 7u, g = t >> 3;
+#pragma unroll 4
+      for (uint32_t j = 0; j < RPT; ++j) {
+        const uint32_t row = g * RPT + j;
+        fls_st128((uint8_t *)out + row * 128u + q * 16u, fls_unpack_row<T>(w.sm, bw, row, q, base));
+      }
+    }
+  }
+};
+
+// ===================================================================== DELTA
+// payload: [lane bases 128 B][packed deltas 128*bw]; deltas are FFOR'd (wrapping + base).
+template <typename T> struct DecDELTA {
+  static constexpr uint32_t TB = sizeof(T) * 8u, L = 1024u / TB;
+  static constexpr uint32_t STAGE = 128u + 128u * TB;
+  static constexpr uint32_t XCH = STAGE + FLS_TILE_BYTES(T);          // T=64 half-lane totals
+  static constexpr uint32_t SMEM = XCH + (sizeof(T) == 8 ? 256u : 0u);
+
+  // Reconstruct into the warp's padded tile (original order).  `add` is added to every value (string offsets).
+  FLS_MEM static void to_tile(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base) {
+    w.stage(0, in, 128u + 128u * bw);
+    w.wait();
+    const T *bases = (const T *)w.sm;
+    const T *pk = (const T *)(w.sm + 128);
+    T *tile = (T *)(w.sm + STAGE);
+    if (sizeof(T) == 8) {
+      // 16 lanes x 64 steps: thread (l = t&15, h = t>>4) owns steps [32h, 32h+32); the upper half needs the
+      // lower half's total first.
+      uint64_t *xch = (uint64_t *)(w.sm + XCH);
+      FLS_LANES(t) {
+        const uint32_t l = t & 15u, h = t >> 4;
+        uint64_t tot = 0;
+        if (bw)
+          for (uint32_t r = 32u * h; r < 32u * h + 32u; ++r) tot += (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l);
+        xch[t] = tot + 32ull * base;
+      }
+      FLS_LANES(t) {
+        const uint32_t l = t & 15u, h = t >> 4;
+        uint64_t acc = (uint64_t)bases[l] + (h ? xch[l] : 0ull);
+        for (uint32_t r = 32u * h; r < 32u * h + 32u; ++r) {
+          acc += (bw ? (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l) : 0ull) + base;
+          tile[fls_tile_slot<T>(64u * l + r)] = (T)acc;
+        }
+      }
+    } else {
+      constexpr uint32_t LPT = L / 32u;  // lanes per thread: 1 (T=32), 2 (T=16), 4 (T=8)
+      FLS_LANES(t) {
+        for (uint32_t a = 0; a < LPT; ++a) {
+          const uint32_t l = t * LPT + a;
+          T acc = bases[l];
+          const uint32_t e0 = fls_lane_start(l);
+          for (uint32_t r = 0; r < TB; ++r) {
+            acc = (T)(acc + (bw ? fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l) : (T)0) + (T)base);
+            tile[fls_tile_slot<T>(e0 + r)] = acc;
+          }
+        }
+      }
+    }
+  }
+  FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
+    to_tile(w, in, bw, base);
+    FLS_LANES(t) { fls_tile_copy_out<T>(w.sm + STAGE, out, t); }
+  }
+};
+
+// ===================================================================== RLE
+// payload: [run values n x T, pad16][idx lane bases 64 x u16][idx packed 128*bw, bw in {0,1}]
+// The run-index stream is a u16 vector in the transposed layout with 0/1 deltas.  Rare scheme: the index
+// stream is staged, run values are gathered straight from global memory (L1-resident, <= 8 KB).
+template <typename T> struct DecRLE {
+  static constexpr uint32_t STAGE = 256u;
+  static constexpr uint32_t SMEM = STAGE + FLS_TILE_BYTES(T);
+  FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint32_t n_runs, T *out) {
+    const T *runs = (const T *)in;
+    const uint8_t *q = in + (((uint64_t)n_runs * sizeof(T) + 15u) & ~(uint64_t)15u);
+    w.stage(0, q, 128u + 128u * bw);
+    w.wait();
+    const uint16_t *bases = (const uint16_t *)w.sm;
+    const uint16_t *pk = (const uint16_t *)(w.sm + 128);
+    T *tile = (T *)(w.sm + STAGE);
+    FLS_LANES(t) {
+      for (uint32_t a = 0; a < 2u; ++a) {
+        const uint32_t l = 2u * t + a;
+        uint32_t idx = bases[l];
+        const uint32_t e0 = fls_lane_start(l);
+        for (uint32_t r = 0; r < 16u; ++r) {
+          if (bw) idx += fls_extract<uint16_t>(pk, bw, fls_chain_row<16>(r), l);
+          tile[fls_tile_slot<T>(e0 + r)] = fls_ldg(runs + (idx & 0x3FFu));
+        }
+      }
+    }
+    FLS_LANES(t) { fls_tile_copy_out<T>(w.sm + STAGE, out, t); }
+  }
+};
+
+// ===================================================================== DICT (u32 FFOR indices -> gather)
+// payload: [packed 128*bw] of u32 lanes; dictionary = raw T values, one per row group (L1/L2 resident).
+template <typename T> struct DecDICT {
+  static constexpr uint32_t SMEM = 4096u;
+  FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, const T *dict, uint32_t n_dict,
+                          T *out) {
+    if (bw) { w.stage(0, in, 128u * bw); w.wait(); }
+    FLS_LANES(t) {
+      const uint32_t q = t & 7u, g = t >> 3;
+      for (uint32_t j = 0; j < 8u; ++j) {
+        const uint32_t row = g * 8u + j;
+        fls_u4 ix;
+        if (bw) ix = fls_unpack32_row(w.sm, bw, row, q, (uint32_t)base);
+        else { ix.x = ix.y = ix.z = ix.w = (uint32_t)base; }
+        T v[4];
+        v[0] = fls_ldg(dict + fls_min(ix.x, n_dict - 1u));
+        v[1] = fls_ldg(dict + fls_min(ix.y, n_dict - 1u));
+        v[2] = fls_ldg(dict + fls_min(ix.z, n_dict - 1u));
+        v[3] = fls_ldg(dict + fls_min(ix.w, n_dict - 1u));
+        T *o = out + row * 32u + q * 4u;
+        if (sizeof(T) == 8) {
+          fls_ul2 a, b;
+          a.x = (uint64_t)v[0]; a.y = (uint64_t)v[1]; b.x = (uint64_t)v[2]; b.y = (uint64_t)v[3];
+          fls_st128(o, a); fls_st128(o + 2, b);
+        } else if (sizeof(T) == 4) {
+          fls_u4 a;
+          a.x = (uint32_t)v[0]; a.y = (uint32_t)v[1]; a.z = (uint32_t)v[2]; a.w = (uint32_t)v[3];
+          fls_st128(o, a);
+        } else {
+          o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3];
+        }
+      }
+    }
+  }
+};
+
+// ===================================================================== ALP (f64)
+// payload: [packed 128*bw][exc values n x f64, pad16][exc positions n x u16, pad16]
+// value = (double)(int64)(bits + for) * (double)FACT[f] * FRAC[e]  — int->fp convert, then two separately
+// rounded IEEE multiplies in this order (alp.hpp:129-134); never fused, never reassociated.
+#ifdef FLS_HOST_EMUL
+#define FLS_CONST_TABLE static const
+#else
+#define FLS_CONST_TABLE __device__ const
+#endif
+FLS_CONST_TABLE double fls_alp_frac[21] = {  // alp_constants.hpp:112-132 (FRAC_ARR), literals verbatim
+    1.0, 0.1, 0.01, 0.001, 0.0001, 0.00001, 0.000001, 0.0000001, 0.00000001, 0.000000001, 0.0000000001,
+    0.00000000001, 0.000000000001, 0.0000000000001, 0.00000000000001, 0.000000000000001, 0.0000000000000001,
+    0.00000000000000001, 0.000000000000000001, 0.0000000000000000001, 0.00000000000000000001};
+FLS_CONST_TABLE double fls_alp_fact[19] = {  // (double)FACT_ARR[f] (alp_constants.hpp:43-61); 10^f, f<=18, is exact
+    1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18};
+
+FLS_DEV uint64_t fls_alp_value(uint64_t bits, double fact, double frac) {
+#ifdef FLS_HOST_EMUL
+  volatile double a = (double)(int64_t)bits * fact;
+  volatile double b = a * frac;
+  double r = b;
+  uint64_t u;
+  memcpy(&u, &r, 8);
+  return u;
+#else
+  return (uint64_t)__double_as_longlong(__dmul_rn(__dmul_rn(__ll2double_rn((long long)bits), fact), frac));
+#endif
+}
+
+struct DecALP {
+  static constexpr uint32_t SMEM = 8192u;
+  FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint32_t e, uint32_t f, uint32_t n_exc,
+                          uint64_t base, double *out) {
+    const double fact = fls_alp_fact[f < 19u ? f : 18u], frac = fls_alp_frac[e < 21u ? e : 20u];
+    if (bw) { w.stage(0, in, 128u * bw); w.wait(); }
+    FLS_LANES(t) {
+      const uint32_t q = t & 7u, g = t >> 3;
+#pragma unroll 4
+      for (uint32_t j = 0; j < 16u; ++j) {
+        const uint32_t row = g * 16u + j;
+        fls_ul2 v;
+        if (bw) v = fls_unpack64_row(w.sm, bw, row, q, base);
+        else { v.x = base; v.y = base; }
+        v.x = fls_alp_value(v.x, fact, frac);
+        v.y = fls_alp_value(v.y, fact, frac);
+        fls_st128((uint8_t *)out + row * 128u + q * 16u, v);
+      }
+    }
+    if (n_exc) {  // patches land after the region barrier above, so they win over the decoded values
+      const uint64_t *xv = (const uint64_t *)(in + 128ull * bw);
+      const uint16_t *xp = (const uint16_t *)(in + 128ull * bw + (((uint64_t)n_exc * 8u + 15u) & ~15ull));
+      FLS_LANES(t) {
+        for (uint32_t i = t; i < n_exc; i += 32u) ((uint64_t *)out)[fls_ldg(xp + i) & 1023u] = fls_ldg(xv + i);
+      }
+    }
+  }
+};
+
+// ===================================================================== ALP-RD (f64 bit patterns)
+// payload: [right packed 128*rbw (u64 lanes)][left packed 128*lbw (u16 lanes)][exc left n x u16, pad16]
+//          [exc pos n x u16, pad16];  out = (dict[left] << rbw) | right; exceptions replace the left part.
+struct DecALPRD {
+  static constexpr uint32_t SMEM = 8192u + 128u * 16u;
+  FLS_MEM static uint64_t dict_at(uint64_t lo, uint64_t hi, uint32_t i) {
+    const uint64_t d = (i & 4u) ? hi : lo;
+    return (d >> (16u * (i & 3u))) & 0xFFFFull;
+  }
+  FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t rbw, uint32_t lbw, uint32_t n_exc, uint64_t dict_lo,
+                          uint64_t dict_hi, uint64_t *out) {
+    w.stage(0, in, 128u * (rbw + lbw));  // right and left parts are adjacent in the payload
+    w.wait();
+    const uint8_t *right = w.sm;
+    const uint16_t *left = (const uint16_t *)(w.sm + 128u * rbw);
+    const uint32_t sh = rbw & 63u;  // rbw in [48,63]
+    FLS_LANES(t) {
+      const uint32_t q = t & 7u, g = t >> 3;
+#pragma unroll 2
+      for (uint32_t j = 0; j < 16u; ++j) {
+        const uint32_t row = g * 16u + j, p = row * 16u + q * 2u;  // positions p, p+1
+        fls_ul2 v;
+        if (rbw) v = fls_unpack64_row(right, rbw, row, q, 0);
+        else { v.x = 0; v.y = 0; }
+        const uint32_t l0 = lbw ? fls_extract<uint16_t>(left, lbw, p >> 6, p & 63u) : 0u;
+        const uint32_t l1 = lbw ? fls_extract<uint16_t>(left, lbw, (p + 1u) >> 6, (p + 1u) & 63u) : 0u;
+        v.x |= dict_at(dict_lo, dict_hi, l0 & 7u) << sh;
+        v.y |= dict_at(dict_lo, dict_hi, l1 & 7u) << sh;
+        fls_st128((uint8_t *)out + row * 128u + q * 16u, v);
+      }
+    }
+    if (n_exc) {
+      const uint16_t *xl = (const uint16_t *)(in + 128ull * (rbw + lbw));
+      const uint16_t *xp = (const uint16_t *)((const uint8_t *)xl + (((uint64_t)n_exc * 2u + 15u) & ~15ull));
+      FLS_LANES(t) {
+        for (uint32_t i = t; i < n_exc; i += 32u) {
+          const uint32_t p = fls_ldg(xp + i) & 1023u;
+          const uint64_t r = rbw ? fls_extract<uint64_t>((const uint64_t *)right, rbw, p >> 4, p & 15u) : 0ull;
+          out[p] = ((uint64_t)fls_ldg(xl + i) << sh) | r;
+        }
+      }
+    }
+  }
+};

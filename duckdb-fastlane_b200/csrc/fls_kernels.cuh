@@ -1,0 +1,132 @@
+// fls_kernels.cuh — chunk descriptors and the per-vector entry points the kernels (and tests/emul) call.
+//
+// One launch decodes one column over a whole batch of row groups: grid = (ceil(64/4), n_chunks), block = 4
+// warps, warp w of block (bx,by) decodes vector 4*bx+w of chunk by.  A chunk = one (row group, column).
+#pragma once
+#include "fls_decode.cuh"
+
+// Device-visible descriptor of one column chunk; built on the host by fls_plan.h.
+struct FlsChunkDev {
+  const uint8_t *seg[FLS_MAX_SEGS];  // device addresses of the chunk's segments
+  void *out;      // fixed width: first output value of this row group; strings: &offsets[first row of rg]
+  uint8_t *pay;   // strings: batch payload base
+  uint32_t n_vec;
+  uint32_t aux32;
+  uint32_t pay_base;  // strings: this row group's first payload byte, relative to `pay`
+  uint32_t scheme;
+  uint64_t aux64[2];
+};
+
+FLS_DEV fls_vechdr fls_load_hdr(const FlsChunkDev &k, uint32_t seg, uint32_t v) {
+  const uint64_t *p = (const uint64_t *)(k.seg[seg]) + 2ull * v;
+  const uint64_t a = fls_ldg(p), b = fls_ldg(p + 1);
+  fls_vechdr h;
+  h.ep = (uint32_t)a; h.meta = (uint32_t)(a >> 32); h.base = b;
+  return h;
+}
+
+template <typename T> struct VecFFOR {
+  static constexpr uint32_t SMEM = DecFFOR<T>::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    const uint32_t bw = FLS_META_BW(h.meta);
+    DecFFOR<T>::run(w, k.seg[1] + 16ull * h.ep, bw > sizeof(T) * 8u ? (uint32_t)sizeof(T) * 8u : bw, h.base,
+                    (T *)k.out + (size_t)v * FLS_VEC);
+  }
+};
+template <typename T> struct VecDELTA {
+  static constexpr uint32_t SMEM = DecDELTA<T>::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    const uint32_t bw = FLS_META_BW(h.meta);
+    DecDELTA<T>::run(w, k.seg[1] + 16ull * h.ep, bw > sizeof(T) * 8u ? (uint32_t)sizeof(T) * 8u : bw, h.base,
+                     (T *)k.out + (size_t)v * FLS_VEC);
+  }
+};
+template <typename T> struct VecRLE {
+  static constexpr uint32_t SMEM = DecRLE<T>::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    DecRLE<T>::run(w, k.seg[1] + 16ull * h.ep, FLS_META_BW(h.meta) ? 1u : 0u, FLS_META_N(h.meta),
+                   (T *)k.out + (size_t)v * FLS_VEC);
+  }
+};
+template <typename T> struct VecDICT {
+  static constexpr uint32_t SMEM = DecDICT<T>::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    const uint32_t bw = FLS_META_BW(h.meta);
+    DecDICT<T>::run(w, k.seg[1] + 16ull * h.ep, bw > 32u ? 32u : bw, h.base, (const T *)k.seg[2], k.aux32,
+                    (T *)k.out + (size_t)v * FLS_VEC);
+  }
+};
+struct VecALP {
+  static constexpr uint32_t SMEM = DecALP::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    const uint32_t bw = FLS_META_BW(h.meta);
+    DecALP::run(w, k.seg[1] + 16ull * h.ep, bw > 64u ? 64u : bw, FLS_META_E(h.meta), FLS_META_F(h.meta),
+                FLS_META_N(h.meta), h.base, (double *)k.out + (size_t)v * FLS_VEC);
+  }
+};
+struct VecALPRD {
+  static constexpr uint32_t SMEM = DecALPRD::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    uint32_t rbw = k.aux32 & 0xFFu, lbw = (k.aux32 >> 8) & 0xFFu;
+    if (rbw > 63u) rbw = 63u;
+    if (lbw > 16u) lbw = 16u;
+    DecALPRD::run(w, k.seg[1] + 16ull * h.ep, rbw, lbw, FLS_META_N(h.meta), k.aux64[0], k.aux64[1],
+                  (uint64_t *)k.out + (size_t)v * FLS_VEC);
+  }
+};
+
+#define FLS_WARPS_PER_BLOCK 4
+
+#ifndef FLS_HOST_EMUL
+// Shared memory layout of a block: [warp 0 slot | ... | warp 3 slot | block-shared (V::BLOCK_SMEM) | 4 mbarriers]
+template <class V> constexpr uint32_t fls_block_smem() {
+  return FLS_WARPS_PER_BLOCK * V::SMEM + V::BLOCK_SMEM + FLS_WARPS_PER_BLOCK * 8u;
+}
+
+template <class V>
+__global__ void __launch_bounds__(FLS_WARPS_PER_BLOCK * 32) fls_vec_kernel(const FlsChunkDev *__restrict__ chunks) {
+  extern __shared__ __align__(128) uint8_t fls_smem[];
+  const FlsChunkDev &k = chunks[blockIdx.y];
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t v = blockIdx.x * FLS_WARPS_PER_BLOCK + warp;
+  uint8_t *bsm = fls_smem + FLS_WARPS_PER_BLOCK * V::SMEM;
+  if constexpr (V::BLOCK_SMEM != 0) {
+    if (blockIdx.x * FLS_WARPS_PER_BLOCK >= k.n_vec) return;
+    V::block_init(k, bsm, threadIdx.x, FLS_WARPS_PER_BLOCK * 32);
+    __syncthreads();
+  }
+  if (v >= k.n_vec) return;
+  FlsWarp w;
+  w.init(fls_smem + warp * V::SMEM, (uint64_t *)(bsm + V::BLOCK_SMEM) + warp);
+  V::run(k, v, w, bsm);
+}
+
+// UNCOMPRESSED / blob copy: chunk by = blockIdx.y copies aux64[1] bytes seg[0] -> out (both 16-byte aligned).
+__global__ void __launch_bounds__(256) fls_copy_kernel(const FlsChunkDev *__restrict__ chunks) {
+  const FlsChunkDev &k = chunks[blockIdx.y];
+  const uint4 *src = (const uint4 *)k.seg[0];
+  uint4 *dst = (uint4 *)k.out;
+  const uint64_t n16 = k.aux64[1] >> 4;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x)
+    __stcs(dst + i, __ldg(src + i));
+}
+// CONSTANT: fill n_vec*1024 values of width aux32 bytes with aux64[0].
+__global__ void __launch_bounds__(256) fls_fill_kernel(const FlsChunkDev *__restrict__ chunks) {
+  const FlsChunkDev &k = chunks[blockIdx.y];
+  const uint32_t wb = k.aux32;
+  uint64_t pat = k.aux64[0];
+  if (wb == 1) pat = (pat & 0xFF) * 0x0101010101010101ull;
+  else if (wb == 2) pat = (pat & 0xFFFF) * 0x0001000100010001ull;
+  else if (wb == 4) pat = (pat & 0xFFFFFFFFull) * 0x0000000100000001ull;
+  uint64_t *dst = (uint64_t *)k.out;
+  const uint64_t n8 = (uint64_t)k.n_vec * FLS_VEC * wb / 8;
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n8; i += (uint64_t)gridDim.x * blockDim.x)
+    dst[i] = pat;
+}
+#endif

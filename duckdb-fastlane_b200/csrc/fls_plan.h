@@ -1,0 +1,156 @@
+// fls_plan.h — turns (table descriptor, row-group range, column, staged base address, output buffers) into
+// launch groups of chunk descriptors.  Host-only, header-only; shared by flsgpu.cu (device addresses) and the
+// host emulation of the kernels in tests/emul (host addresses).
+//
+// This is the per-column "expression interpreter" of the missing FastLanes reader reduced to a table:
+// scheme -> kernel kind.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "fls_kernels.cuh"
+#include "fls_reader.h"
+
+enum FlsKernelKind {
+  FLS_K_FFOR = 0, FLS_K_DELTA, FLS_K_RLE, FLS_K_DICT, FLS_K_ALP, FLS_K_ALPRD, FLS_K_COPY, FLS_K_FILL,
+  FLS_K_STR_OFFSETS,    // DELTA u32 end-offset stream -> offsets[i+1]
+  FLS_K_STR_COPY,       // payload blob copy (unaligned)
+  FLS_K_STR_CONST,
+  FLS_K_STR_DICT,
+  FLS_K_STR_FSST,
+  FLS_K_STR_FSST_DICTPREP,  // decode an FSST-compressed dictionary into scratch
+  FLS_K_N
+};
+
+struct FlsLaunch {
+  int kind;
+  int width;  // bytes per value (fixed width) or 0
+  uint32_t col;
+  std::vector<FlsChunkDev> chunks;
+};
+
+struct FlsColOut {
+  void *data = nullptr;        // fixed width: padded_rows * width bytes
+  uint32_t *offsets = nullptr; // strings: padded_rows + 1
+  uint8_t *payload = nullptr;  // strings: sum of row-group payload bytes (+16 slack)
+  uint8_t *scratch = nullptr;  // strings (FSST_DICT): decoded dictionaries
+};
+
+struct FlsColNeed {  // sizes the caller must provide for a column over a row-group range
+  uint64_t data_bytes = 0, offsets_bytes = 0, payload_bytes = 0, scratch_bytes = 0;
+  uint64_t compressed_bytes = 0;  // segment bytes read
+  uint64_t decoded_bytes = 0;     // algorithmic bytes written (values, or offsets + payload)
+};
+
+static inline FlsLaunch &fls_launch_for(std::vector<FlsLaunch> &ls, int kind, int width, uint32_t col) {
+  for (auto &l : ls)
+    if (l.kind == kind && l.width == width && l.col == col) return l;
+  ls.push_back(FlsLaunch{kind, width, col, {}});
+  return ls.back();
+}
+
+static inline FlsColNeed fls_column_need(const FlsTable &t, uint32_t col, uint32_t g0, uint32_t g1,
+                                         const uint8_t *host_image /* may be null */) {
+  FlsColNeed n;
+  const uint32_t wb = fls_type_bits(t.types[col]) / 8;
+  const uint64_t rows = t.padded_rows(g0, g1);
+  for (uint32_t g = g0; g < g1; ++g) {
+    const fls_colchunk &k = t.chunk(g, col);
+    for (uint32_t s = 0; s < k.n_seg; ++s) n.compressed_bytes += k.seg[s].size;
+    if (!wb) {
+      n.payload_bytes += k.aux64[0];
+      if (k.scheme == FLS_S_STR_FSST_DICT && host_image) {
+        // decoded dictionary size = last entry of dict_dec_offsets (seg[6])
+        const uint8_t *p = host_image + t.rgs[g].off + k.seg[6].off + 4ull * k.aux32;
+        uint32_t sz;
+        memcpy(&sz, p, 4);
+        n.scratch_bytes += ((uint64_t)sz + 31) & ~15ull;
+      }
+    }
+  }
+  if (wb) { n.data_bytes = rows * wb; n.decoded_bytes = n.data_bytes; }
+  else {
+    n.offsets_bytes = (rows + 1) * 4;
+    n.decoded_bytes = n.offsets_bytes + n.payload_bytes;
+    n.payload_bytes += 16;
+  }
+  return n;
+}
+
+// stage_base = address (device or host) of the byte at file offset t.rgs[g0].off
+static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint32_t g0, uint32_t g1,
+                                          const uint8_t *stage_base, const uint8_t *host_image,
+                                          const FlsColOut &out, std::vector<FlsLaunch> &ls) {
+  const uint32_t wb = fls_type_bits(t.types[col]) / 8;
+  uint64_t row_base = 0, pay_base = 0, scratch_off = 0;
+  for (uint32_t g = g0; g < g1; ++g) {
+    const fls_rowgroup &rg = t.rgs[g];
+    const fls_colchunk &k = t.chunk(g, col);
+    FlsChunkDev d;
+    memset(&d, 0, sizeof(d));
+    const uint8_t *rgp = stage_base + (rg.off - t.rgs[g0].off);
+    for (uint32_t s = 0; s < k.n_seg; ++s) d.seg[s] = rgp + k.seg[s].off;
+    d.n_vec = rg.n_vec;
+    d.aux32 = k.aux32;
+    d.aux64[0] = k.aux64[0];
+    d.aux64[1] = k.aux64[1];
+    d.scheme = k.scheme;
+    if (wb) {
+      d.out = (uint8_t *)out.data + row_base * wb;
+      const bool is_dbl = t.types[col] == FLS_T_DOUBLE;
+      switch (k.scheme) {
+        case FLS_S_FFOR: fls_launch_for(ls, FLS_K_FFOR, wb, col).chunks.push_back(d); break;
+        case FLS_S_DELTA: fls_launch_for(ls, FLS_K_DELTA, wb, col).chunks.push_back(d); break;
+        case FLS_S_RLE: fls_launch_for(ls, FLS_K_RLE, wb, col).chunks.push_back(d); break;
+        case FLS_S_DICT: fls_launch_for(ls, FLS_K_DICT, wb, col).chunks.push_back(d); break;
+        case FLS_S_ALP:
+          if (!is_dbl) return "ALP on a non-double column";
+          fls_launch_for(ls, FLS_K_ALP, wb, col).chunks.push_back(d); break;
+        case FLS_S_ALP_RD:
+          if (!is_dbl) return "ALP_RD on a non-double column";
+          fls_launch_for(ls, FLS_K_ALPRD, wb, col).chunks.push_back(d); break;
+        case FLS_S_UNCOMPRESSED:
+          d.aux64[1] = (uint64_t)rg.n_vec * FLS_VEC * wb;
+          fls_launch_for(ls, FLS_K_COPY, wb, col).chunks.push_back(d); break;
+        case FLS_S_CONSTANT:
+          d.aux32 = wb;
+          fls_launch_for(ls, FLS_K_FILL, wb, col).chunks.push_back(d); break;
+        default: return "scheme not valid for a fixed-width column";
+      }
+    } else {
+      d.out = out.offsets + row_base;
+      d.pay = out.payload;
+      d.pay_base = (uint32_t)pay_base;
+      switch (k.scheme) {
+        case FLS_S_STR_UNCOMPRESSED: {
+          fls_launch_for(ls, FLS_K_STR_OFFSETS, 0, col).chunks.push_back(d);
+          FlsChunkDev c2 = d;
+          c2.seg[0] = d.seg[2];
+          fls_launch_for(ls, FLS_K_STR_COPY, 0, col).chunks.push_back(c2);
+          break;
+        }
+        case FLS_S_STR_CONSTANT: fls_launch_for(ls, FLS_K_STR_CONST, 0, col).chunks.push_back(d); break;
+        case FLS_S_STR_DICT: fls_launch_for(ls, FLS_K_STR_DICT, 0, col).chunks.push_back(d); break;
+        case FLS_S_STR_FSST: fls_launch_for(ls, FLS_K_STR_FSST, 0, col).chunks.push_back(d); break;
+        case FLS_S_STR_FSST_DICT: {
+          if (!host_image) return "FSST_DICT planning needs the host image";
+          uint32_t sz;
+          memcpy(&sz, host_image + rg.off + k.seg[6].off + 4ull * k.aux32, 4);
+          FlsChunkDev p = d;
+          p.out = out.scratch + scratch_off;  // decoded dictionary bytes
+          fls_launch_for(ls, FLS_K_STR_FSST_DICTPREP, 0, col).chunks.push_back(p);
+          // gather stage reads the decoded dictionary: offsets = dict_dec_offsets (seg[6]), bytes = scratch
+          d.seg[2] = d.seg[6];
+          d.seg[3] = out.scratch + scratch_off;
+          scratch_off += ((uint64_t)sz + 31) & ~15ull;
+          fls_launch_for(ls, FLS_K_STR_DICT, 0, col).chunks.push_back(d);
+          break;
+        }
+        default: return "scheme not valid for a string column";
+      }
+      pay_base += k.aux64[0];
+    }
+    row_base += (uint64_t)rg.n_vec * FLS_VEC;
+  }
+  return "";
+}

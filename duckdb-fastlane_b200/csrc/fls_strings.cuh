@@ -1,0 +1,266 @@
+// fls_strings.cuh — string column decoders (Arrow layout out: u32 offsets[n+1] + payload bytes).
+//
+// Thread t of the warp that owns a vector is responsible for the 32 strings e = 32t .. 32t+31 (DICT/CONST)
+// or for lane t's 32 contiguous originals (FSST / offset streams, unified transposed layout) — in both cases
+// a CONTIGUOUS run of output bytes, written through FlsByteSink as aligned 8-byte stores.
+//
+// Restated FastLanes primitives (upstream source absent); FSST stream semantics
+// follow duckdb/third_party/fsst/fsst.h:93-104,162-241 (code<255 -> symbol, 255 -> escaped literal byte).
+#pragma once
+#include "fls_kernels.cuh"
+
+// ---- contiguous byte writer: head/tail bytes individually, everything between as aligned u64 stores
+struct FlsByteSink {
+  uint64_t *word;  // aligned address of the word being assembled
+  uint64_t acc;
+  uint32_t n;      // bytes valid in acc (including the `head` foreign bytes of the first word)
+  uint32_t head;   // low bytes of the first word that belong to someone else
+  FLS_MEM void init(uint8_t *p) {
+    const uint32_t a = (uint32_t)((uintptr_t)p & 7u);
+    word = (uint64_t *)(p - a);
+    acc = 0; n = a; head = a;
+  }
+  FLS_MEM void flush_partial(uint32_t lo, uint32_t hi) {
+    uint8_t *b = (uint8_t *)word;
+    for (uint32_t i = lo; i < hi; ++i) b[i] = (uint8_t)(acc >> (8u * i));
+  }
+  // append the low L bytes of s (bytes above L must be zero), 1 <= L <= 8
+  FLS_MEM void push(uint64_t s, uint32_t L) {
+    acc |= s << (8u * n);
+    n += L;
+    if (n >= 8u) {
+      if (head) { flush_partial(head, 8u); head = 0; }
+      else *word = acc;
+      ++word;
+      n -= 8u;
+      acc = n ? (s >> (8u * (L - n))) : 0ull;
+    }
+  }
+  FLS_MEM void finish() {
+    if (n > head) flush_partial(head, n);
+  }
+};
+
+// ---- aligned-word byte reader over a contiguous region
+struct FlsByteSource {
+  const uint64_t *word;
+  uint64_t cur;
+  uint32_t bi;
+  FLS_MEM void init(const uint8_t *p) {
+    const uint32_t a = (uint32_t)((uintptr_t)p & 7u);
+    word = (const uint64_t *)(p - a);
+    cur = fls_ldg(word) >> (8u * a);
+    bi = a;
+  }
+  FLS_MEM uint32_t next() {
+    if (bi == 8u) { ++word; cur = fls_ldg(word); bi = 0; }
+    const uint32_t b = (uint32_t)cur & 0xFFu;
+    cur >>= 8; ++bi;
+    return b;
+  }
+};
+
+// ===================================================================== end-offset stream -> offsets[i+1]
+// chunk: seg[0]=hdr, seg[1]=data ([lane bases 128 B][packed deltas]); out = &offsets[first row of rg]
+struct VecSTROFFS {
+  static constexpr uint32_t SMEM = DecDELTA<uint32_t>::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    const uint32_t bw = FLS_META_BW(h.meta);
+    DecDELTA<uint32_t>::to_tile(w, k.seg[1] + 16ull * h.ep, bw > 32u ? 32u : bw, h.base);
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
+    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + DecDELTA<uint32_t>::STAGE, offs, t, k.pay_base); }
+  }
+};
+
+// ===================================================================== constant string
+// chunk: seg[0] = the value's bytes, aux32 = its length
+struct VecSTRCONST {
+  static constexpr uint32_t SMEM = 16, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &, const uint8_t *) {
+    const uint32_t len = k.aux32, add = k.pay_base + v * FLS_VEC * len;
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;
+    FLS_LANES(t) {
+      for (uint32_t j = 0; j < 32u; ++j) offs[j * 32u + t + 1u] = add + (j * 32u + t + 1u) * len;
+      if (len) {
+        FlsByteSink sink;
+        sink.init(k.pay + add + (uint64_t)32u * t * len);
+        for (uint32_t i = 0; i < 32u; ++i)
+          for (uint32_t b = 0; b < len; ++b) sink.push(fls_ldg(k.seg[0] + b), 1);
+        sink.finish();
+      }
+    }
+  }
+};
+
+// ===================================================================== dictionary strings
+// chunk: seg[0]/[1] = idx stream (u32 FFOR), seg[2] = dict_offsets u32[n+1], seg[3] = dict bytes,
+//        seg[4] = vec_ep u32[n_vec+1] (payload offset of each vector inside the row group)
+struct VecSTRDICT {
+  static constexpr uint32_t TILE = 4096u, XCH = TILE + 4224u;
+  static constexpr uint32_t SMEM = XCH + 128u, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    uint32_t bw = FLS_META_BW(h.meta);
+    if (bw > 32u) bw = 32u;
+    const uint32_t *doff = (const uint32_t *)k.seg[2];
+    const uint8_t *dbytes = k.seg[3];
+    const uint32_t n_dict = k.aux32;
+    const uint32_t vec_ep = fls_ldg((const uint32_t *)k.seg[4] + v);
+    uint32_t *tile = (uint32_t *)(w.sm + TILE), *xch = (uint32_t *)(w.sm + XCH);
+    if (bw) { w.stage(0, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
+    // 1. indices -> tile (original order: FFOR positions are original positions)
+    FLS_LANES(t) {
+      const uint32_t q = t & 7u, g = t >> 3;
+      for (uint32_t j = 0; j < 8u; ++j) {
+        const uint32_t row = g * 8u + j, p = row * 32u + q * 4u;
+        fls_u4 ix;
+        if (bw) ix = fls_unpack32_row(w.sm, bw, row, q, (uint32_t)h.base);
+        else { ix.x = ix.y = ix.z = ix.w = (uint32_t)h.base; }
+        tile[fls_tile_slot<uint32_t>(p)] = fls_min(ix.x, n_dict - 1u);
+        tile[fls_tile_slot<uint32_t>(p + 1u)] = fls_min(ix.y, n_dict - 1u);
+        tile[fls_tile_slot<uint32_t>(p + 2u)] = fls_min(ix.z, n_dict - 1u);
+        tile[fls_tile_slot<uint32_t>(p + 3u)] = fls_min(ix.w, n_dict - 1u);
+      }
+    }
+    // 2. bytes produced by each thread's 32 strings
+    FLS_LANES(t) {
+      uint32_t tot = 0;
+      for (uint32_t i = 0; i < 32u; ++i) {
+        const uint32_t d = tile[33u * t + i];
+        tot += fls_ldg(doff + d + 1) - fls_ldg(doff + d);
+      }
+      xch[t] = tot;
+    }
+    // 3. copy the strings, replace indices by end offsets
+    FLS_LANES(t) {
+      uint32_t pos = vec_ep;
+      for (uint32_t u = 0; u < t; ++u) pos += xch[u];
+      FlsByteSink sink;
+      sink.init(k.pay + k.pay_base + pos);
+      for (uint32_t i = 0; i < 32u; ++i) {
+        const uint32_t d = tile[33u * t + i];
+        const uint32_t a = fls_ldg(doff + d), b = fls_ldg(doff + d + 1);
+        for (uint32_t c = a; c < b; ++c) sink.push(fls_ldg(dbytes + c), 1);
+        pos += b - a;
+        tile[33u * t + i] = pos;
+      }
+      sink.finish();
+    }
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
+    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + TILE, offs, t, k.pay_base); }
+  }
+};
+
+// ===================================================================== FSST strings
+// chunk: seg[0]/[1] = decoded end-offset stream, seg[2]/[3] = compressed end-offset stream (both DELTA u32),
+//        seg[4] = symbol table (u64 symbol[256] | u8 len[256]), seg[5] = compressed bytes (+16 slack).
+// Lane t's 32 strings are contiguous in both the compressed and the decoded space, so the thread decodes ONE
+// contiguous compressed run [c0,c1) into ONE contiguous output run starting at d0.
+struct VecSTRFSST {
+  static constexpr uint32_t CSTAGE = DecDELTA<uint32_t>::SMEM;  // compressed-ends payload staged after the tile
+  static constexpr uint32_t SMEM = CSTAGE + 128u + 4096u;
+  static constexpr uint32_t BLOCK_SMEM = 2304;  // symbol table, shared by the block's warps (same chunk)
+  FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsmem, uint32_t tid, uint32_t nthreads) {
+    const uint64_t *src = (const uint64_t *)k.seg[4];
+    uint64_t *dst = (uint64_t *)bsmem;
+    for (uint32_t i = tid; i < 2304u / 8u; i += nthreads) dst[i] = fls_ldg(src + i);
+  }
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *symtab) {
+    const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
+    uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
+    if (bwd > 32u) bwd = 32u;
+    if (bwc > 32u) bwc = 32u;
+    // both offset streams in flight at once
+    w.stage(CSTAGE, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc);
+    DecDELTA<uint32_t>::to_tile(w, k.seg[1] + 16ull * hd.ep, bwd, hd.base);  // stages, waits for both, fills tile
+    const uint32_t *dbases = (const uint32_t *)w.sm;
+    const uint32_t *cbases = (const uint32_t *)(w.sm + CSTAGE);
+    const uint32_t *cpk = (const uint32_t *)(w.sm + CSTAGE + 128u);
+    const uint64_t *sym = (const uint64_t *)symtab;
+    const uint8_t *len = symtab + 2048;
+    const uint8_t *comp = k.seg[5];
+    uint8_t *pay = k.pay + k.pay_base;
+    FLS_LANES(t) {
+      const uint32_t c0 = cbases[t], d0 = dbases[t];
+      uint32_t c1 = c0 + 32u * (uint32_t)hc.base;
+      if (bwc)
+        for (uint32_t r = 0; r < 32u; ++r) c1 += fls_extract<uint32_t>(cpk, bwc, r, t);
+      if (c1 > c0) {
+        FlsByteSource src;
+        src.init(comp + c0);
+        FlsByteSink sink;
+        sink.init(pay + d0);
+        uint32_t left = c1 - c0;
+        while (left) {
+          const uint32_t code = src.next();
+          --left;
+          if (code == 255u) {
+            if (!left) break;
+            sink.push(src.next(), 1);
+            --left;
+          } else {
+            const uint32_t L = len[code];
+            if (L) sink.push(sym[code], L);
+          }
+        }
+        sink.finish();
+      }
+    }
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
+    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + DecDELTA<uint32_t>::STAGE, offs, t, k.pay_base); }
+  }
+};
+
+// ===================================================================== chunk-level helpers
+// FSST-compressed dictionary -> decoded dictionary bytes in scratch (k.out); one thread per entry.
+//   seg[2] = compressed offsets u32[n+1], seg[3] = compressed bytes, seg[5] = symtab, seg[6] = decoded offsets
+FLS_DEV void fls_fsst_dict_entry(const FlsChunkDev &k, uint32_t d) {
+  const uint32_t *coff = (const uint32_t *)k.seg[2], *doff = (const uint32_t *)k.seg[6];
+  const uint64_t *sym = (const uint64_t *)k.seg[5];
+  const uint8_t *len = k.seg[5] + 2048, *in = k.seg[3];
+  uint8_t *o = (uint8_t *)k.out + fls_ldg(doff + d);
+  for (uint32_t i = fls_ldg(coff + d), e = fls_ldg(coff + d + 1); i < e;) {
+    const uint32_t code = fls_ldg(in + i++);
+    if (code == 255u) { *o++ = fls_ldg(in + i++); }
+    else { uint64_t s = fls_ldg(sym + code); for (uint32_t b = fls_ldg(len + code); b; --b) { *o++ = (uint8_t)s; s >>= 8; } }
+  }
+}
+
+#ifndef FLS_HOST_EMUL
+__global__ void __launch_bounds__(128) fls_fsst_dictprep_kernel(const FlsChunkDev *__restrict__ chunks) {
+  const FlsChunkDev &k = chunks[blockIdx.y];
+  for (uint32_t d = blockIdx.x * blockDim.x + threadIdx.x; d < k.aux32; d += gridDim.x * blockDim.x)
+    fls_fsst_dict_entry(k, d);
+}
+// payload blob copy seg[0] -> pay + pay_base, aux64[0] bytes, arbitrary destination alignment
+__global__ void __launch_bounds__(256) fls_str_copy_kernel(const FlsChunkDev *__restrict__ chunks) {
+  const FlsChunkDev &k = chunks[blockIdx.y];
+  const uint8_t *src = k.seg[0];
+  uint8_t *dst = k.pay + k.pay_base;
+  const uint64_t n = k.aux64[0];
+  const uint32_t head = (uint32_t)((16u - ((uintptr_t)dst & 15u)) & 15u);  // bytes until dst is 16-byte aligned
+  const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x, nthr = (uint64_t)gridDim.x * blockDim.x;
+  if (n <= head + 16u) {
+    for (uint64_t i = tid; i < n; i += nthr) dst[i] = __ldg(src + i);
+    return;
+  }
+  const uint64_t n16 = (n - head) >> 4;
+  for (uint64_t i = tid; i < n16; i += nthr) {  // aligned stores, byte-granular (L1-cached) loads
+    const uint8_t *s = src + head + 16u * i;
+    uint32_t wv[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      wv[j] = (uint32_t)__ldg(s + 4 * j) | ((uint32_t)__ldg(s + 4 * j + 1) << 8) | ((uint32_t)__ldg(s + 4 * j + 2) << 16) |
+              ((uint32_t)__ldg(s + 4 * j + 3) << 24);
+    *(uint4 *)(dst + head + 16u * i) = make_uint4(wv[0], wv[1], wv[2], wv[3]);
+  }
+  for (uint64_t i = tid; i < head; i += nthr) dst[i] = __ldg(src + i);
+  for (uint64_t i = head + 16u * n16 + tid; i < n; i += nthr) dst[i] = __ldg(src + i);
+}
+#else
+static void fls_str_copy_chunk_host(const FlsChunkDev &k) { memcpy(k.pay + k.pay_base, k.seg[0], k.aux64[0]); }
+static void fls_fsst_dictprep_chunk_host(const FlsChunkDev &k) {
+  for (uint32_t d = 0; d < k.aux32; ++d) fls_fsst_dict_entry(k, d);
+}
+#endif
