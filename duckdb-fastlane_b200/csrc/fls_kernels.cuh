@@ -1,7 +1,8 @@
 // fls_kernels.cuh — chunk descriptors and the per-vector entry points the kernels (and tests/emul) call.
 //
-// One launch decodes one column over a whole batch of row groups: grid = (ceil(64/4), n_chunks), block = 4
-// warps, warp w of block (bx,by) decodes vector 4*bx+w of chunk by.  A chunk = one (row group, column).
+// One launch decodes every chunk of one (scheme, width) family in a batch of row groups: grid = 16 * n_chunks
+// blocks of 4 warps; warp w of block b decodes vector 4*(b%16)+w of chunk b/16.  A chunk = one (row group,
+// column).
 #pragma once
 #include "fls_decode.cuh"
 
@@ -82,6 +83,7 @@ struct VecALPRD {
 };
 
 #define FLS_WARPS_PER_BLOCK 4
+#define FLS_BLOCKS_PER_CHUNK (FLS_RG_VECS / FLS_WARPS_PER_BLOCK)
 
 #ifndef FLS_HOST_EMUL
 // Shared memory layout of a block: [warp 0 slot | ... | warp 3 slot | block-shared (V::BLOCK_SMEM) | 4 mbarriers]
@@ -92,12 +94,12 @@ template <class V> constexpr uint32_t fls_block_smem() {
 template <class V>
 __global__ void __launch_bounds__(FLS_WARPS_PER_BLOCK * 32) fls_vec_kernel(const FlsChunkDev *__restrict__ chunks) {
   extern __shared__ __align__(128) uint8_t fls_smem[];
-  const FlsChunkDev &k = chunks[blockIdx.y];
-  const uint32_t warp = threadIdx.x >> 5;
-  const uint32_t v = blockIdx.x * FLS_WARPS_PER_BLOCK + warp;
+  const FlsChunkDev &k = chunks[blockIdx.x / FLS_BLOCKS_PER_CHUNK];
+  const uint32_t warp = threadIdx.x >> 5, bx = blockIdx.x % FLS_BLOCKS_PER_CHUNK;
+  const uint32_t v = bx * FLS_WARPS_PER_BLOCK + warp;
   uint8_t *bsm = fls_smem + FLS_WARPS_PER_BLOCK * V::SMEM;
   if constexpr (V::BLOCK_SMEM != 0) {
-    if (blockIdx.x * FLS_WARPS_PER_BLOCK >= k.n_vec) return;
+    if (bx * FLS_WARPS_PER_BLOCK >= k.n_vec) return;
     V::block_init(k, bsm, threadIdx.x, FLS_WARPS_PER_BLOCK * 32);
     __syncthreads();
   }
@@ -108,17 +110,19 @@ __global__ void __launch_bounds__(FLS_WARPS_PER_BLOCK * 32) fls_vec_kernel(const
 }
 
 // UNCOMPRESSED / blob copy: chunk by = blockIdx.y copies aux64[1] bytes seg[0] -> out (both 16-byte aligned).
-__global__ void __launch_bounds__(256) fls_copy_kernel(const FlsChunkDev *__restrict__ chunks) {
-  const FlsChunkDev &k = chunks[blockIdx.y];
+__global__ void __launch_bounds__(256) fls_copy_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t bpc) {
+  const FlsChunkDev &k = chunks[blockIdx.x / bpc];
+  const uint32_t bx = blockIdx.x % bpc;
   const uint4 *src = (const uint4 *)k.seg[0];
   uint4 *dst = (uint4 *)k.out;
   const uint64_t n16 = k.aux64[1] >> 4;
-  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x)
+  for (uint64_t i = bx * (uint64_t)blockDim.x + threadIdx.x; i < n16; i += (uint64_t)bpc * blockDim.x)
     __stcs(dst + i, __ldg(src + i));
 }
 // CONSTANT: fill n_vec*1024 values of width aux32 bytes with aux64[0].
-__global__ void __launch_bounds__(256) fls_fill_kernel(const FlsChunkDev *__restrict__ chunks) {
-  const FlsChunkDev &k = chunks[blockIdx.y];
+__global__ void __launch_bounds__(256) fls_fill_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t bpc) {
+  const FlsChunkDev &k = chunks[blockIdx.x / bpc];
+  const uint32_t bx = blockIdx.x % bpc;
   const uint32_t wb = k.aux32;
   uint64_t pat = k.aux64[0];
   if (wb == 1) pat = (pat & 0xFF) * 0x0101010101010101ull;
@@ -126,7 +130,7 @@ __global__ void __launch_bounds__(256) fls_fill_kernel(const FlsChunkDev *__rest
   else if (wb == 4) pat = (pat & 0xFFFFFFFFull) * 0x0000000100000001ull;
   uint64_t *dst = (uint64_t *)k.out;
   const uint64_t n8 = (uint64_t)k.n_vec * FLS_VEC * wb / 8;
-  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n8; i += (uint64_t)gridDim.x * blockDim.x)
+  for (uint64_t i = bx * (uint64_t)blockDim.x + threadIdx.x; i < n8; i += (uint64_t)bpc * blockDim.x)
     dst[i] = pat;
 }
 #endif

@@ -25,8 +25,13 @@ enum FlsKernelKind {
 struct FlsLaunch {
   int kind;
   int width;  // bytes per value (fixed width) or 0
-  uint32_t col;
   std::vector<FlsChunkDev> chunks;
+  // algorithmic traffic of the launch: segment bytes read, decoded bytes written
+  uint64_t bytes_read = 0, bytes_written = 0, vectors = 0;
+  void add(const FlsChunkDev &d, uint64_t rd, uint64_t wr) {
+    chunks.push_back(d);
+    bytes_read += rd; bytes_written += wr; vectors += d.n_vec;
+  }
 };
 
 struct FlsColOut {
@@ -34,6 +39,7 @@ struct FlsColOut {
   uint32_t *offsets = nullptr; // strings: padded_rows + 1
   uint8_t *payload = nullptr;  // strings: sum of row-group payload bytes (+16 slack)
   uint8_t *scratch = nullptr;  // strings (FSST_DICT): decoded dictionaries
+  uint64_t pay_base0 = 0;      // strings: payload bytes that precede row group g0 in `payload` (pipeline slices)
 };
 
 struct FlsColNeed {  // sizes the caller must provide for a column over a row-group range
@@ -42,10 +48,13 @@ struct FlsColNeed {  // sizes the caller must provide for a column over a row-gr
   uint64_t decoded_bytes = 0;     // algorithmic bytes written (values, or offsets + payload)
 };
 
-static inline FlsLaunch &fls_launch_for(std::vector<FlsLaunch> &ls, int kind, int width, uint32_t col) {
+// One launch per (kernel kind, value width): chunks of different columns share it.
+static inline FlsLaunch &fls_launch_for(std::vector<FlsLaunch> &ls, int kind, int width) {
   for (auto &l : ls)
-    if (l.kind == kind && l.width == width && l.col == col) return l;
-  ls.push_back(FlsLaunch{kind, width, col, {}});
+    if (l.kind == kind && l.width == width) return l;
+  ls.emplace_back();
+  ls.back().kind = kind;
+  ls.back().width = width;
   return ls.back();
 }
 
@@ -82,7 +91,7 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
                                           const uint8_t *stage_base, const uint8_t *host_image,
                                           const FlsColOut &out, std::vector<FlsLaunch> &ls) {
   const uint32_t wb = fls_type_bits(t.types[col]) / 8;
-  uint64_t row_base = 0, pay_base = 0, scratch_off = 0;
+  uint64_t row_base = 0, pay_base = out.pay_base0, scratch_off = 0;
   for (uint32_t g = g0; g < g1; ++g) {
     const fls_rowgroup &rg = t.rgs[g];
     const fls_colchunk &k = t.chunk(g, col);
@@ -95,55 +104,60 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
     d.aux64[0] = k.aux64[0];
     d.aux64[1] = k.aux64[1];
     d.scheme = k.scheme;
+    uint64_t rd = 0;
+    for (uint32_t s = 0; s < k.n_seg; ++s) rd += k.seg[s].size;
+    const uint64_t vals = (uint64_t)rg.n_vec * FLS_VEC;
     if (wb) {
+      const uint64_t wr = vals * wb;
       d.out = (uint8_t *)out.data + row_base * wb;
       const bool is_dbl = t.types[col] == FLS_T_DOUBLE;
       switch (k.scheme) {
-        case FLS_S_FFOR: fls_launch_for(ls, FLS_K_FFOR, wb, col).chunks.push_back(d); break;
-        case FLS_S_DELTA: fls_launch_for(ls, FLS_K_DELTA, wb, col).chunks.push_back(d); break;
-        case FLS_S_RLE: fls_launch_for(ls, FLS_K_RLE, wb, col).chunks.push_back(d); break;
-        case FLS_S_DICT: fls_launch_for(ls, FLS_K_DICT, wb, col).chunks.push_back(d); break;
+        case FLS_S_FFOR: fls_launch_for(ls, FLS_K_FFOR, wb).add(d, rd, wr); break;
+        case FLS_S_DELTA: fls_launch_for(ls, FLS_K_DELTA, wb).add(d, rd, wr); break;
+        case FLS_S_RLE: fls_launch_for(ls, FLS_K_RLE, wb).add(d, rd, wr); break;
+        case FLS_S_DICT: fls_launch_for(ls, FLS_K_DICT, wb).add(d, rd, wr); break;
         case FLS_S_ALP:
           if (!is_dbl) return "ALP on a non-double column";
-          fls_launch_for(ls, FLS_K_ALP, wb, col).chunks.push_back(d); break;
+          fls_launch_for(ls, FLS_K_ALP, wb).add(d, rd, wr); break;
         case FLS_S_ALP_RD:
           if (!is_dbl) return "ALP_RD on a non-double column";
-          fls_launch_for(ls, FLS_K_ALPRD, wb, col).chunks.push_back(d); break;
+          fls_launch_for(ls, FLS_K_ALPRD, wb).add(d, rd, wr); break;
         case FLS_S_UNCOMPRESSED:
           d.aux64[1] = (uint64_t)rg.n_vec * FLS_VEC * wb;
-          fls_launch_for(ls, FLS_K_COPY, wb, col).chunks.push_back(d); break;
+          fls_launch_for(ls, FLS_K_COPY, wb).add(d, rd, wr); break;
         case FLS_S_CONSTANT:
           d.aux32 = wb;
-          fls_launch_for(ls, FLS_K_FILL, wb, col).chunks.push_back(d); break;
+          fls_launch_for(ls, FLS_K_FILL, wb).add(d, rd, wr); break;
         default: return "scheme not valid for a fixed-width column";
       }
     } else {
       d.out = out.offsets + row_base;
       d.pay = out.payload;
       d.pay_base = (uint32_t)pay_base;
+      const uint64_t wr = vals * 4 + k.aux64[0];  // offsets + payload
       switch (k.scheme) {
         case FLS_S_STR_UNCOMPRESSED: {
-          fls_launch_for(ls, FLS_K_STR_OFFSETS, 0, col).chunks.push_back(d);
+          fls_launch_for(ls, FLS_K_STR_OFFSETS, 0).add(d, k.seg[0].size + k.seg[1].size, vals * 4);
           FlsChunkDev c2 = d;
           c2.seg[0] = d.seg[2];
-          fls_launch_for(ls, FLS_K_STR_COPY, 0, col).chunks.push_back(c2);
+          fls_launch_for(ls, FLS_K_STR_COPY, 0).add(c2, k.seg[2].size, k.aux64[0]);
           break;
         }
-        case FLS_S_STR_CONSTANT: fls_launch_for(ls, FLS_K_STR_CONST, 0, col).chunks.push_back(d); break;
-        case FLS_S_STR_DICT: fls_launch_for(ls, FLS_K_STR_DICT, 0, col).chunks.push_back(d); break;
-        case FLS_S_STR_FSST: fls_launch_for(ls, FLS_K_STR_FSST, 0, col).chunks.push_back(d); break;
+        case FLS_S_STR_CONSTANT: fls_launch_for(ls, FLS_K_STR_CONST, 0).add(d, rd, wr); break;
+        case FLS_S_STR_DICT: fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, rd, wr); break;
+        case FLS_S_STR_FSST: fls_launch_for(ls, FLS_K_STR_FSST, 0).add(d, rd, wr); break;
         case FLS_S_STR_FSST_DICT: {
           if (!host_image) return "FSST_DICT planning needs the host image";
           uint32_t sz;
           memcpy(&sz, host_image + rg.off + k.seg[6].off + 4ull * k.aux32, 4);
           FlsChunkDev p = d;
           p.out = out.scratch + scratch_off;  // decoded dictionary bytes
-          fls_launch_for(ls, FLS_K_STR_FSST_DICTPREP, 0, col).chunks.push_back(p);
+          fls_launch_for(ls, FLS_K_STR_FSST_DICTPREP, 0).add(p, k.seg[2].size + k.seg[3].size + k.seg[5].size, sz);
           // gather stage reads the decoded dictionary: offsets = dict_dec_offsets (seg[6]), bytes = scratch
           d.seg[2] = d.seg[6];
           d.seg[3] = out.scratch + scratch_off;
           scratch_off += ((uint64_t)sz + 31) & ~15ull;
-          fls_launch_for(ls, FLS_K_STR_DICT, 0, col).chunks.push_back(d);
+          fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, k.seg[0].size + k.seg[1].size + k.seg[4].size + k.seg[6].size, wr);
           break;
         }
         default: return "scheme not valid for a string column";

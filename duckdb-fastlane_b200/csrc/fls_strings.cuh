@@ -228,19 +228,19 @@ FLS_DEV void fls_fsst_dict_entry(const FlsChunkDev &k, uint32_t d) {
 }
 
 #ifndef FLS_HOST_EMUL
-__global__ void __launch_bounds__(128) fls_fsst_dictprep_kernel(const FlsChunkDev *__restrict__ chunks) {
-  const FlsChunkDev &k = chunks[blockIdx.y];
-  for (uint32_t d = blockIdx.x * blockDim.x + threadIdx.x; d < k.aux32; d += gridDim.x * blockDim.x)
+__global__ void __launch_bounds__(128) fls_fsst_dictprep_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t bpc) {
+  const FlsChunkDev &k = chunks[blockIdx.x / bpc];
+  for (uint32_t d = (blockIdx.x % bpc) * blockDim.x + threadIdx.x; d < k.aux32; d += bpc * blockDim.x)
     fls_fsst_dict_entry(k, d);
 }
 // payload blob copy seg[0] -> pay + pay_base, aux64[0] bytes, arbitrary destination alignment
-__global__ void __launch_bounds__(256) fls_str_copy_kernel(const FlsChunkDev *__restrict__ chunks) {
-  const FlsChunkDev &k = chunks[blockIdx.y];
+__global__ void __launch_bounds__(256) fls_str_copy_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t bpc) {
+  const FlsChunkDev &k = chunks[blockIdx.x / bpc];
   const uint8_t *src = k.seg[0];
   uint8_t *dst = k.pay + k.pay_base;
   const uint64_t n = k.aux64[0];
   const uint32_t head = (uint32_t)((16u - ((uintptr_t)dst & 15u)) & 15u);  // bytes until dst is 16-byte aligned
-  const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x, nthr = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t tid = (blockIdx.x % bpc) * (uint64_t)blockDim.x + threadIdx.x, nthr = (uint64_t)bpc * blockDim.x;
   if (n <= head + 16u) {
     for (uint64_t i = tid; i < n; i += nthr) dst[i] = __ldg(src + i);
     return;

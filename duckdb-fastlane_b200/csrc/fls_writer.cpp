@@ -19,6 +19,7 @@
 
 #include "fls_format.h"
 #include "fls_pack.h"
+#include "fls_reader.h"
 
 namespace flsw {
 
@@ -768,4 +769,43 @@ int flsw_write_file(flsw_writer *h, const char *path) {
   return 0;
 }
 void flsw_destroy(flsw_writer *h) { delete (flsw::Writer *)h; }
+
+// Build a new image holding `n_total` row groups by repeating the (full) row groups of `image` round-robin.
+// Every repeat is a separate copy of the bytes.  Returns a finished writer (flsw_data/flsw_size) or NULL.
+flsw_writer *flsw_tile(const void *image, uint64_t size, uint32_t n_total) {
+  FlsTable t;
+  if (!fls_parse((const uint8_t *)image, size, t).empty() || t.n_rg == 0) return nullptr;
+  for (auto &r : t.rgs)
+    if (r.n_tuples != FLS_RG_VECS * FLS_VEC) return nullptr;  // only full row groups can be repeated
+  flsw::Writer *w = new flsw::Writer();
+  w->names = t.names;
+  w->types = t.types;
+  w->force.assign(t.n_cols, -1);
+  w->force_bw.assign(t.n_cols, -1);
+  uint64_t total = t.rgs[0].off;
+  for (uint32_t i = 0; i < n_total; ++i) total += flsw::align_up(t.rgs[i % t.n_rg].size, FLS_RG_ALIGN);
+  w->file.reserve(total + 4096 + (size - t.data_end));
+  w->file.assign((const uint8_t *)image, (const uint8_t *)image + t.rgs[0].off);
+  for (uint32_t i = 0; i < n_total; ++i) {
+    const uint32_t g = i % t.n_rg;
+    const fls_rowgroup &r = t.rgs[g];
+    flsw::pad_to(w->file, FLS_RG_ALIGN);
+    fls_rowgroup nr = {w->file.size(), r.size, r.n_vec, r.n_tuples};
+    flsw::put_bytes(w->file, (const uint8_t *)image + r.off, r.size);
+    flsw::put(w->rg_footer, nr);
+    for (uint32_t c = 0; c < t.n_cols; ++c) {
+      const fls_colchunk &k = t.chunk(g, c);
+      flsw::put<uint8_t>(w->rg_footer, k.scheme); flsw::put<uint8_t>(w->rg_footer, k.n_seg);
+      flsw::put<uint16_t>(w->rg_footer, k.flags); flsw::put<uint32_t>(w->rg_footer, k.aux32);
+      flsw::put<uint64_t>(w->rg_footer, k.aux64[0]); flsw::put<uint64_t>(w->rg_footer, k.aux64[1]);
+      for (uint32_t sg = 0; sg < k.n_seg; ++sg) {
+        flsw::put<uint64_t>(w->rg_footer, k.seg[sg].off); flsw::put<uint64_t>(w->rg_footer, k.seg[sg].size);
+      }
+    }
+    w->n_rg++;
+    w->n_rows += r.n_tuples;
+  }
+  flsw::finish(*w);
+  return (flsw_writer *)w;
+}
 }

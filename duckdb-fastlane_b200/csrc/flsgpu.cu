@@ -1,0 +1,625 @@
+// flsgpu.cu — libflsgpu.so: the C ABI of include/flsgpu.h over the sm_100a decode kernels.
+//
+// Replaces, for the reference's read path, FastLanesFacade::openFile + RowgroupReader::materialize()
+// (/root/reference/src/fastlanes_facade.cpp:26-67) and the per-value copy-out of readNextChunk (:69-200):
+// open parses the footer only; flsgpu_decode stages the compressed row groups of a range to HBM with pinned
+// cudaMemcpyAsync (pipelined in slices: H2D | decode | D2H on three streams) and runs one kernel launch per
+// (scheme, width) family per slice.  No CPU decode exists in this library.
+#include <cuda_runtime.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/flsgpu.h"
+#include "fls_plan.h"
+#include "fls_strings.cuh"
+
+// ---------------------------------------------------------------------------------------------------------
+// kernel table
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+
+template <class V> cudaError_t vec_attr() {
+  return cudaFuncSetAttribute(fls_vec_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fls_block_smem<V>());
+}
+template <class V> void vec_launch(const FlsChunkDev *d, uint32_t n, cudaStream_t s) {
+  fls_vec_kernel<V><<<n * FLS_BLOCKS_PER_CHUNK, FLS_WARPS_PER_BLOCK * 32, fls_block_smem<V>(), s>>>(d);
+}
+template <template <typename> class V> cudaError_t vec_attr_all() {
+  cudaError_t e;
+  if ((e = vec_attr<V<uint8_t>>()) != cudaSuccess) return e;
+  if ((e = vec_attr<V<uint16_t>>()) != cudaSuccess) return e;
+  if ((e = vec_attr<V<uint32_t>>()) != cudaSuccess) return e;
+  return vec_attr<V<uint64_t>>();
+}
+template <template <typename> class V> bool vec_launch_w(int width, const FlsChunkDev *d, uint32_t n, cudaStream_t s) {
+  switch (width) {
+    case 1: vec_launch<V<uint8_t>>(d, n, s); return true;
+    case 2: vec_launch<V<uint16_t>>(d, n, s); return true;
+    case 4: vec_launch<V<uint32_t>>(d, n, s); return true;
+    case 8: vec_launch<V<uint64_t>>(d, n, s); return true;
+  }
+  return false;
+}
+
+cudaError_t set_kernel_attrs() {
+  cudaError_t e;
+  if ((e = vec_attr_all<VecFFOR>()) != cudaSuccess) return e;
+  if ((e = vec_attr_all<VecDELTA>()) != cudaSuccess) return e;
+  if ((e = vec_attr_all<VecRLE>()) != cudaSuccess) return e;
+  if ((e = vec_attr_all<VecDICT>()) != cudaSuccess) return e;
+  if ((e = vec_attr<VecALP>()) != cudaSuccess) return e;
+  if ((e = vec_attr<VecALPRD>()) != cudaSuccess) return e;
+  if ((e = vec_attr<VecSTROFFS>()) != cudaSuccess) return e;
+  if ((e = vec_attr<VecSTRCONST>()) != cudaSuccess) return e;
+  if ((e = vec_attr<VecSTRDICT>()) != cudaSuccess) return e;
+  return vec_attr<VecSTRFSST>();
+}
+
+const char *const kKindName[FLS_K_N] = {"ffor",     "delta",     "rle",      "dict",     "alp",  "alp_rd", "copy",
+                                        "fill",     "str_offsets", "str_copy", "str_const", "str_dict", "str_fsst",
+                                        "fsst_dictprep"};
+
+bool launch_kind(const FlsLaunch &l, const FlsChunkDev *d, cudaStream_t s) {
+  const uint32_t n = (uint32_t)l.chunks.size();
+  switch (l.kind) {
+    case FLS_K_FFOR: return vec_launch_w<VecFFOR>(l.width, d, n, s);
+    case FLS_K_DELTA: return vec_launch_w<VecDELTA>(l.width, d, n, s);
+    case FLS_K_RLE: return vec_launch_w<VecRLE>(l.width, d, n, s);
+    case FLS_K_DICT: return vec_launch_w<VecDICT>(l.width, d, n, s);
+    case FLS_K_ALP: vec_launch<VecALP>(d, n, s); return true;
+    case FLS_K_ALPRD: vec_launch<VecALPRD>(d, n, s); return true;
+    case FLS_K_COPY: fls_copy_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;
+    case FLS_K_FILL: fls_fill_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;
+    case FLS_K_STR_OFFSETS: vec_launch<VecSTROFFS>(d, n, s); return true;
+    case FLS_K_STR_COPY: fls_str_copy_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;
+    case FLS_K_STR_CONST: vec_launch<VecSTRCONST>(d, n, s); return true;
+    case FLS_K_STR_DICT: vec_launch<VecSTRDICT>(d, n, s); return true;
+    case FLS_K_STR_FSST: vec_launch<VecSTRFSST>(d, n, s); return true;
+    case FLS_K_STR_FSST_DICTPREP: fls_fsst_dictprep_kernel<<<n * 8, 128, 0, s>>>(d, 8); return true;
+  }
+  return false;
+}
+
+__global__ void fls_flush_kernel(uint4 *p, uint64_t n16, uint32_t v) {
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x)
+    p[i] = make_uint4(v, v, v, v);
+}
+
+thread_local std::string g_open_err;
+
+struct BufPool {  // size-keyed free lists; buffers live until the handle closes
+  std::multimap<size_t, void *> free_dev, free_host;
+  void *get(std::multimap<size_t, void *> &fl, size_t n) {
+    auto it = fl.lower_bound(n);
+    if (it != fl.end() && it->first <= n + n / 4 + 4096) {
+      void *p = it->second;
+      fl.erase(it);
+      return p;
+    }
+    return nullptr;
+  }
+};
+
+struct KStat {
+  std::string name;
+  uint64_t launches = 0, rd = 0, wr = 0, vectors = 0;
+  double ms = 0;
+};
+
+}  // namespace
+
+struct flsgpu {
+  int device = 0;
+  uint32_t flags = 0, slice_rgs = 0;
+  FlsTable t;
+  std::string path;
+  const uint8_t *image = nullptr;  // host image (whole file)
+  uint64_t size = 0;
+  bool image_owned = false, image_registered = false, cuda_ready = false;
+  cudaStream_t s_h2d = nullptr, s_k = nullptr, s_d2h = nullptr;
+  uint8_t *d_res = nullptr;  // resident compressed row groups [res_g0, res_g1)
+  uint64_t res_bytes = 0;
+  uint32_t res_g0 = 0, res_g1 = 0;
+  uint8_t *d_flush = nullptr;
+  uint64_t flush_bytes = 0;
+  std::string err;
+  BufPool pool;
+  std::vector<cudaEvent_t> ev_free;
+  std::vector<KStat> kstats;
+  std::vector<const char *> name_ptrs;
+  std::vector<int32_t> types32;
+
+  int fail(int code, const std::string &m) { err = m; return code; }
+  int fail_cuda(const char *what, cudaError_t e) {
+    err = std::string("CUDA: ") + what + ": " + cudaGetErrorString(e);
+    return FLSGPU_E_CUDA;
+  }
+  cudaEvent_t ev_get() {
+    if (!ev_free.empty()) { cudaEvent_t e = ev_free.back(); ev_free.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+  }
+  void *dev_alloc(size_t n) {
+    n = (n + 255) & ~(size_t)255;
+    if (!n) n = 256;
+    void *p = pool.get(pool.free_dev, n);
+    if (p) return p;
+    if (cudaMalloc(&p, n) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    dev_size[p] = n;
+    return p;
+  }
+  void *host_alloc(size_t n) {
+    n = (n + 4095) & ~(size_t)4095;
+    if (!n) n = 4096;
+    void *p = pool.get(pool.free_host, n);
+    if (p) return p;
+    if (cudaHostAlloc(&p, n, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    host_size[p] = n;
+    return p;
+  }
+  void dev_free(void *p) { if (p) pool.free_dev.emplace(dev_size[p], p); }
+  void host_free(void *p) { if (p) pool.free_host.emplace(host_size[p], p); }
+  std::map<void *, size_t> dev_size, host_size;
+};
+
+#define CK(call)                                          \
+  do {                                                    \
+    cudaError_t e_ = (call);                              \
+    if (e_ != cudaSuccess) return h->fail_cuda(#call, e_); \
+  } while (0)
+
+struct flsgpu_batch {
+  flsgpu *h = nullptr;
+  uint32_t g0 = 0, g1 = 0, flags = 0;
+  std::vector<uint32_t> cols;
+  std::vector<flsgpu_column> out;      // what the caller sees
+  std::vector<FlsColOut> dev;          // device buffers
+  std::vector<FlsColNeed> need;
+  std::vector<void *> dev_bufs, host_bufs;
+  flsgpu_timing tm;
+};
+
+namespace {
+
+// Bring CUDA up for this handle and make the whole host image available (page-locked unless told otherwise).
+int ensure_ready(flsgpu *h) {
+  if (h->cuda_ready) { CK(cudaSetDevice(h->device)); return 0; }
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&h->s_k, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+  CK(set_kernel_attrs());
+  if (!h->image) {  // opened by path: read the file into page-locked memory
+    void *p = nullptr;
+    const bool pin = !(h->flags & FLSGPU_OPEN_NO_PIN);
+    if (pin) CK(cudaHostAlloc(&p, h->size, cudaHostAllocDefault));
+    else if (!(p = malloc(h->size))) return h->fail(FLSGPU_E_NOMEM, "out of host memory");
+    int fd = open(h->path.c_str(), O_RDONLY);
+    uint64_t got = 0;
+    while (fd >= 0 && got < h->size) {
+      ssize_t r = pread(fd, (uint8_t *)p + got, std::min<uint64_t>(h->size - got, 1ull << 30), (off_t)got);
+      if (r <= 0) break;
+      got += (uint64_t)r;
+    }
+    if (fd >= 0) close(fd);
+    if (got != h->size) {
+      if (pin) cudaFreeHost(p); else free(p);
+      return h->fail(FLSGPU_E_IO, "Failed to open FastLanes file: " + h->path);
+    }
+    h->image = (const uint8_t *)p;
+    h->image_owned = true;
+    h->image_registered = false;
+    if (!pin) h->flags |= FLSGPU_OPEN_NO_PIN;
+  } else if (!(h->flags & (FLSGPU_OPEN_PINNED_IMAGE | FLSGPU_OPEN_NO_PIN))) {
+    // caller's pageable image: page-lock it in place (read-only registration is enough for H2D sources)
+    cudaError_t e = cudaHostRegister((void *)h->image, h->size, cudaHostRegisterReadOnly);
+    if (e != cudaSuccess) { cudaGetLastError(); e = cudaHostRegister((void *)h->image, h->size, cudaHostRegisterDefault); }
+    if (e == cudaSuccess) h->image_registered = true;
+    else cudaGetLastError();  // not fatal: copies fall back to the driver's staging path
+  }
+  h->cuda_ready = true;
+  return 0;
+}
+
+uint64_t range_extent(const FlsTable &t, uint32_t g0, uint32_t g1) {
+  return g1 > g0 ? t.rgs[g1 - 1].off + t.rgs[g1 - 1].size - t.rgs[g0].off : 0;
+}
+
+flsgpu *new_handle(const flsgpu_opts *o) {
+  flsgpu *h = new flsgpu();
+  if (o) { h->device = o->device; h->flags = o->flags; h->slice_rgs = o->slice_rowgroups; }
+  h->kstats.resize(FLS_K_N * 5);
+  for (int k = 0; k < FLS_K_N; ++k)
+    for (int w = 0; w < 5; ++w) {
+      static const char *const wn[5] = {"", "_u8", "_u16", "_u32", "_u64"};
+      h->kstats[k * 5 + w].name = std::string(kKindName[k]) + wn[w];
+    }
+  return h;
+}
+void finish_schema(flsgpu *h) {
+  for (auto &n : h->t.names) h->name_ptrs.push_back(n.c_str());
+  for (int ty : h->t.types) h->types32.push_back(ty);
+}
+int width_slot(int width) { return width == 1 ? 1 : width == 2 ? 2 : width == 4 ? 3 : width == 8 ? 4 : 0; }
+
+}  // namespace
+
+extern "C" {
+
+int flsgpu_abi_version(void) { return FLSGPU_ABI_VERSION; }
+
+int flsgpu_open(const char *path, const flsgpu_opts *opts, flsgpu_t **out) {
+  if (!out || !path) { g_open_err = "null argument"; return FLSGPU_E_RANGE; }
+  *out = nullptr;
+  flsgpu *h = new_handle(opts);
+  h->path = path;
+  struct stat st;
+  if (stat(path, &st) != 0 || !S_ISREG(st.st_mode)) {
+    // same text the reference's bind raises (/root/reference/src/scan_fastlanes.cpp:42)
+    g_open_err = std::string("Failed to open FastLanes file: ") + path;
+    delete h;
+    return FLSGPU_E_IO;
+  }
+  std::string e = fls_parse_file(path, h->t, &h->size);
+  if (!e.empty()) {
+    g_open_err = std::string("Failed to open FastLanes file: ") + path + " (" + e + ")";
+    delete h;
+    return FLSGPU_E_FORMAT;
+  }
+  finish_schema(h);
+  *out = h;
+  return FLSGPU_OK;
+}
+
+int flsgpu_open_image(const void *image, uint64_t size, const flsgpu_opts *opts, flsgpu_t **out) {
+  if (!out || !image) { g_open_err = "null argument"; return FLSGPU_E_RANGE; }
+  *out = nullptr;
+  flsgpu *h = new_handle(opts);
+  std::string e = fls_parse((const uint8_t *)image, size, h->t);
+  if (!e.empty()) {
+    g_open_err = "Failed to open FastLanes image (" + e + ")";
+    delete h;
+    return FLSGPU_E_FORMAT;
+  }
+  h->image = (const uint8_t *)image;
+  h->size = size;
+  finish_schema(h);
+  *out = h;
+  return FLSGPU_OK;
+}
+
+void flsgpu_close(flsgpu_t *h) {
+  if (!h) return;
+  if (h->cuda_ready) {
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    for (auto &kv : h->dev_size) cudaFree(kv.first);
+    for (auto &kv : h->host_size) cudaFreeHost(kv.first);
+    if (h->d_res) cudaFree(h->d_res);
+    if (h->d_flush) cudaFree(h->d_flush);
+    for (auto e : h->ev_free) cudaEventDestroy(e);
+    if (h->image_registered) cudaHostUnregister((void *)h->image);
+    if (h->image_owned) { if (h->flags & FLSGPU_OPEN_NO_PIN) free((void *)h->image); else cudaFreeHost((void *)h->image); }
+    cudaStreamDestroy(h->s_h2d);
+    cudaStreamDestroy(h->s_k);
+    cudaStreamDestroy(h->s_d2h);
+  }
+  delete h;
+}
+
+const char *flsgpu_last_error(const flsgpu_t *h) { return h ? h->err.c_str() : g_open_err.c_str(); }
+
+uint32_t flsgpu_num_columns(const flsgpu_t *h) { return h->t.n_cols; }
+uint32_t flsgpu_num_rowgroups(const flsgpu_t *h) { return h->t.n_rg; }
+uint64_t flsgpu_num_rows(const flsgpu_t *h) { return h->t.n_rows; }
+uint32_t flsgpu_rowgroup_rows(const flsgpu_t *h, uint32_t rg) { return rg < h->t.n_rg ? h->t.rgs[rg].n_tuples : 0; }
+
+int flsgpu_schema(const flsgpu_t *h, uint32_t *n_cols, const char *const **names, const int32_t **types) {
+  if (n_cols) *n_cols = h->t.n_cols;
+  if (names) *names = h->name_ptrs.data();
+  if (types) *types = h->types32.data();
+  return FLSGPU_OK;
+}
+
+int flsgpu_chunk_info(const flsgpu_t *h, uint32_t rg, uint32_t col, int32_t *scheme, uint64_t *bytes) {
+  if (rg >= h->t.n_rg || col >= h->t.n_cols) return FLSGPU_E_RANGE;
+  const fls_colchunk &k = h->t.chunk(rg, col);
+  if (scheme) *scheme = k.scheme;
+  if (bytes) {
+    *bytes = 0;
+    for (uint32_t s = 0; s < k.n_seg; ++s) *bytes += k.seg[s].size;
+  }
+  return FLSGPU_OK;
+}
+
+int flsgpu_make_resident(flsgpu_t *h, uint32_t g0, uint32_t g1) {
+  if (g0 > g1 || g1 > h->t.n_rg) return h->fail(FLSGPU_E_RANGE, "bad row-group range");
+  if (int rc = ensure_ready(h)) return rc;
+  if (h->d_res) { CK(cudaFree(h->d_res)); h->d_res = nullptr; h->res_g0 = h->res_g1 = 0; }
+  const uint64_t bytes = range_extent(h->t, g0, g1);
+  if (!bytes) return FLSGPU_OK;
+  CK(cudaMalloc((void **)&h->d_res, bytes));
+  CK(cudaMemcpyAsync(h->d_res, h->image + h->t.rgs[g0].off, bytes, cudaMemcpyHostToDevice, h->s_h2d));
+  CK(cudaStreamSynchronize(h->s_h2d));
+  h->res_bytes = bytes;
+  h->res_g0 = g0;
+  h->res_g1 = g1;
+  return FLSGPU_OK;
+}
+
+int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, uint32_t n_cols, uint32_t flags,
+                  flsgpu_batch_t **out) {
+  if (!out) return h->fail(FLSGPU_E_RANGE, "null argument");
+  *out = nullptr;
+  const FlsTable &t = h->t;
+  if (g0 > g1 || g1 > t.n_rg) return h->fail(FLSGPU_E_RANGE, "bad row-group range");
+  if (int rc = ensure_ready(h)) return rc;
+
+  flsgpu_batch *b = new flsgpu_batch();
+  b->h = h; b->g0 = g0; b->g1 = g1; b->flags = flags;
+  if (cols) b->cols.assign(cols, cols + n_cols);
+  else for (uint32_t c = 0; c < t.n_cols; ++c) b->cols.push_back(c);
+  for (uint32_t c : b->cols)
+    if (c >= t.n_cols) { delete b; return h->fail(FLSGPU_E_RANGE, "bad column id"); }
+  const uint32_t nc = (uint32_t)b->cols.size();
+  const bool to_host = (flags & FLSGPU_OUT_HOST) != 0;
+  memset(&b->tm, 0, sizeof(b->tm));
+
+  auto bail = [&](int code, const std::string &m) {
+    cudaDeviceSynchronize();
+    flsgpu_batch_release(b);
+    return h->fail(code, m);
+  };
+
+  // ---- output buffers
+  b->out.resize(nc); b->dev.resize(nc); b->need.resize(nc);
+  const uint64_t rows = t.rows(g0, g1), prow = t.padded_rows(g0, g1);
+  uint64_t scratch_total = 0;
+  for (uint32_t i = 0; i < nc; ++i) {
+    const uint32_t c = b->cols[i];
+    FlsColNeed n = fls_column_need(t, c, g0, g1, h->image);
+    b->need[i] = n;
+    if (n.payload_bytes >= (1ull << 32)) return bail(FLSGPU_E_LIMIT, "string payload of one batch must stay below 4 GiB; split the row-group range");
+    flsgpu_column &o = b->out[i];
+    memset(&o, 0, sizeof(o));
+    o.type = t.types[c];
+    o.width = fls_type_bits(t.types[c]) / 8;
+    o.rows = rows; o.padded_rows = prow;
+    o.compressed_bytes = n.compressed_bytes; o.decoded_bytes = n.decoded_bytes;
+    b->tm.compressed_bytes += n.compressed_bytes; b->tm.decoded_bytes += n.decoded_bytes;
+    FlsColOut &d = b->dev[i];
+    auto dalloc = [&](size_t sz) { void *p = h->dev_alloc(sz); b->dev_bufs.push_back(p); return p; };
+    auto halloc = [&](size_t sz) { void *p = h->host_alloc(sz); b->host_bufs.push_back(p); return p; };
+    if (o.width) {
+      if (!(d.data = dalloc(n.data_bytes))) return bail(FLSGPU_E_NOMEM, "out of device memory");
+      o.data = d.data;
+      if (to_host && !(o.data = halloc(n.data_bytes))) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+    } else {
+      d.offsets = (uint32_t *)dalloc(n.offsets_bytes);
+      d.payload = (uint8_t *)dalloc(n.payload_bytes);
+      if (!d.offsets || !d.payload) return bail(FLSGPU_E_NOMEM, "out of device memory");
+      o.offsets = d.offsets; o.payload = d.payload;
+      o.payload_bytes = n.payload_bytes - 16;
+      if (to_host) {
+        o.offsets = (uint32_t *)halloc(n.offsets_bytes);
+        o.payload = (uint8_t *)halloc(n.payload_bytes);
+        if (!o.offsets || !o.payload) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+      }
+      scratch_total += n.scratch_bytes;
+    }
+  }
+  if (g1 == g0) { *out = b; return FLSGPU_OK; }
+
+  // ---- compressed bytes: resident, or staged slice by slice
+  const bool resident = h->d_res && g0 >= h->res_g0 && g1 <= h->res_g1;
+  uint8_t *d_stage = nullptr;
+  if (resident) d_stage = h->d_res + (t.rgs[g0].off - t.rgs[h->res_g0].off);
+  else {
+    d_stage = (uint8_t *)h->dev_alloc(range_extent(t, g0, g1));
+    b->dev_bufs.push_back(d_stage);
+    if (!d_stage) return bail(FLSGPU_E_NOMEM, "out of device memory");
+  }
+  uint8_t *d_scratch = nullptr;
+  if (scratch_total) {
+    d_scratch = (uint8_t *)h->dev_alloc(scratch_total + 16);
+    b->dev_bufs.push_back(d_scratch);
+    if (!d_scratch) return bail(FLSGPU_E_NOMEM, "out of device memory");
+  }
+  uint32_t slice = resident && !to_host ? (g1 - g0) : (h->slice_rgs ? h->slice_rgs : 64u);
+  const uint32_t n_slices = (g1 - g0 + slice - 1) / slice;
+  // descriptors: at most 2 chunks per (row group, column)
+  const size_t desc_cap = (size_t)(g1 - g0) * nc * 2;
+  FlsChunkDev *h_desc = (FlsChunkDev *)h->host_alloc(desc_cap * sizeof(FlsChunkDev));
+  FlsChunkDev *d_desc = (FlsChunkDev *)h->dev_alloc(desc_cap * sizeof(FlsChunkDev));
+  b->host_bufs.push_back(h_desc); b->dev_bufs.push_back(d_desc);
+  if (!h_desc || !d_desc) return bail(FLSGPU_E_NOMEM, "out of memory for chunk descriptors");
+
+  struct EvPair { cudaEvent_t a, b; };
+  std::vector<EvPair> ev_h2d, ev_k, ev_d2h;
+  struct KEv { cudaEvent_t a, b; int slot; uint64_t rd, wr, vec; };
+  std::vector<KEv> kev;
+  const bool time_kernels = (h->flags & FLSGPU_OPEN_TIME_KERNELS) != 0;
+  cudaEvent_t ev_start = h->ev_get(), ev_end = h->ev_get();
+  std::vector<cudaEvent_t> used_events = {ev_start, ev_end};
+  auto ev = [&]() { cudaEvent_t e = h->ev_get(); used_events.push_back(e); return e; };
+
+  CK(cudaEventRecord(ev_start, h->s_h2d));
+  CK(cudaStreamWaitEvent(h->s_k, ev_start, 0));
+  for (uint32_t i = 0; i < nc; ++i)
+    if (b->dev[i].offsets) CK(cudaMemsetAsync(b->dev[i].offsets, 0, 4, h->s_k));
+
+  size_t desc_used = 0;
+  std::vector<uint64_t> pay_done(nc, 0), scratch_done(nc, 0);
+  uint64_t scratch_base = 0;
+  std::vector<uint64_t> scratch_col_base(nc, 0);
+  for (uint32_t i = 0; i < nc; ++i) { scratch_col_base[i] = scratch_base; scratch_base += b->need[i].scratch_bytes; }
+  uint64_t rows_done = 0;
+  std::string perr;
+  for (uint32_t si = 0; si < n_slices; ++si) {
+    const uint32_t s0 = g0 + si * slice, s1 = std::min(g1, s0 + slice);
+    const uint64_t rel = t.rgs[s0].off - t.rgs[g0].off, ext = range_extent(t, s0, s1);
+    const uint64_t srows = t.padded_rows(s0, s1);
+    // plan the slice
+    std::vector<FlsLaunch> ls;
+    std::vector<uint64_t> pay_slice(nc, 0);
+    for (uint32_t i = 0; i < nc && perr.empty(); ++i) {
+      const uint32_t c = b->cols[i];
+      FlsColOut o = b->dev[i];
+      const uint32_t wb = b->out[i].width;
+      if (wb) o.data = (uint8_t *)o.data + rows_done * wb;
+      else {
+        o.offsets += rows_done;
+        o.pay_base0 = pay_done[i];
+        FlsColNeed sn = fls_column_need(t, c, s0, s1, h->image);
+        pay_slice[i] = sn.payload_bytes - 16;
+        o.scratch = d_scratch ? d_scratch + scratch_col_base[i] + scratch_done[i] : nullptr;
+        scratch_done[i] += sn.scratch_bytes;
+      }
+      perr = fls_plan_column(t, c, s0, s1, d_stage + rel, h->image, o, ls);
+    }
+    if (!perr.empty()) break;
+    // dictionary preparation must run before the gathers that read it
+    std::stable_sort(ls.begin(), ls.end(), [](const FlsLaunch &a, const FlsLaunch &b2) {
+      return (a.kind == FLS_K_STR_FSST_DICTPREP) > (b2.kind == FLS_K_STR_FSST_DICTPREP);
+    });
+    const size_t desc0 = desc_used;
+    for (auto &l : ls) {
+      if (desc_used + l.chunks.size() > desc_cap) { perr = "internal: descriptor overflow"; break; }
+      memcpy(h_desc + desc_used, l.chunks.data(), l.chunks.size() * sizeof(FlsChunkDev));
+      desc_used += l.chunks.size();
+    }
+    if (!perr.empty()) break;
+    // H2D: compressed bytes (unless resident) + descriptors
+    EvPair eh = {ev(), ev()};
+    CK(cudaEventRecord(eh.a, h->s_h2d));
+    if (!resident) {
+      CK(cudaMemcpyAsync(d_stage + rel, h->image + t.rgs[s0].off, ext, cudaMemcpyHostToDevice, h->s_h2d));
+      b->tm.h2d_bytes += ext;
+    }
+    CK(cudaMemcpyAsync(d_desc + desc0, h_desc + desc0, (desc_used - desc0) * sizeof(FlsChunkDev), cudaMemcpyHostToDevice,
+                       h->s_h2d));
+    CK(cudaEventRecord(eh.b, h->s_h2d));
+    ev_h2d.push_back(eh);
+    // decode
+    CK(cudaStreamWaitEvent(h->s_k, eh.b, 0));
+    EvPair ek = {ev(), ev()};
+    CK(cudaEventRecord(ek.a, h->s_k));
+    size_t dpos = desc0;
+    for (auto &l : ls) {
+      KEv ke = {nullptr, nullptr, l.kind * 5 + width_slot(l.width), l.bytes_read, l.bytes_written, l.vectors};
+      if (time_kernels) { ke.a = ev(); ke.b = ev(); CK(cudaEventRecord(ke.a, h->s_k)); }
+      if (!launch_kind(l, d_desc + dpos, h->s_k)) { perr = "internal: no kernel for launch kind"; break; }
+      CK(cudaGetLastError());
+      if (time_kernels) CK(cudaEventRecord(ke.b, h->s_k));
+      kev.push_back(ke);
+      dpos += l.chunks.size();
+      b->tm.kernel_launches++;
+    }
+    if (!perr.empty()) break;
+    CK(cudaEventRecord(ek.b, h->s_k));
+    ev_k.push_back(ek);
+    // D2H
+    if (to_host) {
+      CK(cudaStreamWaitEvent(h->s_d2h, ek.b, 0));
+      EvPair ed = {ev(), ev()};
+      CK(cudaEventRecord(ed.a, h->s_d2h));
+      for (uint32_t i = 0; i < nc; ++i) {
+        const uint32_t wb = b->out[i].width;
+        if (wb) {
+          CK(cudaMemcpyAsync((uint8_t *)b->out[i].data + rows_done * wb, (uint8_t *)b->dev[i].data + rows_done * wb,
+                             srows * wb, cudaMemcpyDeviceToHost, h->s_d2h));
+          b->tm.d2h_bytes += srows * wb;
+        } else {
+          const uint64_t o0 = rows_done ? rows_done + 1 : 0, o1 = rows_done + srows + 1;
+          CK(cudaMemcpyAsync(b->out[i].offsets + o0, b->dev[i].offsets + o0, (o1 - o0) * 4, cudaMemcpyDeviceToHost, h->s_d2h));
+          if (pay_slice[i])
+            CK(cudaMemcpyAsync(b->out[i].payload + pay_done[i], b->dev[i].payload + pay_done[i], pay_slice[i],
+                               cudaMemcpyDeviceToHost, h->s_d2h));
+          b->tm.d2h_bytes += (o1 - o0) * 4 + pay_slice[i];
+        }
+      }
+      CK(cudaEventRecord(ed.b, h->s_d2h));
+      ev_d2h.push_back(ed);
+    }
+    for (uint32_t i = 0; i < nc; ++i) pay_done[i] += pay_slice[i];
+    rows_done += srows;
+    b->tm.slices++;
+  }
+  if (!perr.empty()) return bail(FLSGPU_E_FORMAT, perr);
+  if (!ev_k.empty()) CK(cudaStreamWaitEvent(h->s_d2h, ev_k.back().b, 0));
+  CK(cudaEventRecord(ev_end, h->s_d2h));
+  cudaError_t se = cudaEventSynchronize(ev_end);
+  if (se != cudaSuccess) return bail(FLSGPU_E_CUDA, std::string("CUDA: decode failed: ") + cudaGetErrorString(se));
+
+  float ms = 0;
+  cudaEventElapsedTime(&b->tm.ms_total, ev_start, ev_end);
+  for (auto &p : ev_h2d) { cudaEventElapsedTime(&ms, p.a, p.b); b->tm.ms_h2d += ms; }
+  for (auto &p : ev_k) { cudaEventElapsedTime(&ms, p.a, p.b); b->tm.ms_kernels += ms; }
+  for (auto &p : ev_d2h) { cudaEventElapsedTime(&ms, p.a, p.b); b->tm.ms_d2h += ms; }
+  if (time_kernels)
+    for (auto &k : kev) {
+      cudaEventElapsedTime(&ms, k.a, k.b);
+      KStat &s = h->kstats[k.slot];
+      s.launches++; s.ms += ms; s.rd += k.rd; s.wr += k.wr; s.vectors += k.vec;
+    }
+  for (auto e : used_events) h->ev_free.push_back(e);
+  *out = b;
+  return FLSGPU_OK;
+}
+
+uint32_t flsgpu_batch_num_columns(const flsgpu_batch_t *b) { return (uint32_t)b->out.size(); }
+int flsgpu_batch_column(const flsgpu_batch_t *b, uint32_t i, flsgpu_column *out) {
+  if (i >= b->out.size() || !out) return FLSGPU_E_RANGE;
+  *out = b->out[i];
+  return FLSGPU_OK;
+}
+int flsgpu_batch_timing(const flsgpu_batch_t *b, flsgpu_timing *out) {
+  if (!out) return FLSGPU_E_RANGE;
+  *out = b->tm;
+  return FLSGPU_OK;
+}
+void flsgpu_batch_release(flsgpu_batch_t *b) {
+  if (!b) return;
+  for (void *p : b->dev_bufs) b->h->dev_free(p);
+  for (void *p : b->host_bufs) b->h->host_free(p);
+  delete b;
+}
+
+uint32_t flsgpu_num_kernel_stats(const flsgpu_t *h) { return (uint32_t)h->kstats.size(); }
+int flsgpu_kernel_stats(const flsgpu_t *h, uint32_t i, flsgpu_kernel_stat *out) {
+  if (i >= h->kstats.size() || !out) return FLSGPU_E_RANGE;
+  const KStat &s = h->kstats[i];
+  out->name = s.name.c_str();
+  out->launches = s.launches; out->ms = s.ms; out->bytes_read = s.rd; out->bytes_written = s.wr; out->vectors = s.vectors;
+  return FLSGPU_OK;
+}
+void flsgpu_reset_kernel_stats(flsgpu_t *h) {
+  for (auto &s : h->kstats) { s.launches = s.rd = s.wr = s.vectors = 0; s.ms = 0; }
+}
+
+int flsgpu_flush_l2(flsgpu_t *h, uint64_t bytes) {
+  if (int rc = ensure_ready(h)) return rc;
+  bytes = (bytes + 15) & ~15ull;
+  if (h->flush_bytes < bytes) {
+    if (h->d_flush) CK(cudaFree(h->d_flush));
+    h->d_flush = nullptr;
+    CK(cudaMalloc((void **)&h->d_flush, bytes));
+    h->flush_bytes = bytes;
+  }
+  static uint32_t v = 0;
+  fls_flush_kernel<<<148 * 8, 256, 0, h->s_k>>>((uint4 *)h->d_flush, bytes / 16, ++v);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->s_k));
+  return FLSGPU_OK;
+}
+
+}  // extern "C"

@@ -53,6 +53,8 @@ def lib():
         L.flsw_error.argtypes = [C.c_void_p]
         L.flsw_write_file.argtypes = [C.c_void_p, C.c_char_p]
         L.flsw_destroy.argtypes = [C.c_void_p]
+        L.flsw_tile.restype = C.c_void_p
+        L.flsw_tile.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32]
         _lib = L
     return _lib
 
@@ -133,5 +135,22 @@ def write_table(columns, names=None, types=None, force=None, min_bw=None, path=N
         if path:
             img.tofile(path)
         return img
+    finally:
+        L.flsw_destroy(w)
+
+
+def tile_rowgroups(image: np.ndarray, n_total: int, pinned_alloc=None) -> np.ndarray:
+    """New image with `n_total` row groups: the (full) row groups of `image` repeated round-robin, each repeat a
+    separate copy of the bytes."""
+    L = lib()
+    image = np.ascontiguousarray(image, dtype=np.uint8)
+    w = L.flsw_tile(image.ctypes.data, image.size, n_total)
+    if not w:
+        raise RuntimeError("tile_rowgroups: image has no row groups or a partial one")
+    try:
+        size = L.flsw_size(w)
+        out = pinned_alloc(size) if pinned_alloc else np.empty(size, dtype=np.uint8)
+        C.memmove(out.ctypes.data, L.flsw_data(w), size)
+        return out
     finally:
         L.flsw_destroy(w)

@@ -1,0 +1,149 @@
+/* flsgpu.h — C ABI of libflsgpu.so, the B200 (sm_100a) FLS read/decode library.
+ *
+ * This is the drop-in boundary of the read_fls / scan_fastlanes path: it is what the reference's
+ * FastLanesFacade would bind instead of the FastLanes C++ reader objects.  Reference interface each entry
+ * point replaces (paths relative to /root/reference):
+ *
+ *   flsgpu_open / flsgpu_open_image   src/fastlanes_facade.cpp:26-67  FastLanesFacade::openFile
+ *                                     (fastlanes::connect :33, Connection::read_fls :34,
+ *                                      TableReader::get_rowgroup_reader :41) — WITHOUT the eager
+ *                                     materialize() of :48: open only parses the footer.
+ *   flsgpu_schema                     src/include/fastlanes_facade.hpp:34-35 getColumnTypes/getColumnNames
+ *                                     (declared, never implemented) and src/type_mapping.cpp:64-105.
+ *   flsgpu_num_rows / _num_rowgroups /
+ *   _rowgroup_rows                    src/fastlanes_facade.cpp:52-56 Rowgroup::ColCount/RowCount.
+ *   flsgpu_decode                     src/fastlanes_facade.cpp:48 RowgroupReader::materialize() (the decode)
+ *                                     plus :69-200 readNextChunk's copy-out: decoded columns come back as
+ *                                     flat typed arrays (strings: u32 offsets + payload bytes), host or device.
+ *   flsgpu_make_resident              no reference twin: stages compressed row groups into HBM once so that
+ *                                     repeated decodes time the kernels only (BASELINE "HBM-resident").
+ *   flsgpu_batch_release / flsgpu_close   src/fastlanes_facade.cpp:202-210 closeFile.
+ *   flsgpu_last_error                 the facade's bool returns + BinderException text
+ *                                     (src/scan_fastlanes.cpp:42 "Failed to open FastLanes file: <path>").
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or an FLSGPU_E_* code;
+ * no exception crosses this boundary.  One caller at a time per handle, from any thread.  There is NO CPU
+ * decode behind this ABI: without a CUDA device every decode call fails with FLSGPU_E_CUDA.
+ */
+#ifndef FLSGPU_H
+#define FLSGPU_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLSGPU_ABI_VERSION 1
+
+enum flsgpu_status {
+  FLSGPU_OK = 0,
+  FLSGPU_E_IO = 1,      /* cannot open / read the file */
+  FLSGPU_E_FORMAT = 2,  /* not an FLS file, or corrupt footer */
+  FLSGPU_E_RANGE = 3,   /* bad row-group range / column id / argument */
+  FLSGPU_E_CUDA = 4,    /* CUDA runtime failure (message in flsgpu_last_error) */
+  FLSGPU_E_LIMIT = 5,   /* batch exceeds a format limit (e.g. > 4 GiB string payload per batch) */
+  FLSGPU_E_NOMEM = 6
+};
+
+/* Column types: values of enum fls_type, the order of the reference's type table
+ * (src/type_mapping.cpp:11-62). */
+enum flsgpu_type {
+  FLSGPU_T_BOOLEAN = 1, FLSGPU_T_INT8, FLSGPU_T_INT16, FLSGPU_T_INT32, FLSGPU_T_INT64, FLSGPU_T_UINT8,
+  FLSGPU_T_UINT16, FLSGPU_T_UINT32, FLSGPU_T_UINT64, FLSGPU_T_FLOAT, FLSGPU_T_DOUBLE, FLSGPU_T_STR,
+  FLSGPU_T_DATE, FLSGPU_T_BYTE_ARRAY
+};
+
+/* open flags */
+#define FLSGPU_OPEN_PINNED_IMAGE 1u /* open_image: the caller's image is already page-locked */
+#define FLSGPU_OPEN_NO_PIN 2u       /* do not page-lock the image (H2D then goes through the driver's bounce buffer) */
+#define FLSGPU_OPEN_TIME_KERNELS 4u /* record a CUDA-event pair around every kernel launch (flsgpu_kernel_stats) */
+
+/* decode flags */
+#define FLSGPU_OUT_DEVICE 0u /* leave decoded columns in HBM; column pointers are device pointers */
+#define FLSGPU_OUT_HOST 1u   /* also copy decoded columns to pinned host memory; column pointers are host pointers */
+
+typedef struct flsgpu flsgpu_t;
+typedef struct flsgpu_batch flsgpu_batch_t;
+
+typedef struct {
+  int32_t device;        /* CUDA device ordinal */
+  uint32_t flags;        /* FLSGPU_OPEN_* */
+  uint32_t slice_rowgroups; /* row groups per H2D/decode/D2H pipeline slice when the range is not resident; 0 = default */
+  uint32_t reserved;
+} flsgpu_opts;
+
+typedef struct {
+  int32_t type;           /* enum flsgpu_type */
+  uint32_t width;         /* bytes per value; 0 for strings */
+  uint64_t rows;          /* valid rows in [g0,g1) */
+  uint64_t padded_rows;   /* rows the buffers hold (every row group padded to whole 1024-value vectors) */
+  void *data;             /* fixed width: padded_rows * width bytes */
+  uint32_t *offsets;      /* strings: padded_rows + 1 Arrow-style offsets into payload, offsets[0] = 0 */
+  uint8_t *payload;       /* strings: payload bytes */
+  uint64_t payload_bytes; /* strings: bytes of payload in use */
+  uint64_t compressed_bytes; /* algorithmic bytes read: segment bytes of this column in [g0,g1) */
+  uint64_t decoded_bytes;    /* algorithmic bytes written: values, or offsets + payload */
+} flsgpu_column;
+
+typedef struct {
+  float ms_total;    /* first enqueue -> last completion, on the device (CUDA events) */
+  float ms_h2d;      /* sum over slices of the compressed-bytes H2D copies */
+  float ms_kernels;  /* sum over slices of the decode kernels */
+  float ms_d2h;      /* sum over slices of the decoded-bytes D2H copies */
+  uint64_t h2d_bytes, d2h_bytes;
+  uint64_t compressed_bytes, decoded_bytes; /* algorithmic, over the selected columns */
+  uint32_t kernel_launches, slices;
+} flsgpu_timing;
+
+typedef struct {
+  const char *name;     /* kernel family, e.g. "ffor_u32" */
+  uint64_t launches;
+  double ms;            /* sum of per-launch CUDA-event durations */
+  uint64_t bytes_read;  /* algorithmic */
+  uint64_t bytes_written;
+  uint64_t vectors;
+} flsgpu_kernel_stat;
+
+/* ---- open / close ------------------------------------------------------------------------------------ */
+int flsgpu_open(const char *path, const flsgpu_opts *opts, flsgpu_t **out);
+/* The image must stay valid until flsgpu_close. */
+int flsgpu_open_image(const void *image, uint64_t size, const flsgpu_opts *opts, flsgpu_t **out);
+void flsgpu_close(flsgpu_t *h);
+/* Error text of the last failing call on `h`; with h == NULL, of the last failing open on this thread. */
+const char *flsgpu_last_error(const flsgpu_t *h);
+int flsgpu_abi_version(void);
+
+/* ---- schema ------------------------------------------------------------------------------------------- */
+uint32_t flsgpu_num_columns(const flsgpu_t *h);
+uint32_t flsgpu_num_rowgroups(const flsgpu_t *h);
+uint64_t flsgpu_num_rows(const flsgpu_t *h);
+uint32_t flsgpu_rowgroup_rows(const flsgpu_t *h, uint32_t rg);
+/* names[i] / types[i] stay valid until flsgpu_close. */
+int flsgpu_schema(const flsgpu_t *h, uint32_t *n_cols, const char *const **names, const int32_t **types);
+/* scheme (enum fls_scheme) and segment bytes of one column chunk */
+int flsgpu_chunk_info(const flsgpu_t *h, uint32_t rg, uint32_t col, int32_t *scheme, uint64_t *bytes);
+
+/* ---- decode ------------------------------------------------------------------------------------------- */
+/* Stage the compressed bytes of row groups [g0,g1) into HBM and keep them until close / the next call. */
+int flsgpu_make_resident(flsgpu_t *h, uint32_t g0, uint32_t g1);
+/* Decode columns cols[0..n_cols) (NULL = all) of row groups [g0,g1).  Returns when the batch is complete. */
+int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, uint32_t n_cols, uint32_t flags,
+                  flsgpu_batch_t **out);
+uint32_t flsgpu_batch_num_columns(const flsgpu_batch_t *b);
+int flsgpu_batch_column(const flsgpu_batch_t *b, uint32_t i, flsgpu_column *out);
+int flsgpu_batch_timing(const flsgpu_batch_t *b, flsgpu_timing *out);
+/* Returns the batch's buffers to the handle's pool. */
+void flsgpu_batch_release(flsgpu_batch_t *b);
+
+/* ---- instrumentation ---------------------------------------------------------------------------------- */
+/* Per-kernel-family accumulators (needs FLSGPU_OPEN_TIME_KERNELS).  i in [0, flsgpu_num_kernel_stats). */
+uint32_t flsgpu_num_kernel_stats(const flsgpu_t *h);
+int flsgpu_kernel_stats(const flsgpu_t *h, uint32_t i, flsgpu_kernel_stat *out);
+void flsgpu_reset_kernel_stats(flsgpu_t *h);
+/* Write `bytes` bytes of a device scratch buffer (L2 flush between timed iterations). */
+int flsgpu_flush_l2(flsgpu_t *h, uint64_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
