@@ -1,0 +1,188 @@
+"""Seeded parity cases shared by the CPU (oracle / emulation) and GPU test files.
+
+Each case is (name, columns, types, force, min_bw): a small table that pins one scheme x type x edge.
+Edge cases follow SURVEY.md §4: tail vectors (n % 1024 != 0), W = 0 and W = T, ALP exceptions
+(NaN / +-inf / -0.0 / huge), empty strings and strings longer than DuckDB's 12-byte inline threshold.
+"""
+import numpy as np
+
+import fls_writer as W
+import synth
+from fls_writer import StrColumn
+
+INT_DTYPES = {8: np.int8, 16: np.int16, 32: np.int32, 64: np.int64}
+UINT_DTYPES = {8: np.uint8, 16: np.uint16, 32: np.uint32, 64: np.uint64}
+
+
+def rng(seed):
+    return np.random.Generator(np.random.PCG64(seed))
+
+
+def ffor_case(bits, width, n, seed=None):
+    v = synth.ffor_values(bits, width, n, seed)
+    return ("ffor_i%d_w%d" % (bits, width), [v], None, [W.FFOR], [width])
+
+
+def all_ffor_cases(n=3 * 1024 + 17):
+    out = []
+    for bits in (8, 16, 32, 64):
+        for w in range(bits + 1):
+            out.append(ffor_case(bits, w, n))
+    return out
+
+
+def delta_cases(n=70_000):
+    r = rng(11)
+    out = []
+    for bits in (8, 16, 32, 64):
+        dt = INT_DTYPES[bits]
+        step = r.integers(0, 3 if bits == 8 else 50, n)
+        v = np.cumsum(step).astype(np.int64)
+        v = (v % (2 ** (bits - 1))).astype(dt) if bits < 64 else v * 1_000_003
+        out.append(("delta_i%d" % bits, [v.astype(dt)], None, [W.DELTA], None))
+    # descending + wrap-around deltas
+    v = (np.arange(n, dtype=np.int64) * -7919 + 2 ** 40).astype(np.int64)
+    out.append(("delta_i64_desc", [v], None, [W.DELTA], None))
+    v = r.integers(-2 ** 31, 2 ** 31, n).astype(np.int32)
+    out.append(("delta_i32_random_fullwidth", [v], None, [W.DELTA], None))
+    v = np.full(n, 77, dtype=np.int32)
+    out.append(("delta_i32_const_w0", [v], None, [W.DELTA], None))
+    return out
+
+
+def rle_cases(n=70_000):
+    r = rng(12)
+    out = []
+    for bits in (8, 16, 32, 64):
+        dt = INT_DTYPES[bits]
+        runs = r.integers(1, 400, n // 50)
+        vals = r.integers(-100, 100, len(runs))
+        v = np.repeat(vals, runs)[:n]
+        if len(v) < n:
+            v = np.concatenate([v, np.full(n - len(v), 5)])
+        out.append(("rle_i%d" % bits, [v.astype(dt)], None, [W.RLE], None))
+    d = np.repeat(r.uniform(0, 1, n // 100 + 1), 100)[:n]
+    out.append(("rle_f64", [d], None, [W.RLE], None))
+    return out
+
+
+def dict_cases(n=70_000):
+    r = rng(13)
+    out = []
+    for bits in (8, 16, 32, 64):
+        dt = INT_DTYPES[bits]
+        pool = r.integers(-2 ** (bits - 1), 2 ** (bits - 1) - 1, 37, dtype=np.int64).astype(dt)
+        v = pool[r.integers(0, len(pool), n)]
+        out.append(("dict_i%d" % bits, [v], None, [W.DICT], None))
+    pool = r.uniform(-1e9, 1e9, 300)
+    out.append(("dict_f64", [pool[r.integers(0, 300, n)]], None, [W.DICT], None))
+    out.append(("dict_single", [np.full(n, -5, dtype=np.int32)], None, [W.DICT], None))
+    return out
+
+
+def misc_fixed_cases(n=70_000):
+    r = rng(14)
+    out = [
+        ("uncompressed_i32", [r.integers(-2 ** 31, 2 ** 31, n).astype(np.int32)], None, [W.UNCOMPRESSED], None),
+        ("uncompressed_f64", [r.normal(size=n)], None, [W.UNCOMPRESSED], None),
+        ("uncompressed_u8", [r.integers(0, 256, n).astype(np.uint8)], None, [W.UNCOMPRESSED], None),
+        ("constant_i64", [np.full(n, -123456789012, dtype=np.int64)], None, [W.CONSTANT], None),
+        ("constant_i16", [np.full(n, -3, dtype=np.int16)], None, [W.CONSTANT], None),
+        ("constant_f64", [np.full(n, 2.5)], None, [W.CONSTANT], None),
+        ("bool_auto", [r.integers(0, 2, n) == 1], None, None, None),
+        ("float32_auto", [r.normal(size=n).astype(np.float32)], None, None, None),
+        ("u16_auto", [r.integers(0, 60000, n).astype(np.uint16)], None, None, None),
+        ("u64_auto_high", [r.integers(2 ** 63, 2 ** 64 - 1, n, dtype=np.uint64)], None, None, None),
+        ("date_auto", [(19000 + r.integers(0, 3000, n)).astype(np.int32)], [W.DATE], None, None),
+        ("one_row", [np.array([42], dtype=np.int32)], None, None, None),
+        ("exactly_one_vector", [np.arange(1024, dtype=np.int64)], None, None, None),
+        ("exactly_one_rowgroup", [np.arange(65536, dtype=np.int32)], None, None, None),
+        ("rowgroup_plus_one", [np.arange(65537, dtype=np.int32) * 3], None, None, None),
+    ]
+    return out
+
+
+SPECIALS = np.array([np.nan, np.inf, -np.inf, -0.0, 1e300, 0.1 + 0.2, 5e-324, -1e-310, 1.7976931348623157e308])
+
+
+def alp_cases(n=70_000):
+    r = rng(15)
+    prices = synth.alp_prices(n, exc_rate=0.002)
+    out = [("alp_prices", [prices], None, [W.ALP], None)]
+    v = np.round(r.uniform(-500, 500, n), 1)
+    out.append(("alp_1dec_signed", [v], None, [W.ALP], None))
+    v = r.integers(-10 ** 6, 10 ** 6, n).astype(np.float64)
+    out.append(("alp_integers", [v], None, [W.ALP], None))
+    v = np.round(r.uniform(0, 1, n), 6)
+    out.append(("alp_6dec", [v], None, [W.ALP], None))
+    v = np.round(r.uniform(0, 1000, n), 2)
+    v[r.choice(n, n // 3, replace=False)] = SPECIALS[r.integers(0, len(SPECIALS), n // 3)]
+    out.append(("alp_many_exceptions", [v], None, [W.ALP], None))
+    v = np.full(n, np.nan)
+    out.append(("alp_all_nan", [v], None, [W.ALP], None))
+    v = np.full(n, 12.5)
+    out.append(("alp_constant_w0", [v], None, [W.ALP], None))
+    v = np.round(r.uniform(0, 9e15, n))
+    out.append(("alp_huge_ints_wide", [v], None, [W.ALP], None))
+    out.append(("alprd_entropy", [synth.alp_entropy(n)], None, [W.ALP_RD], None))
+    v = r.uniform(0, 1, n) * 1000.0
+    out.append(("alprd_uniform", [v], None, [W.ALP_RD], None))
+    v = r.integers(0, 2 ** 64 - 1, n, dtype=np.uint64).view(np.float64)
+    out.append(("alprd_random_bits", [v], None, [W.ALP_RD], None))
+    v = synth.alp_entropy(n)
+    v[r.choice(n, 500, replace=False)] = SPECIALS[r.integers(0, len(SPECIALS), 500)]
+    out.append(("alprd_with_specials", [v], None, [W.ALP_RD], None))
+    out.append(("double_auto_prices", [prices], None, None, None))
+    out.append(("double_auto_entropy", [synth.alp_entropy(n)], None, None, None))
+    return out
+
+
+def _rand_strings(r, n, lo, hi, alphabet=b"abcdefghijklmnopqrstuvwxyz ABCDE0123456789"):
+    lens = r.integers(lo, hi + 1, n)
+    off = np.zeros(n + 1, dtype=np.uint64)
+    np.cumsum(lens, out=off[1:])
+    a = np.frombuffer(alphabet, dtype=np.uint8)
+    return StrColumn(a[r.integers(0, len(a), int(off[-1]))], off)
+
+
+def string_cases(n=70_000):
+    r = rng(16)
+    out = []
+    li = synth.lineitem(n, seed=3)
+    comment, shipmode, returnflag = li[15], li[14], li[8]
+    for f, nm in ((W.STR_UNCOMPRESSED, "uncompressed"), (W.STR_FSST, "fsst")):
+        out.append(("str_%s_comment" % nm, [comment], None, [f], None))
+        out.append(("str_%s_random_0_40" % nm, [_rand_strings(r, n, 0, 40)], None, [f], None))
+        out.append(("str_%s_bytes_all_values" % nm, [_rand_strings(r, 5000, 0, 20, bytes(range(256)))], None, [f], None))
+        out.append(("str_%s_all_empty" % nm, [StrColumn(np.empty(0, np.uint8), np.zeros(3001, np.uint64))], None, [f], None))
+    for f, nm in ((W.STR_DICT, "dict"), (W.STR_FSST_DICT, "fsst_dict")):
+        out.append(("str_%s_shipmode" % nm, [shipmode], None, [f], None))
+        out.append(("str_%s_returnflag" % nm, [returnflag], None, [f], None))
+        pool = _rand_strings(r, 500, 0, 60).to_list()
+        pick = r.integers(0, len(pool), n)
+        out.append(("str_%s_500_entries" % nm, [StrColumn.from_list([pool[i] for i in pick])], None, [f], None))
+    out.append(("str_constant", [StrColumn.from_list([b"FastLanes"] * 5000)], None, [W.STR_CONSTANT], None))
+    out.append(("str_constant_empty", [StrColumn.from_list([b""] * 2500)], None, [W.STR_CONSTANT], None))
+    out.append(("str_auto_user", [synth.basic_usage(n)[0][4]], None, None, None))
+    out.append(("str_auto_comment", [comment], None, None, None))
+    out.append(("str_long_values", [_rand_strings(r, 3000, 100, 900)], None, None, None))
+    return out
+
+
+def all_cases():
+    return (all_ffor_cases() + delta_cases() + rle_cases() + dict_cases() + misc_fixed_cases() + alp_cases() +
+            string_cases())
+
+
+def encode_case(case):
+    name, cols, types, force, min_bw = case
+    return W.write_table(cols, types=types, force=force, min_bw=min_bw)
+
+
+def expected_bytes(col):
+    """What a decoder must produce for a source column: ndarray bytes, or (offsets u32, payload)."""
+    if isinstance(col, StrColumn):
+        off = (col.offsets - col.offsets[0]).astype(np.uint32)
+        pay = col.data[int(col.offsets[0]):int(col.offsets[-1])]
+        return off, pay
+    return np.ascontiguousarray(col).view(np.uint8)

@@ -1,0 +1,144 @@
+"""GPU: the CUDA decode path, called through the C ABI (libflsgpu.so), against the CPU oracle — bit-exact.
+
+Every scheme x type x edge case of tests/cases.py, the three workload shapes, projection, row-group ranges,
+slice pipelining, residency, and full-size properties."""
+import numpy as np
+import pytest
+
+import cases
+import flsgpu
+import fls_writer as W
+import synth
+from fls_writer import StrColumn
+from oracle import oracle
+
+pytestmark = pytest.mark.gpu
+ALL = cases.all_cases()
+
+
+def check_table(img, rd=None, g0=0, g1=None, cols=None, **kw):
+    ora = oracle.OracleTable(img)
+    own = rd is None
+    if own:
+        rd = flsgpu.Reader.from_image(img, **kw)
+    try:
+        g1 = ora.n_rg if g1 is None else g1
+        sel = list(range(ora.n_cols)) if cols is None else cols
+        got = rd.decode(g0, g1, cols)
+        assert len(got) == len(sel)
+        for i, c in enumerate(sel):
+            exp = ora.decode(c, g0, g1, threads=4)
+            if isinstance(exp, tuple):
+                assert np.array_equal(got[i][0], exp[0]), "offsets of column %d" % c
+                assert np.array_equal(got[i][1], exp[1]), "payload of column %d" % c
+            else:
+                assert got[i].dtype == exp.dtype
+                assert np.array_equal(got[i].view(np.uint8), exp.view(np.uint8)), "column %d" % c
+    finally:
+        if own:
+            rd.close()
+    return ora
+
+
+@pytest.mark.parametrize("case", ALL, ids=[c[0] for c in ALL])
+def test_case_bit_exact(case):
+    name, cols, types, force, min_bw = case
+    img = cases.encode_case(case)
+    check_table(img)
+    # and against the source values themselves
+    with flsgpu.Reader.from_image(img) as rd:
+        got = rd.decode()
+    for c, src in enumerate(cols):
+        exp = cases.expected_bytes(src)
+        if isinstance(src, StrColumn):
+            assert np.array_equal(got[c][0], exp[0]) and np.array_equal(got[c][1], exp[1])
+        else:
+            assert np.array_equal(got[c].view(np.uint8), exp)
+
+
+def test_basic_usage_1m():
+    # config 1: 1M-row int32/int64/double/varchar table (976 full vectors + 576-row tail, 16 row groups)
+    cols, names = synth.basic_usage(1_000_000)
+    img = synth.encode(cols, names, synth.basic_usage_types())
+    ora = check_table(img)
+    assert ora.n_rg == 16 and ora.n_rows == 1_000_000
+
+
+def test_lineitem_shape_projection_ranges_slices():
+    img = synth.lineitem_image(5, tail_rows=777)
+    check_table(img)
+    check_table(img, cols=[15, 0, 5])          # projection, any order
+    check_table(img, g0=1, g1=4)               # interior range
+    check_table(img, g0=5, g1=6)               # the partial row group alone
+    check_table(img, g0=2, g1=2)               # empty range
+    check_table(img, slice_rowgroups=1)        # one pipeline slice per row group
+    check_table(img, slice_rowgroups=2, flags=flsgpu.OPEN_NO_PIN)
+    with flsgpu.Reader.from_image(img, flags=flsgpu.OPEN_TIME_KERNELS) as rd:
+        rd.make_resident(1, 5)
+        check_table(img, rd, 1, 5)             # resident range
+        check_table(img, rd, 0, 6)             # range not covered by residency -> staged
+        check_table(img, rd, 2, 4, cols=[15])
+        st = {s["name"]: s for s in rd.kernel_stats()}
+        assert "str_fsst" in st and "alp" in st and st["ffor_u64"]["launches"] >= 3
+
+
+def test_open_by_path(tmp_path):
+    p = str(tmp_path / "li.fls")
+    img = synth.lineitem_image(2, tail_rows=5)
+    img.tofile(p)
+    with flsgpu.Reader.open(p) as rd:
+        check_table(img, rd)
+
+
+def test_device_output_and_timing():
+    img = synth.lineitem_image(3)
+    with flsgpu.Reader.from_image(img) as rd:
+        rd.make_resident()
+        with rd.decode_batch(to_host=False) as b:
+            t = b.timing
+            assert t.h2d_bytes == 0 and t.d2h_bytes == 0 and t.kernel_launches > 0 and t.ms_kernels > 0
+            assert t.decoded_bytes > t.compressed_bytes > 0
+            assert all(c.data or c.offsets for c in b.columns)
+        with rd.decode_batch(to_host=True) as b:
+            assert b.timing.d2h_bytes >= b.timing.decoded_bytes
+
+
+def test_ffor_sweep_full_width_properties():
+    # config 2 at reduced N per width but every width: sum / min / max of the decoded column match the source
+    n = 16 * 65536
+    for bits in (32, 64):
+        for w in range(bits + 1):
+            v = synth.ffor_values(bits, w, n)
+            img = W.write_table([v], force=[W.FFOR], min_bw=[w])
+            with flsgpu.Reader.from_image(img) as rd:
+                got = rd.decode()[0]
+            assert np.array_equal(got, v), (bits, w)
+
+
+def test_large_single_column_properties():
+    # 2^26 int64 values (1024 row groups): idempotence (two decodes identical) + exact equality with the source
+    n = 1 << 26
+    v = synth.ffor_values(64, 21, n)
+    img = W.write_table([v], force=[W.FFOR], min_bw=[21])
+    with flsgpu.Reader.from_image(img) as rd:
+        a = rd.decode()[0]
+        b = rd.decode()[0]
+    assert np.array_equal(a, v) and np.array_equal(a, b)
+
+
+def test_alp_large_bit_exact():
+    n = 1 << 22
+    for v in (synth.alp_prices(n), synth.alp_entropy(n)):
+        img = W.write_table([v])
+        with flsgpu.Reader.from_image(img) as rd:
+            got = rd.decode()[0]
+        assert np.array_equal(got.view(np.uint64), v.view(np.uint64))
+
+
+def test_string_payload_limit_is_an_error_not_a_truncation():
+    img = synth.encode([np.arange(10, dtype=np.int32)])
+    with flsgpu.Reader.from_image(img) as rd:
+        with pytest.raises(flsgpu.FlsError):
+            rd.decode(0, 5)
+        with pytest.raises(flsgpu.FlsError):
+            rd.decode(cols=[3])
