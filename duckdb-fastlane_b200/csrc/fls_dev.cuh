@@ -44,6 +44,9 @@ static inline uint32_t fls_prmt(uint32_t a, uint32_t b, uint32_t sel) {
 template <typename V> static inline void fls_st128(void *p, const V &v) { memcpy(p, &v, 16); }
 template <typename V> static inline V fls_lds128(const void *p) { V v; memcpy(&v, p, 16); return v; }
 static inline uint32_t fls_min(uint32_t a, uint32_t b) { return a < b ? a : b; }
+static inline uint32_t fls_max(uint32_t a, uint32_t b) { return a > b ? a : b; }
+static inline void fls_smem_max(uint32_t *p, uint32_t v) { if (v > *p) *p = v; }
+#define FLS_BLOCK_SYNC() ((void)0)
 #else
 #define FLS_DEV __device__ __forceinline__
 #define FLS_MEM __device__ __forceinline__
@@ -61,6 +64,9 @@ FLS_DEV uint32_t fls_prmt(uint32_t a, uint32_t b, uint32_t sel) { return __byte_
 template <typename V> FLS_DEV void fls_st128(void *p, const V &v) { __stcs((V *)p, v); }
 template <typename V> FLS_DEV V fls_lds128(const void *p) { return *(const V *)p; }
 FLS_DEV uint32_t fls_min(uint32_t a, uint32_t b) { return min(a, b); }
+FLS_DEV uint32_t fls_max(uint32_t a, uint32_t b) { return max(a, b); }
+FLS_DEV void fls_smem_max(uint32_t *p, uint32_t v) { atomicMax(p, v); }
+#define FLS_BLOCK_SYNC() __syncthreads()
 #endif
 
 #define FLS_ORDER_AT(i) ((0x73516240u >> (4u * (i))) & 0xFu) /* FL_ORDER 0,4,2,6,1,5,3,7 packed in nibbles */

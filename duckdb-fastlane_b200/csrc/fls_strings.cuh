@@ -41,22 +41,34 @@ struct FlsByteSink {
   }
 };
 
-// ---- aligned-word byte reader over a contiguous region
-struct FlsByteSource {
-  const uint64_t *word;
-  uint64_t cur;
-  uint32_t bi;
-  FLS_MEM void init(const uint8_t *p) {
+// ---- sequential byte reader over global memory with three 8-byte words of lookahead.
+// The next words are requested long before their bytes are consumed, so the serial decode loop of a lane never
+// waits for DRAM.  Loads are clamped to [.., limit): nothing beyond the lane's own run (rounded up to 8) is read.
+struct FlsByteStream {
+  const uint64_t *next;   // address of the word that follows n2
+  const uint64_t *limit;  // first word that must not be read
+  uint64_t cur, n0, n1, n2;
+  uint32_t bi;            // bytes of `cur` already consumed (0..7)
+  FLS_MEM uint64_t fetch() {
+    const uint64_t v = next < limit ? fls_ldg(next) : 0ull;
+    ++next;
+    return v;
+  }
+  FLS_MEM void init(const uint8_t *p, const uint8_t *end) {
     const uint32_t a = (uint32_t)((uintptr_t)p & 7u);
-    word = (const uint64_t *)(p - a);
-    cur = fls_ldg(word) >> (8u * a);
+    next = (const uint64_t *)(p - a);
+    limit = (const uint64_t *)(((uintptr_t)end + 7u) & ~(uintptr_t)7u);
+    cur = fetch(); n0 = fetch(); n1 = fetch(); n2 = fetch();
     bi = a;
   }
-  FLS_MEM uint32_t next() {
-    if (bi == 8u) { ++word; cur = fls_ldg(word); bi = 0; }
-    const uint32_t b = (uint32_t)cur & 0xFFu;
-    cur >>= 8; ++bi;
-    return b;
+  // the next two bytes (low 16 bits), without consuming them
+  FLS_MEM uint32_t peek2() const {
+    const uint32_t sh = 8u * bi;
+    return (uint32_t)((cur >> sh) | ((n0 << 1) << (63u - sh)));
+  }
+  FLS_MEM void skip(uint32_t k) {  // k in {1,2}
+    bi += k;
+    if (bi >= 8u) { bi -= 8u; cur = n0; n0 = n1; n1 = n2; n2 = fetch(); }
   }
 };
 
@@ -98,8 +110,41 @@ struct VecSTRCONST {
 //        seg[4] = vec_ep u32[n_vec+1] (payload offset of each vector inside the row group)
 struct VecSTRDICT {
   static constexpr uint32_t TILE = 4096u, XCH = TILE + 4224u;
-  static constexpr uint32_t SMEM = XCH + 128u, BLOCK_SMEM = 0;
-  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+  static constexpr uint32_t SMEM = XCH + 128u;
+  // Block-shared dictionary cache (the block's 4 warps decode vectors of the same chunk):
+  //   [hdr: u32 maxlen, u32 stride][lens u16 x 1024][tab: n_dict x stride u64, entries zero padded]
+  // Built when the dictionary is small (<= 1024 entries and <= 8 KB padded); stride = 0 means "not cached".
+  static constexpr uint32_t CACHE_ENTRIES = 1024u, CACHE_BYTES = 8192u;
+  static constexpr uint32_t LENS = 16u, TAB = LENS + 2u * CACHE_ENTRIES;
+  static constexpr uint32_t BLOCK_SMEM = TAB + CACHE_BYTES;
+  FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
+    uint32_t *hdr = (uint32_t *)bsm;
+    uint16_t *lens = (uint16_t *)(bsm + LENS);
+    uint64_t *tab = (uint64_t *)(bsm + TAB);
+    const uint32_t *doff = (const uint32_t *)k.seg[2];
+    const uint8_t *dbytes = k.seg[3];
+    const uint32_t n_dict = k.aux32;
+    if (tid == 0) { hdr[0] = 0; hdr[1] = 0; }
+    FLS_BLOCK_SYNC();
+    if (n_dict > CACHE_ENTRIES) return;  // uniform over the block
+    uint32_t m = 0;
+    for (uint32_t i = tid; i < n_dict; i += nthreads) m = fls_max(m, fls_ldg(doff + i + 1) - fls_ldg(doff + i));
+    fls_smem_max(hdr, m);
+    FLS_BLOCK_SYNC();
+    const uint32_t stride = (hdr[0] + 7u) >> 3;
+    if (stride == 0 || n_dict * stride * 8u > CACHE_BYTES) return;
+    for (uint32_t i = tid; i < n_dict; i += nthreads) {
+      const uint32_t a = fls_ldg(doff + i), L = fls_ldg(doff + i + 1) - a;
+      lens[i] = (uint16_t)L;
+      for (uint32_t wd = 0; wd < stride; ++wd) {
+        uint64_t x = 0;
+        for (uint32_t b = 0; b < 8u && 8u * wd + b < L; ++b) x |= (uint64_t)fls_ldg(dbytes + a + 8u * wd + b) << (8u * b);
+        tab[i * stride + wd] = x;
+      }
+    }
+    if (tid == 0) hdr[1] = stride;
+  }
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *bsm) {
     const fls_vechdr h = fls_load_hdr(k, 0, v);
     uint32_t bw = FLS_META_BW(h.meta);
     if (bw > 32u) bw = 32u;
@@ -107,6 +152,9 @@ struct VecSTRDICT {
     const uint8_t *dbytes = k.seg[3];
     const uint32_t n_dict = k.aux32;
     const uint32_t vec_ep = fls_ldg((const uint32_t *)k.seg[4] + v);
+    const uint32_t stride = ((const uint32_t *)bsm)[1];
+    const uint16_t *lens = (const uint16_t *)(bsm + LENS);
+    const uint64_t *tab = (const uint64_t *)(bsm + TAB);
     uint32_t *tile = (uint32_t *)(w.sm + TILE), *xch = (uint32_t *)(w.sm + XCH);
     if (bw) { w.stage(0, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
     // 1. indices -> tile (original order: FFOR positions are original positions)
@@ -126,9 +174,14 @@ struct VecSTRDICT {
     // 2. bytes produced by each thread's 32 strings
     FLS_LANES(t) {
       uint32_t tot = 0;
-      for (uint32_t i = 0; i < 32u; ++i) {
-        const uint32_t d = tile[33u * t + i];
-        tot += fls_ldg(doff + d + 1) - fls_ldg(doff + d);
+      if (stride) {
+#pragma unroll 8
+        for (uint32_t i = 0; i < 32u; ++i) tot += lens[tile[33u * t + i]];
+      } else {
+        for (uint32_t i = 0; i < 32u; ++i) {
+          const uint32_t d = tile[33u * t + i];
+          tot += fls_ldg(doff + d + 1) - fls_ldg(doff + d);
+        }
       }
       xch[t] = tot;
     }
@@ -138,12 +191,29 @@ struct VecSTRDICT {
       for (uint32_t u = 0; u < t; ++u) pos += xch[u];
       FlsByteSink sink;
       sink.init(k.pay + k.pay_base + pos);
-      for (uint32_t i = 0; i < 32u; ++i) {
-        const uint32_t d = tile[33u * t + i];
-        const uint32_t a = fls_ldg(doff + d), b = fls_ldg(doff + d + 1);
-        for (uint32_t c = a; c < b; ++c) sink.push(fls_ldg(dbytes + c), 1);
-        pos += b - a;
-        tile[33u * t + i] = pos;
+      if (stride == 1u) {  // every entry fits one word: one append per string
+#pragma unroll 4
+        for (uint32_t i = 0; i < 32u; ++i) {
+          const uint32_t d = tile[33u * t + i], L = lens[d];
+          if (L) sink.push(tab[d], L);
+          pos += L;
+          tile[33u * t + i] = pos;
+        }
+      } else if (stride) {
+        for (uint32_t i = 0; i < 32u; ++i) {
+          const uint32_t d = tile[33u * t + i], L = lens[d];
+          for (uint32_t o = 0; o < L; o += 8u) sink.push(tab[d * stride + (o >> 3)], fls_min(8u, L - o));
+          pos += L;
+          tile[33u * t + i] = pos;
+        }
+      } else {
+        for (uint32_t i = 0; i < 32u; ++i) {
+          const uint32_t d = tile[33u * t + i];
+          const uint32_t a = fls_ldg(doff + d), b = fls_ldg(doff + d + 1);
+          for (uint32_t c = a; c < b; ++c) sink.push(fls_ldg(dbytes + c), 1);
+          pos += b - a;
+          tile[33u * t + i] = pos;
+        }
       }
       sink.finish();
     }
@@ -187,22 +257,27 @@ struct VecSTRFSST {
       if (bwc)
         for (uint32_t r = 0; r < 32u; ++r) c1 += fls_extract<uint32_t>(cpk, bwc, r, t);
       if (c1 > c0) {
-        FlsByteSource src;
-        src.init(comp + c0);
+        FlsByteStream src;
+        src.init(comp + c0, comp + c1);
         FlsByteSink sink;
         sink.init(pay + d0);
         uint32_t left = c1 - c0;
-        while (left) {
-          const uint32_t code = src.next();
-          --left;
-          if (code == 255u) {
-            if (!left) break;
-            sink.push(src.next(), 1);
-            --left;
-          } else {
-            const uint32_t L = len[code];
-            if (L) sink.push(sym[code], L);
-          }
+        // software pipeline: the table lookups of code i+1 are issued before code i is appended
+        uint32_t pk = src.peek2(), code = pk & 0xFFu;
+        uint32_t kk = code == 255u ? 2u : 1u;
+        uint32_t L = code == 255u ? 1u : (uint32_t)len[code];
+        uint64_t s = code == 255u ? (uint64_t)((pk >> 8) & 0xFFu) : sym[code];
+        while (kk <= left) {
+          left -= kk;
+          src.skip(kk);
+          const uint32_t cL = L;
+          const uint64_t cs = s;
+          pk = src.peek2(); code = pk & 0xFFu;
+          kk = code == 255u ? 2u : 1u;
+          L = code == 255u ? 1u : (uint32_t)len[code];
+          s = code == 255u ? (uint64_t)((pk >> 8) & 0xFFu) : sym[code];
+          if (cL) sink.push(cs, cL);
+          if (!left) break;
         }
         sink.finish();
       }

@@ -454,6 +454,7 @@ int flso_decode_str(const flso_table *t, uint32_t c, uint32_t g0, uint32_t g1, u
     ps[g - g0 + 1] = ps[g - g0] + t->rg[g].cols[c].aux64[0];
   }
   dec_ctx x = {t, c, g0, rs, ps, NULL, offsets, payload};
+  offsets[0] = 0;
   int rc = par_for(g0, g1, threads, str_job, &x);
   free(rs); free(ps);
   return rc;
