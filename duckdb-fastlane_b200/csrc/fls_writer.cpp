@@ -346,10 +346,12 @@ static void alp_vec(Stream &s, const double *v, const std::vector<AlpCombo> &top
   put_bytes(s.data, pos.data(), pos.size() * 2); pad_to(s.data, 16);
 }
 
+static thread_local int tl_force_alp_ef = -1;  // test knob: e * 32 + f, or -1 (flsw_force_alp_ef)
 static Chunk enc_alp(const double *v, uint32_t n_vec) {
   Chunk c; c.scheme = FLS_S_ALP;
   Stream s;
   std::vector<AlpCombo> topk = alp_topk(v, n_vec);
+  if (tl_force_alp_ef >= 0) topk.assign(1, AlpCombo{tl_force_alp_ef / 32, tl_force_alp_ef % 32, 1, 0});
   for (uint32_t i = 0; i < n_vec; ++i) alp_vec(s, v + i * FLS_VEC, topk);
   s.move_into(c);
   return c;
@@ -651,6 +653,7 @@ struct Writer {
   std::vector<int> types;
   std::vector<int> force;     // per column: forced scheme or -1
   std::vector<int> force_bw;  // per column: minimum FFOR width or -1
+  std::vector<int> force_ef;  // per column: forced ALP exponent * 32 + factor, or -1
   Bytes file;
   Bytes rg_footer;  // serialized row-group descriptors
   uint32_t n_rg = 0;
@@ -680,6 +683,7 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
   for (size_t c = 0; c < w.types.size(); ++c) {
     Chunk ch;
     int t = w.types[c], f = w.force[c];
+    tl_force_alp_ef = c < w.force_ef.size() ? w.force_ef[c] : -1;
     switch (fls_type_bits(t)) {
       case 8: ch = enc_fixed<uint8_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false); break;
       case 16: ch = enc_fixed<uint16_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false); break;
@@ -769,6 +773,15 @@ int flsw_write_file(flsw_writer *h, const char *path) {
   return 0;
 }
 void flsw_destroy(flsw_writer *h) { delete (flsw::Writer *)h; }
+// Test knobs: pin a column's ALP exponent/factor; expose the scalar ALP encode used by the writer.
+int flsw_force_alp_ef(flsw_writer *h, uint32_t col, int32_t e, int32_t f) {
+  flsw::Writer *w = (flsw::Writer *)h;
+  if (col >= w->types.size() || e < 0 || e > 18 || f < 0 || f > e) return 1;
+  w->force_ef.resize(w->types.size(), -1);
+  w->force_ef[col] = e * 32 + f;
+  return 0;
+}
+int64_t flsw_alp_encode_value(double v, int32_t e, int32_t f) { return flsw::alp_encode(v, e, f); }
 
 // Build a new image holding `n_total` row groups by repeating the (full) row groups of `image` round-robin.
 // Every repeat is a separate copy of the bytes.  Returns a finished writer (flsw_data/flsw_size) or NULL.

@@ -53,6 +53,9 @@ def lib():
         L.flsw_error.argtypes = [C.c_void_p]
         L.flsw_write_file.argtypes = [C.c_void_p, C.c_char_p]
         L.flsw_destroy.argtypes = [C.c_void_p]
+        L.flsw_force_alp_ef.argtypes = [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32]
+        L.flsw_alp_encode_value.argtypes = [C.c_double, C.c_int32, C.c_int32]
+        L.flsw_alp_encode_value.restype = C.c_int64
         L.flsw_tile.restype = C.c_void_p
         L.flsw_tile.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32]
         _lib = L
@@ -86,7 +89,7 @@ class StrColumn:
         return StrColumn(self.data, self.offsets[a:b + 1])  # offsets stay absolute into data
 
 
-def write_table(columns, names=None, types=None, force=None, min_bw=None, path=None) -> np.ndarray:
+def write_table(columns, names=None, types=None, force=None, min_bw=None, path=None, alp_ef=None) -> np.ndarray:
     """Encode a table into an FLS image (returned as a uint8 array; also written to `path` if given).
 
     columns: list of np.ndarray (fixed width) or StrColumn.   force/min_bw: optional per-column scheme / FFOR width.
@@ -106,6 +109,9 @@ def write_table(columns, names=None, types=None, force=None, min_bw=None, path=N
             b = -1 if not min_bw or min_bw[i] is None else min_bw[i]
             if f >= 0 or b >= 0:
                 L.flsw_force_scheme(w, i, f, b)
+            if alp_ef and alp_ef[i] is not None:
+                if L.flsw_force_alp_ef(w, i, alp_ef[i][0], alp_ef[i][1]):
+                    raise ValueError("bad ALP exponent/factor")
         cols = [c if isinstance(c, StrColumn) else np.ascontiguousarray(c) for c in columns]
         for r0 in range(0, max(n_rows, 1), RG_ROWS):
             r1 = min(n_rows, r0 + RG_ROWS)

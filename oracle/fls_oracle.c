@@ -246,6 +246,12 @@ static int chunk_alp(const uint8_t *rgp, const ochunk *k, uint32_t n_vec, double
 
 /* ---- ALP-RD: out = (dict[left] << rbw) | right, then patch left-part exceptions.
  *      duckdb/.../alprd/algorithm/alprd.hpp:206-233. */
+void flso_alprd_decode(const uint16_t *dict, const uint16_t *left, const uint64_t *right, uint32_t rbw, uint32_t n,
+                       const uint16_t *xpos, const uint16_t *xleft, uint32_t nx, uint64_t *o) {
+  for (uint32_t i = 0; i < n; ++i) o[i] = ((uint64_t)dict[left[i] & 7] << rbw) | right[i];
+  for (uint32_t i = 0; i < nx; ++i) o[xpos[i]] = ((uint64_t)xleft[i] << rbw) | right[xpos[i]];
+}
+
 static int chunk_alprd(const uint8_t *rgp, const ochunk *k, uint32_t n_vec, uint64_t *out) {
   const ovhdr *h = (const ovhdr *)(rgp + k->seg[0].off);
   const uint8_t *data = rgp + k->seg[1].off;
@@ -259,10 +265,9 @@ static int chunk_alprd(const uint8_t *rgp, const ochunk *k, uint32_t n_vec, uint
     unffor_64((const uint64_t *)p, rbw, 0, right);
     unffor_16((const uint16_t *)(p + 128ull * rbw), lbw, 0, left);
     uint64_t *o = out + (size_t)v * O_VEC;
-    for (unsigned i = 0; i < O_VEC; ++i) o[i] = ((uint64_t)dict[left[i] & 7] << rbw) | right[i];
     const uint16_t *xl = (const uint16_t *)(p + 128ull * rbw + 128ull * lbw);
     const uint16_t *xp = (const uint16_t *)((const uint8_t *)xl + PAD16((uint64_t)nx * 2));
-    for (uint32_t i = 0; i < nx; ++i) o[xp[i]] = ((uint64_t)xl[i] << rbw) | right[xp[i]];
+    flso_alprd_decode(dict, left, right, rbw, O_VEC, xp, xl, nx, o);
   }
   return 0;
 }

@@ -48,6 +48,9 @@ def lib():
         L.flso_alp_decode_value.restype = C.c_double
         L.flso_fsst_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.flso_fsst_decode.restype = C.c_uint64
+        L.flso_alprd_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,
+                                        C.c_uint32, C.c_void_p]
+        L.flso_alprd_decode.restype = None
         _lib = L
     return _lib
 

@@ -79,7 +79,7 @@ def test_lineitem_shape_projection_ranges_slices():
         check_table(img, rd, 0, 6)             # range not covered by residency -> staged
         check_table(img, rd, 2, 4, cols=[15])
         st = {s["name"]: s for s in rd.kernel_stats()}
-        assert "str_fsst" in st and "alp" in st and st["ffor_u64"]["launches"] >= 3
+        assert "str_fsst" in st and "alp_u64" in st and st["ffor_u64"]["launches"] >= 3
 
 
 def test_open_by_path(tmp_path):
@@ -142,3 +142,33 @@ def test_string_payload_limit_is_an_error_not_a_truncation():
             rd.decode(0, 5)
         with pytest.raises(flsgpu.FlsError):
             rd.decode(cols=[3])
+
+
+def test_alp_kernel_against_reference_golden_every_exponent_factor():
+    # tests/golden/alp.npz: DuckDB's own DecodeValue(n, e, f) for all 190 (e, f) pairs.  One table with one column
+    # per pair, the writer pinned to that pair: the CUDA kernel must reproduce the reference's bits.
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "alp.npz"))
+    cols, efs, want = [], [], []
+    for e in range(19):
+        for f in range(e + 1):
+            m = (g["dec_e"] == e) & (g["dec_f"] == f)
+            bits = g["dec_bits"][m]
+            cols.append(bits.view(np.float64)); efs.append((e, f)); want.append(bits)
+    img = W.write_table(cols, force=[W.ALP] * len(cols), alp_ef=efs)
+    with flsgpu.Reader.from_image(img) as rd:
+        got = rd.decode()
+    for c, bits in enumerate(want):
+        assert np.array_equal(got[c].view(np.uint64), bits), efs[c]
+
+
+def test_fsst_kernel_on_reference_golden_strings():
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fsst.npz"))
+    for name in ("comment", "shipinstruct", "user", "binary", "fixture_like"):
+        col = StrColumn(g[name + "_raw"], g[name + "_off"])
+        for f in (W.STR_FSST, W.STR_FSST_DICT):
+            img = W.write_table([col], force=[f])
+            with flsgpu.Reader.from_image(img) as rd:
+                o, p = rd.decode()[0]
+            assert np.array_equal(o.astype(np.uint64), g[name + "_off"]) and np.array_equal(p, g[name + "_raw"])
