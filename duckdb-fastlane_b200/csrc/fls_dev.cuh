@@ -28,6 +28,7 @@
 #define FLS_LANES(t) for (uint32_t t = 0; t < 32u; ++t)
 #define FLS_VAR(T, n) T n##_l[32]
 #define FLS_AT(n) n##_l[t]
+#define FLS_BCAST(n, lane) n##_l[lane]
 struct fls_u4 { uint32_t x, y, z, w; };
 struct fls_ul2 { uint64_t x, y; };
 template <typename T> static inline T fls_ldg(const T *p) { return *p; }
@@ -55,6 +56,7 @@ static inline void fls_smem_max(uint32_t *p, uint32_t v) { if (v > *p) *p = v; }
 #define FLS_LANES(t) for (uint32_t t = threadIdx.x & 31u, fls_once_ = 1u; fls_once_; fls_once_ = 0u, __syncwarp())
 #define FLS_VAR(T, n) T n##_l
 #define FLS_AT(n) n##_l
+#define FLS_BCAST(n, lane) __shfl_sync(0xFFFFFFFFu, n##_l, lane)
 typedef uint4 fls_u4;
 typedef ulonglong2 fls_ul2;
 template <typename T> FLS_DEV T fls_ldg(const T *p) { return __ldg(p); }
@@ -102,6 +104,11 @@ struct FlsWarp {
           : "memory");
     }
   }
+  // Order earlier generic-proxy accesses to the slot before the next bulk copy (async proxy) overwrites it.
+  __device__ __forceinline__ void fence_async() {
+    __syncwarp();
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
   // Wait until every staged byte has landed.
   __device__ __forceinline__ void wait() {
     if ((threadIdx.x & 31u) == 0) {
@@ -121,6 +128,7 @@ struct FlsWarp {
   void init(uint8_t *slot, uint64_t *) { sm = slot; }
   void stage(uint32_t off, const uint8_t *src, uint32_t bytes) { memcpy(sm + off, src, bytes); }
   void wait() {}
+  void fence_async() {}
 #endif
 };
 

@@ -41,6 +41,46 @@ struct FlsByteSink {
   }
 };
 
+// ---- contiguous byte writer, lean variant for the decode loops: 64-bit accumulator, one aligned 8-byte store per
+// completed word, no byte loops on the hot path.  The first (possibly shared) word is parked in a register and
+// written byte-wise in finish(), like the tail, so neighbouring lanes never touch each other's bytes.
+struct FlsWordSink {
+  uint64_t *word;   // aligned address of the word being assembled
+  uint8_t *base;    // aligned address of the first word
+  uint64_t acc, headw;
+  uint32_t n, head;
+  bool first;
+  FLS_MEM void init(uint8_t *p) {
+    const uint32_t a = (uint32_t)((uintptr_t)p & 7u);
+    base = p - a;
+    word = (uint64_t *)base;
+    acc = 0; headw = 0; n = a; head = a; first = true;
+  }
+  // append the low L bytes of s (bytes above L must be zero), 0 <= L <= 8
+  FLS_MEM void push(uint64_t s, uint32_t L) {
+    const uint32_t sh = 8u * n;
+    acc |= s << sh;
+    const uint64_t carry = (s >> 1) >> (63u - sh);  // the bytes that did not fit (none when n == 0)
+    n += L;
+    const bool full = n >= 8u;
+    if (full && !first) *word = acc;   // predicated store
+    headw = (full && first) ? acc : headw;
+    first = first && !full;
+    word += full ? 1 : 0;
+    acc = full ? carry : acc;
+    n &= 7u;
+  }
+  FLS_MEM void finish() {
+    if (!first) {
+      for (uint32_t i = head; i < 8u; ++i) base[i] = (uint8_t)(headw >> (8u * i));
+      uint8_t *b = (uint8_t *)word;
+      for (uint32_t i = 0; i < n; ++i) b[i] = (uint8_t)(acc >> (8u * i));
+    } else {
+      for (uint32_t i = head; i < n; ++i) base[i] = (uint8_t)(acc >> (8u * i));
+    }
+  }
+};
+
 // ---- sequential byte reader over global memory with three 8-byte words of lookahead.
 // The next words are requested long before their bytes are consumed, so the serial decode loop of a lane never
 // waits for DRAM.  Loads are clamped to [.., limit): nothing beyond the lane's own run (rounded up to 8) is read.
@@ -228,13 +268,22 @@ struct VecSTRDICT {
 // Lane t's 32 strings are contiguous in both the compressed and the decoded space, so the thread decodes ONE
 // contiguous compressed run [c0,c1) into ONE contiguous output run starting at d0.
 struct VecSTRFSST {
+  // Phase 1 uses the slot as [decoded-ends DELTA stage + tile | compressed-ends DELTA stage]; phase 2 reuses the
+  // whole slot as the window the vector's compressed bytes are bulk-copied into.
   static constexpr uint32_t CSTAGE = DecDELTA<uint32_t>::SMEM;  // compressed-ends payload staged after the tile
-  static constexpr uint32_t SMEM = CSTAGE + 128u + 4096u;
+  static constexpr uint32_t WINDOW = 18432u;                    // 3 blocks of 4 warps per SM
+  static constexpr uint32_t SMEM = WINDOW;
   static constexpr uint32_t BLOCK_SMEM = 2304;  // symbol table, shared by the block's warps (same chunk)
+  static_assert(CSTAGE + 128u + 4096u <= WINDOW, "phase-1 buffers must fit the slot");
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsmem, uint32_t tid, uint32_t nthreads) {
     const uint64_t *src = (const uint64_t *)k.seg[4];
     uint64_t *dst = (uint64_t *)bsmem;
-    for (uint32_t i = tid; i < 2304u / 8u; i += nthreads) dst[i] = fls_ldg(src + i);
+    for (uint32_t i = tid; i < 2304u / 8u; i += nthreads) {
+      uint64_t x = fls_ldg(src + i);
+      if (i == 255u) x = 0;                                                      // sym[255]
+      if (i == 256u + 31u) x = (x & 0x00FFFFFFFFFFFFFFull) | (1ull << 56);       // len[255] = 1
+      dst[i] = x;
+    }
   }
   FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *symtab) {
     const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
@@ -251,39 +300,76 @@ struct VecSTRFSST {
     const uint8_t *len = symtab + 2048;
     const uint8_t *comp = k.seg[5];
     uint8_t *pay = k.pay + k.pay_base;
+    // lane t's 32 strings are contiguous originals: compressed run [c0,c1) -> decoded run starting at d0
+    FLS_VAR(uint32_t, c0); FLS_VAR(uint32_t, c1); FLS_VAR(uint32_t, d0);
     FLS_LANES(t) {
-      const uint32_t c0 = cbases[t], d0 = dbases[t];
-      uint32_t c1 = c0 + 32u * (uint32_t)hc.base;
+      FLS_AT(c0) = cbases[t];
+      FLS_AT(d0) = dbases[t];
+      uint32_t e = FLS_AT(c0) + 32u * (uint32_t)hc.base;
       if (bwc)
-        for (uint32_t r = 0; r < 32u; ++r) c1 += fls_extract<uint32_t>(cpk, bwc, r, t);
-      if (c1 > c0) {
+        for (uint32_t r = 0; r < 32u; ++r) e += fls_extract<uint32_t>(cpk, bwc, r, t);
+      FLS_AT(c1) = e;
+    }
+    // offsets leave first: afterwards nothing in the slot is live and it becomes the compressed-byte window
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
+    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + DecDELTA<uint32_t>::STAGE, offs, t, k.pay_base); }
+    // lane 0 owns originals [0,32), lane 31 owns [992,1024): the vector's compressed bytes are [cv0, cv1)
+    const uint32_t cv0 = FLS_BCAST(c0, 0), cv1 = FLS_BCAST(c1, 31);
+    const uint32_t wbase = cv0 & ~15u;
+    const uint32_t span = cv1 > wbase ? cv1 - wbase : 0u;
+    if (span != 0u && span + 16u <= WINDOW) {
+      w.fence_async();
+      w.stage(0, comp + wbase, (span + 15u) & ~15u);
+      w.wait();
+      const uint8_t *cb = w.sm;
+      FLS_LANES(t) {
+        uint32_t p = FLS_AT(c0) - wbase;
+        const uint32_t pend = FLS_AT(c1) - wbase;
+        if (pend > p && pend <= span) {
+          FlsWordSink sink;
+          sink.init(pay + FLS_AT(d0));
+          // len[255] is 1 and sym[255] is 0 in the block's copy of the table (block_init), so an escape is
+          // just "take the literal instead of the symbol": no divergent path in the loop.
+          uint32_t code = cb[p], lit = cb[p + 1u];
+          for (;;) {
+            const uint32_t esc = code == 255u ? 1u : 0u;
+            const uint32_t np = p + 1u + esc;
+            if (np > pend) break;  // end of the run (or a dangling escape at its end)
+            const uint32_t L = len[code];
+            uint64_t sv = sym[code];
+            if (esc) sv = lit;
+            p = np;
+            code = cb[p];
+            lit = cb[p + 1u];
+            sink.push(sv, L);
+          }
+          sink.finish();
+        }
+      }
+      return;
+    }
+    // vectors whose compressed bytes do not fit the window: per-lane streaming from global memory
+    FLS_LANES(t) {
+      const uint32_t a0 = FLS_AT(c0), a1 = FLS_AT(c1);
+      if (a1 > a0) {
         FlsByteStream src;
-        src.init(comp + c0, comp + c1);
-        FlsByteSink sink;
-        sink.init(pay + d0);
-        uint32_t left = c1 - c0;
-        // software pipeline: the table lookups of code i+1 are issued before code i is appended
-        uint32_t pk = src.peek2(), code = pk & 0xFFu;
-        uint32_t kk = code == 255u ? 2u : 1u;
-        uint32_t L = code == 255u ? 1u : (uint32_t)len[code];
-        uint64_t s = code == 255u ? (uint64_t)((pk >> 8) & 0xFFu) : sym[code];
-        while (kk <= left) {
+        src.init(comp + a0, comp + a1);
+        FlsWordSink sink;
+        sink.init(pay + FLS_AT(d0));
+        uint32_t left = a1 - a0;
+        while (left) {
+          const uint32_t pk = src.peek2(), code = pk & 0xFFu;
+          const uint32_t kk = code == 255u ? 2u : 1u;
+          if (kk > left) break;
+          const uint32_t L = code == 255u ? 1u : (uint32_t)len[code];
+          const uint64_t sv = code == 255u ? (uint64_t)((pk >> 8) & 0xFFu) : sym[code];
           left -= kk;
           src.skip(kk);
-          const uint32_t cL = L;
-          const uint64_t cs = s;
-          pk = src.peek2(); code = pk & 0xFFu;
-          kk = code == 255u ? 2u : 1u;
-          L = code == 255u ? 1u : (uint32_t)len[code];
-          s = code == 255u ? (uint64_t)((pk >> 8) & 0xFFu) : sym[code];
-          if (cL) sink.push(cs, cL);
-          if (!left) break;
+          sink.push(sv, L);
         }
         sink.finish();
       }
     }
-    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
-    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + DecDELTA<uint32_t>::STAGE, offs, t, k.pay_base); }
   }
 };
 
