@@ -215,10 +215,12 @@ def run_ours(args, rank, world, local, dist):
     sampler = ClockSampler(local) if rank == 0 else None
     barrier()
     w0, c0 = time.perf_counter(), time.time()
-    ev_ms, launches, dec_bytes, cmp_bytes = 0.0, 0, 0, 0
+    ev_ms, launches, dec_bytes, cmp_bytes, plan_ms, kern_ms = 0.0, 0, 0, 0, 0.0, 0.0
     for _ in range(args.steps):
         b = rd.decode_batch(to_host=False)
         ev_ms += b.timing.ms_total
+        plan_ms += b.timing.ms_host_plan
+        kern_ms += b.timing.ms_kernels
         launches += b.timing.kernel_launches
         dec_bytes, cmp_bytes = b.timing.decoded_bytes, b.timing.compressed_bytes
         b.release()
@@ -306,6 +308,7 @@ def run_ours(args, rank, world, local, dist):
                        "parallelism": "row-group sharding, no collective on the data path"},
             "compressed_bytes_per_step": cmp_bytes, "decoded_bytes_per_step": dec_bytes,
             "wall_ms_per_step": wall_step, "setup_s": setup_s,
+            "host_plan_ms_per_step": plan_ms / args.steps, "kernel_ms_per_step": kern_ms / args.steps,
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms, "steps": e2e_steps, "device_ms_per_step": e_ev_ms / e2e_steps,

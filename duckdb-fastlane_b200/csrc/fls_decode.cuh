@@ -90,20 +90,28 @@ template <typename T> struct DecDELTA {
     if (sizeof(T) == 8) {
       // 16 lanes x 64 steps: thread (l = t&15, h = t>>4) owns steps [32h, 32h+32); the upper half needs the
       // lower half's total first.
+      // Each half-lane unpacks its 32 deltas ONCE into registers; only the 16 half totals cross lanes.
       uint64_t *xch = (uint64_t *)(w.sm + XCH);
+      FLS_VAR2(uint64_t, dl, 32);
       FLS_LANES(t) {
         const uint32_t l = t & 15u, h = t >> 4;
         uint64_t tot = 0;
-        if (bw)
-          for (uint32_t r = 32u * h; r < 32u * h + 32u; ++r) tot += (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l);
-        xch[t] = tot + 32ull * base;
+#pragma unroll
+        for (uint32_t j = 0; j < 32u; ++j) {
+          const uint32_t r = 32u * h + j;
+          const uint64_t dv = (bw ? (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l) : 0ull) + base;
+          FLS_AT2(dl, j) = dv;
+          tot += dv;
+        }
+        xch[t] = tot;
       }
       FLS_LANES(t) {
         const uint32_t l = t & 15u, h = t >> 4;
         uint64_t acc = (uint64_t)bases[l] + (h ? xch[l] : 0ull);
-        for (uint32_t r = 32u * h; r < 32u * h + 32u; ++r) {
-          acc += (bw ? (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l) : 0ull) + base;
-          tile[fls_tile_slot<T>(64u * l + r)] = (T)acc;
+#pragma unroll
+        for (uint32_t j = 0; j < 32u; ++j) {
+          acc += FLS_AT2(dl, j);
+          tile[fls_tile_slot<T>(64u * l + 32u * h + j)] = (T)acc;
         }
       }
     } else {

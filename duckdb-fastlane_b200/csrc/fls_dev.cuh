@@ -29,6 +29,8 @@
 #define FLS_VAR(T, n) T n##_l[32]
 #define FLS_AT(n) n##_l[t]
 #define FLS_BCAST(n, lane) n##_l[lane]
+#define FLS_VAR2(T, n, K) T n##_l[32][K]
+#define FLS_AT2(n, j) n##_l[t][j]
 struct fls_u4 { uint32_t x, y, z, w; };
 struct fls_ul2 { uint64_t x, y; };
 template <typename T> static inline T fls_ldg(const T *p) { return *p; }
@@ -57,6 +59,8 @@ static inline void fls_smem_max(uint32_t *p, uint32_t v) { if (v > *p) *p = v; }
 #define FLS_VAR(T, n) T n##_l
 #define FLS_AT(n) n##_l
 #define FLS_BCAST(n, lane) __shfl_sync(0xFFFFFFFFu, n##_l, lane)
+#define FLS_VAR2(T, n, K) T n##_l[K]
+#define FLS_AT2(n, j) n##_l[j]
 typedef uint4 fls_u4;
 typedef ulonglong2 fls_ul2;
 template <typename T> FLS_DEV T fls_ldg(const T *p) { return __ldg(p); }

@@ -164,12 +164,17 @@ struct VecSTRDICT {
     const uint32_t *doff = (const uint32_t *)k.seg[2];
     const uint8_t *dbytes = k.seg[3];
     const uint32_t n_dict = k.aux32;
-    if (tid == 0) { hdr[0] = 0; hdr[1] = 0; }
+    if (tid == 0) { hdr[0] = 0; hdr[1] = 0; hdr[2] = 0; }
     FLS_BLOCK_SYNC();
     if (n_dict > CACHE_ENTRIES) return;  // uniform over the block
-    uint32_t m = 0;
-    for (uint32_t i = tid; i < n_dict; i += nthreads) m = fls_max(m, fls_ldg(doff + i + 1) - fls_ldg(doff + i));
+    uint32_t m = 0, mn = 0xFFFFFFFFu;
+    for (uint32_t i = tid; i < n_dict; i += nthreads) {
+      const uint32_t L = fls_ldg(doff + i + 1) - fls_ldg(doff + i);
+      m = fls_max(m, L);
+      mn = fls_min(mn, L);
+    }
     fls_smem_max(hdr, m);
+    fls_smem_max(hdr + 2, ~mn);  // max of the complement = complement of the min
     FLS_BLOCK_SYNC();
     const uint32_t stride = (hdr[0] + 7u) >> 3;
     if (stride == 0 || n_dict * stride * 8u > CACHE_BYTES) return;
@@ -193,6 +198,9 @@ struct VecSTRDICT {
     const uint32_t n_dict = k.aux32;
     const uint32_t vec_ep = fls_ldg((const uint32_t *)k.seg[4] + v);
     const uint32_t stride = ((const uint32_t *)bsm)[1];
+    const uint32_t maxlen = ((const uint32_t *)bsm)[0], minlen = ~((const uint32_t *)bsm)[2];
+    // every entry has the same power-of-two length (flags, codes): strings pack into whole words
+    const uint32_t ulen = (stride == 1u && maxlen == minlen && (maxlen & (maxlen - 1u)) == 0u) ? maxlen : 0u;
     const uint16_t *lens = (const uint16_t *)(bsm + LENS);
     const uint64_t *tab = (const uint64_t *)(bsm + TAB);
     uint32_t *tile = (uint32_t *)(w.sm + TILE), *xch = (uint32_t *)(w.sm + XCH);
@@ -210,6 +218,24 @@ struct VecSTRDICT {
         tile[fls_tile_slot<uint32_t>(p + 2u)] = fls_min(ix.z, n_dict - 1u);
         tile[fls_tile_slot<uint32_t>(p + 3u)] = fls_min(ix.w, n_dict - 1u);
       }
+    }
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
+    if (ulen) {
+      // fixed-length fast path: offsets are arithmetic, 8/ulen strings fill one 8-byte word
+      const uint32_t per = 8u / ulen, sh = 8u * ulen;
+      FLS_LANES(t) {
+        FlsWordSink sink;
+        sink.init(k.pay + k.pay_base + vec_ep + 32u * t * ulen);
+        for (uint32_t i = 0; i < 32u; i += per) {
+          uint64_t x = 0;
+          for (uint32_t j = 0; j < per; ++j) x |= tab[tile[33u * t + i + j]] << (sh * j);
+          sink.push(x, 8u);
+        }
+        sink.finish();
+#pragma unroll 8
+        for (uint32_t j = 0; j < 32u; ++j) offs[j * 32u + t] = k.pay_base + vec_ep + (j * 32u + t + 1u) * ulen;
+      }
+      return;
     }
     // 2. bytes produced by each thread's 32 strings
     FLS_LANES(t) {
@@ -229,13 +255,13 @@ struct VecSTRDICT {
     FLS_LANES(t) {
       uint32_t pos = vec_ep;
       for (uint32_t u = 0; u < t; ++u) pos += xch[u];
-      FlsByteSink sink;
+      FlsWordSink sink;
       sink.init(k.pay + k.pay_base + pos);
       if (stride == 1u) {  // every entry fits one word: one append per string
 #pragma unroll 4
         for (uint32_t i = 0; i < 32u; ++i) {
           const uint32_t d = tile[33u * t + i], L = lens[d];
-          if (L) sink.push(tab[d], L);
+          sink.push(tab[d], L);
           pos += L;
           tile[33u * t + i] = pos;
         }
@@ -257,7 +283,6 @@ struct VecSTRDICT {
       }
       sink.finish();
     }
-    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
     FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + TILE, offs, t, k.pay_base); }
   }
 };

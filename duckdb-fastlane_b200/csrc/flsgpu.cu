@@ -11,6 +11,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -360,6 +361,8 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
                   flsgpu_batch_t **out) {
   if (!out) return h->fail(FLSGPU_E_RANGE, "null argument");
   *out = nullptr;
+  const auto host_t0 = std::chrono::steady_clock::now();
+  double plan_ms = 0;
   const FlsTable &t = h->t;
   if (g0 > g1 || g1 > t.n_rg) return h->fail(FLSGPU_E_RANGE, "bad row-group range");
   if (int rc = ensure_ready(h)) return rc;
@@ -469,6 +472,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     const uint64_t rel = t.rgs[s0].off - t.rgs[g0].off, ext = range_extent(t, s0, s1);
     const uint64_t srows = t.padded_rows(s0, s1);
     // plan the slice
+    const auto plan_t0 = std::chrono::steady_clock::now();
     std::vector<FlsLaunch> ls;
     std::vector<uint64_t> pay_slice(nc, 0);
     for (uint32_t i = 0; i < nc && perr.empty(); ++i) {
@@ -498,6 +502,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       desc_used += l.chunks.size();
     }
     if (!perr.empty()) break;
+    plan_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - plan_t0).count();
     // H2D: compressed bytes (unless resident) + descriptors
     EvPair eh = {ev(), ev()};
     CK(cudaEventRecord(eh.a, h->s_h2d));
@@ -572,6 +577,8 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       s.launches++; s.ms += ms; s.rd += k.rd; s.wr += k.wr; s.vectors += k.vec;
     }
   for (auto e : used_events) h->ev_free.push_back(e);
+  b->tm.ms_host_plan = (float)plan_ms;
+  b->tm.ms_host_total = (float)std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
   *out = b;
   return FLSGPU_OK;
 }

@@ -37,7 +37,8 @@ class Column(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("ms_total", C.c_float), ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("compressed_bytes", C.c_uint64),
-                ("decoded_bytes", C.c_uint64), ("kernel_launches", C.c_uint32), ("slices", C.c_uint32)]
+                ("decoded_bytes", C.c_uint64), ("kernel_launches", C.c_uint32), ("slices", C.c_uint32),
+                ("ms_host_plan", C.c_float), ("ms_host_total", C.c_float)]
 
 
 class KernelStat(C.Structure):

@@ -93,6 +93,8 @@ typedef struct {
   uint64_t h2d_bytes, d2h_bytes;
   uint64_t compressed_bytes, decoded_bytes; /* algorithmic, over the selected columns */
   uint32_t kernel_launches, slices;
+  float ms_host_plan; /* host time spent building chunk descriptors (inside ms_total) */
+  float ms_host_total; /* host wall time of the whole call */
 } flsgpu_timing;
 
 typedef struct {

@@ -161,6 +161,19 @@ def string_cases(n=70_000):
         pool = _rand_strings(r, 500, 0, 60).to_list()
         pick = r.integers(0, len(pool), n)
         out.append(("str_%s_500_entries" % nm, [StrColumn.from_list([pool[i] for i in pick])], None, [f], None))
+    for L in (2, 4, 8):
+        pool = [bytes(r.integers(65, 91, L).astype(np.uint8)) for _ in range(9)]
+        out.append(("str_dict_uniform_len%d" % L, [StrColumn.from_list([pool[i] for i in r.integers(0, 9, n)])], None,
+                    [W.STR_DICT], None))
+    # first row group has mixed lengths (odd payload size), second one is fixed-length: unaligned fast path
+    mixed = [b"ab", b"c", b"defgh"]
+    strs = [mixed[i] for i in r.integers(0, 3, 65536)] + [(b"XY", b"ZW")[i] for i in r.integers(0, 2, n - 65536 + 4000)]
+    out.append(("str_dict_mixed_then_uniform", [StrColumn.from_list(strs)], None, [W.STR_DICT], None))
+    out.append(("str_dict_entries_17_bytes", [li[13]], None, [W.STR_DICT], None))
+    # compressed bytes of one vector exceed the kernel's shared-memory window -> streaming fallback path
+    out.append(("str_fsst_long_fallback", [_rand_strings(r, 9000, 60, 200)], None, [W.STR_FSST], None))
+    out.append(("str_fsst_dict_long_entries", [StrColumn.from_list([pool2 for pool2 in
+                [b"entry-%04d-" % (i % 300) + b"x" * (i % 300 % 90) for i in range(n)]])], None, [W.STR_FSST_DICT], None))
     out.append(("str_constant", [StrColumn.from_list([b"FastLanes"] * 5000)], None, [W.STR_CONSTANT], None))
     out.append(("str_constant_empty", [StrColumn.from_list([b""] * 2500)], None, [W.STR_CONSTANT], None))
     out.append(("str_auto_user", [synth.basic_usage(n)[0][4]], None, None, None))
