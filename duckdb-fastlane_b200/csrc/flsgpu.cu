@@ -68,8 +68,14 @@ const char *const kKindName[FLS_K_N] = {"ffor",     "delta",     "rle",      "di
                                         "fill",     "str_offsets", "str_copy", "str_const", "str_dict", "str_fsst",
                                         "fsst_dictprep"};
 
-bool launch_kind(const FlsLaunch &l, const FlsChunkDev *d, cudaStream_t s) {
-  const uint32_t n = (uint32_t)l.chunks.size();
+struct LaunchRec {  // what is needed to (re)issue one launch once its descriptors are on the device
+  int kind, width;
+  uint32_t n;
+  uint64_t rd, wr, vec;
+};
+
+bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
+  const uint32_t n = l.n;
   switch (l.kind) {
     case FLS_K_FFOR: return vec_launch_w<VecFFOR>(l.width, d, n, s);
     case FLS_K_DELTA: return vec_launch_w<VecDELTA>(l.width, d, n, s);
@@ -137,6 +143,16 @@ struct flsgpu {
   std::vector<KStat> kstats;
   std::vector<const char *> name_ptrs;
   std::vector<int32_t> types32;
+  // Plan of the last single-slice resident decode: repeated scans of the same range into the same (pooled)
+  // buffers reuse the descriptors already on the device instead of rebuilding and re-uploading them.
+  struct PlanCache {
+    bool valid = false;
+    uint32_t g0 = 0, g1 = 0;
+    std::vector<uint32_t> cols;
+    std::vector<const void *> ptrs;
+    std::vector<LaunchRec> recs;
+    FlsChunkDev *d_desc = nullptr;
+  } plan;
 
   int fail(int code, const std::string &m) { err = m; return code; }
   int fail_cuda(const char *what, cudaError_t e) {
@@ -439,12 +455,30 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
   }
   uint32_t slice = resident && !to_host ? (g1 - g0) : (h->slice_rgs ? h->slice_rgs : 64u);
   const uint32_t n_slices = (g1 - g0 + slice - 1) / slice;
+  // plan cache (single-slice resident decodes only): key = range, columns and every buffer address
+  const bool cacheable = n_slices == 1 && resident && !to_host;
+  std::vector<const void *> key_ptrs;
+  if (cacheable) {
+    key_ptrs.push_back(d_stage); key_ptrs.push_back(d_scratch);
+    for (uint32_t i = 0; i < nc; ++i) { key_ptrs.push_back(b->dev[i].data); key_ptrs.push_back(b->dev[i].offsets); key_ptrs.push_back(b->dev[i].payload); }
+  }
+  const bool plan_hit = cacheable && h->plan.valid && h->plan.g0 == g0 && h->plan.g1 == g1 && h->plan.cols == b->cols &&
+                        h->plan.ptrs == key_ptrs;
   // descriptors: at most 2 chunks per (row group, column)
   const size_t desc_cap = (size_t)(g1 - g0) * nc * 2;
-  FlsChunkDev *h_desc = (FlsChunkDev *)h->host_alloc(desc_cap * sizeof(FlsChunkDev));
-  FlsChunkDev *d_desc = (FlsChunkDev *)h->dev_alloc(desc_cap * sizeof(FlsChunkDev));
-  b->host_bufs.push_back(h_desc); b->dev_bufs.push_back(d_desc);
-  if (!h_desc || !d_desc) return bail(FLSGPU_E_NOMEM, "out of memory for chunk descriptors");
+  FlsChunkDev *h_desc = nullptr, *d_desc = nullptr;
+  if (plan_hit) d_desc = h->plan.d_desc;
+  else {
+    h_desc = (FlsChunkDev *)h->host_alloc(desc_cap * sizeof(FlsChunkDev));
+    d_desc = (FlsChunkDev *)h->dev_alloc(desc_cap * sizeof(FlsChunkDev));
+    b->host_bufs.push_back(h_desc);
+    if (!h_desc || !d_desc) { h->dev_free(d_desc); return bail(FLSGPU_E_NOMEM, "out of memory for chunk descriptors"); }
+    if (cacheable) {  // the cache takes the device descriptors over
+      h->plan.valid = false;
+      h->dev_free(h->plan.d_desc);
+      h->plan.d_desc = d_desc;
+    } else b->dev_bufs.push_back(d_desc);
+  }
 
   struct EvPair { cudaEvent_t a, b; };
   std::vector<EvPair> ev_h2d, ev_k, ev_d2h;
@@ -474,8 +508,10 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     // plan the slice
     const auto plan_t0 = std::chrono::steady_clock::now();
     std::vector<FlsLaunch> ls;
+    std::vector<LaunchRec> recs;
     std::vector<uint64_t> pay_slice(nc, 0);
-    for (uint32_t i = 0; i < nc && perr.empty(); ++i) {
+    if (plan_hit) recs = h->plan.recs;
+    for (uint32_t i = 0; i < nc && perr.empty() && !plan_hit; ++i) {
       const uint32_t c = b->cols[i];
       FlsColOut o = b->dev[i];
       const uint32_t wb = b->out[i].width;
@@ -500,8 +536,13 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       if (desc_used + l.chunks.size() > desc_cap) { perr = "internal: descriptor overflow"; break; }
       memcpy(h_desc + desc_used, l.chunks.data(), l.chunks.size() * sizeof(FlsChunkDev));
       desc_used += l.chunks.size();
+      recs.push_back(LaunchRec{l.kind, l.width, (uint32_t)l.chunks.size(), l.bytes_read, l.bytes_written, l.vectors});
     }
     if (!perr.empty()) break;
+    if (cacheable && !plan_hit) {
+      h->plan.g0 = g0; h->plan.g1 = g1; h->plan.cols = b->cols; h->plan.ptrs = key_ptrs; h->plan.recs = recs;
+      h->plan.valid = true;
+    }
     plan_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - plan_t0).count();
     // H2D: compressed bytes (unless resident) + descriptors
     EvPair eh = {ev(), ev()};
@@ -510,8 +551,9 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       CK(cudaMemcpyAsync(d_stage + rel, h->image + t.rgs[s0].off, ext, cudaMemcpyHostToDevice, h->s_h2d));
       b->tm.h2d_bytes += ext;
     }
-    CK(cudaMemcpyAsync(d_desc + desc0, h_desc + desc0, (desc_used - desc0) * sizeof(FlsChunkDev), cudaMemcpyHostToDevice,
-                       h->s_h2d));
+    if (!plan_hit)
+      CK(cudaMemcpyAsync(d_desc + desc0, h_desc + desc0, (desc_used - desc0) * sizeof(FlsChunkDev), cudaMemcpyHostToDevice,
+                         h->s_h2d));
     CK(cudaEventRecord(eh.b, h->s_h2d));
     ev_h2d.push_back(eh);
     // decode
@@ -519,14 +561,14 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     EvPair ek = {ev(), ev()};
     CK(cudaEventRecord(ek.a, h->s_k));
     size_t dpos = desc0;
-    for (auto &l : ls) {
-      KEv ke = {nullptr, nullptr, l.kind * 5 + width_slot(l.width), l.bytes_read, l.bytes_written, l.vectors};
+    for (auto &l : recs) {
+      KEv ke = {nullptr, nullptr, l.kind * 5 + width_slot(l.width), l.rd, l.wr, l.vec};
       if (time_kernels) { ke.a = ev(); ke.b = ev(); CK(cudaEventRecord(ke.a, h->s_k)); }
       if (!launch_kind(l, d_desc + dpos, h->s_k)) { perr = "internal: no kernel for launch kind"; break; }
       CK(cudaGetLastError());
       if (time_kernels) CK(cudaEventRecord(ke.b, h->s_k));
       kev.push_back(ke);
-      dpos += l.chunks.size();
+      dpos += l.n;
       b->tm.kernel_launches++;
     }
     if (!perr.empty()) break;
@@ -592,6 +634,20 @@ int flsgpu_batch_column(const flsgpu_batch_t *b, uint32_t i, flsgpu_column *out)
 int flsgpu_batch_timing(const flsgpu_batch_t *b, flsgpu_timing *out) {
   if (!out) return FLSGPU_E_RANGE;
   *out = b->tm;
+  return FLSGPU_OK;
+}
+int flsgpu_batch_fetch(const flsgpu_batch_t *b, uint32_t i, void *values, uint32_t *offsets) {
+  flsgpu *h = b->h;
+  if (i >= b->out.size()) return h->fail(FLSGPU_E_RANGE, "bad column index");
+  const flsgpu_column &o = b->out[i];
+  const FlsColOut &d = b->dev[i];
+  CK(cudaSetDevice(h->device));
+  if (o.width) {
+    if (values) CK(cudaMemcpy(values, d.data, o.padded_rows * o.width, cudaMemcpyDeviceToHost));
+  } else {
+    if (offsets) CK(cudaMemcpy(offsets, d.offsets, (o.padded_rows + 1) * 4, cudaMemcpyDeviceToHost));
+    if (values && o.payload_bytes) CK(cudaMemcpy(values, d.payload, o.payload_bytes, cudaMemcpyDeviceToHost));
+  }
   return FLSGPU_OK;
 }
 void flsgpu_batch_release(flsgpu_batch_t *b) {

@@ -90,6 +90,7 @@ def lib():
     L.flsgpu_batch_num_columns.restype = u32
     L.flsgpu_batch_column.argtypes = [vp, u32, C.POINTER(Column)]
     L.flsgpu_batch_timing.argtypes = [vp, C.POINTER(Timing)]
+    L.flsgpu_batch_fetch.argtypes = [vp, u32, vp, vp]
     L.flsgpu_batch_release.argtypes = [vp]
     L.flsgpu_batch_release.restype = None
     L.flsgpu_num_kernel_stats.argtypes = [vp]
@@ -137,6 +138,20 @@ class Batch:
         end = int(offs[n])
         pay = np.ctypeslib.as_array((C.c_uint8 * end).from_address(c.payload)) if end else np.empty(0, np.uint8)
         return (offs.copy(), pay.copy()) if copy else (offs, pay)
+
+    def fetch(self, i, padded=False):
+        """Copy column i of a device-output batch to new host arrays (flsgpu_batch_fetch)."""
+        c = self.columns[i]
+        n = c.padded_rows if padded else c.rows
+        if c.width:
+            a = np.empty(c.padded_rows, dtype=DTYPES[c.type])
+            rc = lib().flsgpu_batch_fetch(self.h, i, a.ctypes.data, None)
+            self.reader._check(rc)
+            return a[:n]
+        offs = np.empty(c.padded_rows + 1, dtype=np.uint32)
+        pay = np.empty(max(int(c.payload_bytes), 1), dtype=np.uint8)
+        self.reader._check(lib().flsgpu_batch_fetch(self.h, i, pay.ctypes.data, offs.ctypes.data))
+        return offs[:n + 1], pay[:int(offs[n])]
 
     def release(self):
         if self.h:

@@ -134,6 +134,9 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
 uint32_t flsgpu_batch_num_columns(const flsgpu_batch_t *b);
 int flsgpu_batch_column(const flsgpu_batch_t *b, uint32_t i, flsgpu_column *out);
 int flsgpu_batch_timing(const flsgpu_batch_t *b, flsgpu_timing *out);
+/* Copy column i of a FLSGPU_OUT_DEVICE batch to caller memory: `values` receives padded_rows * width bytes
+ * (fixed width) or payload_bytes bytes (strings); `offsets` (strings only) receives padded_rows + 1 entries. */
+int flsgpu_batch_fetch(const flsgpu_batch_t *b, uint32_t i, void *values, uint32_t *offsets);
 /* Returns the batch's buffers to the handle's pool. */
 void flsgpu_batch_release(flsgpu_batch_t *b);
 

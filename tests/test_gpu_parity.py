@@ -172,3 +172,27 @@ def test_fsst_kernel_on_reference_golden_strings():
             with flsgpu.Reader.from_image(img) as rd:
                 o, p = rd.decode()[0]
             assert np.array_equal(o.astype(np.uint64), g[name + "_off"]) and np.array_equal(p, g[name + "_raw"])
+
+
+def test_resident_plan_cache_reuse_is_exact():
+    # repeated device-output decodes of a resident range reuse the cached descriptors; results must not change,
+    # also after a different range / projection was decoded in between
+    img = synth.lineitem_image(4)
+    ora = oracle.OracleTable(img)
+    with flsgpu.Reader.from_image(img) as rd:
+        rd.make_resident()
+        for rnd in range(4):
+            cols = None if rnd != 2 else [15, 3]
+            g0, g1 = (0, 4) if rnd != 1 else (1, 3)
+            with rd.decode_batch(g0, g1, cols, to_host=False) as b:
+                assert rnd != 3 or b.timing.ms_host_plan < 0.05
+                for i, c in enumerate(range(ora.n_cols) if cols is None else cols):
+                    exp = ora.decode(c, g0, g1)
+                    got = b.fetch(i)
+                    if isinstance(exp, tuple):
+                        assert np.array_equal(got[0], exp[0]) and np.array_equal(got[1], exp[1])
+                    else:
+                        assert np.array_equal(got.view(np.uint8), exp.view(np.uint8))
+        # rounds 0 and 3 decode the same range into the same pooled buffers
+        with rd.decode_batch(to_host=False) as b:
+            assert b.timing.ms_host_plan < 0.05
