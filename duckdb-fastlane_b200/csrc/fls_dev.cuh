@@ -38,6 +38,15 @@ static inline uint32_t fls_shf_r(uint32_t lo, uint32_t hi, uint32_t s) {
   s &= 31u;
   return s ? (lo >> s) | (hi << (32u - s)) : lo;
 }
+// funnel shift left (wrap): high word of (hi:lo) << (s & 31)
+static inline uint32_t fls_shf_l(uint32_t lo, uint32_t hi, uint32_t s) {
+  s &= 31u;
+  return s ? (hi << s) | (lo >> (32u - s)) : hi;
+}
+// funnel shift right, shift amount clamped to 32: low word of (hi:lo) >> min(s, 32)
+static inline uint32_t fls_shf_rc(uint32_t lo, uint32_t hi, uint32_t s) {
+  return s >= 32u ? hi : (s ? (lo >> s) | (hi << (32u - s)) : lo);
+}
 static inline uint32_t fls_prmt(uint32_t a, uint32_t b, uint32_t sel) {
   const uint64_t v = ((uint64_t)b << 32) | a;
   uint32_t r = 0;
@@ -50,6 +59,16 @@ static inline uint32_t fls_min(uint32_t a, uint32_t b) { return a < b ? a : b; }
 static inline uint32_t fls_max(uint32_t a, uint32_t b) { return a > b ? a : b; }
 static inline void fls_smem_max(uint32_t *p, uint32_t v) { if (v > *p) *p = v; }
 #define FLS_BLOCK_SYNC() ((void)0)
+extern int fls_emul_force_any; /* tests: make every vote succeed, i.e. every lane takes the most general variant */
+#define FLS_ANY(x) ((x) || fls_emul_force_any) /* warp vote among the converged lanes: any variant it selects is correct for every lane */
+// Exclusive prefix sum of a FLS_VAR(uint32_t, n) across the warp's lanes; `total` (warp-uniform) receives the sum.
+// Use OUTSIDE FLS_LANES regions.
+#define FLS_EXCL_SCAN(n, total)                                  \
+  do {                                                           \
+    uint32_t a_ = 0;                                             \
+    for (uint32_t t_ = 0; t_ < 32u; ++t_) { const uint32_t x_ = n##_l[t_]; n##_l[t_] = a_; a_ += x_; } \
+    (total) = a_;                                                \
+  } while (0)
 #else
 #define FLS_DEV __device__ __forceinline__
 #define FLS_MEM __device__ __forceinline__
@@ -65,6 +84,8 @@ typedef uint4 fls_u4;
 typedef ulonglong2 fls_ul2;
 template <typename T> FLS_DEV T fls_ldg(const T *p) { return __ldg(p); }
 FLS_DEV uint32_t fls_shf_r(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_r(lo, hi, s); }
+FLS_DEV uint32_t fls_shf_l(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_l(lo, hi, s); }
+FLS_DEV uint32_t fls_shf_rc(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_rc(lo, hi, s); }
 FLS_DEV uint32_t fls_prmt(uint32_t a, uint32_t b, uint32_t sel) { return __byte_perm(a, b, sel); }
 // streaming 128-bit store: decoded columns are written once and not re-read by this kernel
 template <typename V> FLS_DEV void fls_st128(void *p, const V &v) { __stcs((V *)p, v); }
@@ -73,6 +94,18 @@ FLS_DEV uint32_t fls_min(uint32_t a, uint32_t b) { return min(a, b); }
 FLS_DEV uint32_t fls_max(uint32_t a, uint32_t b) { return max(a, b); }
 FLS_DEV void fls_smem_max(uint32_t *p, uint32_t v) { atomicMax(p, v); }
 #define FLS_BLOCK_SYNC() __syncthreads()
+#define FLS_ANY(x) (__any_sync(__activemask(), (x)) != 0)
+#define FLS_EXCL_SCAN(n, total)                                                   \
+  do {                                                                            \
+    const uint32_t x_ = n##_l;                                                    \
+    uint32_t i_ = x_;                                                             \
+    _Pragma("unroll") for (uint32_t d_ = 1; d_ < 32u; d_ <<= 1) {                 \
+      const uint32_t y_ = __shfl_up_sync(0xFFFFFFFFu, i_, d_);                    \
+      if ((threadIdx.x & 31u) >= d_) i_ += y_;                                    \
+    }                                                                             \
+    (total) = __shfl_sync(0xFFFFFFFFu, i_, 31);                                   \
+    n##_l = i_ - x_;                                                              \
+  } while (0)
 #endif
 
 #define FLS_ORDER_AT(i) ((0x73516240u >> (4u * (i))) & 0xFu) /* FL_ORDER 0,4,2,6,1,5,3,7 packed in nibbles */

@@ -109,6 +109,37 @@ __global__ void __launch_bounds__(FLS_WARPS_PER_BLOCK * 32) fls_vec_kernel(const
   V::run(k, v, w, bsm);
 }
 
+// String columns with a per-chunk lookup table (DICT, FSST): blocks of V::WARPS warps; block b owns vectors
+// [bx*vpb, (bx+1)*vpb) of chunk b / bpc, builds the chunk's table once (V::block_init) and its warps take the
+// vectors one at a time from a shared counter.
+// Shared memory: [warp slots | block-shared (V::BLOCK_SMEM) | mbarriers | vector counter]
+template <class V> constexpr uint32_t fls_chunk_smem() {
+  return V::WARPS * V::SMEM + V::BLOCK_SMEM + V::WARPS * 8u + 16u;
+}
+template <class V>
+__global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t bpc) {
+  extern __shared__ __align__(128) uint8_t fls_smem[];
+  const FlsChunkDev &k = chunks[blockIdx.x / bpc];
+  const uint32_t bx = blockIdx.x % bpc, vpb = (k.n_vec + bpc - 1u) / bpc;
+  const uint32_t v0 = bx * vpb, v1 = min(k.n_vec, v0 + vpb);
+  if (v0 >= v1) return;
+  const uint32_t warp = threadIdx.x >> 5;
+  uint8_t *bsm = fls_smem + V::WARPS * V::SMEM;
+  uint32_t *next = (uint32_t *)(bsm + V::BLOCK_SMEM + V::WARPS * 8u);
+  if (threadIdx.x == 0) *next = v0;
+  V::block_init(k, bsm, threadIdx.x, V::WARPS * 32u);
+  __syncthreads();
+  FlsWarp w;
+  w.init(fls_smem + warp * V::SMEM, (uint64_t *)(bsm + V::BLOCK_SMEM) + warp);
+  for (;;) {
+    uint32_t v = 0;
+    if ((threadIdx.x & 31u) == 0) v = atomicAdd(next, 1u);
+    v = __shfl_sync(0xFFFFFFFFu, v, 0);
+    if (v >= v1) break;
+    V::run(k, v, w, bsm);
+  }
+}
+
 // UNCOMPRESSED / blob copy: chunk by = blockIdx.y copies aux64[1] bytes seg[0] -> out (both 16-byte aligned).
 __global__ void __launch_bounds__(256) fls_copy_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t bpc) {
   const FlsChunkDev &k = chunks[blockIdx.x / bpc];

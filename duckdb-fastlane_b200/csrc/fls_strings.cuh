@@ -1,8 +1,9 @@
 // fls_strings.cuh — string column decoders (Arrow layout out: u32 offsets[n+1] + payload bytes).
 //
-// Thread t of the warp that owns a vector is responsible for the 32 strings e = 32t .. 32t+31 (DICT/CONST)
-// or for lane t's 32 contiguous originals (FSST / offset streams, unified transposed layout) — in both cases
-// a CONTIGUOUS run of output bytes, written through FlsByteSink as aligned 8-byte stores.
+// DICT and FSST columns: a block of WARPS warps owns (a slice of) one column chunk and keeps the chunk's lookup
+// table in shared memory; each warp decodes whole vectors, a quarter (256 strings) at a time, lane t owning 8
+// consecutive strings = one CONTIGUOUS run of output bytes that it appends to the warp's staging buffer
+// (FlsPush); the quarter then leaves for HBM as coalesced 128-bit stores.
 //
 // Restated FastLanes primitives (upstream source absent); FSST stream semantics
 // follow duckdb/third_party/fsst/fsst.h:93-104,162-241 (code<255 -> symbol, 255 -> escaped literal byte).
@@ -41,77 +42,6 @@ struct FlsByteSink {
   }
 };
 
-// ---- contiguous byte writer, lean variant for the decode loops: 64-bit accumulator, one aligned 8-byte store per
-// completed word, no byte loops on the hot path.  The first (possibly shared) word is parked in a register and
-// written byte-wise in finish(), like the tail, so neighbouring lanes never touch each other's bytes.
-struct FlsWordSink {
-  uint64_t *word;   // aligned address of the word being assembled
-  uint8_t *base;    // aligned address of the first word
-  uint64_t acc, headw;
-  uint32_t n, head;
-  bool first;
-  FLS_MEM void init(uint8_t *p) {
-    const uint32_t a = (uint32_t)((uintptr_t)p & 7u);
-    base = p - a;
-    word = (uint64_t *)base;
-    acc = 0; headw = 0; n = a; head = a; first = true;
-  }
-  // append the low L bytes of s (bytes above L must be zero), 0 <= L <= 8
-  FLS_MEM void push(uint64_t s, uint32_t L) {
-    const uint32_t sh = 8u * n;
-    acc |= s << sh;
-    const uint64_t carry = (s >> 1) >> (63u - sh);  // the bytes that did not fit (none when n == 0)
-    n += L;
-    const bool full = n >= 8u;
-    if (full && !first) *word = acc;   // predicated store
-    headw = (full && first) ? acc : headw;
-    first = first && !full;
-    word += full ? 1 : 0;
-    acc = full ? carry : acc;
-    n &= 7u;
-  }
-  FLS_MEM void finish() {
-    if (!first) {
-      for (uint32_t i = head; i < 8u; ++i) base[i] = (uint8_t)(headw >> (8u * i));
-      uint8_t *b = (uint8_t *)word;
-      for (uint32_t i = 0; i < n; ++i) b[i] = (uint8_t)(acc >> (8u * i));
-    } else {
-      for (uint32_t i = head; i < n; ++i) base[i] = (uint8_t)(acc >> (8u * i));
-    }
-  }
-};
-
-// ---- sequential byte reader over global memory with three 8-byte words of lookahead.
-// The next words are requested long before their bytes are consumed, so the serial decode loop of a lane never
-// waits for DRAM.  Loads are clamped to [.., limit): nothing beyond the lane's own run (rounded up to 8) is read.
-struct FlsByteStream {
-  const uint64_t *next;   // address of the word that follows n2
-  const uint64_t *limit;  // first word that must not be read
-  uint64_t cur, n0, n1, n2;
-  uint32_t bi;            // bytes of `cur` already consumed (0..7)
-  FLS_MEM uint64_t fetch() {
-    const uint64_t v = next < limit ? fls_ldg(next) : 0ull;
-    ++next;
-    return v;
-  }
-  FLS_MEM void init(const uint8_t *p, const uint8_t *end) {
-    const uint32_t a = (uint32_t)((uintptr_t)p & 7u);
-    next = (const uint64_t *)(p - a);
-    limit = (const uint64_t *)(((uintptr_t)end + 7u) & ~(uintptr_t)7u);
-    cur = fetch(); n0 = fetch(); n1 = fetch(); n2 = fetch();
-    bi = a;
-  }
-  // the next two bytes (low 16 bits), without consuming them
-  FLS_MEM uint32_t peek2() const {
-    const uint32_t sh = 8u * bi;
-    return (uint32_t)((cur >> sh) | ((n0 << 1) << (63u - sh)));
-  }
-  FLS_MEM void skip(uint32_t k) {  // k in {1,2}
-    bi += k;
-    if (bi >= 8u) { bi -= 8u; cur = n0; n0 = n1; n1 = n2; n2 = fetch(); }
-  }
-};
-
 // ===================================================================== end-offset stream -> offsets[i+1]
 // chunk: seg[0]=hdr, seg[1]=data ([lane bases 128 B][packed deltas]); out = &offsets[first row of rg]
 struct VecSTROFFS {
@@ -145,49 +75,206 @@ struct VecSTRCONST {
   }
 };
 
+// ---- staged word writer.  A lane appends pieces of <= 8 bytes to ONE contiguous run inside the warp's shared
+// staging buffer.  State: `o` = 4-aligned address of the word being filled, `n8` = 8 * (bytes pending in that
+// word, 0..3), `prev` = a word whose TOP n8/8 bytes are the pending bytes.  A piece comes as a 16-byte table
+// entry {lo, hi, tail, L8}: lo/hi = the bytes (zero above the length), L8 = 8 * length, tail = the piece's last
+// four bytes (= lo when the length is < 4).  One push is two funnel shifts, two predicated word stores and one
+// clamped funnel shift:
+//   w0 = (prev:lo) << n8 >> 32      completes the pending word             stored when n8 + L8 >= 32
+//   w1 = (lo:hi)   << n8 >> 32      the next four bytes                    stored when n8 + L8 >= 64
+//   prev' = bytes [L, L+4) of (prev, lo, hi) = L < 4 ? (prev:lo) >> L8 : tail      (SHF.R.CLAMP does the select)
+// A push with L8 = 0 changes nothing.  The first word of a run may be shared with the previous lane's run: it is
+// stored with zeros in the foreign low bytes, and every lane writes its own trailing partial word BYTE-wise in
+// finish(), which runs in a later warp phase — so shared words always end up complete, whatever the order.
+#ifdef FLS_HOST_EMUL
+typedef uint8_t *fls_sptr;  // address inside the warp's shared-memory slot
+FLS_DEV fls_sptr fls_sptr_of(uint8_t *p) { return p; }
+template <uint32_t THR> FLS_DEV void fls_sts32_ge(uint32_t m, fls_sptr a, uint32_t v) { if (m >= THR) *(uint32_t *)a = v; }
+FLS_DEV void fls_sts8(fls_sptr a, uint32_t v) { *a = (uint8_t)v; }
+#else
+typedef uint32_t fls_sptr;  // shared-space address: STS with a 32-bit address register, no generic-address checks
+FLS_DEV fls_sptr fls_sptr_of(uint8_t *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// predicated store (no branch): if (m >= THR) *(u32 *)a = v
+template <uint32_t THR> FLS_DEV void fls_sts32_ge(uint32_t m, fls_sptr a, uint32_t v) {
+  asm volatile("{\n .reg .pred p;\n setp.ge.u32 p, %0, %1;\n @p st.shared.u32 [%2], %3;\n}" ::"r"(m), "n"(THR), "r"(a), "r"(v)
+               : "memory");
+}
+FLS_DEV void fls_sts8(fls_sptr a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+#endif
+
+struct FlsPush {
+  fls_sptr o, o0;
+  uint32_t prev, n8, n8_0;
+  FLS_MEM void init(uint8_t *stg, uint32_t s) {  // s = byte offset of the run's first byte inside stg
+    o = o0 = fls_sptr_of(stg) + (s & ~3u);
+    n8 = n8_0 = 8u * (s & 3u);
+    prev = 0;
+  }
+  FLS_MEM void push(uint32_t lo, uint32_t hi, uint32_t tail, uint32_t L8) {
+    const uint32_t m8 = n8 + L8;
+    fls_sts32_ge<32u>(m8, o, fls_shf_l(prev, lo, n8));
+    fls_sts32_ge<64u>(m8, o + 4u, fls_shf_l(lo, hi, n8));
+    prev = fls_shf_rc(prev, tail, L8);
+    o += (m8 >> 5) << 2;
+    n8 = m8 & 31u;
+  }
+  FLS_MEM void push(const fls_u4 &e) { push(e.x, e.y, e.z, e.w); }
+  FLS_MEM void push_byte(uint32_t b) { push(b, 0u, b, 8u); }
+  FLS_MEM void finish() {
+    const uint32_t n = n8 >> 3, first = (o == o0) ? (n8_0 >> 3) : 0u;
+    for (uint32_t i = first; i < n; ++i) fls_sts8(o + i, (prev >> (8u * (4u - n + i))) & 0xFFu);
+  }
+};
+
+// 16-byte table entry of a piece of L <= 8 bytes held in the low bytes of `v`
+FLS_DEV fls_u4 fls_piece_entry(uint64_t v, uint32_t L) {
+  if (L < 8u) v &= (1ull << (8u * L)) - 1ull;
+  fls_u4 e;
+  e.x = (uint32_t)v;
+  e.y = (uint32_t)(v >> 32);
+  e.z = L < 4u ? e.x : (uint32_t)(v >> (8u * (L - 4u)));
+  e.w = 8u * L;
+  return e;
+}
+
+// Copy `len` staged bytes stg[h .. h+len) to global memory at `g` (h = g & 15, so 16-byte pieces line up):
+// whole pieces as coalesced 128-bit loads/stores, the partial first/last piece byte-wise (those bytes' neighbours
+// belong to another quarter / vector / row group and are written by their own warp).  Call inside FLS_LANES.
+FLS_DEV void fls_stage_copy_out(const uint8_t *stg, uint8_t *g, uint32_t h, uint32_t len, uint32_t t) {
+  const uint32_t end = h + len;
+  const uint32_t p0 = h ? 1u : 0u, p1 = end >> 4;
+  const uint32_t head_end = fls_min(end, 16u * p0);
+  const uint32_t tail_start = fls_max(16u * p1, head_end);
+  uint8_t *gb = g - h;  // 16-byte aligned
+  for (uint32_t p = p0 + t; p < p1; p += 32u) fls_st128(gb + 16u * p, fls_lds128<fls_u4>(stg + 16u * p));
+  for (uint32_t i = h + t; i < head_end; i += 32u) gb[i] = stg[i];
+  for (uint32_t i = tail_start + t; i < end; i += 32u) gb[i] = stg[i];
+}
+
+// DELTA u32 chain walk from a staged payload ([lane bases 128 B][packed deltas]) into a padded tile (original order)
+FLS_DEV void fls_walk32(const uint8_t *stage, uint32_t bw, uint32_t base, uint32_t *tile, uint32_t t) {
+  const uint32_t *bases = (const uint32_t *)stage, *pk = (const uint32_t *)(stage + 128);
+  uint32_t acc = bases[t];
+  const uint32_t e0 = fls_lane_start(t);
+#pragma unroll
+  for (uint32_t r = 0; r < 32u; ++r) {
+    acc += (bw ? fls_extract<uint32_t>(pk, bw, fls_chain_row<32>(r), t) : 0u) + base;
+    tile[fls_tile_slot<uint32_t>(e0 + r)] = acc;
+  }
+}
+
 // ===================================================================== dictionary strings
 // chunk: seg[0]/[1] = idx stream (u32 FFOR), seg[2] = dict_offsets u32[n+1], seg[3] = dict bytes,
 //        seg[4] = vec_ep u32[n_vec+1] (payload offset of each vector inside the row group)
+// A vector is decoded in four quarters of 256 strings; in a quarter lane t owns the 8 consecutive strings
+// 256q + 8t .. +7: their indices sit in ONE packed row (row 8q + t/4, packed lanes 8(t%4) .. +7), so the lane
+// unpacks them straight from the staged payload with 128-bit loads; its strings form one contiguous run of
+// output bytes, appended piece by piece (FlsPush) to the warp's staging buffer, and its 8 end offsets leave as
+// two aligned 128-bit stores {run start, end 0 .. end 6} (end 7 is the next lane's run start).
 struct VecSTRDICT {
-  static constexpr uint32_t TILE = 4096u, XCH = TILE + 4224u;
-  static constexpr uint32_t SMEM = XCH + 128u;
-  // Block-shared dictionary cache (the block's 4 warps decode vectors of the same chunk):
-  //   [hdr: u32 maxlen, u32 stride][lens u16 x 1024][tab: n_dict x stride u64, entries zero padded]
-  // Built when the dictionary is small (<= 1024 entries and <= 8 KB padded); stride = 0 means "not cached".
-  static constexpr uint32_t CACHE_ENTRIES = 1024u, CACHE_BYTES = 8192u;
-  static constexpr uint32_t LENS = 16u, TAB = LENS + 2u * CACHE_ENTRIES;
-  static constexpr uint32_t BLOCK_SMEM = TAB + CACHE_BYTES;
+  static constexpr uint32_t WARPS = 16;
+  static constexpr uint32_t STG = 8448u;     // staging of one quarter's payload (33 bytes per string on average)
+  static constexpr uint32_t IDX = STG;       // staged index payload, <= 128 * 32 bytes
+  static constexpr uint32_t SMEM = STG + 4096u;
+  // block-shared: [hdr 16 B: u32 pieces, u32 maxlen, u32 ~minlen][lens u32 x 1024][pieces: n_dict x P x 16 B]
+  static constexpr uint32_t CACHE_ENTRIES = 1024u, TAB_BYTES = 16384u;
+  static constexpr uint32_t LENS = 16u, TAB = LENS + 4u * CACHE_ENTRIES;
+  static constexpr uint32_t BLOCK_SMEM = TAB + TAB_BYTES;
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
     uint32_t *hdr = (uint32_t *)bsm;
-    uint16_t *lens = (uint16_t *)(bsm + LENS);
-    uint64_t *tab = (uint64_t *)(bsm + TAB);
+    uint32_t *lens = (uint32_t *)(bsm + LENS);
     const uint32_t *doff = (const uint32_t *)k.seg[2];
     const uint8_t *dbytes = k.seg[3];
     const uint32_t n_dict = k.aux32;
     if (tid == 0) { hdr[0] = 0; hdr[1] = 0; hdr[2] = 0; }
     FLS_BLOCK_SYNC();
-    if (n_dict > CACHE_ENTRIES) return;  // uniform over the block
+    if (n_dict > CACHE_ENTRIES) return;  // uniform over the block: P stays 0 = "not cached"
     uint32_t m = 0, mn = 0xFFFFFFFFu;
     for (uint32_t i = tid; i < n_dict; i += nthreads) {
       const uint32_t L = fls_ldg(doff + i + 1) - fls_ldg(doff + i);
+      lens[i] = L;
       m = fls_max(m, L);
       mn = fls_min(mn, L);
     }
-    fls_smem_max(hdr, m);
+    fls_smem_max(hdr + 1, m);
     fls_smem_max(hdr + 2, ~mn);  // max of the complement = complement of the min
     FLS_BLOCK_SYNC();
-    const uint32_t stride = (hdr[0] + 7u) >> 3;
-    if (stride == 0 || n_dict * stride * 8u > CACHE_BYTES) return;
-    for (uint32_t i = tid; i < n_dict; i += nthreads) {
-      const uint32_t a = fls_ldg(doff + i), L = fls_ldg(doff + i + 1) - a;
-      lens[i] = (uint16_t)L;
-      for (uint32_t wd = 0; wd < stride; ++wd) {
-        uint64_t x = 0;
-        for (uint32_t b = 0; b < 8u && 8u * wd + b < L; ++b) x |= (uint64_t)fls_ldg(dbytes + a + 8u * wd + b) << (8u * b);
-        tab[i * stride + wd] = x;
-      }
+    const uint32_t P = (hdr[1] + 7u) >> 3;
+    if (P == 0 || n_dict * P * 16u > TAB_BYTES) return;
+    for (uint32_t i = tid; i < n_dict * P; i += nthreads) {
+      const uint32_t d = i / P, pc = i % P;
+      const uint32_t a = fls_ldg(doff + d), L = fls_ldg(doff + d + 1) - a;
+      const uint32_t Lp = L > 8u * pc ? fls_min(8u, L - 8u * pc) : 0u;
+      uint64_t x = 0;
+      for (uint32_t b = 0; b < Lp; ++b) x |= (uint64_t)fls_ldg(dbytes + a + 8u * pc + b) << (8u * b);
+      *(fls_u4 *)(bsm + TAB + 16u * i) = fls_piece_entry(x, Lp);
     }
-    if (tid == 0) hdr[1] = stride;
+    if (tid == 0) hdr[0] = P;
+  }
+  // the 8 strings of a lane, P pieces each: table loads are issued in batches of up to 8 entries BEFORE the
+  // pushes that consume them (the compiler cannot hoist shared loads over the pushes' shared stores itself)
+  template <uint32_t P> FLS_MEM static void push_strings(FlsPush &p, const uint8_t *tab, const uint32_t (&d)[8]) {
+    constexpr uint32_t SPB = P == 1 ? 8u : P == 2 ? 4u : 2u;  // strings per batch
+#pragma unroll
+    for (uint32_t s0 = 0; s0 < 8u; s0 += SPB) {
+      fls_u4 e[SPB * P];
+#pragma unroll
+      for (uint32_t i = 0; i < SPB; ++i)
+#pragma unroll
+        for (uint32_t pc = 0; pc < P; ++pc) e[i * P + pc] = fls_lds128<fls_u4>(tab + 16u * (d[s0 + i] * P + pc));
+#pragma unroll
+      for (uint32_t i = 0; i < SPB * P; ++i) p.push(e[i]);
+    }
+  }
+  // every entry has the same length U in {1, 2, 4}: the lane's 8 strings are 8U bytes, merged in registers into
+  // U eight-byte pieces — U pushes instead of 8
+  template <uint32_t U> FLS_MEM static void push_uniform(FlsPush &p, const uint8_t *tab, const uint32_t (&d)[8]) {
+    uint32_t x[8], wd[2u * U];
+#pragma unroll
+    for (uint32_t i = 0; i < 8u; ++i) x[i] = *(const uint32_t *)(tab + 16u * d[i]);  // the entry's bytes, zero above U
+    if (U == 1u) {
+      wd[0] = x[0] | (x[1] << 8) | (x[2] << 16) | (x[3] << 24);
+      wd[1] = x[4] | (x[5] << 8) | (x[6] << 16) | (x[7] << 24);
+    } else if (U == 2u) {
+#pragma unroll
+      for (uint32_t j = 0; j < 4u; ++j) wd[j] = x[2u * j] | (x[2u * j + 1u] << 16);
+    } else {
+#pragma unroll
+      for (uint32_t j = 0; j < 8u; ++j) wd[j % (2u * U)] = x[j];
+    }
+#pragma unroll
+    for (uint32_t j = 0; j < U; ++j) p.push(wd[2u * j], wd[2u * j + 1u], wd[2u * j + 1u], 64u);
+  }
+  // the lane's 8 indices: packed row `row`, packed lanes 8(t%4) .. +7 of the staged FFOR payload
+  FLS_MEM static void unpack8(const uint8_t *sm, uint32_t bw, uint32_t row, uint32_t t, uint32_t base, uint32_t lim,
+                              uint32_t (&d)[8]) {
+    if (!bw) {
+#pragma unroll
+      for (uint32_t i = 0; i < 8u; ++i) d[i] = fls_min(base, lim);
+      return;
+    }
+    const uint32_t bit = row * bw, kk = bit >> 5, s = bit & 31u;
+    const uint8_t *pa = sm + kk * 128u + 32u * (t & 3u), *pb = sm + fls_min(kk + 1u, bw - 1u) * 128u + 32u * (t & 3u);
+    const fls_u4 a0 = fls_lds128<fls_u4>(pa), a1 = fls_lds128<fls_u4>(pa + 16);
+    const fls_u4 b0 = fls_lds128<fls_u4>(pb), b1 = fls_lds128<fls_u4>(pb + 16);
+    const uint32_t mask = bw >= 32u ? 0xFFFFFFFFu : ((1u << bw) - 1u);
+    d[0] = fls_min((fls_shf_r(a0.x, b0.x, s) & mask) + base, lim);
+    d[1] = fls_min((fls_shf_r(a0.y, b0.y, s) & mask) + base, lim);
+    d[2] = fls_min((fls_shf_r(a0.z, b0.z, s) & mask) + base, lim);
+    d[3] = fls_min((fls_shf_r(a0.w, b0.w, s) & mask) + base, lim);
+    d[4] = fls_min((fls_shf_r(a1.x, b1.x, s) & mask) + base, lim);
+    d[5] = fls_min((fls_shf_r(a1.y, b1.y, s) & mask) + base, lim);
+    d[6] = fls_min((fls_shf_r(a1.z, b1.z, s) & mask) + base, lim);
+    d[7] = fls_min((fls_shf_r(a1.w, b1.w, s) & mask) + base, lim);
+  }
+  // {run start, end 0 .. end 6} -> offsets[first string of the lane .. +7] (two aligned 128-bit stores)
+  FLS_MEM static void store_offsets(uint32_t *o, uint32_t start, const uint32_t (&len)[8]) {
+    fls_u4 a, b;
+    a.x = start; a.y = a.x + len[0]; a.z = a.y + len[1]; a.w = a.z + len[2];
+    b.x = a.w + len[3]; b.y = b.x + len[4]; b.z = b.y + len[5]; b.w = b.z + len[6];
+    fls_st128(o, a);
+    fls_st128(o + 4, b);
   }
   FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *bsm) {
     const fls_vechdr h = fls_load_hdr(k, 0, v);
@@ -197,202 +284,232 @@ struct VecSTRDICT {
     const uint8_t *dbytes = k.seg[3];
     const uint32_t n_dict = k.aux32;
     const uint32_t vec_ep = fls_ldg((const uint32_t *)k.seg[4] + v);
-    const uint32_t stride = ((const uint32_t *)bsm)[1];
-    const uint32_t maxlen = ((const uint32_t *)bsm)[0], minlen = ~((const uint32_t *)bsm)[2];
-    // every entry has the same power-of-two length (flags, codes): strings pack into whole words
-    const uint32_t ulen = (stride == 1u && maxlen == minlen && (maxlen & (maxlen - 1u)) == 0u) ? maxlen : 0u;
-    const uint16_t *lens = (const uint16_t *)(bsm + LENS);
-    const uint64_t *tab = (const uint64_t *)(bsm + TAB);
-    uint32_t *tile = (uint32_t *)(w.sm + TILE), *xch = (uint32_t *)(w.sm + XCH);
-    if (bw) { w.stage(0, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
-    // 1. indices -> tile (original order: FFOR positions are original positions)
-    FLS_LANES(t) {
-      const uint32_t q = t & 7u, g = t >> 3;
-      for (uint32_t j = 0; j < 8u; ++j) {
-        const uint32_t row = g * 8u + j, p = row * 32u + q * 4u;
-        fls_u4 ix;
-        if (bw) ix = fls_unpack32_row(w.sm, bw, row, q, (uint32_t)h.base);
-        else { ix.x = ix.y = ix.z = ix.w = (uint32_t)h.base; }
-        tile[fls_tile_slot<uint32_t>(p)] = fls_min(ix.x, n_dict - 1u);
-        tile[fls_tile_slot<uint32_t>(p + 1u)] = fls_min(ix.y, n_dict - 1u);
-        tile[fls_tile_slot<uint32_t>(p + 2u)] = fls_min(ix.z, n_dict - 1u);
-        tile[fls_tile_slot<uint32_t>(p + 3u)] = fls_min(ix.w, n_dict - 1u);
-      }
-    }
-    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
-    if (ulen) {
-      // fixed-length fast path: offsets are arithmetic, 8/ulen strings fill one 8-byte word
-      const uint32_t per = 8u / ulen, sh = 8u * ulen;
+    const uint32_t P = ((const uint32_t *)bsm)[0];
+    const uint32_t maxlen = ((const uint32_t *)bsm)[1], minlen = ~((const uint32_t *)bsm)[2];
+    // every entry has the same length 1, 2 or 4: offsets are arithmetic, strings merge into 8-byte pieces
+    const uint32_t U = (P == 1u && maxlen == minlen && (maxlen == 1u || maxlen == 2u || maxlen == 4u)) ? maxlen : 0u;
+    const uint32_t *lens = (const uint32_t *)(bsm + LENS);
+    const uint8_t *tab = bsm + TAB;
+    uint8_t *stg = w.sm;
+    const uint8_t *idx = w.sm + IDX;
+    if (bw) { w.fence_async(); w.stage(IDX, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
+    uint8_t *pay = k.pay + k.pay_base;
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i, offs[i + 1] = its end
+    uint32_t qpos = vec_ep;  // payload offset (row-group relative) of the quarter's first byte
+    for (uint32_t qt = 0; qt < 4u; ++qt) {
+      // 1. the lane's 8 indices and lengths (kept in registers), exclusive scan -> the lane's first output byte
+      FLS_VAR(uint32_t, run);
+      FLS_VAR2(uint32_t, dd, 8);
+      FLS_VAR2(uint32_t, ll, 8);
       FLS_LANES(t) {
-        FlsWordSink sink;
-        sink.init(k.pay + k.pay_base + vec_ep + 32u * t * ulen);
-        for (uint32_t i = 0; i < 32u; i += per) {
-          uint64_t x = 0;
-          for (uint32_t j = 0; j < per; ++j) x |= tab[tile[33u * t + i + j]] << (sh * j);
-          sink.push(x, 8u);
+        uint32_t d[8];
+        unpack8(idx, bw, 8u * qt + (t >> 2), t, (uint32_t)h.base, n_dict - 1u, d);
+        uint32_t tot = 0;
+#pragma unroll
+        for (uint32_t i = 0; i < 8u; ++i) {
+          FLS_AT2(dd, i) = d[i];
+          const uint32_t L = U ? U : (P ? lens[d[i]] : fls_ldg(doff + d[i] + 1) - fls_ldg(doff + d[i]));
+          FLS_AT2(ll, i) = L;
+          tot += L;
         }
-        sink.finish();
-#pragma unroll 8
-        for (uint32_t j = 0; j < 32u; ++j) offs[j * 32u + t] = k.pay_base + vec_ep + (j * 32u + t + 1u) * ulen;
+        FLS_AT(run) = tot;
       }
-      return;
-    }
-    // 2. bytes produced by each thread's 32 strings
-    FLS_LANES(t) {
-      uint32_t tot = 0;
-      if (stride) {
-#pragma unroll 8
-        for (uint32_t i = 0; i < 32u; ++i) tot += lens[tile[33u * t + i]];
-      } else {
-        for (uint32_t i = 0; i < 32u; ++i) {
-          const uint32_t d = tile[33u * t + i];
-          tot += fls_ldg(doff + d + 1) - fls_ldg(doff + d);
-        }
-      }
-      xch[t] = tot;
-    }
-    // 3. copy the strings, replace indices by end offsets
-    FLS_LANES(t) {
-      uint32_t pos = vec_ep;
-      for (uint32_t u = 0; u < t; ++u) pos += xch[u];
-      FlsWordSink sink;
-      sink.init(k.pay + k.pay_base + pos);
-      if (stride == 1u) {  // every entry fits one word: one append per string
-#pragma unroll 4
-        for (uint32_t i = 0; i < 32u; ++i) {
-          const uint32_t d = tile[33u * t + i], L = lens[d];
-          sink.push(tab[d], L);
-          pos += L;
-          tile[33u * t + i] = pos;
-        }
-      } else if (stride) {
-        for (uint32_t i = 0; i < 32u; ++i) {
-          const uint32_t d = tile[33u * t + i], L = lens[d];
-          for (uint32_t o = 0; o < L; o += 8u) sink.push(tab[d * stride + (o >> 3)], fls_min(8u, L - o));
-          pos += L;
-          tile[33u * t + i] = pos;
-        }
-      } else {
-        for (uint32_t i = 0; i < 32u; ++i) {
-          const uint32_t d = tile[33u * t + i];
-          const uint32_t a = fls_ldg(doff + d), b = fls_ldg(doff + d + 1);
-          for (uint32_t c = a; c < b; ++c) sink.push(fls_ldg(dbytes + c), 1);
-          pos += b - a;
-          tile[33u * t + i] = pos;
+      uint32_t qlen;
+      FLS_EXCL_SCAN(run, qlen);
+      uint8_t *g = pay + qpos;
+      const uint32_t hh = (uint32_t)((uintptr_t)g & 15u);
+      const bool staged = P && hh + qlen <= STG;
+      // 2. end offsets, then the pieces of the lane's strings
+      FLS_VAR(FlsPush, ps);
+      FLS_LANES(t) {
+        uint32_t d[8], len[8];
+#pragma unroll
+        for (uint32_t i = 0; i < 8u; ++i) { d[i] = FLS_AT2(dd, i); len[i] = FLS_AT2(ll, i); }
+        const uint32_t start = qpos + FLS_AT(run);
+        store_offsets(offs + 256u * qt + 8u * t, k.pay_base + start, len);
+        if (qt == 3u && t == 31u) offs[FLS_VEC] = k.pay_base + qpos + qlen;  // the vector's last end
+        if (staged) {
+          FlsPush p;
+          p.init(stg, hh + FLS_AT(run));
+          if (U == 1u) push_uniform<1>(p, tab, d);
+          else if (U == 2u) push_uniform<2>(p, tab, d);
+          else if (U == 4u) push_uniform<4>(p, tab, d);
+          else switch (P) {
+            case 1: push_strings<1>(p, tab, d); break;
+            case 2: push_strings<2>(p, tab, d); break;
+            case 3: push_strings<3>(p, tab, d); break;
+            case 4: push_strings<4>(p, tab, d); break;
+            default:
+              for (uint32_t i = 0; i < 8u; ++i)
+                for (uint32_t pc = 0; pc < P; ++pc) p.push(fls_lds128<fls_u4>(tab + 16u * (d[i] * P + pc)));
+          }
+          FLS_AT(ps) = p;
+        } else {
+          // dictionary not cached, or a quarter larger than the staging buffer: byte-wise from global memory
+          uint32_t pos = start;
+          for (uint32_t i = 0; i < 8u; ++i) {
+            const uint32_t a = fls_ldg(doff + d[i]), b = fls_ldg(doff + d[i] + 1);
+            for (uint32_t c = a; c < b; ++c) pay[pos + (c - a)] = fls_ldg(dbytes + c);
+            pos += b - a;
+          }
         }
       }
-      sink.finish();
+      if (staged) {
+        FLS_LANES(t) { FLS_AT(ps).finish(); }
+        FLS_LANES(t) { fls_stage_copy_out(stg, g, hh, qlen, t); }
+      }
+      qpos += qlen;
     }
-    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + TILE, offs, t, k.pay_base); }
   }
 };
 
 // ===================================================================== FSST strings
 // chunk: seg[0]/[1] = decoded end-offset stream, seg[2]/[3] = compressed end-offset stream (both DELTA u32),
 //        seg[4] = symbol table (u64 symbol[256] | u8 len[256]), seg[5] = compressed bytes (+16 slack).
-// Lane t's 32 strings are contiguous in both the compressed and the decoded space, so the thread decodes ONE
-// contiguous compressed run [c0,c1) into ONE contiguous output run starting at d0.
+// The strings of a vector are contiguous in both the compressed and the decoded space.  The vector's compressed
+// bytes are bulk-copied into the warp's window; a vector is decoded in four quarters of 256 strings, lane t
+// owning the 8 consecutive strings 256q + 8t .. +7 = one compressed run -> one output run.  A lane reads its run
+// 8 bytes at a time; every code byte costs one conflict-free 128-bit table load (the block keeps 8 copies of the
+// table, one per 16-byte bank group, lane t uses copy t & 7) and one FlsPush::push.  Escapes (code 255) are rare:
+// a window that holds one, and the partial first/last window of a run, take the byte-by-byte path.
 struct VecSTRFSST {
-  // Phase 1 uses the slot as [decoded-ends DELTA stage + tile | compressed-ends DELTA stage]; phase 2 reuses the
-  // whole slot as the window the vector's compressed bytes are bulk-copied into.
-  static constexpr uint32_t CSTAGE = DecDELTA<uint32_t>::SMEM;  // compressed-ends payload staged after the tile
-  static constexpr uint32_t WINDOW = 18432u;                    // 3 blocks of 4 warps per SM
-  static constexpr uint32_t SMEM = WINDOW;
-  static constexpr uint32_t BLOCK_SMEM = 2304;  // symbol table, shared by the block's warps (same chunk)
-  static_assert(CSTAGE + 128u + 4096u <= WINDOW, "phase-1 buffers must fit the slot");
-  FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsmem, uint32_t tid, uint32_t nthreads) {
-    const uint64_t *src = (const uint64_t *)k.seg[4];
-    uint64_t *dst = (uint64_t *)bsmem;
-    for (uint32_t i = tid; i < 2304u / 8u; i += nthreads) {
-      uint64_t x = fls_ldg(src + i);
-      if (i == 255u) x = 0;                                                      // sym[255]
-      if (i == 256u + 31u) x = (x & 0x00FFFFFFFFFFFFFFull) | (1ull << 56);       // len[255] = 1
-      dst[i] = x;
+  static constexpr uint32_t WARPS = 6;
+  static constexpr uint32_t STG = 12672u;    // staging; phase 1: [decoded-ends stage | compressed-ends stage | tile]
+  static constexpr uint32_t CWIN = 16384u;   // compressed-byte window
+  static constexpr uint32_t BND = 2u * 132u * 4u;  // string boundaries every 8 strings: BD[129], BC[129]
+  static constexpr uint32_t SMEM = STG + CWIN + BND + 96u;  // 30208 = 236 * 128
+  static constexpr uint32_t BLOCK_SMEM = 32768u;  // 256 entries x 8 copies x 16 B; entry e of copy r at e*128 + r*16
+  static_assert(3u * 4224u <= STG, "phase-1 buffers must fit the staging buffer");
+  static_assert(SMEM % 128u == 0, "warp slots stay 128-byte aligned");
+  FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
+    const uint64_t *sym = (const uint64_t *)k.seg[4];
+    const uint8_t *len = k.seg[4] + 2048;
+    for (uint32_t e = tid; e < 256u; e += nthreads) {
+      fls_u4 en;
+      if (e == 255u) { en.x = en.y = en.z = en.w = 0u; }  // the escape marker itself produces nothing
+      else en = fls_piece_entry(fls_ldg(sym + e), fls_min(8u, (uint32_t)fls_ldg(len + e)));
+      for (uint32_t r = 0; r < 8u; ++r) *(fls_u4 *)(bsm + 128u * e + 16u * r) = en;
     }
   }
-  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *symtab) {
+  // Eight consecutive compressed bytes (lo, hi) of a lane's run: eight table loads in flight, then eight pushes —
+  // straight-line code, no branch.  ESC: the window may hold escapes (code 255 -> the next byte is a literal) or
+  // start with a pending literal; `lit` carries that state from byte to byte as a predicate and a literal's entry
+  // is made from the byte itself (only the low byte of lo/tail matters for a one-byte piece).  MASK: bit j of
+  // `vbits` says whether byte j belongs to the run (partial first/last window); other bytes change nothing.
+  template <bool ESC, bool MASK>
+  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, uint32_t lo, uint32_t hi, uint32_t vbits, bool &lit) {
+    fls_u4 e[8];
+    uint32_t x[8];
+#pragma unroll
+    for (uint32_t j = 0; j < 8u; ++j) x[j] = (j < 4u ? lo : hi) >> (8u * (j & 3u));
+#pragma unroll
+    for (uint32_t j = 0; j < 8u; ++j) e[j] = fls_lds128<fls_u4>(tabr + ((x[j] & 0xFFu) << 7));
+#pragma unroll
+    for (uint32_t j = 0; j < 8u; ++j) {
+      fls_u4 en = e[j];
+      if (ESC) {
+        bool nl = (x[j] & 0xFFu) == 0xFFu && !lit;
+        if (lit) { en.x = x[j]; en.z = x[j]; en.w = 8u; }
+        if (MASK) {
+          const bool valid = (vbits >> j) & 1u;
+          if (!valid) { en.w = 0u; nl = lit; }
+        }
+        lit = nl;
+      }
+      p.push(en);
+    }
+  }
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *tab) {
     const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
     uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
     if (bwd > 32u) bwd = 32u;
     if (bwc > 32u) bwc = 32u;
-    // both offset streams in flight at once
-    w.stage(CSTAGE, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc);
-    DecDELTA<uint32_t>::to_tile(w, k.seg[1] + 16ull * hd.ep, bwd, hd.base);  // stages, waits for both, fills tile
-    const uint32_t *dbases = (const uint32_t *)w.sm;
-    const uint32_t *cbases = (const uint32_t *)(w.sm + CSTAGE);
-    const uint32_t *cpk = (const uint32_t *)(w.sm + CSTAGE + 128u);
-    const uint64_t *sym = (const uint64_t *)symtab;
-    const uint8_t *len = symtab + 2048;
+    uint8_t *stg = w.sm;
+    uint8_t *cwin = w.sm + STG;
+    uint32_t *BD = (uint32_t *)(w.sm + STG + CWIN), *BC = BD + 132;
+    uint32_t *tile = (uint32_t *)(w.sm + 8448u);
+    // ---- phase 1: both end-offset streams -> offsets[] and the boundaries of every group of 8 strings
+    w.fence_async();
+    w.stage(0, k.seg[1] + 16ull * hd.ep, 128u + 128u * bwd);
+    w.stage(4224u, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc);
+    w.wait();
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
+    FLS_LANES(t) { fls_walk32(w.sm, bwd, (uint32_t)hd.base, tile, t); }
+    FLS_LANES(t) {
+      fls_tile_copy_out<uint32_t>((const uint8_t *)tile, offs, t, k.pay_base);
+      for (uint32_t i = t; i < 128u; i += 32u) BD[i + 1u] = tile[fls_tile_slot<uint32_t>(8u * i + 7u)];
+      if (t == 0) BD[0] = ((const uint32_t *)w.sm)[0];  // lane 0's base = the end offset before the vector
+    }
+    FLS_LANES(t) { fls_walk32(w.sm + 4224u, bwc, (uint32_t)hc.base, tile, t); }
+    FLS_LANES(t) {
+      for (uint32_t i = t; i < 128u; i += 32u) BC[i + 1u] = tile[fls_tile_slot<uint32_t>(8u * i + 7u)];
+      if (t == 0) BC[0] = ((const uint32_t *)(w.sm + 4224u))[0];
+    }
+    // ---- phase 2: the vector's compressed bytes [cv0, cv1) -> window
     const uint8_t *comp = k.seg[5];
     uint8_t *pay = k.pay + k.pay_base;
-    // lane t's 32 strings are contiguous originals: compressed run [c0,c1) -> decoded run starting at d0
-    FLS_VAR(uint32_t, c0); FLS_VAR(uint32_t, c1); FLS_VAR(uint32_t, d0);
-    FLS_LANES(t) {
-      FLS_AT(c0) = cbases[t];
-      FLS_AT(d0) = dbases[t];
-      uint32_t e = FLS_AT(c0) + 32u * (uint32_t)hc.base;
-      if (bwc)
-        for (uint32_t r = 0; r < 32u; ++r) e += fls_extract<uint32_t>(cpk, bwc, r, t);
-      FLS_AT(c1) = e;
-    }
-    // offsets leave first: afterwards nothing in the slot is live and it becomes the compressed-byte window
-    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
-    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + DecDELTA<uint32_t>::STAGE, offs, t, k.pay_base); }
-    // lane 0 owns originals [0,32), lane 31 owns [992,1024): the vector's compressed bytes are [cv0, cv1)
-    const uint32_t cv0 = FLS_BCAST(c0, 0), cv1 = FLS_BCAST(c1, 31);
+    const uint32_t cv0 = BC[0], cv1 = BC[128];
     const uint32_t wbase = cv0 & ~15u;
     const uint32_t span = cv1 > wbase ? cv1 - wbase : 0u;
-    if (span != 0u && span + 16u <= WINDOW) {
+    const bool windowed = span + 16u <= CWIN;
+    if (windowed && span) {
       w.fence_async();
-      w.stage(0, comp + wbase, (span + 15u) & ~15u);
+      w.stage(STG, comp + wbase, (span + 15u) & ~15u);
       w.wait();
-      const uint8_t *cb = w.sm;
-      FLS_LANES(t) {
-        uint32_t p = FLS_AT(c0) - wbase;
-        const uint32_t pend = FLS_AT(c1) - wbase;
-        if (pend > p && pend <= span) {
-          FlsWordSink sink;
-          sink.init(pay + FLS_AT(d0));
-          // len[255] is 1 and sym[255] is 0 in the block's copy of the table (block_init), so an escape is
-          // just "take the literal instead of the symbol": no divergent path in the loop.
-          uint32_t code = cb[p], lit = cb[p + 1u];
-          for (;;) {
-            const uint32_t esc = code == 255u ? 1u : 0u;
-            const uint32_t np = p + 1u + esc;
-            if (np > pend) break;  // end of the run (or a dangling escape at its end)
-            const uint32_t L = len[code];
-            uint64_t sv = sym[code];
-            if (esc) sv = lit;
-            p = np;
-            code = cb[p];
-            lit = cb[p + 1u];
-            sink.push(sv, L);
-          }
-          sink.finish();
-        }
-      }
-      return;
     }
-    // vectors whose compressed bytes do not fit the window: per-lane streaming from global memory
-    FLS_LANES(t) {
-      const uint32_t a0 = FLS_AT(c0), a1 = FLS_AT(c1);
-      if (a1 > a0) {
-        FlsByteStream src;
-        src.init(comp + a0, comp + a1);
-        FlsWordSink sink;
-        sink.init(pay + FLS_AT(d0));
-        uint32_t left = a1 - a0;
-        while (left) {
-          const uint32_t pk = src.peek2(), code = pk & 0xFFu;
-          const uint32_t kk = code == 255u ? 2u : 1u;
-          if (kk > left) break;
-          const uint32_t L = code == 255u ? 1u : (uint32_t)len[code];
-          const uint64_t sv = code == 255u ? (uint64_t)((pk >> 8) & 0xFFu) : sym[code];
-          left -= kk;
-          src.skip(kk);
-          sink.push(sv, L);
+    const uint64_t *gsym = (const uint64_t *)k.seg[4];
+    const uint8_t *glen = k.seg[4] + 2048;
+    for (uint32_t qt = 0; qt < 4u; ++qt) {
+      const uint32_t Q0 = BD[32u * qt], Q1 = BD[32u * qt + 32u];
+      const uint32_t qlen = Q1 > Q0 ? Q1 - Q0 : 0u;
+      uint8_t *g = pay + Q0;
+      const uint32_t hh = (uint32_t)((uintptr_t)g & 15u);
+      if (windowed && hh + qlen <= STG) {
+        FLS_VAR(FlsPush, ps);
+        FLS_LANES(t) {
+          const uint8_t *tabr = tab + 16u * (t & 7u);
+          const uint32_t c0 = BC[32u * qt + t], c1 = BC[32u * qt + t + 1u], d0 = BD[32u * qt + t];
+          FlsPush p;
+          p.init(stg, hh + (d0 - Q0));
+          if (c1 > c0 && c1 - wbase <= span) {
+            const uint32_t a = c0 - wbase, b = c1 - wbase;
+            const uint32_t *cw = (const uint32_t *)cwin;
+            bool lit = false;
+            uint32_t i = a >> 3;
+            uint32_t lo = cw[2u * i], hi = cw[2u * i + 1u];
+            for (; 8u * i < b; ++i) {
+              // next window's words first (the window has 16 bytes of slack, so this never leaves it)
+              const uint32_t nlo = cw[2u * i + 2u], nhi = cw[2u * i + 3u];
+              const bool partial = 8u * i < a || 8u * i + 8u > b;
+              const uint32_t xlo = ~lo, xhi = ~hi;  // a 0xFF byte <=> a zero byte of the complement
+              const bool esc = ((((xlo - 0x01010101u) & ~xlo) | ((xhi - 0x01010101u) & ~xhi)) & 0x80808080u) != 0u || lit;
+              // the variant is chosen by a vote of the lanes still in the loop, so they stay converged
+              if (FLS_ANY(partial)) {
+                const uint32_t s = 8u * i < a ? a - 8u * i : 0u, e = fls_min(8u, b - 8u * i);
+                window<true, true>(p, tabr, lo, hi, ((1u << e) - 1u) & ~((1u << s) - 1u), lit);
+              } else if (FLS_ANY(esc)) {
+                window<true, false>(p, tabr, lo, hi, 0xFFu, lit);
+              } else {
+                window<false, false>(p, tabr, lo, hi, 0xFFu, lit);
+              }
+              lo = nlo; hi = nhi;
+            }
+          }
+          FLS_AT(ps) = p;
         }
-        sink.finish();
+        FLS_LANES(t) { FLS_AT(ps).finish(); }
+        FLS_LANES(t) { fls_stage_copy_out(stg, g, hh, qlen, t); }
+      } else {
+        // compressed bytes larger than the window, or a quarter larger than the staging buffer: byte-wise from global
+        FLS_LANES(t) {
+          const uint32_t c0 = BC[32u * qt + t], c1 = BC[32u * qt + t + 1u];
+          uint8_t *o = pay + BD[32u * qt + t];
+          for (uint32_t i = c0; i < c1;) {
+            const uint32_t c = fls_ldg(comp + i++);
+            if (c == 255u) { if (i < c1) *o++ = fls_ldg(comp + i++); }
+            else { uint64_t s = fls_ldg(gsym + c); for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(glen + c)); b; --b) { *o++ = (uint8_t)s; s >>= 8; } }
+          }
+        }
       }
     }
   }

@@ -33,6 +33,15 @@ template <class V> cudaError_t vec_attr() {
 template <class V> void vec_launch(const FlsChunkDev *d, uint32_t n, cudaStream_t s) {
   fls_vec_kernel<V><<<n * FLS_BLOCKS_PER_CHUNK, FLS_WARPS_PER_BLOCK * 32, fls_block_smem<V>(), s>>>(d);
 }
+template <class V> cudaError_t chunk_attr() {
+  return cudaFuncSetAttribute(fls_chunk_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fls_chunk_smem<V>());
+}
+// blocks per chunk: enough blocks to fill the GPU several times over when the batch has few chunks
+template <class V> void chunk_launch(const FlsChunkDev *d, uint32_t n, cudaStream_t s) {
+  uint32_t bpc = 1;
+  while (bpc < 4u && n * bpc < 592u) bpc *= 2u;
+  fls_chunk_kernel<V><<<n * bpc, V::WARPS * 32, fls_chunk_smem<V>(), s>>>(d, bpc);
+}
 template <template <typename> class V> cudaError_t vec_attr_all() {
   cudaError_t e;
   if ((e = vec_attr<V<uint8_t>>()) != cudaSuccess) return e;
@@ -60,8 +69,8 @@ cudaError_t set_kernel_attrs() {
   if ((e = vec_attr<VecALPRD>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecSTROFFS>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecSTRCONST>()) != cudaSuccess) return e;
-  if ((e = vec_attr<VecSTRDICT>()) != cudaSuccess) return e;
-  return vec_attr<VecSTRFSST>();
+  if ((e = chunk_attr<VecSTRDICT>()) != cudaSuccess) return e;
+  return chunk_attr<VecSTRFSST>();
 }
 
 const char *const kKindName[FLS_K_N] = {"ffor",     "delta",     "rle",      "dict",     "alp",  "alp_rd", "copy",
@@ -88,8 +97,8 @@ bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
     case FLS_K_STR_OFFSETS: vec_launch<VecSTROFFS>(d, n, s); return true;
     case FLS_K_STR_COPY: fls_str_copy_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;
     case FLS_K_STR_CONST: vec_launch<VecSTRCONST>(d, n, s); return true;
-    case FLS_K_STR_DICT: vec_launch<VecSTRDICT>(d, n, s); return true;
-    case FLS_K_STR_FSST: vec_launch<VecSTRFSST>(d, n, s); return true;
+    case FLS_K_STR_DICT: chunk_launch<VecSTRDICT>(d, n, s); return true;
+    case FLS_K_STR_FSST: chunk_launch<VecSTRFSST>(d, n, s); return true;
     case FLS_K_STR_FSST_DICTPREP: fls_fsst_dictprep_kernel<<<n * 8, 128, 0, s>>>(d, 8); return true;
   }
   return false;

@@ -1,0 +1,155 @@
+// fastlanes_facade.cpp — see include/fastlanes_facade.hpp.  Mirrors /root/reference/src/fastlanes_facade.cpp with
+// the FastLanes objects (Connection / TableReader / RowgroupReader / Rowgroup, :12-20) replaced by one
+// flsgpu_host::FlsScanner, i.e. by the C ABI of include/flsgpu.h.
+#include "fastlanes_facade.hpp"
+
+#include <cstring>
+
+#include "duckdb/common/types/vector.hpp"
+#include "fls_scan.hpp"
+
+namespace duckdb {
+
+class FastLanesFacade::Impl {
+public:
+	flsgpu_host::FlsScanner scanner;
+	std::vector<flsgpu_host::ColumnSlice> slices;
+	std::vector<idx_t> projection; // file column id per output column; empty = identity
+	std::string error;
+	bool initialized = false;
+};
+
+LogicalType FastLanesTypeToDuckDB(int32_t t) {
+	switch (t) {
+	case FLSGPU_T_BOOLEAN: return LogicalType::BOOLEAN;
+	case FLSGPU_T_INT8: return LogicalType::TINYINT;
+	case FLSGPU_T_INT16: return LogicalType::SMALLINT;
+	case FLSGPU_T_INT32: return LogicalType::INTEGER;
+	case FLSGPU_T_INT64: return LogicalType::BIGINT;
+	case FLSGPU_T_UINT8: return LogicalType::UTINYINT;
+	case FLSGPU_T_UINT16: return LogicalType::USMALLINT;
+	case FLSGPU_T_UINT32: return LogicalType::UINTEGER;
+	case FLSGPU_T_UINT64: return LogicalType::UBIGINT;
+	case FLSGPU_T_FLOAT: return LogicalType::FLOAT;
+	case FLSGPU_T_DOUBLE: return LogicalType::DOUBLE;
+	case FLSGPU_T_STR: return LogicalType::VARCHAR;
+	case FLSGPU_T_DATE: return LogicalType::DATE;
+	case FLSGPU_T_BYTE_ARRAY: return LogicalType::BLOB;
+	default: return LogicalType::VARCHAR; // the reference's FALLBACK (src/type_mapping.cpp:100-103)
+	}
+}
+
+FastLanesFacade::FastLanesFacade() : pImpl(std::make_unique<Impl>()) {
+}
+FastLanesFacade::~FastLanesFacade() {
+	closeFile();
+}
+
+bool FastLanesFacade::openFile(const std::string &file_path) {
+	closeFile();
+	if (!pImpl->scanner.open(file_path)) {
+		pImpl->error = pImpl->scanner.error();
+		return false;
+	}
+	pImpl->error.clear();
+	pImpl->initialized = true;
+	return true;
+}
+
+std::vector<LogicalType> FastLanesFacade::getColumnTypes() {
+	std::vector<LogicalType> r;
+	for (auto t : pImpl->scanner.columnTypes()) {
+		r.push_back(FastLanesTypeToDuckDB(t));
+	}
+	return r;
+}
+
+std::vector<std::string> FastLanesFacade::getColumnNames() {
+	return pImpl->scanner.columnNames();
+}
+
+bool FastLanesFacade::setProjection(const std::vector<idx_t> &column_ids) {
+	std::vector<uint32_t> cols(column_ids.begin(), column_ids.end());
+	if (!pImpl->scanner.setProjection(cols)) {
+		pImpl->error = pImpl->scanner.error();
+		return false;
+	}
+	pImpl->projection = column_ids;
+	return true;
+}
+
+template <class T>
+static void CopyFixed(Vector &out, const flsgpu_host::ColumnSlice &s, idx_t rows) {
+	memcpy(FlatVector::GetData<T>(out), s.data, rows * sizeof(T));
+}
+
+bool FastLanesFacade::readNextChunk(DataChunk &result) {
+	if (!pImpl->initialized) {
+		return false;
+	}
+	uint64_t rows = 0;
+	if (!pImpl->scanner.next(STANDARD_VECTOR_SIZE, rows, pImpl->slices)) {
+		pImpl->error = pImpl->scanner.error();
+		return false;
+	}
+	// like the reference (src/fastlanes_facade.cpp:102-104) never touch more columns than the chunk has
+	const idx_t ncol = MinValue<idx_t>(result.ColumnCount(), pImpl->slices.size());
+	result.SetCardinality(rows);
+	for (idx_t c = 0; c < ncol; c++) {
+		auto &s = pImpl->slices[c];
+		auto &out = result.data[c];
+		out.SetVectorType(VectorType::FLAT_VECTOR);
+		switch (s.type) {
+		case FLSGPU_T_BOOLEAN:
+		case FLSGPU_T_INT8:
+		case FLSGPU_T_UINT8: CopyFixed<uint8_t>(out, s, rows); break;
+		case FLSGPU_T_INT16:
+		case FLSGPU_T_UINT16: CopyFixed<uint16_t>(out, s, rows); break;
+		case FLSGPU_T_INT32:
+		case FLSGPU_T_UINT32:
+		case FLSGPU_T_FLOAT:
+		case FLSGPU_T_DATE: CopyFixed<uint32_t>(out, s, rows); break;
+		case FLSGPU_T_INT64:
+		case FLSGPU_T_UINT64:
+		case FLSGPU_T_DOUBLE: CopyFixed<uint64_t>(out, s, rows); break;
+		case FLSGPU_T_STR:
+		case FLSGPU_T_BYTE_ARRAY: {
+			// strings <= 12 bytes are inlined in string_t; longer ones are copied into the vector's heap, so the
+			// chunk stays valid after the scanner recycles its pinned batch buffers
+			auto dst = FlatVector::GetData<string_t>(out);
+			for (idx_t r = 0; r < rows; r++) {
+				const uint32_t a = s.offsets[r], b = s.offsets[r + 1];
+				dst[r] = StringVector::AddStringOrBlob(out, const_char_ptr_cast(s.payload + a), b - a);
+			}
+			break;
+		}
+		default: // unknown column type -> NULLs, as the reference does (src/fastlanes_facade.cpp:173-181)
+			for (idx_t r = 0; r < rows; r++) {
+				FlatVector::SetNull(out, r, true);
+			}
+		}
+	}
+	return true;
+}
+
+void FastLanesFacade::closeFile() {
+	pImpl->scanner.close();
+	pImpl->slices.clear();
+	pImpl->projection.clear();
+	pImpl->initialized = false;
+}
+
+bool FastLanesFacade::isValid() const {
+	return pImpl->initialized;
+}
+idx_t FastLanesFacade::rowCount() const {
+	return pImpl->scanner.rowsInRange();
+}
+idx_t FastLanesFacade::rowsRead() const {
+	return pImpl->scanner.rowsServed();
+}
+const std::string &FastLanesFacade::lastError() const {
+	return pImpl->error;
+}
+
+} // namespace duckdb

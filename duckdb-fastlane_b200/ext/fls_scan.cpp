@@ -1,0 +1,195 @@
+// fls_scan.cpp — see fls_scan.hpp.  Everything goes through the C ABI; there is no CPU decode here.
+#include "fls_scan.hpp"
+
+#include <algorithm>
+#include <future>
+
+namespace flsgpu_host {
+
+namespace {
+struct Decoded {
+  flsgpu_batch_t *batch = nullptr;
+  uint32_t g0 = 0, g1 = 0;
+  int rc = 0;
+  std::string err;
+};
+}  // namespace
+
+struct FlsScanner::Impl {
+  flsgpu_t *h = nullptr;
+  std::string err;
+  std::vector<std::string> names;
+  std::vector<int32_t> types;
+  std::vector<uint32_t> proj;
+  uint32_t n_rg = 0, g_begin = 0, g_end = 0, batch_rgs = 16;
+  uint64_t n_rows = 0, rows_in_range = 0, served = 0;
+  bool started = false;
+
+  Decoded cur;                     // batch being served
+  std::vector<flsgpu_column> cols; // its columns
+  uint32_t rg = 0;                 // row group being served (absolute)
+  uint64_t rg_row = 0;             // next row inside it
+  uint64_t rg_base = 0;            // padded row index of the row group's first row inside the batch
+  std::future<Decoded> ahead;      // batch being decoded by the worker
+  uint32_t next_g = 0;             // first row group not yet handed to the worker
+
+  // Runs on the worker thread; it is the only caller of the handle while it runs (flsgpu.h: one caller at a time).
+  Decoded decode(flsgpu_batch_t *release_first, uint32_t g0, uint32_t g1) {
+    if (release_first) flsgpu_batch_release(release_first);
+    Decoded d;
+    d.g0 = g0; d.g1 = g1;
+    d.rc = flsgpu_decode(h, g0, g1, proj.empty() ? nullptr : proj.data(), (uint32_t)proj.size(), FLSGPU_OUT_HOST, &d.batch);
+    if (d.rc) d.err = flsgpu_last_error(h);
+    return d;
+  }
+  void launch_ahead(flsgpu_batch_t *release_first) {
+    if (next_g >= g_end) {
+      if (release_first) flsgpu_batch_release(release_first);
+      return;
+    }
+    const uint32_t g0 = next_g, g1 = std::min(g_end, g0 + batch_rgs);
+    next_g = g1;
+    ahead = std::async(std::launch::async, [this, release_first, g0, g1] { return decode(release_first, g0, g1); });
+  }
+  void drain() {
+    if (ahead.valid()) {
+      Decoded d = ahead.get();
+      if (d.batch) flsgpu_batch_release(d.batch);
+    }
+    if (cur.batch) { flsgpu_batch_release(cur.batch); cur.batch = nullptr; }
+  }
+  // make `cur` the next batch; false at the end or on error
+  bool advance_batch() {
+    flsgpu_batch_t *old = cur.batch;
+    cur = Decoded();
+    if (!ahead.valid()) {
+      if (old) flsgpu_batch_release(old);
+      return false;
+    }
+    Decoded d = ahead.get();
+    if (d.rc) {
+      err = d.err;
+      if (old) flsgpu_batch_release(old);
+      return false;
+    }
+    cur = d;
+    const uint32_t nc = flsgpu_batch_num_columns(cur.batch);
+    cols.resize(nc);
+    for (uint32_t i = 0; i < nc; ++i) flsgpu_batch_column(cur.batch, i, &cols[i]);
+    rg = cur.g0; rg_row = 0; rg_base = 0;
+    launch_ahead(old);
+    return true;
+  }
+};
+
+FlsScanner::FlsScanner() : p(new Impl()) {}
+FlsScanner::~FlsScanner() { close(); }
+
+bool FlsScanner::open(const std::string &path, int device, uint32_t batch_rowgroups) {
+  close();
+  flsgpu_opts o = {};
+  o.device = device;
+  const int rc = flsgpu_open(path.c_str(), &o, &p->h);
+  if (rc != FLSGPU_OK) {
+    p->err = flsgpu_last_error(nullptr);
+    p->h = nullptr;
+    return false;
+  }
+  p->err.clear();
+  uint32_t nc = 0;
+  const char *const *names = nullptr;
+  const int32_t *types = nullptr;
+  flsgpu_schema(p->h, &nc, &names, &types);
+  p->names.assign(names, names + nc);
+  p->types.assign(types, types + nc);
+  p->n_rg = flsgpu_num_rowgroups(p->h);
+  p->n_rows = flsgpu_num_rows(p->h);
+  p->g_begin = 0; p->g_end = p->n_rg;
+  p->rows_in_range = p->n_rows;
+  p->proj.clear();
+  if (batch_rowgroups) p->batch_rgs = batch_rowgroups;
+  p->started = false;
+  p->served = 0;
+  return true;
+}
+
+void FlsScanner::close() {
+  if (!p->h) return;
+  p->drain();
+  flsgpu_close(p->h);
+  p->h = nullptr;
+  p->names.clear(); p->types.clear(); p->proj.clear();
+  p->n_rg = 0; p->n_rows = 0; p->served = 0; p->started = false;
+}
+
+bool FlsScanner::isOpen() const { return p->h != nullptr; }
+const std::string &FlsScanner::error() const { return p->err; }
+uint32_t FlsScanner::columnCount() const { return (uint32_t)p->names.size(); }
+uint64_t FlsScanner::rowCount() const { return p->n_rows; }
+uint32_t FlsScanner::rowGroupCount() const { return p->n_rg; }
+const std::vector<std::string> &FlsScanner::columnNames() const { return p->names; }
+const std::vector<int32_t> &FlsScanner::columnTypes() const { return p->types; }
+uint64_t FlsScanner::rowsServed() const { return p->served; }
+uint64_t FlsScanner::rowsInRange() const { return p->rows_in_range; }
+
+bool FlsScanner::setProjection(const std::vector<uint32_t> &cols) {
+  if (!p->h || p->started) { p->err = "projection must be set on an open scanner before the first chunk"; return false; }
+  for (uint32_t c : cols)
+    if (c >= p->names.size()) { p->err = "bad column id"; return false; }
+  p->proj = cols;
+  return true;
+}
+
+bool FlsScanner::setRowGroupRange(uint32_t g0, uint32_t g1) {
+  if (!p->h || p->started || g0 > g1 || g1 > p->n_rg) { p->err = "bad row-group range"; return false; }
+  p->g_begin = g0; p->g_end = g1;
+  p->rows_in_range = 0;
+  for (uint32_t g = g0; g < g1; ++g) p->rows_in_range += flsgpu_rowgroup_rows(p->h, g);
+  return true;
+}
+
+bool FlsScanner::next(uint64_t max_rows, uint64_t &rows, std::vector<ColumnSlice> &out) {
+  rows = 0;
+  if (!p->h || !max_rows) return false;
+  if (!p->started) {
+    p->started = true;
+    p->next_g = p->g_begin;
+    p->launch_ahead(nullptr);
+    if (!p->advance_batch()) return false;
+  }
+  for (;;) {
+    if (!p->cur.batch) return false;
+    if (p->rg >= p->cur.g1) {
+      if (!p->advance_batch()) return false;
+      continue;
+    }
+    const uint64_t rg_rows = flsgpu_rowgroup_rows(p->h, p->rg);
+    if (p->rg_row >= rg_rows) {  // next row group: skip the padding of the last vector
+      p->rg_base += (rg_rows + 1023u) / 1024u * 1024u;
+      p->rg++;
+      p->rg_row = 0;
+      continue;
+    }
+    rows = std::min<uint64_t>(max_rows, rg_rows - p->rg_row);
+    const uint64_t at = p->rg_base + p->rg_row;
+    out.resize(p->cols.size());
+    for (size_t i = 0; i < p->cols.size(); ++i) {
+      const flsgpu_column &c = p->cols[i];
+      ColumnSlice &s = out[i];
+      s.type = c.type; s.width = c.width;
+      if (c.width) {
+        s.data = (const uint8_t *)c.data + at * c.width;
+        s.offsets = nullptr; s.payload = nullptr;
+      } else {
+        s.data = nullptr;
+        s.offsets = c.offsets + at;
+        s.payload = c.payload;
+      }
+    }
+    p->rg_row += rows;
+    p->served += rows;
+    return true;
+  }
+}
+
+}  // namespace flsgpu_host

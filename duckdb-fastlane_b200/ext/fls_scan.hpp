@@ -1,0 +1,69 @@
+// fls_scan.hpp — host-side scan cursor over the C ABI (include/flsgpu.h), free of DuckDB types.
+//
+// This is the state the reference keeps in FastLanesFacade::Impl (/root/reference/src/fastlanes_facade.cpp:12-20:
+// connection, table reader, row-group reader, materialised row group, current_row/total_rows) rebuilt on top of
+// libflsgpu: a row cursor over batches of row groups decoded on the GPU into pinned host memory.  While the
+// caller consumes batch i in <= 2048-row slices, batch i+1 is decoded by a worker thread, so the H2D copy, the
+// kernels and the D2H copy of the next batch overlap the engine's processing of the current one.
+//
+// The DuckDB-facing classes (fastlanes_facade.hpp, scan_fastlanes.cpp) sit on top of this; tests drive it
+// directly through ext/fls_scan_check.cpp.
+#pragma once
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "flsgpu.h"
+
+namespace flsgpu_host {
+
+// A run of rows of one column, valid until the next call to FlsScanner::next()/close().
+struct ColumnSlice {
+  int32_t type = 0;        // enum flsgpu_type
+  uint32_t width = 0;      // bytes per value; 0 for strings
+  const void *data = nullptr;          // fixed width: `rows` values
+  const uint32_t *offsets = nullptr;   // strings: rows + 1 offsets into payload (offsets[0] need not be 0)
+  const uint8_t *payload = nullptr;
+};
+
+class FlsScanner {
+ public:
+  FlsScanner();
+  ~FlsScanner();
+  FlsScanner(const FlsScanner &) = delete;
+  FlsScanner &operator=(const FlsScanner &) = delete;
+
+  // Parses the footer only (no decode, unlike the reference's openFile which materialises row group 0).
+  // On failure returns false and error() holds the text the reference's bind raises
+  // ("Failed to open FastLanes file: <path>", /root/reference/src/scan_fastlanes.cpp:42).
+  bool open(const std::string &path, int device = 0, uint32_t batch_rowgroups = 0);
+  void close();
+  bool isOpen() const;
+  const std::string &error() const;
+
+  uint32_t columnCount() const;
+  uint64_t rowCount() const;
+  uint32_t rowGroupCount() const;
+  const std::vector<std::string> &columnNames() const;
+  const std::vector<int32_t> &columnTypes() const;  // enum flsgpu_type per column
+
+  // Projection pushdown: decode only these columns (file column ids, any order, duplicates allowed).
+  // Must be called before the first next(); an empty list means "all columns".
+  bool setProjection(const std::vector<uint32_t> &cols);
+  // Restrict the scan to row groups [g0, g1) — one shard of a multi-GPU / multi-thread scan.
+  bool setRowGroupRange(uint32_t g0, uint32_t g1);
+
+  // Next run of at most max_rows rows (never crossing a row-group boundary).  Returns false at the end of the
+  // scan or on error (error() non-empty).  out[i] describes projected column i.
+  bool next(uint64_t max_rows, uint64_t &rows, std::vector<ColumnSlice> &out);
+  // Rows served so far / rows in the scan range: table_scan_progress.
+  uint64_t rowsServed() const;
+  uint64_t rowsInRange() const;
+
+ private:
+  struct Impl;
+  std::unique_ptr<Impl> p;
+};
+
+}  // namespace flsgpu_host

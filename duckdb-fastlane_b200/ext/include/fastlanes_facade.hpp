@@ -1,0 +1,60 @@
+//===----------------------------------------------------------------------===//
+// fastlanes_facade.hpp — FastLanesFacade over libflsgpu (B200 decode) instead of the FastLanes CPU reader.
+//
+// Same class, namespace and reading methods as the reference's facade
+// (/root/reference/src/include/fastlanes_facade.hpp:22-47): openFile / getColumnTypes / getColumnNames /
+// readNextChunk / closeFile / isValid, PIMPL so no decoder header leaks into DuckDB translation units.
+// Differences, all on purpose:
+//   * openFile parses the footer only — the reference materialises row group 0 on the CPU at bind AND at init
+//     (/root/reference/src/fastlanes_facade.cpp:41-48, called from src/scan_fastlanes.cpp:41 and :57);
+//   * readNextChunk writes typed flat vectors straight from the decoded column arrays instead of one boxed
+//     Value per cell cast to VARCHAR (/root/reference/src/fastlanes_facade.cpp:125-172), and serves every row
+//     group of the file, not only the first;
+//   * getColumnTypes / getColumnNames are implemented (declared but never defined in the reference);
+//   * setProjection: projection pushdown (the reference's dead scanner sets the flag,
+//     /root/reference/src/scanner/scan_fastlanes.cpp:153, but never uses column_ids).
+// The writing half of the reference class (createFile / writeChunk / finalizeFile) is declared there and never
+// implemented; it is out of scope here.
+//===----------------------------------------------------------------------===//
+#pragma once
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "duckdb/common/types.hpp"
+#include "duckdb/common/types/data_chunk.hpp"
+
+namespace duckdb {
+
+class FastLanesFacade {
+private:
+	class Impl;
+	std::unique_ptr<Impl> pImpl;
+
+public:
+	FastLanesFacade();
+	~FastLanesFacade();
+
+	// Reading operations
+	bool openFile(const std::string &file_path);
+	std::vector<LogicalType> getColumnTypes();
+	std::vector<std::string> getColumnNames();
+	//! Projected file column ids, in output order; call between openFile and the first readNextChunk.
+	bool setProjection(const std::vector<idx_t> &column_ids);
+	//! Fills `result` with the next <= STANDARD_VECTOR_SIZE rows; false at the end of the file or on error.
+	bool readNextChunk(DataChunk &result);
+	void closeFile();
+
+	// Utility
+	bool isValid() const;
+	idx_t rowCount() const;
+	idx_t rowsRead() const;
+	//! Text of the last failure ("Failed to open FastLanes file: <path>" for a bad path).
+	const std::string &lastError() const;
+};
+
+//! FastLanes data type (enum flsgpu_type = the reference's type table, src/type_mapping.cpp:64-105) -> LogicalType
+LogicalType FastLanesTypeToDuckDB(int32_t fls_type);
+
+} // namespace duckdb

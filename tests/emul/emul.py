@@ -22,6 +22,11 @@ def lib():
     return _lib
 
 
+def force_any(on):
+    """Make every emulated warp vote succeed: all lanes take the most general code variant."""
+    lib().emul_force_any(int(on))
+
+
 def decode(image, col, ftype, g0, g1):
     """Returns padded output: fixed -> ndarray; strings -> (offsets[n_pad+1], payload)."""
     L = lib()

@@ -14,6 +14,7 @@
 #include "fls_strings.cuh"
 
 static std::string g_err;
+int fls_emul_force_any = 0;
 
 template <class V> static void run_vectors(const FlsLaunch &l) {
   std::vector<uint8_t> smem(V::SMEM + V::BLOCK_SMEM + 256);
@@ -69,6 +70,7 @@ static bool run_launch(const FlsLaunch &l) {
 
 extern "C" {
 const char *emul_error() { return g_err.c_str(); }
+void emul_force_any(int on) { fls_emul_force_any = on; }
 
 // Decode column `col` of row groups [g0,g1) of an in-memory image with the emulated kernels.
 // Buffers sized by the caller exactly like libflsgpu's (see fls_plan.h: fls_column_need).

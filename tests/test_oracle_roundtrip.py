@@ -29,6 +29,12 @@ def test_roundtrip_and_emulation(case):
             assert np.array_equal(got[0], exp[0]) and np.array_equal(got[1], exp[1])
             n = ora.n_rows
             assert np.array_equal(em[0][:n + 1], got[0]) and np.array_equal(em[1][:len(got[1])], got[1])
+            emul.force_any(True)  # every warp vote succeeds: the general (masked, escape-aware) variants run everywhere
+            try:
+                em = emul.decode(img, c, ora.types[c], 0, ora.n_rg)
+            finally:
+                emul.force_any(False)
+            assert np.array_equal(em[0][:n + 1], got[0]) and np.array_equal(em[1][:len(got[1])], got[1])
         else:
             assert np.array_equal(got.view(np.uint8), exp)
             assert np.array_equal(em[:ora.n_rows].view(np.uint8), exp)
