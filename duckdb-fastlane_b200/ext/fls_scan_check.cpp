@@ -1,7 +1,8 @@
 // fls_scan_check — drives FlsScanner the way FastLanesScan drives the facade (one <= 2048-row chunk per call,
 // /root/reference/src/scan_fastlanes.cpp:65-77) and prints one JSON line: row count and, per projected column,
-// an FNV-1a-64 digest of the served values (fixed width: the value bytes; strings: u32 length + bytes per row).
-// tests/test_ext_scan.py compares the digests with the ones computed from the CPU oracle's decode.
+// a digest "A:B" of the served values: A = sum of byte_k * (k + 1) over the column's value bytes in row order
+// (fixed width: the values; strings: the payload bytes), B = the same over the strings' lengths (0 for fixed
+// width), both mod 2^64.  tests/test_ext_scan.py compares them with digests of the CPU oracle's decode.
 //
 //   fls_scan_check <file.fls> [--cols 3,0,7] [--chunk 2048] [--batch 16] [--range g0:g1] [--device 0]
 #include <cstdio>
@@ -12,10 +13,14 @@
 
 #include "fls_scan.hpp"
 
-static inline void fnv(uint64_t &h, const void *p, size_t n) {
-  const uint8_t *b = (const uint8_t *)p;
-  for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 0x100000001B3ull; }
-}
+struct Digest {
+  uint64_t a = 0, ka = 0, b = 0, kb = 0;
+  void bytes(const void *p, size_t n) {
+    const uint8_t *x = (const uint8_t *)p;
+    for (size_t i = 0; i < n; ++i) a += (uint64_t)x[i] * ++ka;
+  }
+  void length(uint32_t len) { b += (uint64_t)len * ++kb; }
+};
 
 int main(int argc, char **argv) {
   if (argc < 2) { fprintf(stderr, "usage: fls_scan_check <file.fls> [--cols a,b] [--chunk n] [--batch n] [--range g0:g1]\n"); return 2; }
@@ -38,18 +43,18 @@ int main(int argc, char **argv) {
   if (!cols.empty() && !sc.setProjection(cols)) { printf("{\"error\": \"%s\"}\n", sc.error().c_str()); return 1; }
   if (have_range && !sc.setRowGroupRange(g0, g1)) { printf("{\"error\": \"%s\"}\n", sc.error().c_str()); return 1; }
   const size_t nc = cols.empty() ? sc.columnCount() : cols.size();
-  std::vector<uint64_t> dig(nc, 0xCBF29CE484222325ull);
+  std::vector<Digest> dig(nc);
   std::vector<flsgpu_host::ColumnSlice> out;
   uint64_t rows = 0, total = 0, chunks = 0;
   while (sc.next(chunk, rows, out)) {
     for (size_t c = 0; c < nc; ++c) {
       const auto &s = out[c];
-      if (s.width) fnv(dig[c], s.data, rows * s.width);
+      if (s.width) dig[c].bytes(s.data, rows * s.width);
       else
         for (uint64_t r = 0; r < rows; ++r) {
           const uint32_t len = s.offsets[r + 1] - s.offsets[r];
-          fnv(dig[c], &len, 4);
-          fnv(dig[c], s.payload + s.offsets[r], len);
+          dig[c].length(len);
+          dig[c].bytes(s.payload + s.offsets[r], len);
         }
     }
     total += rows;
@@ -59,7 +64,7 @@ int main(int argc, char **argv) {
   printf("{\"rows\": %llu, \"chunks\": %llu, \"columns\": %zu, \"names\": [", (unsigned long long)total, (unsigned long long)chunks, nc);
   for (size_t c = 0; c < nc; ++c) printf("%s\"%s\"", c ? ", " : "", sc.columnNames()[cols.empty() ? c : cols[c]].c_str());
   printf("], \"digests\": [");
-  for (size_t c = 0; c < nc; ++c) printf("%s\"%016llx\"", c ? ", " : "", (unsigned long long)dig[c]);
+  for (size_t c = 0; c < nc; ++c) printf("%s\"%016llx:%016llx\"", c ? ", " : "", (unsigned long long)dig[c].a, (unsigned long long)dig[c].b);
   printf("]}\n");
   return 0;
 }
