@@ -77,8 +77,10 @@ template <typename T> struct DecFFOR {
 template <typename T> struct DecDELTA {
   static constexpr uint32_t TB = sizeof(T) * 8u, L = 1024u / TB;
   static constexpr uint32_t STAGE = 128u + 128u * TB;
-  static constexpr uint32_t XCH = STAGE + FLS_TILE_BYTES(T);          // T=64 half-lane totals
-  static constexpr uint32_t SMEM = XCH + (sizeof(T) == 8 ? 256u : 0u);
+  // T=64: the deltas are unpacked into registers first, so the tile takes the place of the staged payload;
+  // XCH = half-lane totals
+  static constexpr uint32_t XCH = FLS_TILE_BYTES(T);
+  static constexpr uint32_t SMEM = sizeof(T) == 8 ? FLS_TILE_BYTES(T) + 256u : STAGE + FLS_TILE_BYTES(T);
 
   // Reconstruct into the warp's padded tile (original order).  `add` is added to every value (string offsets).
   FLS_MEM static void to_tile(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base) {
@@ -87,34 +89,7 @@ template <typename T> struct DecDELTA {
     const T *bases = (const T *)w.sm;
     const T *pk = (const T *)(w.sm + 128);
     T *tile = (T *)(w.sm + STAGE);
-    if (sizeof(T) == 8) {
-      // 16 lanes x 64 steps: thread (l = t&15, h = t>>4) owns steps [32h, 32h+32); the upper half needs the
-      // lower half's total first.
-      // Each half-lane unpacks its 32 deltas ONCE into registers; only the 16 half totals cross lanes.
-      uint64_t *xch = (uint64_t *)(w.sm + XCH);
-      FLS_VAR2(uint64_t, dl, 32);
-      FLS_LANES(t) {
-        const uint32_t l = t & 15u, h = t >> 4;
-        uint64_t tot = 0;
-#pragma unroll
-        for (uint32_t j = 0; j < 32u; ++j) {
-          const uint32_t r = 32u * h + j;
-          const uint64_t dv = (bw ? (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l) : 0ull) + base;
-          FLS_AT2(dl, j) = dv;
-          tot += dv;
-        }
-        xch[t] = tot;
-      }
-      FLS_LANES(t) {
-        const uint32_t l = t & 15u, h = t >> 4;
-        uint64_t acc = (uint64_t)bases[l] + (h ? xch[l] : 0ull);
-#pragma unroll
-        for (uint32_t j = 0; j < 32u; ++j) {
-          acc += FLS_AT2(dl, j);
-          tile[fls_tile_slot<T>(64u * l + 32u * h + j)] = (T)acc;
-        }
-      }
-    } else {
+    {
       constexpr uint32_t LPT = L / 32u;  // lanes per thread: 1 (T=32), 2 (T=16), 4 (T=8)
       FLS_LANES(t) {
         for (uint32_t a = 0; a < LPT; ++a) {
@@ -129,9 +104,51 @@ template <typename T> struct DecDELTA {
       }
     }
   }
+  // T=64: 16 lanes x 64 steps, thread (l = t&15, h = t>>4) owns steps [32h, 32h+32) = originals 64l+32h .. +31.
+  // Each half-lane unpacks its 32 deltas ONCE into registers; only the 16 half totals cross lanes.
+  FLS_MEM static void run64(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
+    w.stage(0, in, 128u + 128u * bw);
+    w.wait();
+    const T *bases = (const T *)w.sm;
+    const T *pk = (const T *)(w.sm + 128);
+    {
+      // the upper half of a lane needs the lower half's total first
+      uint64_t *xch = (uint64_t *)(w.sm + XCH);
+      T *tile = (T *)w.sm;  // overwrites the staged payload: every packed word has been consumed by then
+      FLS_VAR2(uint64_t, dl, 32);
+      FLS_VAR(uint64_t, lane_base);
+      FLS_LANES(t) {
+        const uint32_t l = t & 15u, h = t >> 4;
+        FLS_AT(lane_base) = (uint64_t)bases[l];
+        uint64_t tot = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < 32u; ++j) {
+          const uint32_t r = 32u * h + j;
+          const uint64_t dv = (bw ? (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l) : 0ull) + base;
+          FLS_AT2(dl, j) = dv;
+          tot += dv;
+        }
+        xch[t] = tot;
+      }
+      FLS_LANES(t) {
+        const uint32_t l = t & 15u, h = t >> 4;
+        uint64_t acc = FLS_AT(lane_base) + (h ? xch[l] : 0ull);
+#pragma unroll
+        for (uint32_t j = 0; j < 32u; ++j) {
+          acc += FLS_AT2(dl, j);
+          tile[fls_tile_slot<T>(64u * l + 32u * h + j)] = (T)acc;
+        }
+      }
+      FLS_LANES(t) { fls_tile_copy_out<T>(w.sm, out, t); }
+    }
+  }
   FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
-    to_tile(w, in, bw, base);
-    FLS_LANES(t) { fls_tile_copy_out<T>(w.sm + STAGE, out, t); }
+    if constexpr (sizeof(T) == 8) {
+      run64(w, in, bw, base, out);
+    } else {
+      to_tile(w, in, bw, base);
+      FLS_LANES(t) { fls_tile_copy_out<T>(w.sm + STAGE, out, t); }
+    }
   }
 };
 

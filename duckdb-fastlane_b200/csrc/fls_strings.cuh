@@ -373,143 +373,220 @@ struct VecSTRDICT {
 // table, one per 16-byte bank group, lane t uses copy t & 7) and one FlsPush::push.  Escapes (code 255) are rare:
 // a window that holds one, and the partial first/last window of a run, take the byte-by-byte path.
 struct VecSTRFSST {
-  static constexpr uint32_t WARPS = 6;
-  static constexpr uint32_t STG = 12672u;    // staging; phase 1: [decoded-ends stage | compressed-ends stage | tile]
-  static constexpr uint32_t CWIN = 16384u;   // compressed-byte window
-  static constexpr uint32_t BND = 2u * 132u * 4u;  // string boundaries every 8 strings: BD[129], BC[129]
-  static constexpr uint32_t SMEM = STG + CWIN + BND + 96u;  // 30208 = 236 * 128
-  static constexpr uint32_t BLOCK_SMEM = 32768u;  // 256 entries x 8 copies x 16 B; entry e of copy r at e*128 + r*16
-  static_assert(3u * 4224u <= STG, "phase-1 buffers must fit the staging buffer");
+  static constexpr uint32_t WARPS = 8;
+  static constexpr uint32_t STG = 11264u;    // staging of one quarter's output; phase 1: the two staged offset streams
+  static constexpr uint32_t CWIN = 4096u;    // compressed bytes of one quarter; two windows (the next quarter loads
+                                             // while this one is decoded)
+  static constexpr uint32_t E16N = 1056u;    // 16-bit relative end of every string, padded original order (x2)
+  static constexpr uint32_t SMEM = STG + 2u * CWIN + 4u * E16N + 256u;  // 23936 = 187 * 128
+  // 512 entries (256 codes, 256 escaped literals) x 4 copies x 16 B; entry e of copy r at e*64 + r*16
+  static constexpr uint32_t BLOCK_SMEM = 32768u;
+  static_assert(2u * 4224u <= STG, "phase-1 buffers must fit the staging buffer");
   static_assert(SMEM % 128u == 0, "warp slots stay 128-byte aligned");
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
     const uint64_t *sym = (const uint64_t *)k.seg[4];
     const uint8_t *len = k.seg[4] + 2048;
-    for (uint32_t e = tid; e < 256u; e += nthreads) {
+    for (uint32_t e = tid; e < 512u; e += nthreads) {
       fls_u4 en;
       if (e == 255u) { en.x = en.y = en.z = en.w = 0u; }  // the escape marker itself produces nothing
-      else en = fls_piece_entry(fls_ldg(sym + e), fls_min(8u, (uint32_t)fls_ldg(len + e)));
-      for (uint32_t r = 0; r < 8u; ++r) *(fls_u4 *)(bsm + 128u * e + 16u * r) = en;
+      else if (e < 256u) en = fls_piece_entry(fls_ldg(sym + e), fls_min(8u, (uint32_t)fls_ldg(len + e)));
+      else en = fls_piece_entry(e - 256u, 1u);            // escaped byte e - 256: itself
+      for (uint32_t r = 0; r < 4u; ++r) *(fls_u4 *)(bsm + 64u * e + 16u * r) = en;
     }
   }
-  // Eight consecutive compressed bytes (lo, hi) of a lane's run: eight table loads in flight, then eight pushes —
-  // straight-line code, no branch.  ESC: the window may hold escapes (code 255 -> the next byte is a literal) or
-  // start with a pending literal; `lit` carries that state from byte to byte as a predicate and a literal's entry
-  // is made from the byte itself (only the low byte of lo/tail matters for a one-byte piece).  MASK: bit j of
-  // `vbits` says whether byte j belongs to the run (partial first/last window); other bytes change nothing.
-  template <bool ESC, bool MASK>
-  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, uint32_t lo, uint32_t hi, uint32_t vbits, bool &lit) {
-    fls_u4 e[8];
-    uint32_t x[8];
-#pragma unroll
-    for (uint32_t j = 0; j < 8u; ++j) x[j] = (j < 4u ? lo : hi) >> (8u * (j & 3u));
-#pragma unroll
-    for (uint32_t j = 0; j < 8u; ++j) e[j] = fls_lds128<fls_u4>(tabr + ((x[j] & 0xFFu) << 7));
+  // 0x80 in every byte of x that equals 0xFF (exact, byte by byte)
+  FLS_MEM static uint32_t ff_bytes(uint32_t x) {
+    const uint32_t y = ~x;  // zero byte <=> 0xFF
+    return ~(((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y) & 0x80808080u;
+  }
+  // Eight consecutive compressed bytes (lo, hi) of a lane's run: eight table loads in flight, then eight pushes,
+  // straight-line.  The table index of byte j is its value, plus 256 when the byte is an escaped literal.  Which
+  // bytes are literals is worked out for the whole window at once: byte j is a literal when byte j-1 is an escape
+  // marker (0xFF); with `lit` = the previous window ended in a marker.  That is exact unless two 0xFF bytes are
+  // adjacent (a literal 0xFF); such a window takes the byte-by-byte path.  MASK: only bytes [s, e) of the window
+  // belong to the run (partial first / last window); the others are turned into markers that escape nothing.
+  template <bool MASK>
+  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, uint32_t lo, uint32_t hi, uint32_t s, uint32_t e, bool &lit) {
+    uint32_t fflo = ff_bytes(lo), ffhi = ff_bytes(hi);
+    if (MASK) {
+      uint64_t vm = e >= 8u ? ~0ull : ((1ull << (8u * e)) - 1ull);
+      vm &= ~0ull << (8u * s);
+      const uint32_t vlo = (uint32_t)vm, vhi = (uint32_t)(vm >> 32);
+      fflo &= vlo; ffhi &= vhi;
+      lo |= ~vlo; hi |= ~vhi;  // 0xFF and not a marker: the empty entry
+    }
+    const uint32_t llo = (fflo << 8) | (lit ? 0x80u : 0u), lhi = (ffhi << 8) | (fflo >> 24);  // 0x80 per literal byte
+    if (((fflo & llo) | (ffhi & lhi)) != 0u) {
+      // adjacent 0xFF bytes: byte by byte
+      for (uint32_t j = 0; j < 8u; ++j) {
+        if (MASK && (j < s || j >= e)) continue;
+        const uint32_t c = ((j < 4u ? lo : hi) >> (8u * (j & 3u))) & 0xFFu;
+        if (lit) { p.push(fls_lds128<fls_u4>(tabr + 64u * (256u + c))); lit = false; }
+        else if (c == 255u) lit = true;
+        else p.push(fls_lds128<fls_u4>(tabr + 64u * c));
+      }
+      return;
+    }
+    lit = (ffhi >> 31) != 0u;
+    uint32_t ad[8];
 #pragma unroll
     for (uint32_t j = 0; j < 8u; ++j) {
-      fls_u4 en = e[j];
-      if (ESC) {
-        bool nl = (x[j] & 0xFFu) == 0xFFu && !lit;
-        if (lit) { en.x = x[j]; en.z = x[j]; en.w = 8u; }
-        if (MASK) {
-          const bool valid = (vbits >> j) & 1u;
-          if (!valid) { en.w = 0u; nl = lit; }
-        }
-        lit = nl;
-      }
-      p.push(en);
+      const uint32_t wv = j < 4u ? lo : hi, lv = j < 4u ? llo : lhi, sh = 8u * (j & 3u);
+      const uint32_t cb = sh >= 6u ? (wv >> (sh - 6u)) : (wv << (6u - sh));  // byte j * 64 at bits [6, 14)
+      const uint32_t lb = sh + 7u >= 14u ? (lv >> (sh + 7u - 14u)) : (lv << (14u - sh - 7u));  // its literal flag at bit 14
+      ad[j] = (cb & 0x3FC0u) | (lb & 0x4000u);
+    }
+    fls_u4 en[8];
+#pragma unroll
+    for (uint32_t j = 0; j < 8u; ++j) en[j] = fls_lds128<fls_u4>(tabr + ad[j]);
+#pragma unroll
+    for (uint32_t j = 0; j < 8u; ++j) p.push(en[j]);
+  }
+  // A lane's compressed run = bytes [a, b) of the staged window `cwin`, read 8 bytes at a time.
+  FLS_MEM static void decode_run(FlsPush &p, const uint8_t *tabr, const uint8_t *cwin, uint32_t a, uint32_t b) {
+    const uint32_t *cw = (const uint32_t *)cwin;
+    bool lit = false;
+    uint32_t i = a >> 3;
+    uint32_t lo = cw[2u * i], hi = cw[2u * i + 1u];
+    for (; 8u * i < b; ++i) {
+      // next window's words first (the window has 16 bytes of slack, so this never leaves it)
+      const uint32_t nlo = cw[2u * i + 2u], nhi = cw[2u * i + 3u];
+      const bool partial = 8u * i < a || 8u * i + 8u > b;
+      // the variant is chosen by a vote of the lanes still in the loop, so they stay converged
+      if (FLS_ANY(partial)) window<true>(p, tabr, lo, hi, 8u * i < a ? a - 8u * i : 0u, fls_min(8u, b - 8u * i), lit);
+      else window<false>(p, tabr, lo, hi, 0u, 8u, lit);
+      lo = nlo; hi = nhi;
     }
   }
+  // Slow path (compressed bytes larger than the window, output larger than the staging buffer, offsets that do
+  // not fit 16 bits): compressed bytes [c0, c1) -> o, byte-wise, straight from / to global memory.
+  FLS_MEM static void decode_bytes(const FlsChunkDev &k, uint32_t c0, uint32_t c1, uint8_t *o) {
+    const uint8_t *comp = k.seg[5];
+    const uint64_t *gsym = (const uint64_t *)k.seg[4];
+    const uint8_t *glen = k.seg[4] + 2048;
+    for (uint32_t i = c0; i < c1;) {
+      const uint32_t c = fls_ldg(comp + i++);
+      if (c == 255u) { if (i < c1) *o++ = fls_ldg(comp + i++); }
+      else { uint64_t s = fls_ldg(gsym + c); for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(glen + c)); b; --b) { *o++ = (uint8_t)s; s >>= 8; } }
+    }
+  }
+  // DELTA u32 chain of lane t over a staged end-offset stream.  Writes {lane base, end 0 .. end 30} + add to the
+  // 32 aligned slots line[0..31] (slot i = start of string i; end 31 is the next lane's base) and the 32 ends,
+  // relative to `rel0`, as 16-bit values into e16 (padded original order).  Returns the lane's last end.
+  FLS_MEM static uint32_t walk_ends(const uint8_t *stage, uint32_t bw, uint32_t base, uint32_t t, uint32_t add, uint32_t rel0,
+                                    uint32_t *line, uint16_t *e16) {
+    const uint32_t *bases = (const uint32_t *)stage, *pk = (const uint32_t *)(stage + 128);
+    uint32_t acc = bases[t];
+    uint32_t *e16w = (uint32_t *)(e16 + slot16(fls_lane_start(t)));
+#pragma unroll
+    for (uint32_t r4 = 0; r4 < 32u; r4 += 4u) {
+      uint32_t x[5];
+      x[0] = acc;
+#pragma unroll
+      for (uint32_t j = 0; j < 4u; ++j)
+        x[j + 1u] = x[j] + (bw ? fls_extract<uint32_t>(pk, bw, fls_chain_row<32>(r4 + j), t) : 0u) + base;
+      acc = x[4];
+      if (line) {
+        fls_u4 o;
+        o.x = x[0] + add; o.y = x[1] + add; o.z = x[2] + add; o.w = x[3] + add;
+        fls_st128(line + r4, o);
+      }
+      e16w[r4 / 2u] = ((x[1] - rel0) & 0xFFFFu) | ((x[2] - rel0) << 16);
+      e16w[r4 / 2u + 1u] = ((x[3] - rel0) & 0xFFFFu) | ((x[4] - rel0) << 16);
+    }
+    return acc;
+  }
+  // padded position of string e in the 16-bit end arrays: the 32 lanes of a walk write distinct banks
+  FLS_MEM static uint32_t slot16(uint32_t e) { return e + ((e >> 6) << 1); }
+  // start offset (relative) of string s: the end of string s - 1
+  FLS_MEM static uint32_t start16(const uint16_t *e16, uint32_t s) { return s ? (uint32_t)e16[slot16(s - 1u)] : 0u; }
   FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *tab) {
     const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
     uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
     if (bwd > 32u) bwd = 32u;
     if (bwc > 32u) bwc = 32u;
     uint8_t *stg = w.sm;
-    uint8_t *cwin = w.sm + STG;
-    uint32_t *BD = (uint32_t *)(w.sm + STG + CWIN), *BC = BD + 132;
-    uint32_t *tile = (uint32_t *)(w.sm + 8448u);
-    // ---- phase 1: both end-offset streams -> offsets[] and the boundaries of every group of 8 strings
+    uint16_t *DE = (uint16_t *)(w.sm + STG + 2u * CWIN), *CE = DE + E16N;
+    uint32_t *LS = (uint32_t *)(CE + E16N);  // LS[0..32] = first string of each lane, LS[34..37] = vector extents
+    const uint8_t *comp = k.seg[5];
+    uint8_t *pay = k.pay + k.pay_base;
+    // ---- phase 1: both end-offset streams -> offsets[] (global) and 16-bit relative ends of every string (shared)
     w.fence_async();
     w.stage(0, k.seg[1] + 16ull * hd.ep, 128u + 128u * bwd);
     w.stage(4224u, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc);
     w.wait();
-    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC + 1;
-    FLS_LANES(t) { fls_walk32(w.sm, bwd, (uint32_t)hd.base, tile, t); }
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i
+    const uint32_t dv0 = ((const uint32_t *)w.sm)[0], cv0 = ((const uint32_t *)(w.sm + 4224u))[0];  // lane 0's bases
+    FLS_VAR(uint32_t, lc0); FLS_VAR(uint32_t, lc1); FLS_VAR(uint32_t, ld0);
     FLS_LANES(t) {
-      fls_tile_copy_out<uint32_t>((const uint8_t *)tile, offs, t, k.pay_base);
-      for (uint32_t i = t; i < 128u; i += 32u) BD[i + 1u] = tile[fls_tile_slot<uint32_t>(8u * i + 7u)];
-      if (t == 0) BD[0] = ((const uint32_t *)w.sm)[0];  // lane 0's base = the end offset before the vector
+      FLS_AT(ld0) = ((const uint32_t *)w.sm)[t];
+      FLS_AT(lc0) = ((const uint32_t *)(w.sm + 4224u))[t];
+      const uint32_t dend = walk_ends(w.sm, bwd, (uint32_t)hd.base, t, k.pay_base, dv0, offs + fls_lane_start(t), DE);
+      const uint32_t cend = walk_ends(w.sm + 4224u, bwc, (uint32_t)hc.base, t, 0u, cv0, nullptr, CE);
+      FLS_AT(lc1) = cend;
+      if (t == 31u) { offs[FLS_VEC] = dend + k.pay_base; LS[34] = dend; LS[35] = cend; }  // lane 31 owns the last strings
     }
-    FLS_LANES(t) { fls_walk32(w.sm + 4224u, bwc, (uint32_t)hc.base, tile, t); }
-    FLS_LANES(t) {
-      for (uint32_t i = t; i < 128u; i += 32u) BC[i + 1u] = tile[fls_tile_slot<uint32_t>(8u * i + 7u)];
-      if (t == 0) BC[0] = ((const uint32_t *)(w.sm + 4224u))[0];
+    const uint32_t dv1 = LS[34], cv1 = LS[35];
+    if (dv1 - dv0 >= 65536u || cv1 - cv0 >= 65536u) {
+      // offsets do not fit 16 bits: every lane decodes the 32 strings of its own chain, byte-wise
+      FLS_LANES(t) { decode_bytes(k, FLS_AT(lc0), FLS_AT(lc1), pay + FLS_AT(ld0)); }
+      return;
     }
-    // ---- phase 2: the vector's compressed bytes [cv0, cv1) -> window
-    const uint8_t *comp = k.seg[5];
-    uint8_t *pay = k.pay + k.pay_base;
-    const uint32_t cv0 = BC[0], cv1 = BC[128];
-    const uint32_t wbase = cv0 & ~15u;
-    const uint32_t span = cv1 > wbase ? cv1 - wbase : 0u;
-    const bool windowed = span + 16u <= CWIN;
-    if (windowed && span) {
-      w.fence_async();
-      w.stage(STG, comp + wbase, (span + 15u) & ~15u);
-      w.wait();
-    }
-    const uint64_t *gsym = (const uint64_t *)k.seg[4];
-    const uint8_t *glen = k.seg[4] + 2048;
+    // ---- phase 2: quarter by quarter (256 strings); the quarter's compressed bytes are split into 32 runs of
+    //      (nearly) equal length that start on string boundaries, one per lane; the compressed bytes of quarter
+    //      q+1 are bulk-copied into the other window while quarter q is decoded
+    uint32_t qc0 = 0, qc1 = start16(CE, 256u);  // compressed extent of the quarter, relative to cv0
+    uint32_t wbase = cv0 & ~15u;
+    uint32_t span = cv0 + qc1 - wbase;
+    bool windowed = span + 16u <= CWIN;
+    if (windowed && span) { w.fence_async(); w.stage(STG, comp + wbase, (span + 15u) & ~15u); }
     for (uint32_t qt = 0; qt < 4u; ++qt) {
-      const uint32_t Q0 = BD[32u * qt], Q1 = BD[32u * qt + 32u];
-      const uint32_t qlen = Q1 > Q0 ? Q1 - Q0 : 0u;
-      uint8_t *g = pay + Q0;
+      if (windowed && span) w.wait();
+      const uint8_t *cwin = w.sm + STG + (qt & 1u) * CWIN;
+      const uint32_t cur_wbase = wbase, cur_c0 = qc0, cur_c1 = qc1;
+      const bool cur_windowed = windowed;
+      if (qt < 3u) {  // next quarter's window
+        qc0 = qc1;
+        qc1 = start16(CE, 256u * qt + 512u);
+        wbase = (cv0 + qc0) & ~15u;
+        span = cv0 + qc1 - wbase;
+        windowed = span + 16u <= CWIN;
+        if (windowed && span) { w.fence_async(); w.stage(STG + ((qt + 1u) & 1u) * CWIN, comp + wbase, (span + 15u) & ~15u); }
+      }
+      const uint32_t S0 = 256u * qt, S1 = S0 + 256u;
+      const uint32_t qd0 = start16(DE, S0), qlen = start16(DE, S1) - qd0;
+      uint8_t *g = pay + dv0 + qd0;
       const uint32_t hh = (uint32_t)((uintptr_t)g & 15u);
-      if (windowed && hh + qlen <= STG) {
-        FLS_VAR(FlsPush, ps);
-        FLS_LANES(t) {
-          const uint8_t *tabr = tab + 16u * (t & 7u);
-          const uint32_t c0 = BC[32u * qt + t], c1 = BC[32u * qt + t + 1u], d0 = BD[32u * qt + t];
-          FlsPush p;
-          p.init(stg, hh + (d0 - Q0));
-          if (c1 > c0 && c1 - wbase <= span) {
-            const uint32_t a = c0 - wbase, b = c1 - wbase;
-            const uint32_t *cw = (const uint32_t *)cwin;
-            bool lit = false;
-            uint32_t i = a >> 3;
-            uint32_t lo = cw[2u * i], hi = cw[2u * i + 1u];
-            for (; 8u * i < b; ++i) {
-              // next window's words first (the window has 16 bytes of slack, so this never leaves it)
-              const uint32_t nlo = cw[2u * i + 2u], nhi = cw[2u * i + 3u];
-              const bool partial = 8u * i < a || 8u * i + 8u > b;
-              const uint32_t xlo = ~lo, xhi = ~hi;  // a 0xFF byte <=> a zero byte of the complement
-              const bool esc = ((((xlo - 0x01010101u) & ~xlo) | ((xhi - 0x01010101u) & ~xhi)) & 0x80808080u) != 0u || lit;
-              // the variant is chosen by a vote of the lanes still in the loop, so they stay converged
-              if (FLS_ANY(partial)) {
-                const uint32_t s = 8u * i < a ? a - 8u * i : 0u, e = fls_min(8u, b - 8u * i);
-                window<true, true>(p, tabr, lo, hi, ((1u << e) - 1u) & ~((1u << s) - 1u), lit);
-              } else if (FLS_ANY(esc)) {
-                window<true, false>(p, tabr, lo, hi, 0xFFu, lit);
-              } else {
-                window<false, false>(p, tabr, lo, hi, 0xFFu, lit);
-              }
-              lo = nlo; hi = nhi;
-            }
-          }
-          FLS_AT(ps) = p;
+      // first string of lane t: the first one that starts at or after t/32 of the quarter's compressed bytes
+      FLS_LANES(t) {
+        const uint32_t target = cur_c0 + (((cur_c1 - cur_c0) * t) >> 5);
+        uint32_t lo = S0, hi = S1;
+#pragma unroll
+        for (uint32_t it = 0; it < 9u; ++it) {
+          const uint32_t mid = (lo + hi) >> 1;
+          const bool below = lo < hi && start16(CE, mid) < target;
+          if (lo < hi) { if (below) lo = mid + 1u; else hi = mid; }
         }
+        LS[t] = lo;
+        if (t == 0) LS[32] = S1;
+      }
+      const bool staged = cur_windowed && hh + qlen <= STG;
+      FLS_VAR(FlsPush, ps);
+      FLS_LANES(t) {
+        const uint32_t sa = LS[t], sb = LS[t + 1u];
+        const uint32_t c0 = start16(CE, sa), c1 = start16(CE, sb), d0 = start16(DE, sa);
+        if (staged) {
+          FlsPush p;
+          p.init(stg, hh + (d0 - qd0));
+          if (c1 > c0) decode_run(p, tab + 16u * (t & 3u), cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
+          FLS_AT(ps) = p;
+        } else {
+          decode_bytes(k, cv0 + c0, cv0 + c1, pay + dv0 + d0);
+        }
+      }
+      if (staged) {
         FLS_LANES(t) { FLS_AT(ps).finish(); }
         FLS_LANES(t) { fls_stage_copy_out(stg, g, hh, qlen, t); }
-      } else {
-        // compressed bytes larger than the window, or a quarter larger than the staging buffer: byte-wise from global
-        FLS_LANES(t) {
-          const uint32_t c0 = BC[32u * qt + t], c1 = BC[32u * qt + t + 1u];
-          uint8_t *o = pay + BD[32u * qt + t];
-          for (uint32_t i = c0; i < c1;) {
-            const uint32_t c = fls_ldg(comp + i++);
-            if (c == 255u) { if (i < c1) *o++ = fls_ldg(comp + i++); }
-            else { uint64_t s = fls_ldg(gsym + c); for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(glen + c)); b; --b) { *o++ = (uint8_t)s; s >>= 8; } }
-          }
-        }
       }
     }
   }

@@ -39,7 +39,7 @@ template <class V> cudaError_t chunk_attr() {
 // blocks per chunk: enough blocks to fill the GPU several times over when the batch has few chunks
 template <class V> void chunk_launch(const FlsChunkDev *d, uint32_t n, cudaStream_t s) {
   uint32_t bpc = 1;
-  while (bpc < 4u && n * bpc < 592u) bpc *= 2u;
+  while (bpc < 4u && n * bpc < 148u * 12u) bpc *= 2u;  // at least a dozen waves of blocks: short tail
   fls_chunk_kernel<V><<<n * bpc, V::WARPS * 32, fls_chunk_smem<V>(), s>>>(d, bpc);
 }
 template <template <typename> class V> cudaError_t vec_attr_all() {
@@ -141,6 +141,7 @@ struct flsgpu {
   uint64_t size = 0;
   bool image_owned = false, image_registered = false, cuda_ready = false;
   cudaStream_t s_h2d = nullptr, s_k = nullptr, s_d2h = nullptr;
+  cudaStream_t s_kx[3] = {nullptr, nullptr, nullptr};  // side streams: independent kernels of a slice overlap
   uint8_t *d_res = nullptr;  // resident compressed row groups [res_g0, res_g1)
   uint64_t res_bytes = 0;
   uint32_t res_g0 = 0, res_g1 = 0;
@@ -223,6 +224,7 @@ int ensure_ready(flsgpu *h) {
   CK(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&h->s_k, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+  for (auto &sx : h->s_kx) CK(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
   CK(set_kernel_attrs());
   if (!h->image) {  // opened by path: read the file into page-locked memory
     void *p = nullptr;
@@ -338,6 +340,7 @@ void flsgpu_close(flsgpu_t *h) {
     cudaStreamDestroy(h->s_h2d);
     cudaStreamDestroy(h->s_k);
     cudaStreamDestroy(h->s_d2h);
+    for (auto sx : h->s_kx) cudaStreamDestroy(sx);
   }
   delete h;
 }
@@ -537,9 +540,9 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     }
     if (!perr.empty()) break;
     // dictionary preparation must run before the gathers that read it
-    std::stable_sort(ls.begin(), ls.end(), [](const FlsLaunch &a, const FlsLaunch &b2) {
-      return (a.kind == FLS_K_STR_FSST_DICTPREP) > (b2.kind == FLS_K_STR_FSST_DICTPREP);
-    });
+    // ... and the longest kernels go first
+    auto rank_of = [](int kind) { return kind == FLS_K_STR_FSST_DICTPREP ? 0 : kind == FLS_K_STR_FSST ? 1 : kind == FLS_K_STR_DICT ? 2 : 3; };
+    std::stable_sort(ls.begin(), ls.end(), [&](const FlsLaunch &a, const FlsLaunch &b2) { return rank_of(a.kind) < rank_of(b2.kind); });
     const size_t desc0 = desc_used;
     for (auto &l : ls) {
       if (desc_used + l.chunks.size() > desc_cap) { perr = "internal: descriptor overflow"; break; }
@@ -570,16 +573,34 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     EvPair ek = {ev(), ev()};
     CK(cudaEventRecord(ek.a, h->s_k));
     size_t dpos = desc0;
+    // Without per-kernel timing the launches of a slice are independent (different columns) except that a
+    // dictionary must be prepared before the gather that reads it: dictprep + str_dict stay on s_k, in order;
+    // the long FSST kernel and the bandwidth-bound kernels go to side streams so that one kernel's tail overlaps
+    // the next kernel's start.
+    bool side_used[3] = {false, false, false};
+    uint32_t rr = 1;
     for (auto &l : recs) {
       KEv ke = {nullptr, nullptr, l.kind * 5 + width_slot(l.width), l.rd, l.wr, l.vec};
-      if (time_kernels) { ke.a = ev(); ke.b = ev(); CK(cudaEventRecord(ke.a, h->s_k)); }
-      if (!launch_kind(l, d_desc + dpos, h->s_k)) { perr = "internal: no kernel for launch kind"; break; }
+      cudaStream_t ks = h->s_k;
+      if (!time_kernels && recs.size() > 1 && l.kind != FLS_K_STR_FSST_DICTPREP && l.kind != FLS_K_STR_DICT) {
+        const uint32_t si = l.kind == FLS_K_STR_FSST ? 0u : 1u + (rr++ & 1u);
+        ks = h->s_kx[si];
+        if (!side_used[si]) { CK(cudaStreamWaitEvent(ks, ek.a, 0)); side_used[si] = true; }
+      }
+      if (time_kernels) { ke.a = ev(); ke.b = ev(); CK(cudaEventRecord(ke.a, ks)); }
+      if (!launch_kind(l, d_desc + dpos, ks)) { perr = "internal: no kernel for launch kind"; break; }
       CK(cudaGetLastError());
-      if (time_kernels) CK(cudaEventRecord(ke.b, h->s_k));
+      if (time_kernels) CK(cudaEventRecord(ke.b, ks));
       kev.push_back(ke);
       dpos += l.n;
       b->tm.kernel_launches++;
     }
+    for (uint32_t si = 0; si < 3u; ++si)
+      if (side_used[si]) {
+        cudaEvent_t je = ev();
+        CK(cudaEventRecord(je, h->s_kx[si]));
+        CK(cudaStreamWaitEvent(h->s_k, je, 0));
+      }
     if (!perr.empty()) break;
     CK(cudaEventRecord(ek.b, h->s_k));
     ev_k.push_back(ek);
