@@ -113,8 +113,11 @@ FLS_DEV void fls_smem_max(uint32_t *p, uint32_t v) { atomicMax(p, v); }
 // ---------------------------------------------------------------------------------------------------------
 // The warp's staging slot + mbarrier.
 // ---------------------------------------------------------------------------------------------------------
+#define FLS_NO_VECTOR 0xFFFFFFFFu
 struct FlsWarp {
   uint8_t *sm;  // this warp's shared-memory scratch, 128-byte aligned
+  // pipelined kernels: vector whose payload has already been staged (or is in flight) and where
+  uint32_t pf_v = FLS_NO_VECTOR, pf_off = 0;
 #ifndef FLS_HOST_EMUL
   uint32_t bar;     // shared-space address of the warp's mbarrier
   uint32_t parity;  // phase parity the next wait() waits for

@@ -131,12 +131,15 @@ __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsCh
   __syncthreads();
   FlsWarp w;
   w.init(fls_smem + warp * V::SMEM, (uint64_t *)(bsm + V::BLOCK_SMEM) + warp);
-  for (;;) {
-    uint32_t v = 0;
-    if ((threadIdx.x & 31u) == 0) v = atomicAdd(next, 1u);
-    v = __shfl_sync(0xFFFFFFFFu, v, 0);
-    if (v >= v1) break;
-    V::run(k, v, w, bsm);
+  auto grab = [&]() {
+    uint32_t x = 0;
+    if ((threadIdx.x & 31u) == 0) x = atomicAdd(next, 1u);
+    return __shfl_sync(0xFFFFFFFFu, x, 0);
+  };
+  for (uint32_t v = grab(); v < v1;) {  // one vector ahead, so that run() can prefetch the next one's payload
+    const uint32_t vn = grab();
+    V::run(k, v, vn < v1 ? vn : FLS_NO_VECTOR, w, bsm);
+    v = vn;
   }
 }
 

@@ -104,25 +104,43 @@ FLS_DEV void fls_sts8(fls_sptr a, uint32_t v) { asm volatile("st.shared.u8 [%0],
 #endif
 
 struct FlsPush {
-  fls_sptr o, o0;
-  uint32_t prev, n8, n8_0;
+  fls_sptr o0;   // address of the run's first (possibly shared) word
+  uint32_t T;    // bits appended so far + 8 * (bytes of the first word that precede the run)
+  uint32_t T0;   // the initial T
+  uint32_t prev; // a word whose top (T & 31) / 8 bytes are the pending bytes
   FLS_MEM void init(uint8_t *stg, uint32_t s) {  // s = byte offset of the run's first byte inside stg
-    o = o0 = fls_sptr_of(stg) + (s & ~3u);
-    n8 = n8_0 = 8u * (s & 3u);
+    o0 = fls_sptr_of(stg) + (s & ~3u);
+    T = T0 = 8u * (s & 3u);
     prev = 0;
   }
+  // everything a piece needs is a function of (T before, T after, prev before): the pieces of a batch only
+  // chain through one add (T) and one funnel shift (prev) each, the rest is independent work
+  FLS_MEM static void emit(fls_sptr o0, uint32_t Tb, uint32_t Ta, uint32_t pv, uint32_t lo, uint32_t hi) {
+    const uint32_t a = Tb >> 5, d = (Ta >> 5) - a;
+    const fls_sptr addr = o0 + 4u * a;
+    fls_sts32_ge<1u>(d, addr, fls_shf_l(pv, lo, Tb));       // funnel shifts use T mod 32
+    fls_sts32_ge<2u>(d, addr + 4u, fls_shf_l(lo, hi, Tb));
+  }
   FLS_MEM void push(uint32_t lo, uint32_t hi, uint32_t tail, uint32_t L8) {
-    const uint32_t m8 = n8 + L8;
-    fls_sts32_ge<32u>(m8, o, fls_shf_l(prev, lo, n8));
-    fls_sts32_ge<64u>(m8, o + 4u, fls_shf_l(lo, hi, n8));
+    const uint32_t Ta = T + L8;
+    emit(o0, T, Ta, prev, lo, hi);
     prev = fls_shf_rc(prev, tail, L8);
-    o += (m8 >> 5) << 2;
-    n8 = m8 & 31u;
+    T = Ta;
   }
   FLS_MEM void push(const fls_u4 &e) { push(e.x, e.y, e.z, e.w); }
+  template <uint32_t N> FLS_MEM void push_all(const fls_u4 (&e)[N]) {
+    uint32_t Tj[N + 1], pj[N + 1];
+    Tj[0] = T; pj[0] = prev;
+#pragma unroll
+    for (uint32_t j = 0; j < N; ++j) { Tj[j + 1] = Tj[j] + e[j].w; pj[j + 1] = fls_shf_rc(pj[j], e[j].z, e[j].w); }
+#pragma unroll
+    for (uint32_t j = 0; j < N; ++j) emit(o0, Tj[j], Tj[j + 1], pj[j], e[j].x, e[j].y);
+    T = Tj[N]; prev = pj[N];
+  }
   FLS_MEM void push_byte(uint32_t b) { push(b, 0u, b, 8u); }
   FLS_MEM void finish() {
-    const uint32_t n = n8 >> 3, first = (o == o0) ? (n8_0 >> 3) : 0u;
+    const uint32_t n = (T & 31u) >> 3, first = (T >> 5) == 0u ? (T0 >> 3) : 0u;
+    const fls_sptr o = o0 + 4u * (T >> 5);
     for (uint32_t i = first; i < n; ++i) fls_sts8(o + i, (prev >> (8u * (4u - n + i))) & 0xFFu);
   }
 };
@@ -180,10 +198,17 @@ struct VecSTRDICT {
   // block-shared: [hdr 16 B: u32 pieces, u32 maxlen, u32 ~minlen][lens u32 x 1024][pieces: n_dict x P x 16 B]
   static constexpr uint32_t CACHE_ENTRIES = 1024u, TAB_BYTES = 16384u;
   static constexpr uint32_t LENS = 16u, TAB = LENS + 4u * CACHE_ENTRIES;
-  static constexpr uint32_t BLOCK_SMEM = TAB + TAB_BYTES;
+  // ... [vector headers 64 x 16 B][vec_ep u32 x 65]: read once per block instead of once per vector from HBM
+  static constexpr uint32_t HDRS = TAB + TAB_BYTES, VEP = HDRS + 64u * 16u;
+  static constexpr uint32_t BLOCK_SMEM = VEP + 68u * 4u;
+  static constexpr bool PIPELINED = true;
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
     uint32_t *hdr = (uint32_t *)bsm;
     uint32_t *lens = (uint32_t *)(bsm + LENS);
+    if (k.n_vec <= 64u) {
+      for (uint32_t i = tid; i < 2u * k.n_vec; i += nthreads) ((uint64_t *)(bsm + HDRS))[i] = fls_ldg((const uint64_t *)k.seg[0] + i);
+      for (uint32_t i = tid; i <= k.n_vec; i += nthreads) ((uint32_t *)(bsm + VEP))[i] = fls_ldg((const uint32_t *)k.seg[4] + i);
+    }
     const uint32_t *doff = (const uint32_t *)k.seg[2];
     const uint8_t *dbytes = k.seg[3];
     const uint32_t n_dict = k.aux32;
@@ -223,8 +248,7 @@ struct VecSTRDICT {
       for (uint32_t i = 0; i < SPB; ++i)
 #pragma unroll
         for (uint32_t pc = 0; pc < P; ++pc) e[i * P + pc] = fls_lds128<fls_u4>(tab + 16u * (d[s0 + i] * P + pc));
-#pragma unroll
-      for (uint32_t i = 0; i < SPB * P; ++i) p.push(e[i]);
+      p.push_all(e);
     }
   }
   // every entry has the same length U in {1, 2, 4}: the lane's 8 strings are 8U bytes, merged in registers into
@@ -276,14 +300,23 @@ struct VecSTRDICT {
     fls_st128(o, a);
     fls_st128(o + 4, b);
   }
-  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *bsm) {
-    const fls_vechdr h = fls_load_hdr(k, 0, v);
+  FLS_MEM static fls_vechdr header(const FlsChunkDev &k, const uint8_t *bsm, uint32_t v) {
+    if (k.n_vec > 64u) return fls_load_hdr(k, 0, v);
+    const uint64_t *p = (const uint64_t *)(bsm + HDRS) + 2u * v;
+    fls_vechdr h;
+    h.ep = (uint32_t)p[0]; h.meta = (uint32_t)(p[0] >> 32); h.base = p[1];
+    return h;
+  }
+  // v_next: the vector this warp decodes next (FLS_NO_VECTOR if none): its index payload is bulk-copied into the
+  // other half of the index buffer while v is decoded
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, uint32_t v_next, FlsWarp &w, const uint8_t *bsm) {
+    const fls_vechdr h = header(k, bsm, v);
     uint32_t bw = FLS_META_BW(h.meta);
     if (bw > 32u) bw = 32u;
     const uint32_t *doff = (const uint32_t *)k.seg[2];
     const uint8_t *dbytes = k.seg[3];
     const uint32_t n_dict = k.aux32;
-    const uint32_t vec_ep = fls_ldg((const uint32_t *)k.seg[4] + v);
+    const uint32_t vec_ep = k.n_vec <= 64u ? ((const uint32_t *)(bsm + VEP))[v] : fls_ldg((const uint32_t *)k.seg[4] + v);
     const uint32_t P = ((const uint32_t *)bsm)[0];
     const uint32_t maxlen = ((const uint32_t *)bsm)[1], minlen = ~((const uint32_t *)bsm)[2];
     // every entry has the same length 1, 2 or 4: offsets are arithmetic, strings merge into 8-byte pieces
@@ -291,8 +324,23 @@ struct VecSTRDICT {
     const uint32_t *lens = (const uint32_t *)(bsm + LENS);
     const uint8_t *tab = bsm + TAB;
     uint8_t *stg = w.sm;
-    const uint8_t *idx = w.sm + IDX;
-    if (bw) { w.fence_async(); w.stage(IDX, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
+    uint32_t ioff = IDX;  // where this vector's index payload is (half 0, half 1, or the whole buffer)
+    if (w.pf_v == v) { ioff = w.pf_off; w.wait(); }
+    else if (w.pf_v != FLS_NO_VECTOR) { w.wait(); w.pf_v = FLS_NO_VECTOR; }  // drain a copy nobody will use
+    if (ioff != IDX || w.pf_v == v) { /* payload already staged */ }
+    else if (bw) { w.fence_async(); w.stage(IDX, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
+    w.pf_v = FLS_NO_VECTOR;
+    if (v_next != FLS_NO_VECTOR && 128u * bw <= 2048u) {
+      const fls_vechdr hn = header(k, bsm, v_next);
+      const uint32_t bwn = FLS_META_BW(hn.meta);
+      if (bwn && 128u * bwn <= 2048u) {
+        w.pf_v = v_next;
+        w.pf_off = ioff == IDX ? IDX + 2048u : IDX;
+        w.fence_async();
+        w.stage(w.pf_off, k.seg[1] + 16ull * hn.ep, 128u * bwn);
+      }
+    }
+    const uint8_t *idx = w.sm + ioff;
     uint8_t *pay = k.pay + k.pay_base;
     uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i, offs[i + 1] = its end
     uint32_t qpos = vec_ep;  // payload offset (row-group relative) of the quarter's first byte
@@ -375,23 +423,25 @@ struct VecSTRDICT {
 struct VecSTRFSST {
   static constexpr uint32_t WARPS = 8;
   static constexpr uint32_t STG = 11264u;    // staging of one quarter's output; phase 1: the two staged offset streams
-  static constexpr uint32_t CWIN = 4096u;    // compressed bytes of one quarter; two windows (the next quarter loads
-                                             // while this one is decoded)
+  static constexpr uint32_t CWIN = 4096u;    // compressed bytes of one quarter
   static constexpr uint32_t E16N = 1056u;    // 16-bit relative end of every string, padded original order (x2)
-  static constexpr uint32_t SMEM = STG + 2u * CWIN + 4u * E16N + 256u;  // 23936 = 187 * 128
-  // 512 entries (256 codes, 256 escaped literals) x 4 copies x 16 B; entry e of copy r at e*64 + r*16
-  static constexpr uint32_t BLOCK_SMEM = 32768u;
+  static constexpr uint32_t SMEM = STG + CWIN + 4u * E16N + 256u;  // 19840 = 155 * 128
+  // 512 entries (code * 2 + escaped) x 8 copies x 16 B, entry i of copy r at i*128 + r*16: a lane reads copy
+  // t & 7, so the eight lanes of a 128-bit load phase never share a bank group
+  static constexpr uint32_t BLOCK_SMEM = 65536u;
+  static constexpr bool PIPELINED = true;
   static_assert(2u * 4224u <= STG, "phase-1 buffers must fit the staging buffer");
   static_assert(SMEM % 128u == 0, "warp slots stay 128-byte aligned");
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
     const uint64_t *sym = (const uint64_t *)k.seg[4];
     const uint8_t *len = k.seg[4] + 2048;
-    for (uint32_t e = tid; e < 512u; e += nthreads) {
+    for (uint32_t i = tid; i < 512u; i += nthreads) {  // i = code * 2 + (escaped literal ? 1 : 0)
+      const uint32_t c = i >> 1;
       fls_u4 en;
-      if (e == 255u) { en.x = en.y = en.z = en.w = 0u; }  // the escape marker itself produces nothing
-      else if (e < 256u) en = fls_piece_entry(fls_ldg(sym + e), fls_min(8u, (uint32_t)fls_ldg(len + e)));
-      else en = fls_piece_entry(e - 256u, 1u);            // escaped byte e - 256: itself
-      for (uint32_t r = 0; r < 4u; ++r) *(fls_u4 *)(bsm + 64u * e + 16u * r) = en;
+      if (i & 1u) en = fls_piece_entry(c, 1u);                 // escaped byte c: itself
+      else if (c == 255u) { en.x = en.y = en.z = en.w = 0u; }  // the escape marker itself produces nothing
+      else en = fls_piece_entry(fls_ldg(sym + c), fls_min(8u, (uint32_t)fls_ldg(len + c)));
+      for (uint32_t r = 0; r < 8u; ++r) *(fls_u4 *)(bsm + 128u * i + 16u * r) = en;
     }
   }
   // 0x80 in every byte of x that equals 0xFF (exact, byte by byte)
@@ -399,63 +449,80 @@ struct VecSTRFSST {
     const uint32_t y = ~x;  // zero byte <=> 0xFF
     return ~(((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y) & 0x80808080u;
   }
-  // Eight consecutive compressed bytes (lo, hi) of a lane's run: eight table loads in flight, then eight pushes,
-  // straight-line.  The table index of byte j is its value, plus 256 when the byte is an escaped literal.  Which
-  // bytes are literals is worked out for the whole window at once: byte j is a literal when byte j-1 is an escape
-  // marker (0xFF); with `lit` = the previous window ended in a marker.  That is exact unless two 0xFF bytes are
-  // adjacent (a literal 0xFF); such a window takes the byte-by-byte path.  MASK: only bytes [s, e) of the window
-  // belong to the run (partial first / last window); the others are turned into markers that escape nothing.
-  template <bool MASK>
-  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, uint32_t lo, uint32_t hi, uint32_t s, uint32_t e, bool &lit) {
-    uint32_t fflo = ff_bytes(lo), ffhi = ff_bytes(hi);
+  // NW/2 x eight consecutive compressed bytes (32-bit words w[]) of a lane's run: all table loads in flight, then
+  // all pushes, straight-line.  The table index of byte j is 2 * value + (byte j is an escaped literal).  Byte j is
+  // a literal when byte j-1 is an escape marker (0xFF), `lit` standing for byte -1; that is exact unless two 0xFF
+  // bytes are adjacent (a literal 0xFF), and such a window takes the byte-by-byte path.  The literal flag of byte j
+  // belongs at bit 8j-1, which is the top bit of byte j-1: with the top bits of the odd (even) bytes replaced by
+  // their marker flags, the 9 bits [8j-1, 8j+8) ARE the table index of an even (odd) byte j — one shift and one
+  // mask per byte.  MASK: only bytes [s, e) of the window belong to the run (partial first / last window); the
+  // others are turned into markers that escape nothing.
+  template <uint32_t NW, bool MASK>
+  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, uint32_t (&w)[NW], uint32_t s, uint32_t e, bool &lit) {
+    uint32_t ff[NW];
+#pragma unroll
+    for (uint32_t k = 0; k < NW; ++k) ff[k] = ff_bytes(w[k]);
     if (MASK) {
-      uint64_t vm = e >= 8u ? ~0ull : ((1ull << (8u * e)) - 1ull);
-      vm &= ~0ull << (8u * s);
-      const uint32_t vlo = (uint32_t)vm, vhi = (uint32_t)(vm >> 32);
-      fflo &= vlo; ffhi &= vhi;
-      lo |= ~vlo; hi |= ~vhi;  // 0xFF and not a marker: the empty entry
+#pragma unroll
+      for (uint32_t k = 0; k < NW; ++k) {
+        const uint32_t ek = e > 4u * k ? fls_min(4u, e - 4u * k) : 0u, sk = s > 4u * k ? fls_min(4u, s - 4u * k) : 0u;
+        const uint32_t vm = (ek >= 4u ? ~0u : ((1u << (8u * ek)) - 1u)) & ~(sk >= 4u ? ~0u : ((1u << (8u * sk)) - 1u));
+        ff[k] &= vm;
+        w[k] |= ~vm;  // 0xFF and not a marker: the empty entry
+      }
     }
-    const uint32_t llo = (fflo << 8) | (lit ? 0x80u : 0u), lhi = (ffhi << 8) | (fflo >> 24);  // 0x80 per literal byte
-    if (((fflo & llo) | (ffhi & lhi)) != 0u) {
+    const uint32_t c7 = lit ? 0x80u : 0u;
+    uint32_t adj = ((ff[0] << 8) | c7) & ff[0];
+#pragma unroll
+    for (uint32_t k = 1; k < NW; ++k) adj |= ((ff[k] << 8) | (ff[k - 1u] >> 24)) & ff[k];
+    if (adj) {
       // adjacent 0xFF bytes: byte by byte
-      for (uint32_t j = 0; j < 8u; ++j) {
+      for (uint32_t j = 0; j < 4u * NW; ++j) {
         if (MASK && (j < s || j >= e)) continue;
-        const uint32_t c = ((j < 4u ? lo : hi) >> (8u * (j & 3u))) & 0xFFu;
-        if (lit) { p.push(fls_lds128<fls_u4>(tabr + 64u * (256u + c))); lit = false; }
+        const uint32_t c = (w[j >> 2] >> (8u * (j & 3u))) & 0xFFu;
+        if (lit) { p.push(fls_lds128<fls_u4>(tabr + 128u * (2u * c + 1u))); lit = false; }
         else if (c == 255u) lit = true;
-        else p.push(fls_lds128<fls_u4>(tabr + 64u * c));
+        else p.push(fls_lds128<fls_u4>(tabr + 256u * c));
       }
       return;
     }
-    lit = (ffhi >> 31) != 0u;
-    uint32_t ad[8];
+    lit = (ff[NW - 1u] >> 31) != 0u;
+    uint32_t ad[4u * NW];  // index * 128
 #pragma unroll
-    for (uint32_t j = 0; j < 8u; ++j) {
-      const uint32_t wv = j < 4u ? lo : hi, lv = j < 4u ? llo : lhi, sh = 8u * (j & 3u);
-      const uint32_t cb = sh >= 6u ? (wv >> (sh - 6u)) : (wv << (6u - sh));  // byte j * 64 at bits [6, 14)
-      const uint32_t lb = sh + 7u >= 14u ? (lv >> (sh + 7u - 14u)) : (lv << (14u - sh - 7u));  // its literal flag at bit 14
-      ad[j] = (cb & 0x3FC0u) | (lb & 0x4000u);
+    for (uint32_t k = 0; k < NW; ++k) {
+      // E: odd bytes carry their marker flag in the top bit (index of the even bytes); O: the other way round
+      const uint32_t E = (w[k] & 0x7FFF7FFFu) | (ff[k] & 0x80008000u), O = (w[k] & 0xFF7FFF7Fu) | (ff[k] & 0x00800080u);
+      const uint32_t below = k ? ((w[k - 1u] & 0x7FFFFFFFu) | (ff[k - 1u] & 0x80000000u)) : 0u;  // E of the word before
+      ad[4u * k] = (k ? fls_shf_r(below, E, 24u) : ((E << 8) | c7)) & 0xFF80u;
+      ad[4u * k + 1u] = O & 0xFF80u;
+      ad[4u * k + 2u] = (E >> 8) & 0xFF80u;
+      ad[4u * k + 3u] = (O >> 16) & 0xFF80u;
     }
-    fls_u4 en[8];
+    fls_u4 en[4u * NW];
 #pragma unroll
-    for (uint32_t j = 0; j < 8u; ++j) en[j] = fls_lds128<fls_u4>(tabr + ad[j]);
-#pragma unroll
-    for (uint32_t j = 0; j < 8u; ++j) p.push(en[j]);
+    for (uint32_t j = 0; j < 4u * NW; ++j) en[j] = fls_lds128<fls_u4>(tabr + ad[j]);
+    p.push_all(en);
   }
-  // A lane's compressed run = bytes [a, b) of the staged window `cwin`, read 8 bytes at a time.
+  // A lane's compressed run = bytes [a, b) of the staged window `cwin`, read 16 bytes at a time (8 at the end).
   FLS_MEM static void decode_run(FlsPush &p, const uint8_t *tabr, const uint8_t *cwin, uint32_t a, uint32_t b) {
     const uint32_t *cw = (const uint32_t *)cwin;
     bool lit = false;
-    uint32_t i = a >> 3;
-    uint32_t lo = cw[2u * i], hi = cw[2u * i + 1u];
-    for (; 8u * i < b; ++i) {
-      // next window's words first (the window has 16 bytes of slack, so this never leaves it)
-      const uint32_t nlo = cw[2u * i + 2u], nhi = cw[2u * i + 3u];
-      const bool partial = 8u * i < a || 8u * i + 8u > b;
+    uint32_t i = a >> 3;  // 8-byte unit
+    while (8u * i < b) {
+      uint32_t w[4];
+      w[0] = cw[2u * i]; w[1] = cw[2u * i + 1u];
+      const uint32_t s = 8u * i < a ? a - 8u * i : 0u, left = b - 8u * i;
       // the variant is chosen by a vote of the lanes still in the loop, so they stay converged
-      if (FLS_ANY(partial)) window<true>(p, tabr, lo, hi, 8u * i < a ? a - 8u * i : 0u, fls_min(8u, b - 8u * i), lit);
-      else window<false>(p, tabr, lo, hi, 0u, 8u, lit);
-      lo = nlo; hi = nhi;
+      if (FLS_ANY(left > 8u)) {
+        w[2] = cw[2u * i + 2u]; w[3] = cw[2u * i + 3u];  // the window has 16 bytes of slack
+        if (FLS_ANY(s != 0u || left < 16u)) window<4, true>(p, tabr, w, s, fls_min(16u, left), lit);
+        else window<4, false>(p, tabr, w, 0u, 16u, lit);
+        i += 2u;
+      } else {
+        uint32_t w2[2] = {w[0], w[1]};
+        window<2, true>(p, tabr, w2, s, fls_min(8u, left), lit);
+        i += 1u;
+      }
     }
   }
   // Slow path (compressed bytes larger than the window, output larger than the staging buffer, offsets that do
@@ -500,13 +567,13 @@ struct VecSTRFSST {
   FLS_MEM static uint32_t slot16(uint32_t e) { return e + ((e >> 6) << 1); }
   // start offset (relative) of string s: the end of string s - 1
   FLS_MEM static uint32_t start16(const uint16_t *e16, uint32_t s) { return s ? (uint32_t)e16[slot16(s - 1u)] : 0u; }
-  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *tab) {
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, uint32_t /*v_next*/, FlsWarp &w, const uint8_t *tab) {
     const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
     uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
     if (bwd > 32u) bwd = 32u;
     if (bwc > 32u) bwc = 32u;
     uint8_t *stg = w.sm;
-    uint16_t *DE = (uint16_t *)(w.sm + STG + 2u * CWIN), *CE = DE + E16N;
+    uint16_t *DE = (uint16_t *)(w.sm + STG + CWIN), *CE = DE + E16N;
     uint32_t *LS = (uint32_t *)(CE + E16N);  // LS[0..32] = first string of each lane, LS[34..37] = vector extents
     const uint8_t *comp = k.seg[5];
     uint8_t *pay = k.pay + k.pay_base;
@@ -534,25 +601,17 @@ struct VecSTRFSST {
     }
     // ---- phase 2: quarter by quarter (256 strings); the quarter's compressed bytes are split into 32 runs of
     //      (nearly) equal length that start on string boundaries, one per lane; the compressed bytes of quarter
-    //      q+1 are bulk-copied into the other window while quarter q is decoded
+    //      q+1 are bulk-copied into the window as soon as quarter q has been read, while q is copied out
     uint32_t qc0 = 0, qc1 = start16(CE, 256u);  // compressed extent of the quarter, relative to cv0
     uint32_t wbase = cv0 & ~15u;
     uint32_t span = cv0 + qc1 - wbase;
     bool windowed = span + 16u <= CWIN;
+    const uint8_t *cwin = w.sm + STG;
     if (windowed && span) { w.fence_async(); w.stage(STG, comp + wbase, (span + 15u) & ~15u); }
     for (uint32_t qt = 0; qt < 4u; ++qt) {
       if (windowed && span) w.wait();
-      const uint8_t *cwin = w.sm + STG + (qt & 1u) * CWIN;
       const uint32_t cur_wbase = wbase, cur_c0 = qc0, cur_c1 = qc1;
       const bool cur_windowed = windowed;
-      if (qt < 3u) {  // next quarter's window
-        qc0 = qc1;
-        qc1 = start16(CE, 256u * qt + 512u);
-        wbase = (cv0 + qc0) & ~15u;
-        span = cv0 + qc1 - wbase;
-        windowed = span + 16u <= CWIN;
-        if (windowed && span) { w.fence_async(); w.stage(STG + ((qt + 1u) & 1u) * CWIN, comp + wbase, (span + 15u) & ~15u); }
-      }
       const uint32_t S0 = 256u * qt, S1 = S0 + 256u;
       const uint32_t qd0 = start16(DE, S0), qlen = start16(DE, S1) - qd0;
       uint8_t *g = pay + dv0 + qd0;
@@ -578,11 +637,19 @@ struct VecSTRFSST {
         if (staged) {
           FlsPush p;
           p.init(stg, hh + (d0 - qd0));
-          if (c1 > c0) decode_run(p, tab + 16u * (t & 3u), cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
+          if (c1 > c0) decode_run(p, tab + 16u * (t & 7u), cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
           FLS_AT(ps) = p;
         } else {
           decode_bytes(k, cv0 + c0, cv0 + c1, pay + dv0 + d0);
         }
+      }
+      if (qt < 3u) {  // next quarter's window
+        qc0 = qc1;
+        qc1 = start16(CE, 256u * qt + 512u);
+        wbase = (cv0 + qc0) & ~15u;
+        span = cv0 + qc1 - wbase;
+        windowed = span + 16u <= CWIN;
+        if (windowed && span) { w.fence_async(); w.stage(STG, comp + wbase, (span + 15u) & ~15u); }
       }
       if (staged) {
         FLS_LANES(t) { FLS_AT(ps).finish(); }

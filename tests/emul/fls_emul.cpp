@@ -8,6 +8,7 @@
 #define FLS_HOST_EMUL 1
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "fls_plan.h"
@@ -16,16 +17,25 @@
 static std::string g_err;
 int fls_emul_force_any = 0;
 
+template <class V, class = void> struct is_pipelined { static constexpr bool value = false; };
+template <class V> struct is_pipelined<V, std::enable_if_t<V::PIPELINED>> { static constexpr bool value = true; };
+
 template <class V> static void run_vectors(const FlsLaunch &l) {
   std::vector<uint8_t> smem(V::SMEM + V::BLOCK_SMEM + 256);
   uint8_t *slot = (uint8_t *)(((uintptr_t)smem.data() + 127) & ~(uintptr_t)127);
   uint8_t *bsm = slot + V::SMEM;
   for (const FlsChunkDev &k : l.chunks) {
     if constexpr (V::BLOCK_SMEM != 0) V::block_init(k, bsm, 0, 1);
-    for (uint32_t v = 0; v < k.n_vec; ++v) {
-      FlsWarp w;
+    if constexpr (is_pipelined<V>::value) {
+      FlsWarp w;  // one warp decodes the chunk's vectors in order, each call prefetching the next vector
       w.init(slot, nullptr);
-      V::run(k, v, w, bsm);
+      for (uint32_t v = 0; v < k.n_vec; ++v) V::run(k, v, v + 1 < k.n_vec ? v + 1 : FLS_NO_VECTOR, w, bsm);
+    } else {
+      for (uint32_t v = 0; v < k.n_vec; ++v) {
+        FlsWarp w;
+        w.init(slot, nullptr);
+        V::run(k, v, w, bsm);
+      }
     }
   }
 }
