@@ -48,6 +48,17 @@ def parse_args():
     return ap.parse_args()
 
 
+def measured_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
+    capture of this same command (profiles/traffic.json, written from the .ncu-rep by profiles/ncu_summary.py);
+    None if no capture of that kernel at this workload size is on record."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return t.get(kernel)
+    except Exception:
+        return None
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -276,7 +287,9 @@ def run_ours(args, rank, world, local, dist):
         ach = per_launch / (top["ms"] / top["launches"] * 1e-3) / GB
         tot_ms = sum(s["ms"] for s in kstats)
         roof = {"bound": "hbm", "kernel": top["name"], "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": per_launch,
+                "traffic": (measured_traffic(top["name"]) or {}).get("dram_bytes_per_launch")
+                if n_rg == (measured_traffic(top["name"]) or {}).get("rowgroups") else None,
+                "peak_source": peak_src, "algorithmic_bytes_per_launch": per_launch,
                 "share_of_step": top["ms"] / tot_ms, "serialised_ms_per_step": ser_ms / args.steps,
                 "whole_step": {"achieved": (dec_bytes + cmp_bytes) / (ev_ms / args.steps * 1e-3) / GB,
                                "frac": (dec_bytes + cmp_bytes) / (ev_ms / args.steps * 1e-3) / GB / peak},
