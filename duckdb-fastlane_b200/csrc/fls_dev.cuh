@@ -59,6 +59,7 @@ static inline uint32_t fls_min(uint32_t a, uint32_t b) { return a < b ? a : b; }
 static inline uint32_t fls_max(uint32_t a, uint32_t b) { return a > b ? a : b; }
 static inline void fls_smem_max(uint32_t *p, uint32_t v) { if (v > *p) *p = v; }
 #define FLS_BLOCK_SYNC() ((void)0)
+#define FLS_GROUP_SYNC(nthreads) ((void)(nthreads))
 extern int fls_emul_force_any; /* tests: make every vote succeed, i.e. every lane takes the most general variant */
 #define FLS_ANY(x) ((x) || fls_emul_force_any) /* warp vote among the converged lanes: any variant it selects is correct for every lane */
 // Exclusive prefix sum of a FLS_VAR(uint32_t, n) across the warp's lanes; `total` (warp-uniform) receives the sum.
@@ -94,6 +95,8 @@ FLS_DEV uint32_t fls_min(uint32_t a, uint32_t b) { return min(a, b); }
 FLS_DEV uint32_t fls_max(uint32_t a, uint32_t b) { return max(a, b); }
 FLS_DEV void fls_smem_max(uint32_t *p, uint32_t v) { atomicMax(p, v); }
 #define FLS_BLOCK_SYNC() __syncthreads()
+// barrier of a group of `nthreads` threads that all call it: one warp (32) or the whole block
+#define FLS_GROUP_SYNC(nthreads) do { if ((nthreads) == 32u) __syncwarp(); else __syncthreads(); } while (0)
 #define FLS_ANY(x) (__any_sync(__activemask(), (x)) != 0)
 #define FLS_EXCL_SCAN(n, total)                                                   \
   do {                                                                            \

@@ -109,37 +109,85 @@ __global__ void __launch_bounds__(FLS_WARPS_PER_BLOCK * 32) fls_vec_kernel(const
   V::run(k, v, w, bsm);
 }
 
-// String columns with a per-chunk lookup table (DICT, FSST): blocks of V::WARPS warps; block b owns vectors
-// [bx*vpb, (bx+1)*vpb) of chunk b / bpc, builds the chunk's table once (V::block_init) and its warps take the
-// vectors one at a time from a shared counter.
-// Shared memory: [warp slots | block-shared (V::BLOCK_SMEM) | mbarriers | vector counter]
+// String columns with a per-chunk lookup table (DICT, FSST): a PERSISTENT grid of (at most) one block per SM.
+// The launch's vectors are numbered chunk-major (FLS_RG_VECS slots per chunk) and block b owns the contiguous
+// slot range [S*b/G, S*(b+1)/G): every block gets the same number of vectors (+-1) whatever the number of
+// chunks, so there is no wave quantisation.  A block's range is a sequence of SEGMENTS (chunk, vector range);
+// a segment needs its chunk's lookup table (V::block_init).  The block keeps V::NBUF table buffers; segment s
+// uses buffer s % NBUF.  Warps take vectors from the segment's shared counter and never meet at a block-wide
+// barrier after the prologue: the warp that retires LAST from segment s (an atomic count) is by construction
+// the only one still touching that buffer, so it builds the table of segment s + NBUF in place and publishes
+// it (ready[buf] = s + NBUF + 1); warps arriving at a segment spin on its ready word.  With NBUF = 2 the table
+// of the next segment is always there already and nobody waits; with NBUF = 1 (a table too large to double)
+// the others wait for the last warp's vector + one table build per segment.
+// Shared memory: [warp slots | constant area (V::CONST_SMEM) | NBUF tables (V::BLOCK_SMEM) | mbarriers | control]
 template <class V> constexpr uint32_t fls_chunk_smem() {
-  return V::WARPS * V::SMEM + V::BLOCK_SMEM + V::WARPS * 8u + 16u;
+  return V::WARPS * V::SMEM + V::CONST_SMEM + V::NBUF * V::BLOCK_SMEM + V::WARPS * 8u + 64u;
 }
 template <class V>
-__global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t bpc) {
+__global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t n_chunks) {
   extern __shared__ __align__(128) uint8_t fls_smem[];
-  const FlsChunkDev &k = chunks[blockIdx.x / bpc];
-  const uint32_t bx = blockIdx.x % bpc, vpb = (k.n_vec + bpc - 1u) / bpc;
-  const uint32_t v0 = bx * vpb, v1 = min(k.n_vec, v0 + vpb);
-  if (v0 >= v1) return;
-  const uint32_t warp = threadIdx.x >> 5;
-  uint8_t *bsm = fls_smem + V::WARPS * V::SMEM;
-  uint32_t *next = (uint32_t *)(bsm + V::BLOCK_SMEM + V::WARPS * 8u);
-  if (threadIdx.x == 0) *next = v0;
-  V::block_init(k, bsm, threadIdx.x, V::WARPS * 32u);
+  constexpr uint32_t NB = V::NBUF;
+  const uint32_t S = n_chunks * FLS_RG_VECS;
+  const uint32_t G0 = (uint32_t)((uint64_t)S * blockIdx.x / gridDim.x), G1 = (uint32_t)((uint64_t)S * (blockIdx.x + 1u) / gridDim.x);
+  if (G0 >= G1) return;
+  const uint32_t c0 = G0 / FLS_RG_VECS, nseg = (G1 - 1u) / FLS_RG_VECS - c0 + 1u;
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+  uint8_t *csm = fls_smem + V::WARPS * V::SMEM;
+  uint8_t *tabs = csm + V::CONST_SMEM;
+  uint64_t *mbar = (uint64_t *)(tabs + NB * V::BLOCK_SMEM);
+  uint32_t *next = (uint32_t *)(mbar + V::WARPS);  // next[NB]: vector counter of the segment in each buffer
+  uint32_t *done = next + NB;                      // done[NB]: warps that have retired from it
+  volatile uint32_t *ready = done + NB;            // ready[NB]: 1 + the segment whose table the buffer holds
+  auto seg_lo = [&](uint32_t s) { const uint32_t b0 = (c0 + s) * FLS_RG_VECS; return max(G0, b0) - b0; };
+  auto seg_hi = [&](uint32_t s) { const uint32_t b0 = (c0 + s) * FLS_RG_VECS; return min(min(G1, b0 + FLS_RG_VECS) - b0, chunks[c0 + s].n_vec); };
+  // prologue: the first NB tables, built by the whole block
+  V::const_init(csm, threadIdx.x, V::WARPS * 32u);
+  for (uint32_t s = 0; s < NB && s < nseg; ++s) V::block_init(chunks[c0 + s], tabs + s * V::BLOCK_SMEM, threadIdx.x, V::WARPS * 32u);
+  if (threadIdx.x < NB) {
+    next[threadIdx.x] = threadIdx.x < nseg ? seg_lo(threadIdx.x) : 0u;
+    done[threadIdx.x] = 0u;
+    ready[threadIdx.x] = threadIdx.x + 1u;
+  }
   __syncthreads();
   FlsWarp w;
-  w.init(fls_smem + warp * V::SMEM, (uint64_t *)(bsm + V::BLOCK_SMEM) + warp);
-  auto grab = [&]() {
-    uint32_t x = 0;
-    if ((threadIdx.x & 31u) == 0) x = atomicAdd(next, 1u);
-    return __shfl_sync(0xFFFFFFFFu, x, 0);
-  };
-  for (uint32_t v = grab(); v < v1;) {  // one vector ahead, so that run() can prefetch the next one's payload
-    const uint32_t vn = grab();
-    V::run(k, v, vn < v1 ? vn : FLS_NO_VECTOR, w, bsm);
-    v = vn;
+  w.init(fls_smem + warp * V::SMEM, mbar + warp);
+  for (uint32_t s = 0; s < nseg; ++s) {
+    const uint32_t b = s % NB;
+    const FlsChunkDev &k = chunks[c0 + s];
+    const uint8_t *bsm = tabs + b * V::BLOCK_SMEM;
+    const uint32_t v1 = seg_hi(s);
+    if (s >= NB) {
+      while (ready[b] != s + 1u) __nanosleep(32);
+      __threadfence_block();
+      __syncwarp();
+    }
+    auto grab = [&]() {
+      uint32_t x = 0;
+      if (lane == 0) x = atomicAdd(next + b, 1u);
+      return __shfl_sync(0xFFFFFFFFu, x, 0);
+    };
+    for (uint32_t v = grab(); v < v1;) {  // one vector ahead, so that run() can prefetch the next one's payload
+      const uint32_t vn = grab();
+      V::run(k, v, vn < v1 ? vn : FLS_NO_VECTOR, w, bsm, csm);
+      v = vn;
+    }
+    if (s + NB < nseg) {  // block-uniform: somebody has to build the table of segment s + NB in this buffer
+      __syncwarp();
+      uint32_t last = 0;
+      if (lane == 0) {
+        __threadfence_block();
+        last = atomicAdd(done + b, 1u) == V::WARPS - 1u ? 1u : 0u;
+      }
+      if (__shfl_sync(0xFFFFFFFFu, last, 0)) {
+        __threadfence_block();
+        V::block_init(chunks[c0 + s + NB], tabs + b * V::BLOCK_SMEM, lane, 32u);
+        if (lane == 0) { next[b] = seg_lo(s + NB); done[b] = 0u; }
+        __threadfence_block();
+        __syncwarp();
+        if (lane == 0) ready[b] = s + NB + 1u;
+      }
+    }
   }
 }
 

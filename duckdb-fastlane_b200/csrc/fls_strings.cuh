@@ -193,15 +193,20 @@ FLS_DEV void fls_walk32(const uint8_t *stage, uint32_t bw, uint32_t base, uint32
 struct VecSTRDICT {
   static constexpr uint32_t WARPS = 16;
   static constexpr uint32_t STG = 8448u;     // staging of one quarter's payload (33 bytes per string on average)
-  static constexpr uint32_t IDX = STG;       // staged index payload, <= 128 * 32 bytes
-  static constexpr uint32_t SMEM = STG + 4096u;
+  // staged index payload: two halves of HALF bytes (this vector's and the prefetched next one's, widths <= 10 bits),
+  // or one vector's payload up to 20 bits wide, or — wider still — the packed rows of one quarter at a time
+  static constexpr uint32_t IDX = STG, HALF = 1280u;
+  static constexpr uint32_t SMEM = STG + 2u * HALF;
   // block-shared: [hdr 16 B: u32 pieces, u32 maxlen, u32 ~minlen][lens u32 x 1024][pieces: n_dict x P x 16 B]
   static constexpr uint32_t CACHE_ENTRIES = 1024u, TAB_BYTES = 16384u;
   static constexpr uint32_t LENS = 16u, TAB = LENS + 4u * CACHE_ENTRIES;
   // ... [vector headers 64 x 16 B][vec_ep u32 x 65]: read once per block instead of once per vector from HBM
   static constexpr uint32_t HDRS = TAB + TAB_BYTES, VEP = HDRS + 64u * 16u;
   static constexpr uint32_t BLOCK_SMEM = VEP + 68u * 4u;
+  static constexpr uint32_t NBUF = 2, CONST_SMEM = 0;  // two tables per block: the next chunk's is built ahead
   static constexpr bool PIPELINED = true;
+  FLS_MEM static void const_init(uint8_t *, uint32_t, uint32_t) {}
+  // called by all `nthreads` threads of a group (a whole block, or ONE warp: nthreads == 32)
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
     uint32_t *hdr = (uint32_t *)bsm;
     uint32_t *lens = (uint32_t *)(bsm + LENS);
@@ -213,7 +218,7 @@ struct VecSTRDICT {
     const uint8_t *dbytes = k.seg[3];
     const uint32_t n_dict = k.aux32;
     if (tid == 0) { hdr[0] = 0; hdr[1] = 0; hdr[2] = 0; }
-    FLS_BLOCK_SYNC();
+    FLS_GROUP_SYNC(nthreads);
     if (n_dict > CACHE_ENTRIES) return;  // uniform over the block: P stays 0 = "not cached"
     uint32_t m = 0, mn = 0xFFFFFFFFu;
     for (uint32_t i = tid; i < n_dict; i += nthreads) {
@@ -224,7 +229,7 @@ struct VecSTRDICT {
     }
     fls_smem_max(hdr + 1, m);
     fls_smem_max(hdr + 2, ~mn);  // max of the complement = complement of the min
-    FLS_BLOCK_SYNC();
+    FLS_GROUP_SYNC(nthreads);
     const uint32_t P = (hdr[1] + 7u) >> 3;
     if (P == 0 || n_dict * P * 16u > TAB_BYTES) return;
     for (uint32_t i = tid; i < n_dict * P; i += nthreads) {
@@ -309,7 +314,7 @@ struct VecSTRDICT {
   }
   // v_next: the vector this warp decodes next (FLS_NO_VECTOR if none): its index payload is bulk-copied into the
   // other half of the index buffer while v is decoded
-  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, uint32_t v_next, FlsWarp &w, const uint8_t *bsm) {
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, uint32_t v_next, FlsWarp &w, const uint8_t *bsm, const uint8_t *) {
     const fls_vechdr h = header(k, bsm, v);
     uint32_t bw = FLS_META_BW(h.meta);
     if (bw > 32u) bw = 32u;
@@ -325,17 +330,18 @@ struct VecSTRDICT {
     const uint8_t *tab = bsm + TAB;
     uint8_t *stg = w.sm;
     uint32_t ioff = IDX;  // where this vector's index payload is (half 0, half 1, or the whole buffer)
+    const bool by_quarter = 128u * bw > 2u * HALF;  // too wide for the buffer: the packed rows of one quarter at a time
     if (w.pf_v == v) { ioff = w.pf_off; w.wait(); }
     else if (w.pf_v != FLS_NO_VECTOR) { w.wait(); w.pf_v = FLS_NO_VECTOR; }  // drain a copy nobody will use
     if (ioff != IDX || w.pf_v == v) { /* payload already staged */ }
-    else if (bw) { w.fence_async(); w.stage(IDX, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
+    else if (bw && !by_quarter) { w.fence_async(); w.stage(IDX, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
     w.pf_v = FLS_NO_VECTOR;
-    if (v_next != FLS_NO_VECTOR && 128u * bw <= 2048u) {
+    if (v_next != FLS_NO_VECTOR && 128u * bw <= HALF) {
       const fls_vechdr hn = header(k, bsm, v_next);
       const uint32_t bwn = FLS_META_BW(hn.meta);
-      if (bwn && 128u * bwn <= 2048u) {
+      if (bwn && 128u * bwn <= HALF) {
         w.pf_v = v_next;
-        w.pf_off = ioff == IDX ? IDX + 2048u : IDX;
+        w.pf_off = ioff == IDX ? IDX + HALF : IDX;
         w.fence_async();
         w.stage(w.pf_off, k.seg[1] + 16ull * hn.ep, 128u * bwn);
       }
@@ -345,6 +351,14 @@ struct VecSTRDICT {
     uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i, offs[i + 1] = its end
     uint32_t qpos = vec_ep;  // payload offset (row-group relative) of the quarter's first byte
     for (uint32_t qt = 0; qt < 4u; ++qt) {
+      if (by_quarter) {
+        // the quarter's indices are rows 8qt .. 8qt+7 = 32-bit words [k0, k1] of every packed lane (<= 9 word rows)
+        const uint32_t k0 = (8u * qt * bw) >> 5, k1 = fls_min(((8u * qt + 8u) * bw - 1u) >> 5, bw - 1u);
+        w.fence_async();
+        w.stage(IDX, k.seg[1] + 16ull * h.ep + 128u * k0, 128u * (k1 - k0 + 1u));
+        w.wait();
+        idx = w.sm + IDX - 128u * k0;  // unpack8 addresses word rows absolutely; it reads rows k0 .. k1 only
+      }
       // 1. the lane's 8 indices and lengths (kept in registers), exclusive scan -> the lane's first output byte
       FLS_VAR(uint32_t, run);
       FLS_VAR2(uint32_t, dd, 8);
@@ -429,7 +443,9 @@ struct VecSTRFSST {
   // 512 entries (code * 2 + escaped) x 8 copies x 16 B, entry i of copy r at i*128 + r*16: a lane reads copy
   // t & 7, so the eight lanes of a 128-bit load phase never share a bank group
   static constexpr uint32_t BLOCK_SMEM = 65536u;
+  static constexpr uint32_t NBUF = 1, CONST_SMEM = 0;  // the table is too large to keep two
   static constexpr bool PIPELINED = true;
+  FLS_MEM static void const_init(uint8_t *, uint32_t, uint32_t) {}
   static_assert(2u * 4224u <= STG, "phase-1 buffers must fit the staging buffer");
   static_assert(SMEM % 128u == 0, "warp slots stay 128-byte aligned");
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
@@ -567,7 +583,7 @@ struct VecSTRFSST {
   FLS_MEM static uint32_t slot16(uint32_t e) { return e + ((e >> 6) << 1); }
   // start offset (relative) of string s: the end of string s - 1
   FLS_MEM static uint32_t start16(const uint16_t *e16, uint32_t s) { return s ? (uint32_t)e16[slot16(s - 1u)] : 0u; }
-  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, uint32_t /*v_next*/, FlsWarp &w, const uint8_t *tab) {
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, uint32_t /*v_next*/, FlsWarp &w, const uint8_t *tab, const uint8_t *) {
     const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
     uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
     if (bwd > 32u) bwd = 32u;

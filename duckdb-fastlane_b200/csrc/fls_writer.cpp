@@ -567,7 +567,7 @@ static Chunk enc_str_fsst(const uint8_t *bytes, const uint64_t *off, uint32_t n_
 }
 
 static bool enc_str_dict(const uint8_t *bytes, const uint64_t *off, uint32_t n_vec, uint32_t max_dict, bool fsst,
-                         Chunk &c) {
+                         Chunk &c, int force_bw = -1) {
   size_t n = (size_t)n_vec * FLS_VEC;
   std::map<std::string, uint32_t> m;
   for (size_t i = 0; i < n; ++i) {
@@ -587,7 +587,7 @@ static bool enc_str_dict(const uint8_t *bytes, const uint64_t *off, uint32_t n_v
       idx[j] = m[std::string((const char *)bytes + off[i], off[i + 1] - off[i])];
       run += off[i + 1] - off[i];
     }
-    ffor_vec<uint32_t>(s, idx.data());
+    ffor_vec<uint32_t>(s, idx.data(), 0, 0, 0, force_bw);
   }
   vec_ep[n_vec] = (uint32_t)run;
   c.aux64[0] = run;
@@ -617,13 +617,13 @@ static bool enc_str_dict(const uint8_t *bytes, const uint64_t *off, uint32_t n_v
   return true;
 }
 
-static Chunk enc_str_auto(const uint8_t *bytes, const uint64_t *off, uint32_t n_vec, int force) {
+static Chunk enc_str_auto(const uint8_t *bytes, const uint64_t *off, uint32_t n_vec, int force, int force_bw = -1) {
   size_t n = (size_t)n_vec * FLS_VEC;
   Chunk c;
   if (force == FLS_S_STR_UNCOMPRESSED) return enc_str_uncompressed(bytes, off, n_vec);
   if (force == FLS_S_STR_FSST) return enc_str_fsst(bytes, off, n_vec);
   if (force == FLS_S_STR_DICT || force == FLS_S_STR_FSST_DICT) {
-    if (enc_str_dict(bytes, off, n_vec, 1u << 20, force == FLS_S_STR_FSST_DICT, c)) return c;
+    if (enc_str_dict(bytes, off, n_vec, 1u << 20, force == FLS_S_STR_FSST_DICT, c, force_bw)) return c;
     return enc_str_fsst(bytes, off, n_vec);
   }
   bool all_same = true;
@@ -695,7 +695,7 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
         memcpy(off.data(), str_off[c], (size_t)(n_rows + 1) * 8);
         for (size_t i = n_rows + 1; i < off.size(); ++i) off[i] = off[n_rows];
         if (off[n_rows] - off[0] >= (1ull << 31)) { w.err = "row group string payload exceeds 2 GiB"; return 1; }
-        ch = enc_str_auto((const uint8_t *)col_data[c], off.data(), n_vec, f);
+        ch = enc_str_auto((const uint8_t *)col_data[c], off.data(), n_vec, f, w.force_bw[c]);
       }
     }
     if (ch.segs.size() > FLS_MAX_SEGS) { w.err = "internal: too many segments"; return 1; }

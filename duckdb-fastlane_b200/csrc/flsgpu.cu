@@ -36,11 +36,12 @@ template <class V> void vec_launch(const FlsChunkDev *d, uint32_t n, cudaStream_
 template <class V> cudaError_t chunk_attr() {
   return cudaFuncSetAttribute(fls_chunk_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fls_chunk_smem<V>());
 }
-// blocks per chunk: enough blocks to fill the GPU several times over when the batch has few chunks
+// persistent grid: one block per SM (fewer when the launch has fewer than two vectors per warp to hand out)
+int g_num_sms = 148;
 template <class V> void chunk_launch(const FlsChunkDev *d, uint32_t n, cudaStream_t s) {
-  uint32_t bpc = 1;
-  while (bpc < 4u && n * bpc < 148u * 12u) bpc *= 2u;  // at least a dozen waves of blocks: short tail
-  fls_chunk_kernel<V><<<n * bpc, V::WARPS * 32, fls_chunk_smem<V>(), s>>>(d, bpc);
+  const uint32_t slots = n * FLS_RG_VECS;
+  const uint32_t grid = std::max(1u, std::min((uint32_t)g_num_sms, slots / (2u * V::WARPS)));
+  fls_chunk_kernel<V><<<grid, V::WARPS * 32, fls_chunk_smem<V>(), s>>>(d, n);
 }
 template <template <typename> class V> cudaError_t vec_attr_all() {
   cudaError_t e;
@@ -226,6 +227,7 @@ int ensure_ready(flsgpu *h) {
   CK(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
   for (auto &sx : h->s_kx) CK(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
   CK(set_kernel_attrs());
+  CK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, h->device));
   if (!h->image) {  // opened by path: read the file into page-locked memory
     void *p = nullptr;
     const bool pin = !(h->flags & FLSGPU_OPEN_NO_PIN);

@@ -170,6 +170,14 @@ def string_cases(n=70_000):
     strs = [mixed[i] for i in r.integers(0, 3, 65536)] + [(b"XY", b"ZW")[i] for i in r.integers(0, 2, n - 65536 + 4000)]
     out.append(("str_dict_mixed_then_uniform", [StrColumn.from_list(strs)], None, [W.STR_DICT], None))
     out.append(("str_dict_entries_17_bytes", [li[13]], None, [W.STR_DICT], None))
+    # index widths beyond the prefetch halves (<= 10 bits): whole-buffer staging (<= 20) and quarter-wise staging
+    for bw in (11, 20, 21, 27, 32):
+        out.append(("str_dict_shipmode_index_bw%d" % bw, [shipmode], None, [W.STR_DICT], [bw]))
+    big = _rand_strings(r, 3000, 0, 12).to_list()
+    out.append(("str_dict_3000_entries", [StrColumn.from_list([big[i] for i in r.integers(0, len(big), n)])], None,
+                [W.STR_DICT], None))
+    out.append(("str_dict_3000_entries_bw23", [StrColumn.from_list([big[i] for i in r.integers(0, len(big), n)])], None,
+                [W.STR_DICT], [23]))
     # compressed bytes of one vector exceed the kernel's shared-memory window -> streaming fallback path
     out.append(("str_fsst_long_fallback", [_rand_strings(r, 9000, 60, 200)], None, [W.STR_FSST], None))
     out.append(("str_fsst_dict_long_entries", [StrColumn.from_list([pool2 for pool2 in

@@ -29,7 +29,7 @@ template <class V> static void run_vectors(const FlsLaunch &l) {
     if constexpr (is_pipelined<V>::value) {
       FlsWarp w;  // one warp decodes the chunk's vectors in order, each call prefetching the next vector
       w.init(slot, nullptr);
-      for (uint32_t v = 0; v < k.n_vec; ++v) V::run(k, v, v + 1 < k.n_vec ? v + 1 : FLS_NO_VECTOR, w, bsm);
+      for (uint32_t v = 0; v < k.n_vec; ++v) V::run(k, v, v + 1 < k.n_vec ? v + 1 : FLS_NO_VECTOR, w, bsm, nullptr);
     } else {
       for (uint32_t v = 0; v < k.n_vec; ++v) {
         FlsWarp w;
