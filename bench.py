@@ -117,6 +117,28 @@ def dist_setup(args):
     return rank, world, local, dist
 
 
+def bind_near_gpu(local):
+    """Run this rank on the CPUs next to its GPU (NVML's affinity mask for the device) BEFORE any pinned buffer is
+    allocated, so that the page-locked image and result buffers are first-touched on the GPU's own NUMA node
+    (SURVEY.md section 8e).  Best effort: returns the CPU list used, or None when NVML / the cgroup says otherwise."""
+    try:
+        import pynvml
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(("%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)).encode())
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (max(ncpu, 1024) + 63) // 64)
+        near = {i for i in range(64 * len(words)) if (words[i // 64] >> (i % 64)) & 1}
+        cpus = sorted(near & os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return cpus
+    except Exception:
+        pass
+    return None
+
+
 def make_image(args, rank, pinned):
     """The rank's shard: `rowgroups` row groups of lineitem-shaped data, in (optionally pinned) host memory."""
     import synth
@@ -175,7 +197,7 @@ def run_reference(args, rank, world, dist):
     dt = time.perf_counter() - t0
     val = nbytes / dt / GB
     desc = "%d row groups (%d rows) of the lineitem-shaped shard per step" % (sample, sample * RG_ROWS)
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": "read_fls decoded GB/s", "value": val, "unit": "GB/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "int64/f64/u8", "data": "synthetic",
@@ -193,6 +215,7 @@ def run_ours(args, rank, world, local, dist):
     assert torch.cuda.is_available(), "bench.py --impl ours needs a CUDA device (there is no CPU fallback)"
     torch.cuda.set_device(local)
     t_setup = time.time()
+    near = bind_near_gpu(local) if world > 1 else None
     img, keep = make_image(args, rank, pinned=True)
     setup_s = time.time() - t_setup
 
@@ -263,6 +286,7 @@ def run_ours(args, rank, world, local, dist):
     barrier()
     e2e_ms = allmax((time.perf_counter() - e0) * 1e3 / e2e_steps)   # wall clock: includes every host-side cost
     e2e_val = total_dec / (e2e_ms * 1e-3) / GB
+    e2e_dev_ms = allmax(e_ev_ms / e2e_steps)
     rd2.close()
 
     # ---------------- roofline of the dominant kernel: the same pass with a CUDA-event pair around every launch
@@ -320,7 +344,7 @@ def run_ours(args, rank, world, local, dist):
                          % (sample, sample * RG_ROWS, reps, cores, min(sample, 16))}
 
     if rank == 0:
-        print(json.dumps({
+        emit(({
             "metric": "read_fls decoded GB/s", "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int64/f64/u8", "data": "synthetic",
@@ -337,7 +361,8 @@ def run_ours(args, rank, world, local, dist):
             "host_plan_ms_per_step": plan_ms / args.steps, "kernel_ms_per_step": kern_ms / args.steps,
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": e2e_ms, "steps": e2e_steps, "device_ms_per_step": e_ev_ms / e2e_steps,
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "device_ms_per_step": e2e_dev_ms,
+                    "cpus_near_gpu": len(near) if near else None,
                     "rows_per_s": total_rows / (e2e_ms * 1e-3)},
             "roofline": roof, "cpu_baseline": cpu,
         }))
@@ -346,8 +371,23 @@ def run_ours(args, rank, world, local, dist):
         dist.destroy_process_group()
 
 
+_RESULT = sys.stdout
+
+
+def emit(obj):
+    """The ONE JSON line of the contract, on the process's real stdout."""
+    _RESULT.write(json.dumps(obj) + "\n")
+    _RESULT.flush()
+
+
 def main():
+    global _RESULT
     args = parse_args()
+    # Libraries (NCCL prints its version banner when NCCL_DEBUG is set on the box) must not add lines to stdout:
+    # keep the real stdout for the result line and point fd 1 at stderr for everything else.
+    sys.stdout.flush()
+    _RESULT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     import __graft_entry__ as g
     g.build()
     if args.impl == "reference":  # rank 0 alone runs the CPU arm; the other ranks exit without work

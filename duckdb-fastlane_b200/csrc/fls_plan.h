@@ -5,6 +5,7 @@
 // This is the per-column "expression interpreter" of the missing FastLanes reader reduced to a table:
 // scheme -> kernel kind.
 #pragma once
+#include <algorithm>
 #include <string>
 #include <vector>
 
@@ -28,11 +29,25 @@ struct FlsLaunch {
   std::vector<FlsChunkDev> chunks;
   // algorithmic traffic of the launch: segment bytes read, decoded bytes written
   uint64_t bytes_read = 0, bytes_written = 0, vectors = 0;
-  void add(const FlsChunkDev &d, uint64_t rd, uint64_t wr) {
+  // persistent chunk kernels hand each block a contiguous range of `chunks`: sort_by_key() interleaves the
+  // columns (row-group-major order) so that every range holds the same mix of cheap and expensive columns
+  std::vector<uint32_t> keys;
+  void add(const FlsChunkDev &d, uint64_t rd, uint64_t wr, uint32_t key = 0) {
     chunks.push_back(d);
+    keys.push_back(key);
     bytes_read += rd; bytes_written += wr; vectors += d.n_vec;
   }
 };
+
+inline void fls_sort_by_key(FlsLaunch &l) {
+  std::vector<uint32_t> idx(l.chunks.size());
+  for (uint32_t i = 0; i < idx.size(); ++i) idx[i] = i;
+  std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return l.keys[a] < l.keys[b]; });
+  std::vector<FlsChunkDev> c(l.chunks.size());
+  for (uint32_t i = 0; i < idx.size(); ++i) c[i] = l.chunks[idx[i]];
+  l.chunks.swap(c);
+  std::sort(l.keys.begin(), l.keys.end());
+}
 
 struct FlsColOut {
   void *data = nullptr;        // fixed width: padded_rows * width bytes
@@ -144,8 +159,8 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
           break;
         }
         case FLS_S_STR_CONSTANT: fls_launch_for(ls, FLS_K_STR_CONST, 0).add(d, rd, wr); break;
-        case FLS_S_STR_DICT: fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, rd, wr); break;
-        case FLS_S_STR_FSST: fls_launch_for(ls, FLS_K_STR_FSST, 0).add(d, rd, wr); break;
+        case FLS_S_STR_DICT: fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, rd, wr, g); break;
+        case FLS_S_STR_FSST: fls_launch_for(ls, FLS_K_STR_FSST, 0).add(d, rd, wr, g); break;
         case FLS_S_STR_FSST_DICT: {
           if (!host_image) return "FSST_DICT planning needs the host image";
           uint32_t sz;
@@ -157,7 +172,7 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
           d.seg[2] = d.seg[6];
           d.seg[3] = out.scratch + scratch_off;
           scratch_off += ((uint64_t)sz + 31) & ~15ull;
-          fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, k.seg[0].size + k.seg[1].size + k.seg[4].size + k.seg[6].size, wr);
+          fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, k.seg[0].size + k.seg[1].size + k.seg[4].size + k.seg[6].size, wr, g);
           break;
         }
         default: return "scheme not valid for a string column";

@@ -9,6 +9,9 @@
 // follow duckdb/third_party/fsst/fsst.h:93-104,162-241 (code<255 -> symbol, 255 -> escaped literal byte).
 #pragma once
 #include "fls_kernels.cuh"
+#ifndef FLS_EXP
+#define FLS_EXP 0  /* timing-only knock-out experiments (profiles/exp.sh); 0 = the product */
+#endif
 
 // ---- contiguous byte writer: head/tail bytes individually, everything between as aligned u64 stores
 struct FlsByteSink {
@@ -118,8 +121,12 @@ struct FlsPush {
   FLS_MEM static void emit(fls_sptr o0, uint32_t Tb, uint32_t Ta, uint32_t pv, uint32_t lo, uint32_t hi) {
     const uint32_t a = Tb >> 5, d = (Ta >> 5) - a;
     const fls_sptr addr = o0 + 4u * a;
+#if FLS_EXP == 1
+    if (d == 77u) fls_sts32_ge<1u>(d, addr, fls_shf_l(pv, lo, Tb) + fls_shf_l(lo, hi, Tb));
+#else
     fls_sts32_ge<1u>(d, addr, fls_shf_l(pv, lo, Tb));       // funnel shifts use T mod 32
     fls_sts32_ge<2u>(d, addr + 4u, fls_shf_l(lo, hi, Tb));
+#endif
   }
   FLS_MEM void push(uint32_t lo, uint32_t hi, uint32_t tail, uint32_t L8) {
     const uint32_t Ta = T + L8;
@@ -350,6 +357,58 @@ struct VecSTRDICT {
     uint8_t *pay = k.pay + k.pay_base;
     uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i, offs[i + 1] = its end
     uint32_t qpos = vec_ep;  // payload offset (row-group relative) of the quarter's first byte
+    if (U && !by_quarter && ((uintptr_t)(pay + vec_ep) & 15u) == 0u) {
+      // Every entry is U = 1, 2 or 4 bytes long and the vector's payload starts on a 16-byte boundary: offsets are
+      // arithmetic and a lane's 8 strings are 8U contiguous, aligned bytes — straight from registers to HBM, no
+      // staging.  Dictionaries of up to 8 one-byte entries (flag columns) live in two registers and a lane's 8
+      // bytes are two byte permutes of them.
+      const bool tiny = U == 1u && n_dict <= 8u;
+      uint32_t dlo = 0, dhi = 0;
+      if (tiny) {
+#pragma unroll
+        for (uint32_t e = 0; e < 4u; ++e) {
+          dlo |= (*(const uint32_t *)(tab + 16u * e) & 0xFFu) << (8u * e);
+          dhi |= (*(const uint32_t *)(tab + 16u * (e + 4u)) & 0xFFu) << (8u * e);
+        }
+      }
+      for (uint32_t qt = 0; qt < 4u; ++qt) {
+        FLS_LANES(t) {
+          uint32_t d[8];
+          unpack8(idx, bw, 8u * qt + (t >> 2), t, (uint32_t)h.base, n_dict - 1u, d);
+          const uint32_t s0 = 256u * qt + 8u * t;  // the lane's first string
+          const uint32_t start = k.pay_base + vec_ep + s0 * U;
+          fls_u4 a, b;
+          a.x = start; a.y = start + U; a.z = start + 2u * U; a.w = start + 3u * U;
+          b.x = start + 4u * U; b.y = start + 5u * U; b.z = start + 6u * U; b.w = start + 7u * U;
+          fls_st128(offs + s0, a);
+          fls_st128(offs + s0 + 4u, b);
+          if (s0 == FLS_VEC - 8u) offs[FLS_VEC] = start + 8u * U;  // the vector's last end
+          uint8_t *o = pay + vec_ep + s0 * U;
+          if (tiny) {
+            fls_st64(o, fls_prmt(dlo, dhi, d[0] | (d[1] << 4) | (d[2] << 8) | (d[3] << 12)),
+                     fls_prmt(dlo, dhi, d[4] | (d[5] << 4) | (d[6] << 8) | (d[7] << 12)));
+          } else {
+            uint32_t x[8];
+#pragma unroll
+            for (uint32_t i = 0; i < 8u; ++i) x[i] = *(const uint32_t *)(tab + 16u * d[i]);  // the entry's bytes, zero above U
+            if (U == 1u) {
+              fls_st64(o, x[0] | (x[1] << 8) | (x[2] << 16) | (x[3] << 24), x[4] | (x[5] << 8) | (x[6] << 16) | (x[7] << 24));
+            } else if (U == 2u) {
+              fls_u4 y;
+              y.x = x[0] | (x[1] << 16); y.y = x[2] | (x[3] << 16); y.z = x[4] | (x[5] << 16); y.w = x[6] | (x[7] << 16);
+              fls_st128(o, y);
+            } else {
+              fls_u4 y0, y1;
+              y0.x = x[0]; y0.y = x[1]; y0.z = x[2]; y0.w = x[3];
+              y1.x = x[4]; y1.y = x[5]; y1.z = x[6]; y1.w = x[7];
+              fls_st128(o, y0);
+              fls_st128(o + 16, y1);
+            }
+          }
+        }
+      }
+      return;
+    }
     for (uint32_t qt = 0; qt < 4u; ++qt) {
       if (by_quarter) {
         // the quarter's indices are rows 8qt .. 8qt+7 = 32-bit words [k0, k1] of every packed lane (<= 9 word rows)
@@ -434,20 +493,32 @@ struct VecSTRDICT {
 // 8 bytes at a time; every code byte costs one conflict-free 128-bit table load (the block keeps 8 copies of the
 // table, one per 16-byte bank group, lane t uses copy t & 7) and one FlsPush::push.  Escapes (code 255) are rare:
 // a window that holds one, and the partial first/last window of a run, take the byte-by-byte path.
+#ifndef FLS_FSST_WARPS
+#define FLS_FSST_WARPS 10
+#define FLS_FSST_COPIES 8
+#define FLS_FSST_STG 8448
+#define FLS_FSST_CWIN 3584
+#endif
 struct VecSTRFSST {
-  static constexpr uint32_t WARPS = 8;
-  static constexpr uint32_t STG = 11264u;    // staging of one quarter's output; phase 1: the two staged offset streams
-  static constexpr uint32_t CWIN = 4096u;    // compressed bytes of one quarter
+  // The kernel is bound by instruction issue and latency, not by shared-memory bandwidth (profiles/r01_SUMMARY.md,
+  // knock-out runs): shared memory is spent on WARPS, not on table copies or large passes.
+  static constexpr uint32_t WARPS = FLS_FSST_WARPS;
+  // A vector is decoded in passes of 256 strings — or 128 / 64 / 32 when a pass of the larger size would not fit:
+  static constexpr uint32_t STG = FLS_FSST_STG;      // staging of one pass's output
+  static constexpr uint32_t CWIN = FLS_FSST_CWIN;    // compressed bytes of one pass
   static constexpr uint32_t E16N = 1056u;    // 16-bit relative end of every string, padded original order (x2)
-  static constexpr uint32_t SMEM = STG + CWIN + 4u * E16N + 256u;  // 19840 = 155 * 128
-  // 512 entries (code * 2 + escaped) x 8 copies x 16 B, entry i of copy r at i*128 + r*16: a lane reads copy
-  // t & 7, so the eight lanes of a 128-bit load phase never share a bank group
-  static constexpr uint32_t BLOCK_SMEM = 65536u;
-  static constexpr uint32_t NBUF = 1, CONST_SMEM = 0;  // the table is too large to keep two
+  static constexpr uint32_t P1 = 2176u;      // phase 1: each staged offset stream (lane bases + deltas up to 16 bits wide)
+  static constexpr uint32_t SMEM = STG + CWIN + 4u * E16N + 256u;
+  // 512 entries (code * 2 + escaped) x COPIES x 16 B, entry i of copy r at (i * COPIES + r) * 16: a lane reads copy
+  // t % COPIES (8 copies: the eight lanes of a 128-bit load phase never share a bank group)
+  static constexpr uint32_t COPIES = FLS_FSST_COPIES, SH = COPIES == 8 ? 7u : COPIES == 4 ? 6u : COPIES == 2 ? 5u : 4u;
+  static constexpr uint32_t BLOCK_SMEM = 512u * 16u * COPIES;
+  static constexpr uint32_t NBUF = 1, CONST_SMEM = 0;
   static constexpr bool PIPELINED = true;
   FLS_MEM static void const_init(uint8_t *, uint32_t, uint32_t) {}
-  static_assert(2u * 4224u <= STG, "phase-1 buffers must fit the staging buffer");
-  static_assert(SMEM % 128u == 0, "warp slots stay 128-byte aligned");
+  static_assert(2u * P1 <= STG + CWIN && 4224u <= STG + CWIN, "phase-1 buffers must fit the staging buffer + window");
+  static_assert(SMEM % 128u == 0 && STG % 128u == 0, "warp slots stay 128-byte aligned");
+  static_assert((16u << 0) * COPIES == (1u << SH), "SH = log2 of an entry's stride");
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
     const uint64_t *sym = (const uint64_t *)k.seg[4];
     const uint8_t *len = k.seg[4] + 2048;
@@ -457,7 +528,7 @@ struct VecSTRFSST {
       if (i & 1u) en = fls_piece_entry(c, 1u);                 // escaped byte c: itself
       else if (c == 255u) { en.x = en.y = en.z = en.w = 0u; }  // the escape marker itself produces nothing
       else en = fls_piece_entry(fls_ldg(sym + c), fls_min(8u, (uint32_t)fls_ldg(len + c)));
-      for (uint32_t r = 0; r < 8u; ++r) *(fls_u4 *)(bsm + 128u * i + 16u * r) = en;
+      for (uint32_t r = 0; r < COPIES; ++r) *(fls_u4 *)(bsm + ((i * COPIES + r) << 4)) = en;
     }
   }
   // 0x80 in every byte of x that equals 0xFF (exact, byte by byte)
@@ -496,27 +567,32 @@ struct VecSTRFSST {
       for (uint32_t j = 0; j < 4u * NW; ++j) {
         if (MASK && (j < s || j >= e)) continue;
         const uint32_t c = (w[j >> 2] >> (8u * (j & 3u))) & 0xFFu;
-        if (lit) { p.push(fls_lds128<fls_u4>(tabr + 128u * (2u * c + 1u))); lit = false; }
+        if (lit) { p.push(fls_lds128<fls_u4>(tabr + ((2u * c + 1u) << SH))); lit = false; }
         else if (c == 255u) lit = true;
-        else p.push(fls_lds128<fls_u4>(tabr + 256u * c));
+        else p.push(fls_lds128<fls_u4>(tabr + ((2u * c) << SH)));
       }
       return;
     }
     lit = (ff[NW - 1u] >> 31) != 0u;
-    uint32_t ad[4u * NW];  // index * 128
+    constexpr uint32_t IM = 0x1FFu << SH;  // the 9 index bits at the entry stride
+    uint32_t ad[4u * NW];  // index << SH
 #pragma unroll
     for (uint32_t k = 0; k < NW; ++k) {
       // E: odd bytes carry their marker flag in the top bit (index of the even bytes); O: the other way round
       const uint32_t E = (w[k] & 0x7FFF7FFFu) | (ff[k] & 0x80008000u), O = (w[k] & 0xFF7FFF7Fu) | (ff[k] & 0x00800080u);
       const uint32_t below = k ? ((w[k - 1u] & 0x7FFFFFFFu) | (ff[k - 1u] & 0x80000000u)) : 0u;  // E of the word before
-      ad[4u * k] = (k ? fls_shf_r(below, E, 24u) : ((E << 8) | c7)) & 0xFF80u;
-      ad[4u * k + 1u] = O & 0xFF80u;
-      ad[4u * k + 2u] = (E >> 8) & 0xFF80u;
-      ad[4u * k + 3u] = (O >> 16) & 0xFF80u;
+      ad[4u * k] = (k ? fls_shf_r(below, E, 31u - SH) : ((E << (SH + 1u)) | (c7 >> (7u - SH)))) & IM;
+      ad[4u * k + 1u] = (O >> (7u - SH)) & IM;
+      ad[4u * k + 2u] = (E >> (15u - SH)) & IM;
+      ad[4u * k + 3u] = (O >> (23u - SH)) & IM;
     }
     fls_u4 en[4u * NW];
 #pragma unroll
+#if FLS_EXP == 2
+    for (uint32_t j = 0; j < 4u * NW; ++j) { en[j].x = ad[j]; en[j].y = 0; en[j].z = ad[j]; en[j].w = (ad[j] & 0x300u) ? 16u : 24u; }
+#else
     for (uint32_t j = 0; j < 4u * NW; ++j) en[j] = fls_lds128<fls_u4>(tabr + ad[j]);
+#endif
     p.push_all(en);
   }
   // A lane's compressed run = bytes [a, b) of the staged window `cwin`, read 16 bytes at a time (8 at the end).
@@ -593,21 +669,30 @@ struct VecSTRFSST {
     uint32_t *LS = (uint32_t *)(CE + E16N);  // LS[0..32] = first string of each lane, LS[34..37] = vector extents
     const uint8_t *comp = k.seg[5];
     uint8_t *pay = k.pay + k.pay_base;
-    // ---- phase 1: both end-offset streams -> offsets[] (global) and 16-bit relative ends of every string (shared)
+    // ---- phase 1: both end-offset streams -> offsets[] (global) and 16-bit relative ends of every string (shared).
+    //      Streams up to 16 bits wide are staged side by side; wider ones (strings of 64 KB and more, which end in
+    //      the byte-wise path below anyway) one after the other.
+    const bool both = bwd <= 16u && bwc <= 16u;
     w.fence_async();
     w.stage(0, k.seg[1] + 16ull * hd.ep, 128u + 128u * bwd);
-    w.stage(4224u, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc);
+    if (both) w.stage(P1, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc);
     w.wait();
     uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i
-    const uint32_t dv0 = ((const uint32_t *)w.sm)[0], cv0 = ((const uint32_t *)(w.sm + 4224u))[0];  // lane 0's bases
+    const uint32_t dv0 = ((const uint32_t *)w.sm)[0];          // lane 0's base
     FLS_VAR(uint32_t, lc0); FLS_VAR(uint32_t, lc1); FLS_VAR(uint32_t, ld0);
     FLS_LANES(t) {
       FLS_AT(ld0) = ((const uint32_t *)w.sm)[t];
-      FLS_AT(lc0) = ((const uint32_t *)(w.sm + 4224u))[t];
       const uint32_t dend = walk_ends(w.sm, bwd, (uint32_t)hd.base, t, k.pay_base, dv0, offs + fls_lane_start(t), DE);
-      const uint32_t cend = walk_ends(w.sm + 4224u, bwc, (uint32_t)hc.base, t, 0u, cv0, nullptr, CE);
+      if (t == 31u) { offs[FLS_VEC] = dend + k.pay_base; LS[34] = dend; }  // lane 31 owns the last strings
+    }
+    if (!both) { w.fence_async(); w.stage(0, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc); w.wait(); }
+    const uint8_t *cst = w.sm + (both ? P1 : 0u);
+    const uint32_t cv0 = ((const uint32_t *)cst)[0];
+    FLS_LANES(t) {
+      FLS_AT(lc0) = ((const uint32_t *)cst)[t];
+      const uint32_t cend = walk_ends(cst, bwc, (uint32_t)hc.base, t, 0u, cv0, nullptr, CE);
       FLS_AT(lc1) = cend;
-      if (t == 31u) { offs[FLS_VEC] = dend + k.pay_base; LS[34] = dend; LS[35] = cend; }  // lane 31 owns the last strings
+      if (t == 31u) LS[35] = cend;
     }
     const uint32_t dv1 = LS[34], cv1 = LS[35];
     if (dv1 - dv0 >= 65536u || cv1 - cv0 >= 65536u) {
@@ -615,20 +700,42 @@ struct VecSTRFSST {
       FLS_LANES(t) { decode_bytes(k, FLS_AT(lc0), FLS_AT(lc1), pay + FLS_AT(ld0)); }
       return;
     }
+#if FLS_EXP == 3
+    return;
+#endif
     // ---- phase 2: quarter by quarter (256 strings); the quarter's compressed bytes are split into 32 runs of
     //      (nearly) equal length that start on string boundaries, one per lane; the compressed bytes of quarter
     //      q+1 are bulk-copied into the window as soon as quarter q has been read, while q is copied out
-    uint32_t qc0 = 0, qc1 = start16(CE, 256u);  // compressed extent of the quarter, relative to cv0
+    // pass size: the largest of 256 / 128 / 64 / 32 strings for which every pass of this vector fits the staging
+    // buffer and the window (lane t checks pass t of each size; the counts of misfits add up in one scan)
+    FLS_VAR(uint32_t, bad);
+    FLS_LANES(t) {
+      uint32_t b = 0;
+#pragma unroll
+      for (uint32_t lv = 0; lv < 3u; ++lv) {
+        const uint32_t ps = 256u >> lv;
+        if (t < FLS_VEC / ps) {
+          const uint32_t d = start16(DE, (t + 1u) * ps) - start16(DE, t * ps), c = start16(CE, (t + 1u) * ps) - start16(CE, t * ps);
+          if (d + 15u > STG || c + 31u > CWIN) b |= 1u << (8u * lv);
+        }
+      }
+      FLS_AT(bad) = b;
+    }
+    uint32_t misfits;
+    FLS_EXCL_SCAN(bad, misfits);
+    const uint32_t lg = (misfits & 0xFFu) == 0u ? 0u : (misfits & 0xFF00u) == 0u ? 1u : (misfits & 0xFF0000u) == 0u ? 2u : 3u;
+    const uint32_t PASS = 256u >> lg, NPASS = 4u << lg;
+    uint32_t qc0 = 0, qc1 = start16(CE, PASS);  // compressed extent of the pass, relative to cv0
     uint32_t wbase = cv0 & ~15u;
     uint32_t span = cv0 + qc1 - wbase;
     bool windowed = span + 16u <= CWIN;
     const uint8_t *cwin = w.sm + STG;
     if (windowed && span) { w.fence_async(); w.stage(STG, comp + wbase, (span + 15u) & ~15u); }
-    for (uint32_t qt = 0; qt < 4u; ++qt) {
+    for (uint32_t qt = 0; qt < NPASS; ++qt) {
       if (windowed && span) w.wait();
       const uint32_t cur_wbase = wbase, cur_c0 = qc0, cur_c1 = qc1;
       const bool cur_windowed = windowed;
-      const uint32_t S0 = 256u * qt, S1 = S0 + 256u;
+      const uint32_t S0 = PASS * qt, S1 = S0 + PASS;
       const uint32_t qd0 = start16(DE, S0), qlen = start16(DE, S1) - qd0;
       uint8_t *g = pay + dv0 + qd0;
       const uint32_t hh = (uint32_t)((uintptr_t)g & 15u);
@@ -653,24 +760,28 @@ struct VecSTRFSST {
         if (staged) {
           FlsPush p;
           p.init(stg, hh + (d0 - qd0));
-          if (c1 > c0) decode_run(p, tab + 16u * (t & 7u), cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
+#if FLS_EXP != 5
+          if (c1 > c0) decode_run(p, tab + 16u * (t & (COPIES - 1u)), cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
+#endif
           FLS_AT(ps) = p;
         } else {
           decode_bytes(k, cv0 + c0, cv0 + c1, pay + dv0 + d0);
         }
       }
-      if (qt < 3u) {  // next quarter's window
+      if (qt + 1u < NPASS) {  // next pass's window
         qc0 = qc1;
-        qc1 = start16(CE, 256u * qt + 512u);
+        qc1 = start16(CE, PASS * qt + 2u * PASS);
         wbase = (cv0 + qc0) & ~15u;
         span = cv0 + qc1 - wbase;
         windowed = span + 16u <= CWIN;
         if (windowed && span) { w.fence_async(); w.stage(STG, comp + wbase, (span + 15u) & ~15u); }
       }
+#if FLS_EXP != 4
       if (staged) {
         FLS_LANES(t) { FLS_AT(ps).finish(); }
         FLS_LANES(t) { fls_stage_copy_out(stg, g, hh, qlen, t); }
       }
+#endif
     }
   }
 };

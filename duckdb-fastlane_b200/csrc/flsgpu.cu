@@ -547,6 +547,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     std::stable_sort(ls.begin(), ls.end(), [&](const FlsLaunch &a, const FlsLaunch &b2) { return rank_of(a.kind) < rank_of(b2.kind); });
     const size_t desc0 = desc_used;
     for (auto &l : ls) {
+      if (l.kind == FLS_K_STR_DICT || l.kind == FLS_K_STR_FSST) fls_sort_by_key(l);
       if (desc_used + l.chunks.size() > desc_cap) { perr = "internal: descriptor overflow"; break; }
       memcpy(h_desc + desc_used, l.chunks.data(), l.chunks.size() * sizeof(FlsChunkDev));
       desc_used += l.chunks.size();

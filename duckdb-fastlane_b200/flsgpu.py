@@ -54,7 +54,8 @@ def header_symbols():
 
 
 def lib_path():
-    return os.path.join(_HERE, "libflsgpu.so")
+    # FLSGPU_LIB: another build of the same CUDA library (kernel experiments under profiles/); never a CPU path
+    return os.environ.get("FLSGPU_LIB") or os.path.join(_HERE, "libflsgpu.so")
 
 
 def lib():

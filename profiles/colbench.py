@@ -9,25 +9,29 @@ sys.path.insert(0, os.path.join(ROOT, "duckdb-fastlane_b200"))
 sys.path.insert(0, ROOT)
 import __graft_entry__  # noqa: E402
 
-__graft_entry__.build()
+if not os.environ.get("FLSGPU_LIB"):
+    __graft_entry__.build()
 import flsgpu  # noqa: E402
 import synth  # noqa: E402
 import fls_writer as W  # noqa: E402
 
 n_rg = int(sys.argv[1]) if len(sys.argv) > 1 else 916
 passes = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+only = sys.argv[3].split(",") if len(sys.argv) > 3 else None
 peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"] if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else 6650.0
 small = synth.lineitem_image(64, seed=7)
 img = W.tile_rowgroups(small, n_rg)
 with flsgpu.Reader.from_image(img, device=0, flags=flsgpu.OPEN_TIME_KERNELS) as rd:
     rd.make_resident()
     for c in range(rd.n_cols):
+        if only and rd.names[c] not in only:
+            continue
         for _ in range(2):
-            rd.decode_batch(0, rd.n_rowgroups, cols=[c]).close()
+            rd.decode_batch(0, rd.n_rowgroups, cols=[c]).release()
         rd.reset_kernel_stats()
         for _ in range(passes):
             rd.flush_l2()
-            rd.decode_batch(0, rd.n_rowgroups, cols=[c]).close()
+            rd.decode_batch(0, rd.n_rowgroups, cols=[c]).release()
         for s in rd.kernel_stats():
             ms = s["ms"] / passes
             by = (s["bytes_read"] + s["bytes_written"]) / passes

@@ -165,6 +165,9 @@ def string_cases(n=70_000):
         pool = [bytes(r.integers(65, 91, L).astype(np.uint8)) for _ in range(9)]
         out.append(("str_dict_uniform_len%d" % L, [StrColumn.from_list([pool[i] for i in r.integers(0, 9, n)])], None,
                     [W.STR_DICT], None))
+    letters = [bytes([65 + i]) for i in range(20)]
+    out.append(("str_dict_uniform_len1_20_entries", [StrColumn.from_list([letters[i] for i in r.integers(0, 20, n)])], None,
+                [W.STR_DICT], None))
     # first row group has mixed lengths (odd payload size), second one is fixed-length: unaligned fast path
     mixed = [b"ab", b"c", b"defgh"]
     strs = [mixed[i] for i in r.integers(0, 3, 65536)] + [(b"XY", b"ZW")[i] for i in r.integers(0, 2, n - 65536 + 4000)]
@@ -180,6 +183,12 @@ def string_cases(n=70_000):
                 [W.STR_DICT], [23]))
     # compressed bytes of one vector exceed the kernel's shared-memory window -> streaming fallback path
     out.append(("str_fsst_long_fallback", [_rand_strings(r, 9000, 60, 200)], None, [W.STR_FSST], None))
+    # pass sizes 128 / 64 / 32 strings (a pass of 256 would not fit the staging buffer), and a mix within one column
+    for lo, hi in ((35, 60), (70, 120), (150, 250)):
+        out.append(("str_fsst_len_%d_%d" % (lo, hi), [_rand_strings(r, 20000, lo, hi)], None, [W.STR_FSST], None))
+    mix = _rand_strings(r, 3000, 0, 12).to_list() + _rand_strings(r, 3000, 150, 260).to_list() + comment.to_list()[:6000]
+    out.append(("str_fsst_mixed_lengths", [StrColumn.from_list([mix[i] for i in r.permutation(len(mix))])], None,
+                [W.STR_FSST], None))
     out.append(("str_fsst_dict_long_entries", [StrColumn.from_list([pool2 for pool2 in
                 [b"entry-%04d-" % (i % 300) + b"x" * (i % 300 % 90) for i in range(n)]])], None, [W.STR_FSST_DICT], None))
     out.append(("str_constant", [StrColumn.from_list([b"FastLanes"] * 5000)], None, [W.STR_CONSTANT], None))
