@@ -141,9 +141,11 @@ __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsCh
   volatile uint32_t *ready = done + NB;            // ready[NB]: 1 + the segment whose table the buffer holds
   auto seg_lo = [&](uint32_t s) { const uint32_t b0 = (c0 + s) * FLS_RG_VECS; return max(G0, b0) - b0; };
   auto seg_hi = [&](uint32_t s) { const uint32_t b0 = (c0 + s) * FLS_RG_VECS; return min(min(G1, b0 + FLS_RG_VECS) - b0, chunks[c0 + s].n_vec); };
-  // prologue: the first NB tables, built by the whole block
+  // prologue: the first NB tables (one table: by the whole block; several: one warp each, so that their
+  // global-memory round trips overlap)
   V::const_init(csm, threadIdx.x, V::WARPS * 32u);
-  for (uint32_t s = 0; s < NB && s < nseg; ++s) V::block_init(chunks[c0 + s], tabs + s * V::BLOCK_SMEM, threadIdx.x, V::WARPS * 32u);
+  if (NB == 1u) V::block_init(chunks[c0], tabs, threadIdx.x, V::WARPS * 32u);
+  else if (warp < NB && warp < nseg) V::block_init(chunks[c0 + warp], tabs + warp * V::BLOCK_SMEM, lane, 32u);  // side by side
   if (threadIdx.x < NB) {
     next[threadIdx.x] = threadIdx.x < nseg ? seg_lo(threadIdx.x) : 0u;
     done[threadIdx.x] = 0u;

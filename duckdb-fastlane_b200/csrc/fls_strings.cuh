@@ -214,44 +214,88 @@ struct VecSTRDICT {
   static constexpr bool PIPELINED = true;
   FLS_MEM static void const_init(uint8_t *, uint32_t, uint32_t) {}
   // called by all `nthreads` threads of a group (a whole block, or ONE warp: nthreads == 32)
+  // Global loads are issued in batches of independent loads held in registers (B per thread) and stored
+  // afterwards: a loop of load -> store iterations would expose one full memory latency per iteration, and this
+  // runs on ONE warp between two segments.  Three dependent rounds in all: (headers, entry points, entry lengths),
+  // entry offsets, entry bytes.
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
+    constexpr uint32_t B = 4;
     uint32_t *hdr = (uint32_t *)bsm;
     uint32_t *lens = (uint32_t *)(bsm + LENS);
-    if (k.n_vec <= 64u) {
-      for (uint32_t i = tid; i < 2u * k.n_vec; i += nthreads) ((uint64_t *)(bsm + HDRS))[i] = fls_ldg((const uint64_t *)k.seg[0] + i);
-      for (uint32_t i = tid; i <= k.n_vec; i += nthreads) ((uint32_t *)(bsm + VEP))[i] = fls_ldg((const uint32_t *)k.seg[4] + i);
-    }
     const uint32_t *doff = (const uint32_t *)k.seg[2];
     const uint8_t *dbytes = k.seg[3];
     const uint32_t n_dict = k.aux32;
+    const bool cached = n_dict <= CACHE_ENTRIES;
     if (tid == 0) { hdr[0] = 0; hdr[1] = 0; hdr[2] = 0; }
     FLS_GROUP_SYNC(nthreads);
-    if (n_dict > CACHE_ENTRIES) return;  // uniform over the block: P stays 0 = "not cached"
     uint32_t m = 0, mn = 0xFFFFFFFFu;
-    for (uint32_t i = tid; i < n_dict; i += nthreads) {
-      const uint32_t L = fls_ldg(doff + i + 1) - fls_ldg(doff + i);
-      lens[i] = L;
-      m = fls_max(m, L);
-      mn = fls_min(mn, L);
+    {
+      const uint32_t nh = k.n_vec <= 64u ? 2u * k.n_vec : 0u, ne = k.n_vec <= 64u ? k.n_vec + 1u : 0u, nl = cached ? n_dict : 0u;
+      for (uint32_t i0 = 0; i0 < fls_max(fls_max(nh, ne), nl); i0 += B * nthreads) {
+        uint64_t rh[B];
+        uint32_t re[B], ra[B], rb[B];
+#pragma unroll
+        for (uint32_t j = 0; j < B; ++j) {
+          const uint32_t i = i0 + j * nthreads + tid;
+          rh[j] = i < nh ? fls_ldg((const uint64_t *)k.seg[0] + i) : 0ull;
+          re[j] = i < ne ? fls_ldg((const uint32_t *)k.seg[4] + i) : 0u;
+          ra[j] = i < nl ? fls_ldg(doff + i) : 0u;
+          rb[j] = i < nl ? fls_ldg(doff + i + 1) : 0u;
+        }
+#pragma unroll
+        for (uint32_t j = 0; j < B; ++j) {
+          const uint32_t i = i0 + j * nthreads + tid;
+          if (i < nh) ((uint64_t *)(bsm + HDRS))[i] = rh[j];
+          if (i < ne) ((uint32_t *)(bsm + VEP))[i] = re[j];
+          if (i < nl) { const uint32_t L = rb[j] - ra[j]; lens[i] = L; m = fls_max(m, L); mn = fls_min(mn, L); }
+        }
+      }
     }
+    if (!cached) return;  // uniform over the group: P stays 0 = "not cached"
     fls_smem_max(hdr + 1, m);
     fls_smem_max(hdr + 2, ~mn);  // max of the complement = complement of the min
     FLS_GROUP_SYNC(nthreads);
     const uint32_t P = (hdr[1] + 7u) >> 3;
     if (P == 0 || n_dict * P * 16u > TAB_BYTES) return;
-    for (uint32_t i = tid; i < n_dict * P; i += nthreads) {
-      const uint32_t d = i / P, pc = i % P;
-      const uint32_t a = fls_ldg(doff + d), L = fls_ldg(doff + d + 1) - a;
-      const uint32_t Lp = L > 8u * pc ? fls_min(8u, L - 8u * pc) : 0u;
-      uint64_t x = 0;
-      for (uint32_t b = 0; b < Lp; ++b) x |= (uint64_t)fls_ldg(dbytes + a + 8u * pc + b) << (8u * b);
-      *(fls_u4 *)(bsm + TAB + 16u * i) = fls_piece_entry(x, Lp);
+    // small tables are kept 8 times (entry i, copy r at i * 128 + r * 16; lane t reads copy t & 7): the eight lanes
+    // of a 128-bit load phase then never share a bank group, whatever entries they look up
+    const uint32_t sh = n_dict * P * 128u <= TAB_BYTES ? 7u : 4u;
+    for (uint32_t i0 = 0; i0 < n_dict * P; i0 += B * nthreads) {
+      uint32_t a[B], pos[B], Lp[B];
+      uint64_t lo[B], hi[B];
+#pragma unroll
+      for (uint32_t j = 0; j < B; ++j) {
+        const uint32_t i = i0 + j * nthreads + tid, d = i / P;
+        a[j] = i < n_dict * P ? fls_ldg(doff + d) : 0u;
+      }
+#pragma unroll
+      for (uint32_t j = 0; j < B; ++j) {
+        const uint32_t i = i0 + j * nthreads + tid, d = fls_min(i / P, n_dict - 1u), pc = i % P;
+        const uint32_t L = lens[d];
+        Lp[j] = (i < n_dict * P && L > 8u * pc) ? fls_min(8u, L - 8u * pc) : 0u;
+        pos[j] = a[j] + 8u * pc;
+        // the piece's <= 8 bytes at an arbitrary byte address = two aligned 8-byte words (the dictionary's
+        // segment is 16-byte aligned and followed by 16 bytes of slack)
+        const uint64_t *q = (const uint64_t *)(dbytes + (pos[j] & ~7u));
+        lo[j] = Lp[j] ? fls_ldg(q) : 0ull;
+        hi[j] = Lp[j] ? fls_ldg(q + 1) : 0ull;
+      }
+#pragma unroll
+      for (uint32_t j = 0; j < B; ++j) {
+        const uint32_t i = i0 + j * nthreads + tid, bs = 8u * (pos[j] & 7u);
+        const uint64_t x = bs ? (lo[j] >> bs) | (hi[j] << (64u - bs)) : lo[j];
+        if (i < n_dict * P) {
+          const fls_u4 en = fls_piece_entry(x, Lp[j]);
+          if (sh == 7u) { for (uint32_t r = 0; r < 8u; ++r) *(fls_u4 *)(bsm + TAB + 128u * i + 16u * r) = en; }
+          else *(fls_u4 *)(bsm + TAB + 16u * i) = en;
+        }
+      }
     }
-    if (tid == 0) hdr[0] = P;
+    if (tid == 0) { hdr[0] = P; hdr[3] = sh; }
   }
   // the 8 strings of a lane, P pieces each: table loads are issued in batches of up to 8 entries BEFORE the
   // pushes that consume them (the compiler cannot hoist shared loads over the pushes' shared stores itself)
-  template <uint32_t P> FLS_MEM static void push_strings(FlsPush &p, const uint8_t *tab, const uint32_t (&d)[8]) {
+  template <uint32_t P> FLS_MEM static void push_strings(FlsPush &p, const uint8_t *tab, uint32_t sh, const uint32_t (&d)[8]) {
     constexpr uint32_t SPB = P == 1 ? 8u : P == 2 ? 4u : 2u;  // strings per batch
 #pragma unroll
     for (uint32_t s0 = 0; s0 < 8u; s0 += SPB) {
@@ -259,16 +303,16 @@ struct VecSTRDICT {
 #pragma unroll
       for (uint32_t i = 0; i < SPB; ++i)
 #pragma unroll
-        for (uint32_t pc = 0; pc < P; ++pc) e[i * P + pc] = fls_lds128<fls_u4>(tab + 16u * (d[s0 + i] * P + pc));
+        for (uint32_t pc = 0; pc < P; ++pc) e[i * P + pc] = fls_lds128<fls_u4>(tab + ((d[s0 + i] * P + pc) << sh));
       p.push_all(e);
     }
   }
   // every entry has the same length U in {1, 2, 4}: the lane's 8 strings are 8U bytes, merged in registers into
   // U eight-byte pieces — U pushes instead of 8
-  template <uint32_t U> FLS_MEM static void push_uniform(FlsPush &p, const uint8_t *tab, const uint32_t (&d)[8]) {
+  template <uint32_t U> FLS_MEM static void push_uniform(FlsPush &p, const uint8_t *tab, uint32_t sh, const uint32_t (&d)[8]) {
     uint32_t x[8], wd[2u * U];
 #pragma unroll
-    for (uint32_t i = 0; i < 8u; ++i) x[i] = *(const uint32_t *)(tab + 16u * d[i]);  // the entry's bytes, zero above U
+    for (uint32_t i = 0; i < 8u; ++i) x[i] = *(const uint32_t *)(tab + (d[i] << sh));  // the entry's bytes, zero above U
     if (U == 1u) {
       wd[0] = x[0] | (x[1] << 8) | (x[2] << 16) | (x[3] << 24);
       wd[1] = x[4] | (x[5] << 8) | (x[6] << 16) | (x[7] << 24);
@@ -335,6 +379,7 @@ struct VecSTRDICT {
     const uint32_t U = (P == 1u && maxlen == minlen && (maxlen == 1u || maxlen == 2u || maxlen == 4u)) ? maxlen : 0u;
     const uint32_t *lens = (const uint32_t *)(bsm + LENS);
     const uint8_t *tab = bsm + TAB;
+    const uint32_t sh = ((const uint32_t *)bsm)[3];  // log2 of the table's entry stride: 4, or 7 when kept 8 times
     uint8_t *stg = w.sm;
     uint32_t ioff = IDX;  // where this vector's index payload is (half 0, half 1, or the whole buffer)
     const bool by_quarter = 128u * bw > 2u * HALF;  // too wide for the buffer: the packed rows of one quarter at a time
@@ -367,14 +412,20 @@ struct VecSTRDICT {
       if (tiny) {
 #pragma unroll
         for (uint32_t e = 0; e < 4u; ++e) {
-          dlo |= (*(const uint32_t *)(tab + 16u * e) & 0xFFu) << (8u * e);
-          dhi |= (*(const uint32_t *)(tab + 16u * (e + 4u)) & 0xFFu) << (8u * e);
+          dlo |= (*(const uint32_t *)(tab + (e << sh)) & 0xFFu) << (8u * e);
+          dhi |= (*(const uint32_t *)(tab + ((e + 4u) << sh)) & 0xFFu) << (8u * e);
         }
       }
+#if FLS_EXP == 12
+      return;
+#endif
       for (uint32_t qt = 0; qt < 4u; ++qt) {
         FLS_LANES(t) {
           uint32_t d[8];
           unpack8(idx, bw, 8u * qt + (t >> 2), t, (uint32_t)h.base, n_dict - 1u, d);
+#if FLS_EXP == 11
+          if (d[0] + d[1] + d[2] + d[3] + d[4] + d[5] + d[6] + d[7] != 0x12345u) continue;
+#endif
           const uint32_t s0 = 256u * qt + 8u * t;  // the lane's first string
           const uint32_t start = k.pay_base + vec_ep + s0 * U;
           fls_u4 a, b;
@@ -390,7 +441,7 @@ struct VecSTRDICT {
           } else {
             uint32_t x[8];
 #pragma unroll
-            for (uint32_t i = 0; i < 8u; ++i) x[i] = *(const uint32_t *)(tab + 16u * d[i]);  // the entry's bytes, zero above U
+            for (uint32_t i = 0; i < 8u; ++i) x[i] = *(const uint32_t *)(tab + (d[i] << sh));  // the entry's bytes, zero above U
             if (U == 1u) {
               fls_st64(o, x[0] | (x[1] << 8) | (x[2] << 16) | (x[3] << 24), x[4] | (x[5] << 8) | (x[6] << 16) | (x[7] << 24));
             } else if (U == 2u) {
@@ -452,17 +503,18 @@ struct VecSTRDICT {
         if (staged) {
           FlsPush p;
           p.init(stg, hh + FLS_AT(run));
-          if (U == 1u) push_uniform<1>(p, tab, d);
-          else if (U == 2u) push_uniform<2>(p, tab, d);
-          else if (U == 4u) push_uniform<4>(p, tab, d);
+          const uint8_t *tabr = tab + (sh == 7u ? 16u * (t & 7u) : 0u);  // this lane's copy of the table
+          if (U == 1u) push_uniform<1>(p, tab, sh, d);
+          else if (U == 2u) push_uniform<2>(p, tab, sh, d);
+          else if (U == 4u) push_uniform<4>(p, tab, sh, d);
           else switch (P) {
-            case 1: push_strings<1>(p, tab, d); break;
-            case 2: push_strings<2>(p, tab, d); break;
-            case 3: push_strings<3>(p, tab, d); break;
-            case 4: push_strings<4>(p, tab, d); break;
+            case 1: push_strings<1>(p, tabr, sh, d); break;
+            case 2: push_strings<2>(p, tabr, sh, d); break;
+            case 3: push_strings<3>(p, tabr, sh, d); break;
+            case 4: push_strings<4>(p, tabr, sh, d); break;
             default:
               for (uint32_t i = 0; i < 8u; ++i)
-                for (uint32_t pc = 0; pc < P; ++pc) p.push(fls_lds128<fls_u4>(tab + 16u * (d[i] * P + pc)));
+                for (uint32_t pc = 0; pc < P; ++pc) p.push(fls_lds128<fls_u4>(tabr + ((d[i] * P + pc) << sh)));
           }
           FLS_AT(ps) = p;
         } else {
@@ -519,16 +571,31 @@ struct VecSTRFSST {
   static_assert(2u * P1 <= STG + CWIN && 4224u <= STG + CWIN, "phase-1 buffers must fit the staging buffer + window");
   static_assert(SMEM % 128u == 0 && STG % 128u == 0, "warp slots stay 128-byte aligned");
   static_assert((16u << 0) * COPIES == (1u << SH), "SH = log2 of an entry's stride");
+  // (all of a thread's symbol loads are issued before the first table store: one memory round trip per build)
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
     const uint64_t *sym = (const uint64_t *)k.seg[4];
     const uint8_t *len = k.seg[4] + 2048;
-    for (uint32_t i = tid; i < 512u; i += nthreads) {  // i = code * 2 + (escaped literal ? 1 : 0)
-      const uint32_t c = i >> 1;
-      fls_u4 en;
-      if (i & 1u) en = fls_piece_entry(c, 1u);                 // escaped byte c: itself
-      else if (c == 255u) { en.x = en.y = en.z = en.w = 0u; }  // the escape marker itself produces nothing
-      else en = fls_piece_entry(fls_ldg(sym + c), fls_min(8u, (uint32_t)fls_ldg(len + c)));
-      for (uint32_t r = 0; r < COPIES; ++r) *(fls_u4 *)(bsm + ((i * COPIES + r) << 4)) = en;
+    constexpr uint32_t B = 8;
+    for (uint32_t c0 = 0; c0 < 256u; c0 += B * nthreads) {
+      uint64_t sv[B];
+      uint32_t lv[B];
+#pragma unroll
+      for (uint32_t j = 0; j < B; ++j) {
+        const uint32_t c = c0 + j * nthreads + tid;
+        sv[j] = c < 255u ? fls_ldg(sym + c) : 0ull;
+        lv[j] = c < 255u ? fls_min(8u, (uint32_t)fls_ldg(len + c)) : 0u;  // 255, the escape marker, produces nothing
+      }
+#pragma unroll
+      for (uint32_t j = 0; j < B; ++j) {
+        const uint32_t c = c0 + j * nthreads + tid;
+        if (c < 256u) {
+          const fls_u4 en = fls_piece_entry(sv[j], lv[j]), el = fls_piece_entry(c, 1u);  // el: escaped byte c, itself
+          for (uint32_t r = 0; r < COPIES; ++r) {
+            *(fls_u4 *)(bsm + (((2u * c) * COPIES + r) << 4)) = en;
+            *(fls_u4 *)(bsm + (((2u * c + 1u) * COPIES + r) << 4)) = el;
+          }
+        }
+      }
     }
   }
   // 0x80 in every byte of x that equals 0xFF (exact, byte by byte)
