@@ -45,7 +45,7 @@ std::string parse_footer(const uint8_t *foot, uint64_t fsz, uint64_t foot_off, F
         r.n_tuples > r.n_vec * FLS_VEC || r.n_tuples + FLS_VEC <= r.n_vec * FLS_VEC)
       return "corrupt FLS row-group descriptor";
     // only the last row group may be partial (decoded rows stay contiguous across row groups)
-    if (g + 1 < t.n_rg && r.n_tuples != FLS_RG_VECS * FLS_VEC) return "unsupported: partial row group before the last";
+    if (g + 1 < t.n_rg && r.n_tuples != r.n_vec * FLS_VEC) return "unsupported: partial vector before the last row group";
     if (g && r.off < t.rgs[g - 1].off + t.rgs[g - 1].size) return "corrupt FLS row-group order";
     rows += r.n_tuples;
     for (uint32_t col = 0; col < t.n_cols; ++col) {

@@ -673,9 +673,9 @@ static Chunk enc_fixed(const void *src, uint32_t n_rows, uint32_t n_vec, int for
 
 static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_data, const uint64_t *const *str_off) {
   if (w.finished) { w.err = "writer already finished"; return 1; }
-  if (w.last_partial) { w.err = "only the last row group may hold fewer than 65536 rows"; return 1; }
+  if (w.last_partial) { w.err = "only the last row group may end in a partial vector (rows not a multiple of 1024)"; return 1; }
   if (n_rows == 0 || n_rows > FLS_RG_VECS * FLS_VEC) { w.err = "row group must hold 1..65536 rows"; return 1; }
-  if (n_rows != FLS_RG_VECS * FLS_VEC) w.last_partial = true;
+  if (n_rows % FLS_VEC) w.last_partial = true;
   uint32_t n_vec = (n_rows + FLS_VEC - 1) / FLS_VEC;
   pad_to(w.file, FLS_RG_ALIGN);
   uint64_t rg_off = w.file.size();

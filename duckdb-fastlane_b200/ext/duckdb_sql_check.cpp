@@ -13,6 +13,7 @@
 
 #include "duckdb.hpp"
 #include "scan_fastlanes.hpp"
+#include "write_fastlane.hpp"
 
 static std::string esc(const std::string &s) {
 	std::string o;
@@ -38,6 +39,7 @@ static std::string esc(const std::string &s) {
 int main(int argc, char **argv) {
 	duckdb::DuckDB db(nullptr);
 	duckdb::ScanFastLanes::Register(*db.instance);
+	duckdb::ext_fastlane::RegisterFastlaneStreamCopyFunction(*db.instance);
 	duckdb::Connection con(db);
 	int rc = 0;
 	for (int i = 1; i < argc; i++) {

@@ -89,10 +89,11 @@ class StrColumn:
         return StrColumn(self.data, self.offsets[a:b + 1])  # offsets stay absolute into data
 
 
-def write_table(columns, names=None, types=None, force=None, min_bw=None, path=None, alp_ef=None) -> np.ndarray:
+def write_table(columns, names=None, types=None, force=None, min_bw=None, path=None, alp_ef=None, rg_rows=RG_ROWS) -> np.ndarray:
     """Encode a table into an FLS image (returned as a uint8 array; also written to `path` if given).
 
     columns: list of np.ndarray (fixed width) or StrColumn.   force/min_bw: optional per-column scheme / FFOR width.
+    rg_rows: rows per row group, a multiple of 1024 up to 65,536 (what COPY's ROW_GROUP_SIZE sets).
     """
     L = lib()
     n_cols = len(columns)
@@ -113,8 +114,10 @@ def write_table(columns, names=None, types=None, force=None, min_bw=None, path=N
                 if L.flsw_force_alp_ef(w, i, alp_ef[i][0], alp_ef[i][1]):
                     raise ValueError("bad ALP exponent/factor")
         cols = [c if isinstance(c, StrColumn) else np.ascontiguousarray(c) for c in columns]
-        for r0 in range(0, max(n_rows, 1), RG_ROWS):
-            r1 = min(n_rows, r0 + RG_ROWS)
+        if rg_rows % 1024 or not 0 < rg_rows <= RG_ROWS:
+            raise ValueError("rg_rows must be a multiple of 1024 in [1024, 65536]")
+        for r0 in range(0, max(n_rows, 1), rg_rows):
+            r1 = min(n_rows, r0 + rg_rows)
             if r1 <= r0:
                 break
             data = (C.c_void_p * n_cols)()

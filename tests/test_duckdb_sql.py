@@ -109,3 +109,60 @@ def test_typed_scan_aggregates_projection_multifile_replacement(tmp_path):
     assert [r[0] for r in res[5]["rows"]] == [str(int(ids[i])) for i in top]
     assert [r[1] for r in res[5]["rows"]] == [user[i].decode() for i in top]
     assert [float(r[2]) for r in res[5]["rows"]] == [float(rnd[i]) for i in top]
+
+
+# ---------------------------------------------------------------------------------------------- COPY ... TO (FORMAT FLS)
+# the sink the reference declares in src/writer/write_fastlane_stream.cpp, serving the
+# statement of examples/basic_usage.sql:27-36.  Writing is host code: these run without a GPU; the oracle reads back.
+_COPY_SRC = ("SELECT i::INTEGER AS id, (i * 1000003 + 1234567890123)::BIGINT AS big, round(i * 0.37, 2)::DOUBLE AS score, "
+             "'user_' || i AS username, (i % 2 = 0) AS is_active, DATE '2023-01-01' + (i % 365)::INTEGER AS join_date, "
+             "(i % 7)::DECIMAL(9,2) AS amount FROM range(1, 150001) t(i)")
+
+
+def test_copy_to_fls_writes_what_the_oracle_reads(tmp_path):
+    from oracle import oracle
+    path = str(tmp_path / "users.fls")
+    res = sql("COPY (%s) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 50000)" % (_COPY_SRC, path),
+              "DESCRIBE SELECT * FROM read_fls('%s')" % path)
+    assert res[0]["rows"] == [["150000"]], res[0]
+    assert [(r[0], r[1]) for r in res[1]["rows"]] == [
+        ("id", "INTEGER"), ("big", "BIGINT"), ("score", "DOUBLE"), ("username", "VARCHAR"), ("is_active", "BOOLEAN"),
+        ("join_date", "DATE"), ("amount", "VARCHAR")]            # DECIMAL is FALLBACK -> VARCHAR (type_mapping.cpp:58-60)
+    ora = oracle.OracleTable(np.fromfile(path, dtype=np.uint8))
+    assert ora.n_rows == 150000 and ora.n_rg == 3                # 50000 rounds up to 49 whole vectors per row group
+    i = np.arange(1, 150001, dtype=np.int64)
+    assert np.array_equal(ora.decode(0), i.astype(np.int32))
+    assert np.array_equal(ora.decode(1), i * 1000003 + 1234567890123)
+    assert np.array_equal(ora.decode(4).view(np.uint8), (i % 2 == 0).astype(np.uint8))
+    assert np.array_equal(ora.decode(5), (19358 + i % 365).astype(np.int32))
+    offs, pay = ora.decode(3)
+    assert bytes(pay[offs[0]:offs[2]]) == b"user_1user_2" and bytes(pay[offs[149999]:offs[150000]]) == b"user_150000"
+    offs, pay = ora.decode(6)
+    assert bytes(pay[offs[0]:offs[2]]) == b"1.002.00"
+
+
+def test_copy_to_fls_options_and_errors(tmp_path):
+    p = str(tmp_path / "x.fls")
+    res = sql("COPY (SELECT 1 AS a) TO '%s' (FORMAT FLS, FOO 3)" % p,
+              "COPY (SELECT 1 AS a) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 2048, ROW_GROUP_SIZE_BYTES '1MB')" % p,
+              "COPY (SELECT NULL::INTEGER AS a) TO '%s' (FORMAT FLS)" % p,
+              "COPY (SELECT 42 AS a) TO '%s'" % str(tmp_path / "y.fastlane"),      # format from the file extension
+              "COPY (SELECT 42 AS a) TO '%s' (FORMAT FLS, CHUNK_SIZE 4096, ROW_GROUPS_PER_FILE 10)" % p)
+    assert "Unknown option for FastLanes: FOO" in res[0]["error"]                  # write_fastlane_stream.cpp:104
+    assert "mutually exclusive" in res[1]["error"]                                 # :85-87
+    assert "NULL in column" in res[2]["error"]
+    assert res[3]["rows"] == [["1"]] and res[4]["rows"] == [["1"]]
+
+
+@pytest.mark.gpu
+def test_copy_then_read_fls_round_trip(tmp_path):
+    """examples/basic_usage.sql end to end: COPY a table out, scan it back on the GPU, compare with the source query."""
+    path = str(tmp_path / "users.fls")
+    agg = "count(*), sum(id), sum(big), sum(score), min(username), max(username), count(*) FILTER (is_active), max(join_date)"
+    res = sql("COPY (%s) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 20480)" % (_COPY_SRC, path),
+              "SELECT %s FROM (%s)" % (agg, _COPY_SRC),
+              "SELECT %s FROM read_fls('%s')" % (agg, path),
+              "SELECT count(*) FROM (SELECT * FROM (%s) EXCEPT SELECT * REPLACE (amount::DECIMAL(9,2) AS amount) FROM read_fls('%s'))"
+              % (_COPY_SRC, path))
+    assert res[1]["rows"] == res[2]["rows"], (res[1], res[2])
+    assert res[3]["rows"] == [["0"]], res[3]

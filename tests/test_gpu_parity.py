@@ -82,6 +82,17 @@ def test_lineitem_shape_projection_ranges_slices():
         assert "str_fsst" in st and "alp_u64" in st and st["ffor_u64"]["launches"] >= 2
 
 
+def test_small_row_groups():
+    """Row groups of 1 / 3 / 16 vectors (COPY ... ROW_GROUP_SIZE n), with a partial last vector."""
+    import fls_writer as W
+    cols, names = synth.basic_usage(30_000)
+    for rg_rows in (1024, 3072, 16384):
+        img = W.write_table(cols, names=names, types=synth.basic_usage_types(), rg_rows=rg_rows)
+        check_table(img)
+        check_table(img, g0=1, g1=2)
+        check_table(img, slice_rowgroups=2)
+
+
 def test_open_by_path(tmp_path):
     p = str(tmp_path / "li.fls")
     img = synth.lineitem_image(2, tail_rows=5)

@@ -80,3 +80,32 @@ def test_oracle_rejects_garbage():
     bad[:8] = 0
     with pytest.raises(IOError):
         oracle.OracleTable(bad)
+
+
+def test_small_row_groups_whole_vectors():
+    """Row groups of fewer than 64 vectors (COPY ... ROW_GROUP_SIZE n): every one but the last holds whole vectors."""
+    import synth
+    import fls_writer as W
+    cols, names = synth.basic_usage(30_000)
+    for rg_rows in (1024, 3072, 16384):
+        img = W.write_table(cols, names=names, types=synth.basic_usage_types(), rg_rows=rg_rows)
+        ora = oracle.OracleTable(img)
+        assert ora.n_rows == 30_000 and ora.n_rg == -(-30_000 // rg_rows)
+        for c, src in enumerate(cols):
+            exp = cases.expected_bytes(src)
+            got = ora.decode(c)
+            em = emul.decode(img, c, ora.types[c], 0, ora.n_rg)
+            if isinstance(src, StrColumn):
+                assert np.array_equal(got[0], exp[0]) and np.array_equal(got[1], exp[1])
+                assert np.array_equal(em[0][:30_001], got[0]) and np.array_equal(em[1][:len(got[1])], got[1])
+            else:
+                assert np.array_equal(got.view(np.uint8), exp) and np.array_equal(em[:30_000].view(np.uint8), exp)
+    # a partial vector can only end the file: appending after it is refused
+    import ctypes as C
+    lib = W.lib()
+    w = lib.flsw_create(1, (C.c_char_p * 1)(b"a"), (C.c_int32 * 1)(W.INT32))
+    a = np.arange(1500, dtype=np.int32)
+    d, o = (C.c_void_p * 1)(a.ctypes.data), (C.c_void_p * 1)(None)
+    assert lib.flsw_append_rowgroup(w, 1500, d, o) == 0
+    assert lib.flsw_append_rowgroup(w, 1024, d, o) != 0 and b"partial vector" in lib.flsw_error(w)
+    lib.flsw_destroy(w)
