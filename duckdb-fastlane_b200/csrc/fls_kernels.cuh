@@ -1,7 +1,7 @@
 // fls_kernels.cuh — chunk descriptors and the per-vector entry points the kernels (and tests/emul) call.
 //
-// One launch decodes every chunk of one (scheme, width) family in a batch of row groups: grid = 16 * n_chunks
-// blocks of 4 warps; warp w of block b decodes vector 4*(b%16)+w of chunk b/16.  A chunk = one (row group,
+// One launch decodes every chunk of one (scheme, width) family in a batch of row groups: grid = 32 * n_chunks
+// blocks of 2 warps; warp w of block b decodes vector 2*(b%32)+w of chunk b/32.  A chunk = one (row group,
 // column).
 #pragma once
 #include "fls_decode.cuh"
@@ -82,11 +82,15 @@ struct VecALPRD {
   }
 };
 
-#define FLS_WARPS_PER_BLOCK 4
+// 2 warps per block: measured 6 % faster than 4 on ALP and 2 % on FFOR u64 (more, smaller blocks fill the SMs'
+// shared memory more evenly); 1 is no better and costs FFOR u32 its occupancy (32 resident blocks per SM)
+#ifndef FLS_WARPS_PER_BLOCK
+#define FLS_WARPS_PER_BLOCK 2
+#endif
 #define FLS_BLOCKS_PER_CHUNK (FLS_RG_VECS / FLS_WARPS_PER_BLOCK)
 
 #ifndef FLS_HOST_EMUL
-// Shared memory layout of a block: [warp 0 slot | ... | warp 3 slot | block-shared (V::BLOCK_SMEM) | 4 mbarriers]
+// Shared memory layout of a block: [warp slots | block-shared (V::BLOCK_SMEM) | one mbarrier per warp]
 template <class V> constexpr uint32_t fls_block_smem() {
   return FLS_WARPS_PER_BLOCK * V::SMEM + V::BLOCK_SMEM + FLS_WARPS_PER_BLOCK * 8u;
 }

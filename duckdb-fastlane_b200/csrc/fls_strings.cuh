@@ -198,7 +198,10 @@ FLS_DEV void fls_walk32(const uint8_t *stage, uint32_t bw, uint32_t base, uint32
 // output bytes, appended piece by piece (FlsPush) to the warp's staging buffer, and its 8 end offsets leave as
 // two aligned 128-bit stores {run start, end 0 .. end 6} (end 7 is the next lane's run start).
 struct VecSTRDICT {
-  static constexpr uint32_t WARPS = 16;
+#ifndef FLS_DICT_WARPS
+#define FLS_DICT_WARPS 14  /* measured: 12 / 14 / 16 warps -> 0.697 / 0.668 / 0.683 ms on the SF10 launch */
+#endif
+  static constexpr uint32_t WARPS = FLS_DICT_WARPS;
   static constexpr uint32_t STG = 8448u;     // staging of one quarter's payload (33 bytes per string on average)
   // staged index payload: two halves of HALF bytes (this vector's and the prefetched next one's, widths <= 10 bits),
   // or one vector's payload up to 20 bits wide, or — wider still — the packed rows of one quarter at a time
