@@ -372,6 +372,77 @@ int flsgpu_chunk_info(const flsgpu_t *h, uint32_t rg, uint32_t col, int32_t *sch
   return FLSGPU_OK;
 }
 
+int flsgpu_rowgroup_minmax(flsgpu_t *h, uint32_t rg, uint32_t col, int64_t *mn, int64_t *mx, int32_t *known) {
+  if (!known || !mn || !mx) return h->fail(FLSGPU_E_RANGE, "null argument");
+  *known = 0;
+  if (rg >= h->t.n_rg || col >= h->t.n_cols) return h->fail(FLSGPU_E_RANGE, "bad row group / column id");
+  const int type = h->t.types[col];
+  const uint32_t tb = fls_type_bits(type);
+  const bool is_signed = type == FLS_T_INT8 || type == FLS_T_INT16 || type == FLS_T_INT32 || type == FLS_T_INT64 || type == FLS_T_DATE;
+  const bool is_unsigned = type == FLS_T_UINT8 || type == FLS_T_UINT16 || type == FLS_T_UINT32 || type == FLS_T_UINT64 || type == FLS_T_BOOLEAN;
+  if (!tb || !(is_signed || is_unsigned)) return FLSGPU_OK;
+  const fls_colchunk &k = h->t.chunk(rg, col);
+  const fls_rowgroup &r = h->t.rgs[rg];
+  const uint64_t tmask = tb == 64 ? ~0ull : ((1ull << tb) - 1ull);
+  auto as_i64 = [&](uint64_t v, int64_t *o) {  // value of the column's type -> int64; false if it does not fit
+    if (is_signed) { *o = tb == 64 ? (int64_t)v : (int64_t)(v << (64 - tb)) >> (64 - tb); return true; }
+    if (v > (uint64_t)INT64_MAX) return false;
+    *o = (int64_t)v;
+    return true;
+  };
+  if (k.scheme == FLS_S_CONSTANT) {
+    int64_t v;
+    if (!as_i64(k.aux64[0] & tmask, &v)) return FLSGPU_OK;
+    *mn = *mx = v; *known = 1;
+    return FLSGPU_OK;
+  }
+  const bool delta = k.scheme == FLS_S_DELTA;
+  if ((k.scheme != FLS_S_FFOR && !delta) || k.n_seg < 2 || k.seg[0].size < 16ull * r.n_vec) return FLSGPU_OK;
+  int fd = -1;
+  auto read_at = [&](uint64_t off, void *dst, size_t n) {  // bytes of the file: the host image, or the file itself
+    if (h->image) { memcpy(dst, h->image + off, n); return true; }
+    if (fd < 0) fd = open(h->path.c_str(), O_RDONLY);
+    return fd >= 0 && pread(fd, dst, n, (off_t)off) == (ssize_t)n;
+  };
+  struct Closer { int &fd; ~Closer() { if (fd >= 0) close(fd); } } closer{fd};
+  std::vector<uint64_t> hdr(2ull * r.n_vec);
+  if (!read_at(r.off + k.seg[0].off, hdr.data(), hdr.size() * 8)) return h->fail(FLSGPU_E_IO, "cannot read vector headers");
+  const int64_t tmax = is_signed ? (tb == 64 ? INT64_MAX : (int64_t)((1ull << (tb - 1)) - 1)) : (tb == 64 ? INT64_MAX : (int64_t)tmask);
+  const int64_t tmin = is_signed ? -tmax - 1 : 0;
+  __int128 lo = tmax, hi = tmin;
+  for (uint32_t v = 0; v < r.n_vec; ++v) {
+    const uint32_t bw = FLS_META_BW((uint32_t)(hdr[2 * v] >> 32));
+    if (bw >= tb) return FLSGPU_OK;  // the vector spans the whole type
+    const uint64_t base = hdr[2 * v + 1] & tmask, span = (1ull << bw) - 1ull;
+    if (!delta) {
+      // FFOR: values in [base, base + span]; the interval must not wrap in the column's own order
+      int64_t a;
+      if (!as_i64(base, &a)) return FLSGPU_OK;
+      lo = std::min<__int128>(lo, a);
+      hi = std::max<__int128>(hi, (__int128)a + span);
+    } else {
+      // DELTA: element r (1..T) of a lane = lane base + r deltas, every delta in [dmin, dmin + span] (signed)
+      const uint32_t ep = (uint32_t)hdr[2 * v];
+      uint8_t lb[128];
+      if (k.seg[1].size < 16ull * ep + 128u || !read_at(r.off + k.seg[1].off + 16ull * ep, lb, 128)) return FLSGPU_OK;
+      const int64_t dmin = tb == 64 ? (int64_t)base : (int64_t)(base << (64 - tb)) >> (64 - tb);
+      const __int128 dmax = (__int128)dmin + span;
+      const __int128 down = std::min<__int128>(dmin, (__int128)tb * dmin), up = std::max<__int128>(dmax, (__int128)tb * dmax);
+      for (uint32_t l = 0; l < 1024u / tb; ++l) {
+        uint64_t b = 0;
+        memcpy(&b, lb + l * (tb / 8), tb / 8);
+        int64_t a;
+        if (!as_i64(b, &a)) return FLSGPU_OK;
+        lo = std::min<__int128>(lo, (__int128)a + down);
+        hi = std::max<__int128>(hi, (__int128)a + up);
+      }
+    }
+  }
+  if (lo < tmin || hi > tmax) return FLSGPU_OK;  // the bounds leave the type: wrapping arithmetic, nothing to say
+  *mn = (int64_t)lo; *mx = (int64_t)hi; *known = 1;
+  return FLSGPU_OK;
+}
+
 int flsgpu_make_resident(flsgpu_t *h, uint32_t g0, uint32_t g1) {
   if (g0 > g1 || g1 > h->t.n_rg) return h->fail(FLSGPU_E_RANGE, "bad row-group range");
   if (int rc = ensure_ready(h)) return rc;

@@ -78,6 +78,10 @@ bool FastLanesFacade::setProjection(const std::vector<idx_t> &column_ids) {
 	return true;
 }
 
+idx_t FastLanesFacade::pruneRowGroups(const std::vector<flsgpu_host::ZonePredicate> &predicates) {
+	return pImpl->scanner.pruneRowGroups(predicates);
+}
+
 template <class T>
 static void CopyFixed(Vector &out, const flsgpu_host::ColumnSlice &s, idx_t rows) {
 	memcpy(FlatVector::GetData<T>(out), s.data, rows * sizeof(T));

@@ -2,6 +2,8 @@
 #include "fls_scan.hpp"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <future>
 
 namespace flsgpu_host {
@@ -42,12 +44,19 @@ struct FlsScanner::Impl {
     if (d.rc) d.err = flsgpu_last_error(h);
     return d;
   }
+  std::vector<uint8_t> skip;       // per row group: pruned by a zone predicate
+  uint32_t n_skipped = 0;
+  bool skipped(uint32_t g) const { return g < skip.size() && skip[g]; }
   void launch_ahead(flsgpu_batch_t *release_first) {
+    while (next_g < g_end && skipped(next_g)) ++next_g;
     if (next_g >= g_end) {
       if (release_first) flsgpu_batch_release(release_first);
       return;
     }
-    const uint32_t g0 = next_g, g1 = std::min(g_end, g0 + batch_rgs);
+    // the next contiguous run of row groups that survive pruning, at most one batch long
+    const uint32_t g0 = next_g;
+    uint32_t g1 = g0 + 1;
+    while (g1 < g_end && g1 - g0 < batch_rgs && !skipped(g1)) ++g1;
     next_g = g1;
     ahead = std::async(std::launch::async, [this, release_first, g0, g1] { return decode(release_first, g0, g1); });
   }
@@ -110,6 +119,7 @@ bool FlsScanner::open(const std::string &path, int device, uint32_t batch_rowgro
   if (batch_rowgroups) p->batch_rgs = batch_rowgroups;
   p->started = false;
   p->served = 0;
+  p->skip.clear(); p->n_skipped = 0;
   return true;
 }
 
@@ -143,10 +153,43 @@ bool FlsScanner::setProjection(const std::vector<uint32_t> &cols) {
 bool FlsScanner::setRowGroupRange(uint32_t g0, uint32_t g1) {
   if (!p->h || p->started || g0 > g1 || g1 > p->n_rg) { p->err = "bad row-group range"; return false; }
   p->g_begin = g0; p->g_end = g1;
+  p->skip.clear(); p->n_skipped = 0;
   p->rows_in_range = 0;
   for (uint32_t g = g0; g < g1; ++g) p->rows_in_range += flsgpu_rowgroup_rows(p->h, g);
   return true;
 }
+
+uint32_t FlsScanner::pruneRowGroups(const std::vector<ZonePredicate> &preds) {
+  if (!p->h || p->started) return 0;
+  p->skip.assign(p->n_rg, 0);
+  p->n_skipped = 0;
+  for (uint32_t g = p->g_begin; g < p->g_end; ++g) {
+    for (const ZonePredicate &z : preds) {
+      int64_t mn = 0, mx = 0;
+      int32_t known = 0;
+      if (z.col >= p->names.size() || flsgpu_rowgroup_minmax(p->h, g, z.col, &mn, &mx, &known) != FLSGPU_OK || !known) continue;
+      bool none = false;  // no value in [mn, mx] satisfies the predicate
+      switch (z.op) {
+        case ZONE_EQ: none = z.value < mn || z.value > mx; break;
+        case ZONE_NE: none = mn == mx && mn == z.value; break;
+        case ZONE_LT: none = mn >= z.value; break;
+        case ZONE_LE: none = mn > z.value; break;
+        case ZONE_GT: none = mx <= z.value; break;
+        case ZONE_GE: none = mx < z.value; break;
+      }
+      if (none) {
+        p->skip[g] = 1;
+        p->n_skipped++;
+        p->rows_in_range -= flsgpu_rowgroup_rows(p->h, g);
+        break;
+      }
+    }
+  }
+  if (getenv("FLS_SCAN_TRACE"))
+    fprintf(stderr, "fls_scan: skipped %u of %u row groups\n", p->n_skipped, p->g_end - p->g_begin);
+  return p->n_skipped;
+}
+uint32_t FlsScanner::rowGroupsSkipped() const { return p->n_skipped; }
 
 bool FlsScanner::next(uint64_t max_rows, uint64_t &rows, std::vector<ColumnSlice> &out) {
   rows = 0;

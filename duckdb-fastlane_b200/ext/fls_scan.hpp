@@ -27,6 +27,15 @@ struct ColumnSlice {
   const uint8_t *payload = nullptr;
 };
 
+// A comparison `column <op> constant` on an integer / DATE column, used to skip row groups whose bounds
+// (flsgpu_rowgroup_minmax: read off the FFOR / DELTA vector headers, no decode) cannot satisfy it.
+enum ZoneOp { ZONE_EQ, ZONE_NE, ZONE_LT, ZONE_LE, ZONE_GT, ZONE_GE };
+struct ZonePredicate {
+  uint32_t col = 0;  // file column id
+  ZoneOp op = ZONE_EQ;
+  int64_t value = 0;
+};
+
 class FlsScanner {
  public:
   FlsScanner();
@@ -53,6 +62,13 @@ class FlsScanner {
   bool setProjection(const std::vector<uint32_t> &cols);
   // Restrict the scan to row groups [g0, g1) — one shard of a multi-GPU / multi-thread scan.
   bool setRowGroupRange(uint32_t g0, uint32_t g1);
+
+  // Row-group skipping: a row group is dropped from the scan when one of the predicates
+  // (a conjunction) is false for every value its bounds allow.  The caller still applies the predicates to the rows
+  // it gets — this only saves the H2D copy and the decode of row groups that cannot contribute.  Call after
+  // setRowGroupRange / before the first next().  Returns the number of row groups skipped.
+  uint32_t pruneRowGroups(const std::vector<ZonePredicate> &preds);
+  uint32_t rowGroupsSkipped() const;
 
   // Next run of at most max_rows rows (never crossing a row-group boundary).  Returns false at the end of the
   // scan or on error (error() non-empty).  out[i] describes projected column i.

@@ -14,7 +14,7 @@
 //   * setProjection: projection pushdown (the reference's dead scanner sets the flag,
 //     /root/reference/src/scanner/scan_fastlanes.cpp:153, but never uses column_ids).
 // The writing half of the reference class (createFile / writeChunk / finalizeFile) is declared there and never
-// implemented; it is out of scope here.
+// implemented; COPY ... TO binds the writer's C ABI directly (ext/write_fastlane.cpp).
 //===----------------------------------------------------------------------===//
 #pragma once
 
@@ -24,6 +24,7 @@
 
 #include "duckdb/common/types.hpp"
 #include "duckdb/common/types/data_chunk.hpp"
+#include "fls_scan.hpp"
 
 namespace duckdb {
 
@@ -42,6 +43,9 @@ public:
 	std::vector<std::string> getColumnNames();
 	//! Projected file column ids, in output order; call between openFile and the first readNextChunk.
 	bool setProjection(const std::vector<idx_t> &column_ids);
+	//! Skip the row groups whose FFOR / DELTA bounds rule out `column <op> constant` (a conjunction); returns how
+	//! many were skipped.  The engine keeps the filters: this only avoids decoding what cannot match.
+	idx_t pruneRowGroups(const std::vector<flsgpu_host::ZonePredicate> &predicates);
 	//! Fills `result` with the next <= STANDARD_VECTOR_SIZE rows; false at the end of the file or on error.
 	bool readNextChunk(DataChunk &result);
 	void closeFile();

@@ -11,7 +11,11 @@
 //   * a LIST(VARCHAR) overload scans several files one after the other, `read_fls` is registered as an alias and
 //     `*.fls` / `*.fastlane` table names resolve through a replacement scan (reference
 //     intent at /root/reference/src/scanner/scan_fastlanes.cpp:151-185);
-//   * cardinality and scan progress are reported from the footer.
+//   * cardinality and scan progress are reported from the footer;
+//   * comparisons `column <op> constant` on integer / DATE columns are looked at (pushdown_complex_filter) and used
+//     to skip row groups whose FFOR / DELTA vector headers rule them out — the filters stay in the plan, only the
+//     decode of row groups that cannot match is saved (the reference leaves its filter flags
+//     off, /root/reference/src/scanner/scan_fastlanes.cpp:154-155).
 // MaxThreads stays 1 like the reference: the parallelism is on the GPU, behind the facade.
 #include "scan_fastlanes.hpp"
 
@@ -24,6 +28,11 @@
 #include "duckdb/parser/expression/constant_expression.hpp"
 #include "duckdb/parser/expression/function_expression.hpp"
 #include "duckdb/parser/tableref/table_function_ref.hpp"
+#include "duckdb/planner/expression/bound_between_expression.hpp"
+#include "duckdb/planner/expression/bound_columnref_expression.hpp"
+#include "duckdb/planner/expression/bound_comparison_expression.hpp"
+#include "duckdb/planner/expression/bound_constant_expression.hpp"
+#include "duckdb/planner/operator/logical_get.hpp"
 #include "duckdb/storage/statistics/node_statistics.hpp"
 #include "fastlanes_facade.hpp"
 
@@ -34,6 +43,7 @@ struct FastLanesBindData : public TableFunctionData {
 	vector<LogicalType> return_types;
 	vector<string> return_names;
 	idx_t total_rows = 0;
+	vector<flsgpu_host::ZonePredicate> zone_predicates; // from pushdown_complex_filter; file column ids
 };
 
 struct FastLanesScanState : public GlobalTableFunctionState {
@@ -64,6 +74,9 @@ static bool OpenNext(FastLanesScanState &state, const FastLanesBindData &bind, s
 		if (!state.projection.empty() && !facade->setProjection(state.projection)) {
 			err = facade->lastError();
 			return false;
+		}
+		if (!bind.zone_predicates.empty()) {
+			facade->pruneRowGroups(bind.zone_predicates);
 		}
 		state.facade = std::move(facade);
 		return true;
@@ -177,6 +190,83 @@ static double FastLanesProgress(ClientContext &context, const FunctionData *bind
 	return 100.0 * double(done) / double(bind_data.total_rows);
 }
 
+// `column <op> constant` (and `column BETWEEN a AND b`, which is what the optimizer makes of a two-sided range) with
+// integer / DATE constants -> zone predicates; everything stays in `filters`.
+static bool ZoneOperand(const LogicalGet &get, const FastLanesBindData &bind_data, Expression &col_e, Expression &const_e,
+                        flsgpu_host::ZonePredicate &z) {
+	if (col_e.GetExpressionClass() != ExpressionClass::BOUND_COLUMN_REF ||
+	    const_e.GetExpressionClass() != ExpressionClass::BOUND_CONSTANT) {
+		return false;
+	}
+	auto &col = col_e.Cast<BoundColumnRefExpression>();
+	auto &ids = get.GetColumnIds();
+	if (col.binding.table_index != get.table_index || col.binding.column_index >= ids.size() ||
+	    ids[col.binding.column_index].IsRowIdColumn()) {
+		return false;
+	}
+	const idx_t file_col = ids[col.binding.column_index].GetPrimaryIndex();
+	auto &v = const_e.Cast<BoundConstantExpression>().value;
+	if (v.IsNull() || file_col >= bind_data.return_types.size() || v.type() != bind_data.return_types[file_col]) {
+		return false;
+	}
+	z.col = (uint32_t)file_col;
+	switch (v.type().id()) {
+	case LogicalTypeId::TINYINT:
+	case LogicalTypeId::SMALLINT:
+	case LogicalTypeId::INTEGER:
+	case LogicalTypeId::BIGINT:
+	case LogicalTypeId::UTINYINT:
+	case LogicalTypeId::USMALLINT:
+	case LogicalTypeId::UINTEGER: z.value = v.GetValue<int64_t>(); return true;
+	case LogicalTypeId::DATE: z.value = DateValue::Get(v).days; return true;
+	default: return false;
+	}
+}
+
+static void FastLanesComplexFilter(ClientContext &context, LogicalGet &get, FunctionData *bind_data_p,
+                                   vector<unique_ptr<Expression>> &filters) {
+	auto &bind_data = bind_data_p->Cast<FastLanesBindData>();
+	bind_data.zone_predicates.clear();
+	for (auto &f : filters) {
+		flsgpu_host::ZonePredicate z;
+		if (f->GetExpressionClass() == ExpressionClass::BOUND_BETWEEN) {
+			auto &bt = f->Cast<BoundBetweenExpression>();
+			if (ZoneOperand(get, bind_data, *bt.input, *bt.lower, z)) {
+				z.op = bt.lower_inclusive ? flsgpu_host::ZONE_GE : flsgpu_host::ZONE_GT;
+				bind_data.zone_predicates.push_back(z);
+			}
+			if (ZoneOperand(get, bind_data, *bt.input, *bt.upper, z)) {
+				z.op = bt.upper_inclusive ? flsgpu_host::ZONE_LE : flsgpu_host::ZONE_LT;
+				bind_data.zone_predicates.push_back(z);
+			}
+			continue;
+		}
+		if (f->GetExpressionClass() != ExpressionClass::BOUND_COMPARISON) {
+			continue;
+		}
+		auto &cmp = f->Cast<BoundComparisonExpression>();
+		auto type = cmp.GetExpressionType();
+		Expression *l = cmp.left.get(), *r = cmp.right.get();
+		if (l->GetExpressionClass() == ExpressionClass::BOUND_CONSTANT) {
+			std::swap(l, r);
+			type = FlipComparisonExpression(type);
+		}
+		if (!ZoneOperand(get, bind_data, *l, *r, z)) {
+			continue;
+		}
+		switch (type) {
+		case ExpressionType::COMPARE_EQUAL: z.op = flsgpu_host::ZONE_EQ; break;
+		case ExpressionType::COMPARE_NOTEQUAL: z.op = flsgpu_host::ZONE_NE; break;
+		case ExpressionType::COMPARE_LESSTHAN: z.op = flsgpu_host::ZONE_LT; break;
+		case ExpressionType::COMPARE_LESSTHANOREQUALTO: z.op = flsgpu_host::ZONE_LE; break;
+		case ExpressionType::COMPARE_GREATERTHAN: z.op = flsgpu_host::ZONE_GT; break;
+		case ExpressionType::COMPARE_GREATERTHANOREQUALTO: z.op = flsgpu_host::ZONE_GE; break;
+		default: continue;
+		}
+		bind_data.zone_predicates.push_back(z);
+	}
+}
+
 static unique_ptr<TableRef> FastLanesReplacementScan(ClientContext &context, ReplacementScanInput &input,
                                                      optional_ptr<ReplacementScanData> data) {
 	auto table_name = ReplacementScan::GetFullPath(input);
@@ -198,6 +288,7 @@ void ScanFastLanes::Register(DatabaseInstance &db) {
 		fn.projection_pushdown = true;
 		fn.cardinality = FastLanesCardinality;
 		fn.table_scan_progress = FastLanesProgress;
+		fn.pushdown_complex_filter = FastLanesComplexFilter;
 		ExtensionUtil::RegisterFunction(db, fn);
 		// a list of paths as well, e.g. ['a.fls', 'b.fls'] (/root/reference/src/scanner/scan_fastlanes.cpp:164-165)
 		fn.arguments = {LogicalType::LIST(LogicalType::VARCHAR)};

@@ -85,6 +85,7 @@ def lib():
     L.flsgpu_rowgroup_rows.restype = u32
     L.flsgpu_schema.argtypes = [vp, C.POINTER(u32), C.POINTER(C.POINTER(C.c_char_p)), C.POINTER(C.POINTER(C.c_int32))]
     L.flsgpu_chunk_info.argtypes = [vp, u32, u32, C.POINTER(C.c_int32), C.POINTER(u64)]
+    L.flsgpu_rowgroup_minmax.argtypes = [vp, u32, u32, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
     L.flsgpu_make_resident.argtypes = [vp, u32, u32]
     L.flsgpu_decode.argtypes = [vp, u32, u32, C.POINTER(u32), u32, u32, C.POINTER(vp)]
     L.flsgpu_batch_num_columns.argtypes = [vp]
@@ -222,6 +223,12 @@ class Reader:
         s, b = C.c_int32(), C.c_uint64()
         self._check(lib().flsgpu_chunk_info(self.h, g, c, C.byref(s), C.byref(b)))
         return s.value, b.value
+
+    def rowgroup_minmax(self, g, c):
+        """(min, max) bounds of an integer / DATE column in row group g read off the compressed form, or None."""
+        mn, mx, known = C.c_int64(), C.c_int64(), C.c_int32()
+        self._check(lib().flsgpu_rowgroup_minmax(self.h, g, c, C.byref(mn), C.byref(mx), C.byref(known)))
+        return (mn.value, mx.value) if known.value else None
 
     def make_resident(self, g0=0, g1=None):
         self._check(lib().flsgpu_make_resident(self.h, g0, self.n_rowgroups if g1 is None else g1))

@@ -124,6 +124,13 @@ uint32_t flsgpu_rowgroup_rows(const flsgpu_t *h, uint32_t rg);
 int flsgpu_schema(const flsgpu_t *h, uint32_t *n_cols, const char *const **names, const int32_t **types);
 /* scheme (enum fls_scheme) and segment bytes of one column chunk */
 int flsgpu_chunk_info(const flsgpu_t *h, uint32_t rg, uint32_t col, int32_t *scheme, uint64_t *bytes);
+/* Bounds of an integer / DATE column inside one row group, read off the compressed form: an FFOR vector holds
+ * values in [base, base + 2^W), a CONSTANT chunk one value — the per-vector headers are a zone map that costs no
+ * decode (row-group skipping for the filters the reference leaves switched off,
+ * /root/reference/src/scanner/scan_fastlanes.cpp:154-155).  Needs no CUDA device.  *known = 1 and min <= every
+ * value <= max (signed order for signed types and DATE; unsigned types are reported when they fit int64), or
+ * *known = 0 when the chunk's scheme gives no bounds. */
+int flsgpu_rowgroup_minmax(flsgpu_t *h, uint32_t rg, uint32_t col, int64_t *min, int64_t *max, int32_t *known);
 
 /* ---- decode ------------------------------------------------------------------------------------------- */
 /* Stage the compressed bytes of row groups [g0,g1) into HBM and keep them until close / the next call. */

@@ -66,3 +66,47 @@ def test_decode_without_gpu_fails_loudly():
 def test_product_does_not_link_the_oracle():
     out = os.popen("ldd %s; nm -D --defined-only %s" % (flsgpu.lib_path(), flsgpu.lib_path())).read()
     assert "fls_oracle" not in out and "flso_" not in out and "emul_" not in out
+
+
+def test_rowgroup_minmax_bounds_hold_without_a_gpu():
+    """flsgpu_rowgroup_minmax reads FFOR / DELTA / CONSTANT bounds off the vector headers: no CUDA, and the bounds
+    must contain every value of the row group (checked against the source columns)."""
+    import numpy as np
+    import synth
+    import flsgpu
+    import fls_writer as W
+    n = 3 * 65536 + 1000
+    cols = synth.lineitem(n, seed=5)
+    img = synth.encode(cols, synth.LINEITEM_NAMES, synth.LINEITEM_TYPES)
+    with flsgpu.Reader.from_image(img) as rd:
+        known = 0
+        for c, src in enumerate(cols):
+            for g in range(rd.n_rowgroups):
+                b = rd.rowgroup_minmax(g, c)
+                if isinstance(src, np.ndarray) and src.dtype.kind in "iu":
+                    part = src[g * 65536:(g + 1) * 65536].astype(np.int64)
+                    scheme, _ = rd.chunk_info(g, c)
+                    if scheme in (W.FFOR, W.DELTA, W.CONSTANT):
+                        assert b is not None, (c, g, scheme)
+                    if b is not None:
+                        known += 1
+                        assert b[0] <= part.min() and part.max() <= b[1], (c, g, b, part.min(), part.max())
+                        if scheme == W.FFOR:   # one vector's bound is at most 2x its range: never wider than the type
+                            assert b[1] - b[0] <= 2 * (int(part.max()) - int(part.min())) + 2
+                else:
+                    assert b is None            # doubles and strings have no integer bounds
+        assert known >= 7 * rd.n_rowgroups      # 4 keys + 3 dates
+    # negative values, unsigned columns, wide vectors
+    r = np.random.default_rng(3)
+    a = r.integers(-5000, 5000, 70000).astype(np.int32)
+    u = r.integers(0, 2 ** 32, 70000, dtype=np.uint64).astype(np.uint32)
+    s16 = np.sort(r.integers(-30000, 30000, 70000)).astype(np.int16)
+    img = W.write_table([a, u, s16], force=[W.FFOR, W.FFOR, W.DELTA])
+    with flsgpu.Reader.from_image(img) as rd:
+        for g in range(2):
+            sl = slice(g * 65536, (g + 1) * 65536)
+            b = rd.rowgroup_minmax(g, 0)
+            assert b is not None and b[0] <= a[sl].min() and a[sl].max() <= b[1] and b[0] >= -2 ** 31
+            assert rd.rowgroup_minmax(g, 1) is None or rd.rowgroup_minmax(g, 1)[1] >= int(u[sl].max())
+            b = rd.rowgroup_minmax(g, 2)
+            assert b is None or (b[0] <= s16[sl].min() and s16[sl].max() <= b[1])

@@ -23,13 +23,17 @@ CHECK = os.path.join(EXT, "duckdb_sql_check")
 pytestmark = pytest.mark.skipif(not os.path.exists(CHECK), reason="ext/duckdb_sql_check not built (needs the DuckDB sources)")
 
 
-def sql(*stmts):
+def sql(*stmts, trace=None):
     env = dict(os.environ)
+    if trace is not None:
+        env["FLS_SCAN_TRACE"] = "1"
     env["LD_LIBRARY_PATH"] = os.path.join(EXT, "_duckdb") + ":" + os.path.join(ROOT, "duckdb-fastlane_b200") + ":" + \
         env.get("LD_LIBRARY_PATH", "")
     r = subprocess.run([CHECK] + list(stmts), capture_output=True, text=True, timeout=600, env=env)
     out = [json.loads(line) for line in r.stdout.strip().splitlines() if line.startswith("{")]
     assert len(out) == len(stmts), r.stdout + r.stderr
+    if trace is not None:
+        trace.extend(line for line in r.stderr.splitlines() if line.startswith("fls_scan:"))
     return out
 
 
@@ -166,3 +170,27 @@ def test_copy_then_read_fls_round_trip(tmp_path):
               % (_COPY_SRC, path))
     assert res[1]["rows"] == res[2]["rows"], (res[1], res[2])
     assert res[3]["rows"] == [["0"]], res[3]
+
+
+@pytest.mark.gpu
+def test_row_groups_are_skipped_by_their_compressed_bounds(tmp_path):
+    """comparisons on integer / DATE columns skip the row groups whose FFOR / DELTA vector
+    headers rule them out; the filter itself stays with DuckDB, so results equal the unfiltered source."""
+    path = str(tmp_path / "sorted.fls")
+    src = ("SELECT i::BIGINT AS k, (i % 1000)::INTEGER AS m, DATE '2020-01-01' + (i // 4096)::INTEGER AS d, "
+           "'row_' || i AS s FROM range(0, 400000) t(i)")
+    trace = []
+    res = sql("COPY (%s) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 16384)" % (src, path),
+              "SELECT count(*), sum(k), min(s), max(s) FROM read_fls('%s') WHERE k >= 100000 AND k < 120000" % path,
+              "SELECT count(*), sum(k), min(s), max(s) FROM (%s) WHERE k >= 100000 AND k < 120000" % src,
+              "SELECT count(*), sum(m) FROM read_fls('%s') WHERE d = DATE '2020-02-01'" % path,
+              "SELECT count(*), sum(m) FROM (%s) WHERE d = DATE '2020-02-01'" % src,
+              "SELECT count(*) FROM read_fls('%s') WHERE m = 7" % path,          # every row group holds m = 7: none skipped
+              "SELECT count(*) FROM read_fls('%s') WHERE k > 1000000" % path,    # nothing qualifies: all skipped
+              trace=trace)
+    assert res[1]["rows"] == res[2]["rows"] and res[1]["rows"][0][0] == "20000"
+    assert res[3]["rows"] == res[4]["rows"] and res[3]["rows"][0][0] == "4096"
+    assert res[5]["rows"] == [["400"]] and res[6]["rows"] == [["0"]]
+    skipped = [int(t.split()[2]) for t in trace]
+    total = [int(t.split()[4]) for t in trace]
+    assert total == [25, 25, 25, 25] and skipped == [23, 24, 0, 25], trace
