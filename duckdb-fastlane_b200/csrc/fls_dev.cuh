@@ -55,6 +55,9 @@ static inline uint32_t fls_prmt(uint32_t a, uint32_t b, uint32_t sel) {
 }
 template <typename V> static inline void fls_st128(void *p, const V &v) { memcpy(p, &v, 16); }
 template <typename V> static inline V fls_lds128(const void *p) { V v; memcpy(&v, p, 16); return v; }
+struct fls_u2 { uint32_t x, y; };
+static inline fls_u2 fls_lds64(const void *p) { fls_u2 v; memcpy(&v, p, 8); return v; }
+static inline void fls_sts64(void *p, uint32_t lo, uint32_t hi) { memcpy(p, &lo, 4); memcpy((uint8_t *)p + 4, &hi, 4); }
 static inline void fls_st64(void *p, uint32_t lo, uint32_t hi) { memcpy(p, &lo, 4); memcpy((uint8_t *)p + 4, &hi, 4); }
 static inline uint32_t fls_min(uint32_t a, uint32_t b) { return a < b ? a : b; }
 static inline uint32_t fls_max(uint32_t a, uint32_t b) { return a > b ? a : b; }
@@ -92,6 +95,9 @@ FLS_DEV uint32_t fls_prmt(uint32_t a, uint32_t b, uint32_t sel) { return __byte_
 // streaming 128-bit store: decoded columns are written once and not re-read by this kernel
 template <typename V> FLS_DEV void fls_st128(void *p, const V &v) { __stcs((V *)p, v); }
 template <typename V> FLS_DEV V fls_lds128(const void *p) { return *(const V *)p; }
+typedef uint2 fls_u2;
+FLS_DEV fls_u2 fls_lds64(const void *p) { return *(const uint2 *)p; }
+FLS_DEV void fls_sts64(void *p, uint32_t lo, uint32_t hi) { *(uint2 *)p = make_uint2(lo, hi); }
 FLS_DEV void fls_st64(void *p, uint32_t lo, uint32_t hi) { __stcs((uint2 *)p, make_uint2(lo, hi)); }  // 8-byte aligned
 FLS_DEV uint32_t fls_min(uint32_t a, uint32_t b) { return min(a, b); }
 FLS_DEV uint32_t fls_max(uint32_t a, uint32_t b) { return max(a, b); }

@@ -260,8 +260,10 @@ struct VecSTRDICT {
     FLS_GROUP_SYNC(nthreads);
     const uint32_t P = (hdr[1] + 7u) >> 3;
     if (P == 0 || n_dict * P * 16u > TAB_BYTES) return;
-    // small tables are kept 8 times (entry i, copy r at i * 128 + r * 16; lane t reads copy t & 7): the eight lanes
-    // of a 128-bit load phase then never share a bank group, whatever entries they look up
+    // small tables keep only the pieces' 8 bytes, 16 times (piece i, copy r at i * 128 + r * 8; lane t reads copy
+    // t & 15 with one 64-bit load): the sixteen lanes of a 64-bit load phase never share a bank, whatever pieces they
+    // look up, and a lookup costs 2 shared-memory wavefronts instead of 4 — a piece's length and last four bytes
+    // follow from the string's length, which the lane already holds
     const uint32_t sh = n_dict * P * 128u <= TAB_BYTES ? 7u : 4u;
     for (uint32_t i0 = 0; i0 < n_dict * P; i0 += B * nthreads) {
       uint32_t a[B], pos[B], Lp[B];
@@ -289,7 +291,7 @@ struct VecSTRDICT {
         const uint64_t x = bs ? (lo[j] >> bs) | (hi[j] << (64u - bs)) : lo[j];
         if (i < n_dict * P) {
           const fls_u4 en = fls_piece_entry(x, Lp[j]);
-          if (sh == 7u) { for (uint32_t r = 0; r < 8u; ++r) *(fls_u4 *)(bsm + TAB + 128u * i + 16u * r) = en; }
+          if (sh == 7u) { for (uint32_t r = 0; r < 16u; ++r) fls_sts64(bsm + TAB + 128u * i + 8u * r, en.x, en.y); }
           else *(fls_u4 *)(bsm + TAB + 16u * i) = en;
         }
       }
@@ -298,6 +300,27 @@ struct VecSTRDICT {
   }
   // the 8 strings of a lane, P pieces each: table loads are issued in batches of up to 8 entries BEFORE the
   // pushes that consume them (the compiler cannot hoist shared loads over the pushes' shared stores itself)
+  // piece pc of a string of length L8 / 8, from the replicated 8-byte table
+  FLS_MEM static fls_u4 piece_rep(const uint8_t *tabr, uint32_t idx, uint32_t pc, uint32_t L8) {
+    const fls_u2 v = fls_lds64(tabr + 128u * idx);
+    const uint32_t Lp8 = L8 > 64u * pc ? fls_min(64u, L8 - 64u * pc) : 0u;
+    fls_u4 e;
+    e.x = v.x; e.y = v.y; e.w = Lp8;
+    e.z = fls_shf_rc(v.x, v.y, fls_max(Lp8, 32u) - 32u);  // last four bytes: lo for <= 4 bytes, else (lo:hi) >> 8(L - 4)
+    return e;
+  }
+  template <uint32_t P> FLS_MEM static void push_strings_rep(FlsPush &p, const uint8_t *tabr, const uint32_t (&d)[8], const uint32_t (&len)[8]) {
+    constexpr uint32_t SPB = P == 1 ? 8u : P == 2 ? 4u : 2u;  // strings per batch
+#pragma unroll
+    for (uint32_t s0 = 0; s0 < 8u; s0 += SPB) {
+      fls_u4 e[SPB * P];
+#pragma unroll
+      for (uint32_t i = 0; i < SPB; ++i)
+#pragma unroll
+        for (uint32_t pc = 0; pc < P; ++pc) e[i * P + pc] = piece_rep(tabr, d[s0 + i] * P + pc, pc, 8u * len[s0 + i]);
+      p.push_all(e);
+    }
+  }
   template <uint32_t P> FLS_MEM static void push_strings(FlsPush &p, const uint8_t *tab, uint32_t sh, const uint32_t (&d)[8]) {
     constexpr uint32_t SPB = P == 1 ? 8u : P == 2 ? 4u : 2u;  // strings per batch
 #pragma unroll
@@ -506,18 +529,27 @@ struct VecSTRDICT {
         if (staged) {
           FlsPush p;
           p.init(stg, hh + FLS_AT(run));
-          const uint8_t *tabr = tab + (sh == 7u ? 16u * (t & 7u) : 0u);  // this lane's copy of the table
+          const uint8_t *tabr = tab + 8u * (t & 15u);  // this lane's copy of a replicated table
           if (U == 1u) push_uniform<1>(p, tab, sh, d);
           else if (U == 2u) push_uniform<2>(p, tab, sh, d);
           else if (U == 4u) push_uniform<4>(p, tab, sh, d);
-          else switch (P) {
-            case 1: push_strings<1>(p, tabr, sh, d); break;
-            case 2: push_strings<2>(p, tabr, sh, d); break;
-            case 3: push_strings<3>(p, tabr, sh, d); break;
-            case 4: push_strings<4>(p, tabr, sh, d); break;
+          else if (sh == 7u) switch (P) {
+            case 1: push_strings_rep<1>(p, tabr, d, len); break;
+            case 2: push_strings_rep<2>(p, tabr, d, len); break;
+            case 3: push_strings_rep<3>(p, tabr, d, len); break;
+            case 4: push_strings_rep<4>(p, tabr, d, len); break;
             default:
               for (uint32_t i = 0; i < 8u; ++i)
-                for (uint32_t pc = 0; pc < P; ++pc) p.push(fls_lds128<fls_u4>(tabr + ((d[i] * P + pc) << sh)));
+                for (uint32_t pc = 0; pc < P; ++pc) p.push(piece_rep(tabr, d[i] * P + pc, pc, 8u * len[i]));
+          }
+          else switch (P) {
+            case 1: push_strings<1>(p, tab, sh, d); break;
+            case 2: push_strings<2>(p, tab, sh, d); break;
+            case 3: push_strings<3>(p, tab, sh, d); break;
+            case 4: push_strings<4>(p, tab, sh, d); break;
+            default:
+              for (uint32_t i = 0; i < 8u; ++i)
+                for (uint32_t pc = 0; pc < P; ++pc) p.push(fls_lds128<fls_u4>(tab + ((d[i] * P + pc) << sh)));
           }
           FLS_AT(ps) = p;
         } else {
