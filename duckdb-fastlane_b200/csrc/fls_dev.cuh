@@ -47,6 +47,8 @@ static inline uint32_t fls_shf_l(uint32_t lo, uint32_t hi, uint32_t s) {
 static inline uint32_t fls_shf_rc(uint32_t lo, uint32_t hi, uint32_t s) {
   return s >= 32u ? hi : (s ? (lo >> s) | (hi << (32u - s)) : lo);
 }
+// x << min(n, 32): 0 for n >= 32
+static inline uint32_t fls_shl_c(uint32_t x, uint32_t n) { return n >= 32u ? 0u : x << n; }
 static inline uint32_t fls_prmt(uint32_t a, uint32_t b, uint32_t sel) {
   const uint64_t v = ((uint64_t)b << 32) | a;
   uint32_t r = 0;
@@ -91,6 +93,7 @@ template <typename T> FLS_DEV T fls_ldg(const T *p) { return __ldg(p); }
 FLS_DEV uint32_t fls_shf_r(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_r(lo, hi, s); }
 FLS_DEV uint32_t fls_shf_l(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_l(lo, hi, s); }
 FLS_DEV uint32_t fls_shf_rc(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_rc(lo, hi, s); }
+FLS_DEV uint32_t fls_shl_c(uint32_t x, uint32_t n) { return __funnelshift_lc(0u, x, n); }  // x << min(n, 32)
 FLS_DEV uint32_t fls_prmt(uint32_t a, uint32_t b, uint32_t sel) { return __byte_perm(a, b, sel); }
 // streaming 128-bit store: decoded columns are written once and not re-read by this kernel
 template <typename V> FLS_DEV void fls_st128(void *p, const V &v) { __stcs((V *)p, v); }

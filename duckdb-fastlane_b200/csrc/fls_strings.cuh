@@ -653,9 +653,11 @@ struct VecSTRFSST {
     for (uint32_t k = 0; k < NW; ++k) ff[k] = ff_bytes(w[k]);
     if (MASK) {
 #pragma unroll
+      const uint32_t s8 = 8u * s, e8 = 8u * e;
       for (uint32_t k = 0; k < NW; ++k) {
-        const uint32_t ek = e > 4u * k ? fls_min(4u, e - 4u * k) : 0u, sk = s > 4u * k ? fls_min(4u, s - 4u * k) : 0u;
-        const uint32_t vm = (ek >= 4u ? ~0u : ((1u << (8u * ek)) - 1u)) & ~(sk >= 4u ? ~0u : ((1u << (8u * sk)) - 1u));
+        // bytes [s, e) of the window that fall into word k: (all ones << bits below s) & ~(all ones << bits below e),
+        // the shifts clamped at 32
+        const uint32_t vm = fls_shl_c(~0u, fls_max(s8, 32u * k) - 32u * k) & ~fls_shl_c(~0u, fls_max(e8, 32u * k) - 32u * k);
         ff[k] &= vm;
         w[k] |= ~vm;  // 0xFF and not a marker: the empty entry
       }
@@ -731,6 +733,12 @@ struct VecSTRFSST {
       else { uint64_t s = fls_ldg(gsym + c); for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(glen + c)); b; --b) { *o++ = (uint8_t)s; s >>= 8; } }
     }
   }
+  // value (row, lane) of a packed u32 vector, 1 <= W <= 32: two loads and one funnel shift, no branch
+  FLS_MEM static uint32_t extract32(const uint32_t *pk, uint32_t W, uint32_t row, uint32_t lane) {
+    const uint32_t bit = row * W, k = bit >> 5;
+    const uint32_t lo = pk[k * 32u + lane], hi = pk[fls_min(k + 1u, W - 1u) * 32u + lane];
+    return fls_shf_r(lo, hi, bit) & (W >= 32u ? 0xFFFFFFFFu : ((1u << W) - 1u));
+  }
   // DELTA u32 chain of lane t over a staged end-offset stream.  Writes {lane base, end 0 .. end 30} + add to the
   // 32 aligned slots line[0..31] (slot i = start of string i; end 31 is the next lane's base) and the 32 ends,
   // relative to `rel0`, as 16-bit values into e16 (padded original order).  Returns the lane's last end.
@@ -745,7 +753,7 @@ struct VecSTRFSST {
       x[0] = acc;
 #pragma unroll
       for (uint32_t j = 0; j < 4u; ++j)
-        x[j + 1u] = x[j] + (bw ? fls_extract<uint32_t>(pk, bw, fls_chain_row<32>(r4 + j), t) : 0u) + base;
+        x[j + 1u] = x[j] + (bw ? extract32(pk, bw, fls_chain_row<32>(r4 + j), t) : 0u) + base;
       acc = x[4];
       if (line) {
         fls_u4 o;
