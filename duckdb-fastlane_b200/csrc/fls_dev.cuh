@@ -194,6 +194,14 @@ struct FlsWarp {
 template <typename T> FLS_DEV T fls_extract(const T *sm, uint32_t W, uint32_t row, uint32_t lane) {
   constexpr uint32_t TB = sizeof(T) * 8u, L = 1024u / TB;
   const uint32_t bit = row * W, k = bit / TB, s = bit % TB;
+  if (sizeof(T) >= 4) {
+    // branch-free: the word holding the value's first bit and the next one (clamped: it is only used when the value
+    // straddles), joined by a funnel shift
+    const T lo = sm[k * L + lane], hi = sm[fls_min(k + 1u, W - 1u) * L + lane];
+    if (sizeof(T) == 4) return (T)(fls_shf_r((uint32_t)lo, (uint32_t)hi, s) & (W >= 32u ? 0xFFFFFFFFu : ((1u << W) - 1u)));
+    const uint64_t x = ((uint64_t)lo >> s) | (((uint64_t)hi << 1) << (63u - s));  // hi << (64 - s), 0 for s == 0
+    return (T)(W < 64u ? x & ((1ull << W) - 1ull) : x);
+  }
   uint64_t x = (uint64_t)sm[k * L + lane] >> s;
   if (s + W > TB) x |= (uint64_t)sm[(k + 1u) * L + lane] << (TB - s);
   if (W < 64u) x &= (1ull << W) - 1ull;
