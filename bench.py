@@ -112,7 +112,7 @@ def dist_setup(args):
         import torch
         import torch.distributed as dist_
         torch.cuda.set_device(local)
-        dist_.init_process_group("nccl")
+        dist_.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist = dist_
     return rank, world, local, dist
 
