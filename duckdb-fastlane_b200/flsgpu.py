@@ -181,7 +181,7 @@ class Reader:
         names = C.POINTER(C.c_char_p)()
         types = C.POINTER(C.c_int32)()
         L.flsgpu_schema(handle, C.byref(n), C.byref(names), C.byref(types))
-        self.names = [names[i].decode() for i in range(n.value)]
+        self.names = [names[i].decode("utf-8", "replace") for i in range(n.value)]
         self.types = [types[i] for i in range(n.value)]
 
     @staticmethod
