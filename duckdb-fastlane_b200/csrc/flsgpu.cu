@@ -443,6 +443,46 @@ int flsgpu_rowgroup_minmax(flsgpu_t *h, uint32_t rg, uint32_t col, int64_t *mn, 
   return FLSGPU_OK;
 }
 
+int flsgpu_rowgroup_dict_contains(flsgpu_t *h, uint32_t rg, uint32_t col, const uint8_t *bytes, uint64_t len,
+                                  int32_t *found, int32_t *known) {
+  if (!known || !found || (!bytes && len)) return h->fail(FLSGPU_E_RANGE, "null argument");
+  *known = 0; *found = 0;
+  if (rg >= h->t.n_rg || col >= h->t.n_cols) return h->fail(FLSGPU_E_RANGE, "bad row group / column id");
+  if (fls_type_bits(h->t.types[col])) return FLSGPU_OK;  // not a string column
+  const fls_colchunk &k = h->t.chunk(rg, col);
+  const fls_rowgroup &r = h->t.rgs[rg];
+  int fd = -1;
+  auto read_at = [&](uint64_t off, void *dst, size_t n) {
+    if (!n) return true;
+    if (h->image) { memcpy(dst, h->image + off, n); return true; }
+    if (fd < 0) fd = open(h->path.c_str(), O_RDONLY);
+    return fd >= 0 && pread(fd, dst, n, (off_t)off) == (ssize_t)n;
+  };
+  struct Closer { int &fd; ~Closer() { if (fd >= 0) close(fd); } } closer{fd};
+  if (k.scheme == FLS_S_STR_CONSTANT) {
+    if (k.n_seg < 1 || k.seg[0].size < k.aux32) return FLSGPU_OK;
+    *known = 1;
+    if (k.aux32 != len) return FLSGPU_OK;
+    std::vector<uint8_t> v(len);
+    if (!read_at(r.off + k.seg[0].off, v.data(), len)) { *known = 0; return h->fail(FLSGPU_E_IO, "cannot read the constant"); }
+    *found = !len || memcmp(v.data(), bytes, len) == 0;
+    return FLSGPU_OK;
+  }
+  // STR_DICT: seg[2] = entry offsets u32[n + 1], seg[3] = entry bytes; dictionaries beyond 64 MiB are left alone
+  const uint64_t n = k.aux32;
+  if (k.scheme != FLS_S_STR_DICT || k.n_seg < 4 || k.seg[2].size < 4ull * (n + 1) || k.seg[3].size > (64ull << 20)) return FLSGPU_OK;
+  std::vector<uint32_t> off(n + 1);
+  std::vector<uint8_t> dict(k.seg[3].size);
+  if (!read_at(r.off + k.seg[2].off, off.data(), 4ull * (n + 1)) || !read_at(r.off + k.seg[3].off, dict.data(), dict.size()))
+    return h->fail(FLSGPU_E_IO, "cannot read the dictionary");
+  for (uint64_t i = 0; i < n; ++i)
+    if (off[i] > off[i + 1] || off[i + 1] > dict.size()) return FLSGPU_OK;  // a dictionary that lies says nothing
+  *known = 1;
+  for (uint64_t i = 0; i < n && !*found; ++i)
+    *found = off[i + 1] - off[i] == len && (!len || memcmp(dict.data() + off[i], bytes, len) == 0);
+  return FLSGPU_OK;
+}
+
 int flsgpu_make_resident(flsgpu_t *h, uint32_t g0, uint32_t g1) {
   if (g0 > g1 || g1 > h->t.n_rg) return h->fail(FLSGPU_E_RANGE, "bad row-group range");
   if (int rc = ensure_ready(h)) return rc;

@@ -167,6 +167,17 @@ uint32_t FlsScanner::pruneRowGroups(const std::vector<ZonePredicate> &preds) {
     for (const ZonePredicate &z : preds) {
       int64_t mn = 0, mx = 0;
       int32_t known = 0;
+      if (z.is_text) {
+        int32_t found = 0;
+        if (z.op != ZONE_EQ || z.col >= p->names.size() ||
+            flsgpu_rowgroup_dict_contains(p->h, g, z.col, (const uint8_t *)z.text.data(), z.text.size(), &found, &known) != FLSGPU_OK ||
+            !known || found)
+          continue;
+        p->skip[g] = 1;
+        p->n_skipped++;
+        p->rows_in_range -= flsgpu_rowgroup_rows(p->h, g);
+        break;
+      }
       if (z.col >= p->names.size() || flsgpu_rowgroup_minmax(p->h, g, z.col, &mn, &mx, &known) != FLSGPU_OK || !known) continue;
       bool none = false;  // no value in [mn, mx] satisfies the predicate
       switch (z.op) {

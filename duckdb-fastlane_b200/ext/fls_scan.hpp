@@ -34,6 +34,9 @@ struct ZonePredicate {
   uint32_t col = 0;  // file column id
   ZoneOp op = ZONE_EQ;
   int64_t value = 0;
+  // string columns: `column = text` against the row group's dictionary (flsgpu_rowgroup_dict_contains); op is ZONE_EQ
+  bool is_text = false;
+  std::string text;
 };
 
 class FlsScanner {

@@ -191,7 +191,8 @@ static double FastLanesProgress(ClientContext &context, const FunctionData *bind
 }
 
 // `column <op> constant` (and `column BETWEEN a AND b`, which is what the optimizer makes of a two-sided range) with
-// integer / DATE constants -> zone predicates; everything stays in `filters`.
+// integer / DATE constants -> zone predicates, `column = 'text'` -> a dictionary predicate; everything stays in
+// `filters`.
 static bool ZoneOperand(const LogicalGet &get, const FastLanesBindData &bind_data, Expression &col_e, Expression &const_e,
                         flsgpu_host::ZonePredicate &z) {
 	if (col_e.GetExpressionClass() != ExpressionClass::BOUND_COLUMN_REF ||
@@ -219,6 +220,10 @@ static bool ZoneOperand(const LogicalGet &get, const FastLanesBindData &bind_dat
 	case LogicalTypeId::USMALLINT:
 	case LogicalTypeId::UINTEGER: z.value = v.GetValue<int64_t>(); return true;
 	case LogicalTypeId::DATE: z.value = DateValue::Get(v).days; return true;
+	case LogicalTypeId::VARCHAR:  // `column = 'text'` is checked against the row group's dictionary
+		z.is_text = true;
+		z.text = StringValue::Get(v);
+		return true;
 	default: return false;
 	}
 }
@@ -231,11 +236,11 @@ static void FastLanesComplexFilter(ClientContext &context, LogicalGet &get, Func
 		flsgpu_host::ZonePredicate z;
 		if (f->GetExpressionClass() == ExpressionClass::BOUND_BETWEEN) {
 			auto &bt = f->Cast<BoundBetweenExpression>();
-			if (ZoneOperand(get, bind_data, *bt.input, *bt.lower, z)) {
+			if (ZoneOperand(get, bind_data, *bt.input, *bt.lower, z) && !z.is_text) {
 				z.op = bt.lower_inclusive ? flsgpu_host::ZONE_GE : flsgpu_host::ZONE_GT;
 				bind_data.zone_predicates.push_back(z);
 			}
-			if (ZoneOperand(get, bind_data, *bt.input, *bt.upper, z)) {
+			if (ZoneOperand(get, bind_data, *bt.input, *bt.upper, z) && !z.is_text) {
 				z.op = bt.upper_inclusive ? flsgpu_host::ZONE_LE : flsgpu_host::ZONE_LT;
 				bind_data.zone_predicates.push_back(z);
 			}
@@ -262,6 +267,9 @@ static void FastLanesComplexFilter(ClientContext &context, LogicalGet &get, Func
 		case ExpressionType::COMPARE_GREATERTHAN: z.op = flsgpu_host::ZONE_GT; break;
 		case ExpressionType::COMPARE_GREATERTHANOREQUALTO: z.op = flsgpu_host::ZONE_GE; break;
 		default: continue;
+		}
+		if (z.is_text && z.op != flsgpu_host::ZONE_EQ) {
+			continue;
 		}
 		bind_data.zone_predicates.push_back(z);
 	}

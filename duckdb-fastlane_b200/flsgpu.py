@@ -86,6 +86,7 @@ def lib():
     L.flsgpu_schema.argtypes = [vp, C.POINTER(u32), C.POINTER(C.POINTER(C.c_char_p)), C.POINTER(C.POINTER(C.c_int32))]
     L.flsgpu_chunk_info.argtypes = [vp, u32, u32, C.POINTER(C.c_int32), C.POINTER(u64)]
     L.flsgpu_rowgroup_minmax.argtypes = [vp, u32, u32, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
+    L.flsgpu_rowgroup_dict_contains.argtypes = [vp, u32, u32, C.c_char_p, C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.flsgpu_make_resident.argtypes = [vp, u32, u32]
     L.flsgpu_decode.argtypes = [vp, u32, u32, C.POINTER(u32), u32, u32, C.POINTER(vp)]
     L.flsgpu_batch_num_columns.argtypes = [vp]
@@ -229,6 +230,14 @@ class Reader:
         mn, mx, known = C.c_int64(), C.c_int64(), C.c_int32()
         self._check(lib().flsgpu_rowgroup_minmax(self.h, g, c, C.byref(mn), C.byref(mx), C.byref(known)))
         return (mn.value, mx.value) if known.value else None
+
+    def rowgroup_dict_contains(self, g, c, text):
+        """True / False: the dictionary of string column c in row group g holds `text` (bytes or str); None when the
+        chunk's scheme cannot say."""
+        raw = text.encode() if isinstance(text, str) else bytes(text)
+        found, known = C.c_int32(), C.c_int32()
+        self._check(lib().flsgpu_rowgroup_dict_contains(self.h, g, c, raw, len(raw), C.byref(found), C.byref(known)))
+        return bool(found.value) if known.value else None
 
     def make_resident(self, g0=0, g1=None):
         self._check(lib().flsgpu_make_resident(self.h, g0, self.n_rowgroups if g1 is None else g1))

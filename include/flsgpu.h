@@ -131,6 +131,13 @@ int flsgpu_chunk_info(const flsgpu_t *h, uint32_t rg, uint32_t col, int32_t *sch
  * value <= max (signed order for signed types and DATE; unsigned types are reported when they fit int64), or
  * *known = 0 when the chunk's scheme gives no bounds. */
 int flsgpu_rowgroup_minmax(flsgpu_t *h, uint32_t rg, uint32_t col, int64_t *min, int64_t *max, int32_t *known);
+/* Dictionary predicate on a string column (same row of SURVEY.md section 8f): does the row group's dictionary hold
+ * the string bytes[0..len)?  A STR_DICT chunk answers from its dictionary segment and a STR_CONSTANT chunk from its
+ * one value — read on the host, nothing is decoded; *known = 1 and *found = 0 means no row of the row group equals
+ * the string, so `column = 'x'` can skip it.  *known = 0 for every other scheme (FSST-compressed dictionaries
+ * included: the product has no CPU decoder to open them with).  Needs no CUDA device. */
+int flsgpu_rowgroup_dict_contains(flsgpu_t *h, uint32_t rg, uint32_t col, const uint8_t *bytes, uint64_t len,
+                                  int32_t *found, int32_t *known);
 
 /* ---- decode ------------------------------------------------------------------------------------------- */
 /* Stage the compressed bytes of row groups [g0,g1) into HBM and keep them until close / the next call. */

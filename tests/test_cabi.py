@@ -110,3 +110,39 @@ def test_rowgroup_minmax_bounds_hold_without_a_gpu():
             assert rd.rowgroup_minmax(g, 1) is None or rd.rowgroup_minmax(g, 1)[1] >= int(u[sl].max())
             b = rd.rowgroup_minmax(g, 2)
             assert b is None or (b[0] <= s16[sl].min() and s16[sl].max() <= b[1])
+
+
+def test_rowgroup_dict_contains_without_a_gpu():
+    """flsgpu_rowgroup_dict_contains answers `column = 'x'` from the row group's dictionary (STR_DICT) or its one
+    value (STR_CONSTANT): the answer must agree with the source rows, row group by row group; other schemes say
+    nothing."""
+    modes = [b"REG AIR", b"AIR", b"RAIL", b"SHIP", b"TRUCK", b"MAIL", b"FOB", b""]
+    r = np.random.default_rng(11)
+    n = 3 * 65536 + 500
+    idx = np.empty(n, dtype=np.int64)
+    idx[:65536] = r.integers(0, 3, 65536)            # row group 0: REG AIR, AIR, RAIL
+    idx[65536:2 * 65536] = r.integers(3, 8, 65536)   # row group 1: SHIP .. FOB and the empty string
+    idx[2 * 65536:3 * 65536] = 5                     # row group 2: MAIL only -> a constant chunk
+    idx[3 * 65536:] = r.integers(0, 8, 500)
+    col = synth._pick(modes, idx)
+    ids = np.arange(n, dtype=np.int64)
+    img = W.write_table([ids, col], force=[None, W.STR_DICT])
+    with flsgpu.Reader.from_image(img) as rd:
+        for g in range(rd.n_rowgroups):
+            assert rd.chunk_info(g, 1)[0] == W.STR_DICT
+            here = set(idx[g * 65536:(g + 1) * 65536].tolist())
+            for i, m in enumerate(modes):
+                assert rd.rowgroup_dict_contains(g, 1, m) == (i in here), (g, m)
+            assert rd.rowgroup_dict_contains(g, 1, "AI") is False          # a prefix of an entry is not an entry
+            assert rd.rowgroup_dict_contains(g, 1, b"REG AIR\0") is False
+            assert rd.rowgroup_dict_contains(g, 0, b"1") is None            # not a string column
+        with pytest.raises(flsgpu.FlsError):
+            rd.rowgroup_dict_contains(99, 1, b"AIR")
+    # the encoder's own choice: a one-valued row group becomes STR_CONSTANT, long distinct text FSST (no answer)
+    img = W.write_table([ids, col, synth.lineitem(n, seed=3)[15]])
+    with flsgpu.Reader.from_image(img) as rd:
+        schemes = [rd.chunk_info(g, 1)[0] for g in range(rd.n_rowgroups)]
+        assert schemes[2] == W.STR_CONSTANT
+        assert rd.rowgroup_dict_contains(2, 1, b"MAIL") is True and rd.rowgroup_dict_contains(2, 1, b"AIR") is False
+        assert rd.rowgroup_dict_contains(2, 1, b"") is False
+        assert rd.chunk_info(0, 2)[0] == W.STR_FSST and rd.rowgroup_dict_contains(0, 2, b"x") is None

@@ -194,3 +194,37 @@ def test_row_groups_are_skipped_by_their_compressed_bounds(tmp_path):
     skipped = [int(t.split()[2]) for t in trace]
     total = [int(t.split()[4]) for t in trace]
     assert total == [25, 25, 25, 25] and skipped == [23, 24, 0, 25], trace
+
+
+@pytest.mark.gpu
+def test_row_groups_are_skipped_by_their_dictionaries(tmp_path):
+    """SURVEY.md section 8f rank 3, dictionary predicate: `column = 'text'` skips the row groups whose dictionary
+    (or constant) does not hold the text; the filter stays with DuckDB, results equal the source's."""
+    path = str(tmp_path / "modes.fls")
+    modes = ["REG AIR", "AIR", "RAIL", "SHIP", "TRUCK", "MAIL", "FOB"]
+    src = ("SELECT i::BIGINT AS k, (%s)[1 + ((i // 50000) + (i %% 2)) %% 7] AS mode FROM range(0, 400000) t(i)"
+           % ("[" + ", ".join("'%s'" % m for m in modes) + "]"))
+    trace = []
+    res = sql("COPY (%s) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 16384)" % (src, path),
+              "SELECT count(*), sum(k) FROM read_fls('%s') WHERE mode = 'SHIP'" % path,
+              "SELECT count(*), sum(k) FROM (%s) WHERE mode = 'SHIP'" % src,
+              "SELECT count(*) FROM read_fls('%s') WHERE mode = 'NOPE'" % path,
+              "SELECT count(*) FROM read_fls('%s') WHERE 'AIR' = mode AND k < 60000" % path,
+              "SELECT count(*) FROM (%s) WHERE 'AIR' = mode AND k < 60000" % src,
+              "SELECT count(*) FROM read_fls('%s') WHERE mode <> 'SHIP'" % path,     # not an equality: no pruning pass at all
+              "SELECT count(*) FROM (%s) WHERE mode <> 'SHIP'" % src,
+              trace=trace)
+    assert res[1]["rows"] == res[2]["rows"] and int(res[1]["rows"][0][0]) > 0
+    assert res[3]["rows"] == [["0"]]
+    assert res[4]["rows"] == res[5]["rows"]
+    assert res[6]["rows"] == res[7]["rows"]
+
+    def holds(g, m):   # does row group g hold mode index m?
+        lo, hi = 16384 * g, min(16384 * (g + 1), 400000)
+        return any(((i // 50000) + (i % 2)) % 7 == m for i in (lo, lo + 1, hi - 2, hi - 1))
+    n_rg = (400000 + 16383) // 16384
+    want_ship = sum(not holds(g, 3) for g in range(n_rg))
+    want_air = sum((not holds(g, 1)) or 16384 * g >= 60000 for g in range(n_rg))
+    skipped = [int(t.split()[2]) for t in trace]
+    assert skipped == [want_ship, n_rg, want_air], (trace, want_ship, want_air)
+    assert 0 < want_ship < n_rg and 0 < want_air < n_rg and int(res[4]["rows"][0][0]) > 0
