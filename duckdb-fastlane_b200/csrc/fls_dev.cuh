@@ -158,6 +158,22 @@ struct FlsWarp {
           : "memory");
     }
   }
+  // Bulk copy OUT: `bytes` (multiple of 16) from sm+off to global memory at `dst` (both 16-byte aligned), issued by
+  // lane 0 as one asynchronous copy that does not pass through the load/store pipe.  Call from all lanes after
+  // the region that wrote the bytes; store_wait() before the bytes are overwritten (and before the block exits).
+  __device__ __forceinline__ void store_out(uint8_t *dst, uint32_t off, uint32_t bytes) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the lanes' shared-memory writes -> async proxy
+    __syncwarp();
+    if ((threadIdx.x & 31u) == 0 && bytes) {
+      const uint32_t src = (uint32_t)__cvta_generic_to_shared(sm + off);
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    }
+  }
+  __device__ __forceinline__ void store_wait() {
+    if ((threadIdx.x & 31u) == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    __syncwarp();
+  }
   // Order earlier generic-proxy accesses to the slot before the next bulk copy (async proxy) overwrites it.
   __device__ __forceinline__ void fence_async() {
     __syncwarp();
@@ -183,6 +199,8 @@ struct FlsWarp {
   void stage(uint32_t off, const uint8_t *src, uint32_t bytes) { memcpy(sm + off, src, bytes); }
   void wait() {}
   void fence_async() {}
+  void store_out(uint8_t *dst, uint32_t off, uint32_t bytes) { memcpy(dst, sm + off, bytes); }
+  void store_wait() {}
 #endif
 };
 

@@ -212,6 +212,7 @@ __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsCh
       }
     }
   }
+  w.store_wait();  // a bulk copy out of the warp's slot may still be reading it
 }
 
 // UNCOMPRESSED / blob copy: chunk by = blockIdx.y copies aux64[1] bytes seg[0] -> out (both 16-byte aligned).

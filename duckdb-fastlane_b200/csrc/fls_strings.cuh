@@ -177,6 +177,23 @@ FLS_DEV void fls_stage_copy_out(const uint8_t *stg, uint8_t *g, uint32_t h, uint
   for (uint32_t i = tail_start + t; i < end; i += 32u) gb[i] = stg[i];
 }
 
+// The same, for a whole warp (call OUTSIDE FLS_LANES): the whole 16-byte pieces leave as ONE bulk copy shared ->
+// global (no load/store-pipe work; w.store_wait() before the staging buffer is written again), the partial first /
+// last piece byte-wise.  `stg` is the warp's slot (w.sm).
+FLS_DEV void fls_stage_store(FlsWarp &w, uint8_t *g, uint32_t h, uint32_t len) {
+  const uint8_t *stg = w.sm;
+  const uint32_t end = h + len;
+  const uint32_t p0 = h ? 1u : 0u, p1 = end >> 4;
+  const uint32_t head_end = fls_min(end, 16u * p0);
+  const uint32_t tail_start = fls_max(16u * p1, head_end);
+  uint8_t *gb = g - h;  // 16-byte aligned
+  w.store_out(gb + 16u * p0, 16u * p0, p1 > p0 ? 16u * (p1 - p0) : 0u);
+  FLS_LANES(t) {
+    for (uint32_t i = h + t; i < head_end; i += 32u) gb[i] = stg[i];
+    for (uint32_t i = tail_start + t; i < end; i += 32u) gb[i] = stg[i];
+  }
+}
+
 // DELTA u32 chain walk from a staged payload ([lane bases 128 B][packed deltas]) into a padded tile (original order)
 FLS_DEV void fls_walk32(const uint8_t *stage, uint32_t bw, uint32_t base, uint32_t *tile, uint32_t t) {
   const uint32_t *bases = (const uint32_t *)stage, *pk = (const uint32_t *)(stage + 128);
@@ -519,6 +536,7 @@ struct VecSTRDICT {
       const bool staged = P && hh + qlen <= STG;
       // 2. end offsets, then the pieces of the lane's strings
       FLS_VAR(FlsPush, ps);
+      w.store_wait();  // the previous quarter's bulk copy has read the staging buffer
       FLS_LANES(t) {
         uint32_t d[8], len[8];
 #pragma unroll
@@ -564,7 +582,11 @@ struct VecSTRDICT {
       }
       if (staged) {
         FLS_LANES(t) { FLS_AT(ps).finish(); }
+#if FLS_EXP == 23
         FLS_LANES(t) { fls_stage_copy_out(stg, g, hh, qlen, t); }
+#else
+        fls_stage_store(w, g, hh, qlen);
+#endif
       }
       qpos += qlen;
     }
@@ -783,6 +805,7 @@ struct VecSTRFSST {
     //      Streams up to 16 bits wide are staged side by side; wider ones (strings of 64 KB and more, which end in
     //      the byte-wise path below anyway) one after the other.
     const bool both = bwd <= 16u && bwc <= 16u;
+    w.store_wait();  // the previous vector's last bulk copy has read the staging buffer
     w.fence_async();
     w.stage(0, k.seg[1] + 16ull * hd.ep, 128u + 128u * bwd);
     if (both) w.stage(P1, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc);
@@ -864,6 +887,7 @@ struct VecSTRFSST {
       }
       const bool staged = cur_windowed && hh + qlen <= STG;
       FLS_VAR(FlsPush, ps);
+      w.store_wait();  // the previous pass's bulk copy has read the staging buffer
       FLS_LANES(t) {
         const uint32_t sa = LS[t], sb = LS[t + 1u];
         const uint32_t c0 = start16(CE, sa), c1 = start16(CE, sb), d0 = start16(DE, sa);
@@ -889,7 +913,11 @@ struct VecSTRFSST {
 #if FLS_EXP != 4
       if (staged) {
         FLS_LANES(t) { FLS_AT(ps).finish(); }
+#if FLS_EXP == 23
         FLS_LANES(t) { fls_stage_copy_out(stg, g, hh, qlen, t); }
+#else
+        fls_stage_store(w, g, hh, qlen);
+#endif
       }
 #endif
     }
