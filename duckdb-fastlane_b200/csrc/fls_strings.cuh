@@ -216,7 +216,8 @@ FLS_DEV void fls_walk32(const uint8_t *stage, uint32_t bw, uint32_t base, uint32
 // two aligned 128-bit stores {run start, end 0 .. end 6} (end 7 is the next lane's run start).
 struct VecSTRDICT {
 #ifndef FLS_DICT_WARPS
-#define FLS_DICT_WARPS 14  /* measured: 12 / 14 / 16 warps -> 0.697 / 0.668 / 0.683 ms on the SF10 launch */
+#define FLS_DICT_WARPS 16  /* the most that fit.  With the LDS/STG copy-out 14 was best (12 / 14 / 16 warps: 0.697 / 0.668 /
+                              0.683 ms on the SF10 launch); with the bulk-copy copy-out 16 is (see profiles/r01_SUMMARY.md) */
 #endif
   static constexpr uint32_t WARPS = FLS_DICT_WARPS;
   static constexpr uint32_t STG = 8448u;     // staging of one quarter's payload (33 bytes per string on average)
