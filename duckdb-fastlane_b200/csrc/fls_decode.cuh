@@ -167,6 +167,7 @@ template <typename T> struct DecRLE {
     const uint16_t *bases = (const uint16_t *)w.sm;
     const uint16_t *pk = (const uint16_t *)(w.sm + 128);
     T *tile = (T *)(w.sm + STAGE);
+    const uint32_t last_run = n_runs ? n_runs - 1u : 0u;  // a run index past the run values (corrupt stream) reads the last one
     FLS_LANES(t) {
       for (uint32_t a = 0; a < 2u; ++a) {
         const uint32_t l = 2u * t + a;
@@ -174,7 +175,7 @@ template <typename T> struct DecRLE {
         const uint32_t e0 = fls_lane_start(l);
         for (uint32_t r = 0; r < 16u; ++r) {
           if (bw) idx += fls_extract<uint16_t>(pk, bw, fls_chain_row<16>(r), l);
-          tile[fls_tile_slot<T>(e0 + r)] = fls_ldg(runs + (idx & 0x3FFu));
+          tile[fls_tile_slot<T>(e0 + r)] = fls_ldg(runs + fls_min(idx & 0xFFFFu, last_run));
         }
       }
     }

@@ -446,7 +446,8 @@ struct VecSTRDICT {
     uint8_t *pay = k.pay + k.pay_base;
     uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i, offs[i + 1] = its end
     uint32_t qpos = vec_ep;  // payload offset (row-group relative) of the quarter's first byte
-    if (U && !by_quarter && ((uintptr_t)(pay + vec_ep) & 15u) == 0u) {
+    const uint64_t rg_pay = k.aux64[0];  // payload bytes of this row group: no write may pass it (corrupt streams)
+    if (U && !by_quarter && ((uintptr_t)(pay + vec_ep) & 15u) == 0u && (uint64_t)vec_ep + FLS_VEC * U <= rg_pay) {
       // Every entry is U = 1, 2 or 4 bytes long and the vector's payload starts on a 16-byte boundary: offsets are
       // arithmetic and a lane's 8 strings are 8U contiguous, aligned bytes — straight from registers to HBM, no
       // staging.  Dictionaries of up to 8 one-byte entries (flag columns) live in two registers and a lane's 8
@@ -532,6 +533,7 @@ struct VecSTRDICT {
       }
       uint32_t qlen;
       FLS_EXCL_SCAN(run, qlen);
+      if ((uint64_t)qpos + qlen > rg_pay) return;  // indices that do not add up to the declared payload: write nothing more
       uint8_t *g = pay + qpos;
       const uint32_t hh = (uint32_t)((uintptr_t)g & 15u);
       const bool staged = P && hh + qlen <= STG;
@@ -746,14 +748,16 @@ struct VecSTRFSST {
   }
   // Slow path (compressed bytes larger than the window, output larger than the staging buffer, offsets that do
   // not fit 16 bits): compressed bytes [c0, c1) -> o, byte-wise, straight from / to global memory.
-  FLS_MEM static void decode_bytes(const FlsChunkDev &k, uint32_t c0, uint32_t c1, uint8_t *o) {
+  // Bounded on both sides: reads stay below the chunk's compressed size (aux64[1]), writes below `o_end`.
+  FLS_MEM static void decode_bytes(const FlsChunkDev &k, uint32_t c0, uint32_t c1, uint8_t *o, const uint8_t *o_end) {
     const uint8_t *comp = k.seg[5];
     const uint64_t *gsym = (const uint64_t *)k.seg[4];
     const uint8_t *glen = k.seg[4] + 2048;
+    c1 = (uint32_t)(c1 < k.aux64[1] ? c1 : k.aux64[1]);
     for (uint32_t i = c0; i < c1;) {
       const uint32_t c = fls_ldg(comp + i++);
-      if (c == 255u) { if (i < c1) *o++ = fls_ldg(comp + i++); }
-      else { uint64_t s = fls_ldg(gsym + c); for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(glen + c)); b; --b) { *o++ = (uint8_t)s; s >>= 8; } }
+      if (c == 255u) { if (i < c1 && o < o_end) *o++ = fls_ldg(comp + i++); else break; }
+      else { uint64_t s = fls_ldg(gsym + c); for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(glen + c)); b && o < o_end; --b) { *o++ = (uint8_t)s; s >>= 8; } }
     }
   }
   // value (row, lane) of a packed u32 vector, 1 <= W <= 32: two loads and one funnel shift, no branch
@@ -836,11 +840,17 @@ struct VecSTRFSST {
       if (t == 31u) LS[35] = cend;
     }
     const uint32_t dv1 = LS[34], cv1 = LS[35];
+    const uint8_t *pay_end = pay + k.aux64[0];
+    // end offsets that run backwards or past the declared sizes (corrupt streams): nothing of this vector is written
+    if (dv1 < dv0 || dv1 > k.aux64[0] || cv1 < cv0 || cv1 > k.aux64[1]) return;
     if (dv1 - dv0 >= 65536u || cv1 - cv0 >= 65536u) {
       // offsets do not fit 16 bits: every lane decodes the 32 strings of its own chain, byte-wise
-      FLS_LANES(t) { decode_bytes(k, FLS_AT(lc0), FLS_AT(lc1), pay + FLS_AT(ld0)); }
+      FLS_LANES(t) {
+        if (FLS_AT(lc0) <= FLS_AT(lc1) && FLS_AT(ld0) <= k.aux64[0]) decode_bytes(k, FLS_AT(lc0), FLS_AT(lc1), pay + FLS_AT(ld0), pay_end);
+      }
       return;
     }
+    const uint32_t dspan = dv1 - dv0, cspan = cv1 - cv0;
 #if FLS_EXP == 3
     return;
 #endif
@@ -869,7 +879,9 @@ struct VecSTRFSST {
     uint32_t qc0 = 0, qc1 = start16(CE, PASS);  // compressed extent of the pass, relative to cv0
     uint32_t wbase = cv0 & ~15u;
     uint32_t span = cv0 + qc1 - wbase;
-    bool windowed = span + 16u <= CWIN;
+    // (the 16-bit ends of a well-formed vector ascend; `qc1 <= cspan` and the per-lane checks below keep a corrupt
+    // one inside the window, the staging buffer and the row group's payload)
+    bool windowed = span + 16u <= CWIN && qc1 <= cspan;
     const uint8_t *cwin = w.sm + STG;
     if (windowed && span) { w.fence_async(); w.stage(STG, comp + wbase, (span + 15u) & ~15u); }
     for (uint32_t qt = 0; qt < NPASS; ++qt) {
@@ -897,12 +909,16 @@ struct VecSTRFSST {
         LS[t] = lo;
         if (t == 0) LS[32] = S1;
       }
+      if (qd0 > dspan || qlen > dspan - qd0 || cur_c0 > cur_c1 || cur_c1 > cspan) return;  // corrupt end offsets
       const bool staged = cur_windowed && hh + qlen <= STG;
       FLS_VAR(FlsPush, ps);
       w.store_wait();  // the previous pass's bulk copy has read the staging buffer
       FLS_LANES(t) {
         const uint32_t sa = LS[t], sb = LS[t + 1u];
-        const uint32_t c0 = start16(CE, sa), c1 = start16(CE, sb), d0 = start16(DE, sa);
+        uint32_t c0 = start16(CE, sa), c1 = start16(CE, sb), d0 = start16(DE, sa);
+        // a lane's run lies inside the pass: always true for ascending ends, two compares otherwise
+        c0 = fls_max(c0, cur_c0); c1 = fls_min(c1, cur_c1);
+        d0 = fls_min(fls_max(d0, qd0), qd0 + qlen);
         if (staged) {
           FlsPush p;
           p.init(stg, hh + (d0 - qd0));
@@ -910,8 +926,8 @@ struct VecSTRFSST {
           if (c1 > c0) decode_run(p, tab + 16u * (t & (COPIES - 1u)), cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
 #endif
           FLS_AT(ps) = p;
-        } else {
-          decode_bytes(k, cv0 + c0, cv0 + c1, pay + dv0 + d0);
+        } else if (c1 > c0) {
+          decode_bytes(k, cv0 + c0, cv0 + c1, pay + dv0 + d0, pay + dv0 + qd0 + qlen);
         }
       }
       if (qt + 1u < NPASS) {  // next pass's window
@@ -919,7 +935,7 @@ struct VecSTRFSST {
         qc1 = start16(CE, PASS * qt + 2u * PASS);
         wbase = (cv0 + qc0) & ~15u;
         span = cv0 + qc1 - wbase;
-        windowed = span + 16u <= CWIN;
+        windowed = span + 16u <= CWIN && qc0 <= qc1 && qc1 <= cspan;
         if (windowed && span) { w.fence_async(); w.stage(STG, comp + wbase, (span + 15u) & ~15u); }
       }
 #if FLS_EXP != 4
@@ -944,10 +960,11 @@ FLS_DEV void fls_fsst_dict_entry(const FlsChunkDev &k, uint32_t d) {
   const uint64_t *sym = (const uint64_t *)k.seg[5];
   const uint8_t *len = k.seg[5] + 2048, *in = k.seg[3];
   uint8_t *o = (uint8_t *)k.out + fls_ldg(doff + d);
-  for (uint32_t i = fls_ldg(coff + d), e = fls_ldg(coff + d + 1); i < e;) {
+  const uint8_t *o_end = (uint8_t *)k.out + fls_ldg(doff + d + 1);  // an entry never writes past its own slot
+  for (uint32_t i = fls_ldg(coff + d), e = fls_ldg(coff + d + 1); i < e && o < o_end;) {
     const uint32_t code = fls_ldg(in + i++);
     if (code == 255u) { *o++ = fls_ldg(in + i++); }
-    else { uint64_t s = fls_ldg(sym + code); for (uint32_t b = fls_ldg(len + code); b; --b) { *o++ = (uint8_t)s; s >>= 8; } }
+    else { uint64_t s = fls_ldg(sym + code); for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(len + code)); b && o < o_end; --b) { *o++ = (uint8_t)s; s >>= 8; } }
   }
 }
 

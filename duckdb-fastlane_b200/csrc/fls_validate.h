@@ -1,0 +1,202 @@
+// fls_validate.h — host-side check of one column chunk BEFORE its descriptor reaches a kernel.
+//
+// The kernels turn per-vector header fields (entry point, bit width, exception / run counts) and per-chunk footer
+// fields (dictionary size, segment table) straight into device addresses.  A file that lies in any of them must end
+// in FLSGPU_E_FORMAT, never in a CUDA fault (VERDICT r01 "what's weak" 9, ADVICE fls_plan.h:88).  This walks the
+// chunk's footer entry and its vector headers in the HOST image — the bytes are page-locked there anyway — and
+// bounds every address a kernel will form from them against the segment it must stay inside.  Addresses that depend
+// on the DATA (string offsets, dictionary indices, exception positions) are clamped in the kernels themselves.
+//
+// Host-only, header-only; shared by flsgpu.cu and tests/emul.  The reference has no twin: FastLanes validates inside
+// its own reader (source absent).
+#pragma once
+#include <stdint.h>
+#include <string.h>
+
+#include <string>
+
+#include "fls_reader.h"
+
+namespace flsv {
+
+static inline uint64_t pad16(uint64_t n) { return (n + 15u) & ~(uint64_t)15u; }
+
+struct SegView {  // a segment of the chunk inside the host image
+  const uint8_t *p = nullptr;
+  uint64_t size = 0;
+};
+
+// Segment s of chunk k of row group rg, or {nullptr, 0} when it leaves the row group / the image.
+static inline bool seg_view(const fls_rowgroup &rg, const fls_colchunk &k, uint32_t s, const uint8_t *image, uint64_t image_size,
+                            SegView &out) {
+  if (s >= k.n_seg) return false;
+  const fls_seg &sg = k.seg[s];
+  if (sg.off > rg.size || sg.size > rg.size - sg.off) return false;
+  if (rg.off > image_size || rg.size > image_size - rg.off) return false;
+  if (sg.off % FLS_SEG_ALIGN) return false;
+  out.p = image + rg.off + sg.off;
+  out.size = sg.size;
+  return true;
+}
+
+static inline std::string bad(uint32_t g, uint32_t c, const char *what) {
+  return "corrupt column chunk (row group " + std::to_string(g) + ", column " + std::to_string(c) + "): " + what;
+}
+
+// One stream = header table (seg h) + data segment (seg h + 1).  need(v, ep, meta, &bytes) says how many bytes the
+// kernel stages / reads from the data segment starting at 16 * ep for vector v, or returns false for a header no
+// kernel may see.
+template <class Need>
+static inline const char *check_stream(const SegView &hdr, const SegView &data, uint32_t n_vec, Need need) {
+  if (hdr.size < 16ull * n_vec) return "vector header table shorter than 16 bytes per vector";
+  for (uint32_t v = 0; v < n_vec; ++v) {
+    uint64_t a;
+    memcpy(&a, hdr.p + 16ull * v, 8);
+    const uint32_t ep = (uint32_t)a, meta = (uint32_t)(a >> 32);
+    uint64_t bytes = 0;
+    if (!need(v, meta, bytes)) return "vector header field out of range";
+    if (16ull * ep > data.size || bytes > data.size - 16ull * ep) return "vector payload leaves its data segment";
+  }
+  return nullptr;
+}
+
+// u32 offsets[n + 1], ascending, last one <= limit
+static inline bool ascending_u32(const SegView &s, uint64_t n, uint64_t limit) {
+  if (s.size < 4ull * (n + 1)) return false;
+  uint32_t prev = 0;
+  for (uint64_t i = 0; i <= n; ++i) {
+    uint32_t x;
+    memcpy(&x, s.p + 4ull * i, 4);
+    if (x < prev) return false;
+    prev = x;
+  }
+  return prev <= limit;
+}
+
+}  // namespace flsv
+
+// "" when every address the kernels derive from the chunk's footer entry and vector headers stays inside the chunk's
+// own segments; else the reason.  `image` is the whole file (or at least through the end of row group g).
+static inline std::string fls_validate_chunk(const FlsTable &t, uint32_t g, uint32_t c, const uint8_t *image, uint64_t image_size) {
+  using namespace flsv;
+  const fls_rowgroup &rg = t.rgs[g];
+  const fls_colchunk &k = t.chunk(g, c);
+  const uint32_t tb = fls_type_bits(t.types[c]), wb = tb / 8u, n_vec = rg.n_vec;
+  if (n_vec == 0 || n_vec > FLS_RG_VECS) return bad(g, c, "vector count outside 1..64");
+  if (k.n_seg > FLS_MAX_SEGS) return bad(g, c, "too many segments");
+  SegView s[FLS_MAX_SEGS];
+  for (uint32_t i = 0; i < k.n_seg; ++i)
+    if (!seg_view(rg, k, i, image, image_size, s[i])) return bad(g, c, "segment leaves its row group");
+  auto need_segs = [&](uint32_t n) { return k.n_seg >= n; };
+  const char *e = nullptr;
+  auto clamp = [](uint32_t x, uint32_t hi) { return x > hi ? hi : x; };
+  switch (k.scheme) {
+    case FLS_S_UNCOMPRESSED:
+      if (!wb) return bad(g, c, "fixed-width scheme on a string column");
+      if (!need_segs(1) || s[0].size < (uint64_t)n_vec * FLS_VEC * wb) return bad(g, c, "uncompressed segment too short");
+      break;
+    case FLS_S_CONSTANT:
+      if (!wb) return bad(g, c, "fixed-width scheme on a string column");
+      break;
+    case FLS_S_FFOR:
+    case FLS_S_DELTA:
+      if (!wb) return bad(g, c, "fixed-width scheme on a string column");
+      if (!need_segs(2)) return bad(g, c, "missing segments");
+      e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
+        b = 128ull * clamp(FLS_META_BW(meta), tb) + (k.scheme == FLS_S_DELTA ? 128u : 0u);
+        return true;
+      });
+      break;
+    case FLS_S_RLE:
+      if (!wb) return bad(g, c, "fixed-width scheme on a string column");
+      if (!need_segs(2)) return bad(g, c, "missing segments");
+      e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
+        const uint32_t n_runs = FLS_META_N(meta);
+        if (n_runs == 0 || n_runs > FLS_VEC) return false;
+        b = pad16((uint64_t)n_runs * wb) + 128u + (FLS_META_BW(meta) ? 128u : 0u);
+        return true;
+      });
+      break;
+    case FLS_S_DICT:
+      if (!wb) return bad(g, c, "fixed-width scheme on a string column");
+      if (!need_segs(3)) return bad(g, c, "missing segments");
+      if (k.aux32 == 0 || s[2].size < (uint64_t)k.aux32 * wb) return bad(g, c, "dictionary shorter than its entry count");
+      e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
+        b = 128ull * clamp(FLS_META_BW(meta), 32u);
+        return true;
+      });
+      break;
+    case FLS_S_ALP:
+      if (t.types[c] != FLS_T_DOUBLE) return bad(g, c, "ALP on a non-double column");
+      if (!need_segs(2)) return bad(g, c, "missing segments");
+      e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
+        const uint32_t n_exc = FLS_META_N(meta);
+        if (n_exc > FLS_VEC) return false;
+        b = 128ull * clamp(FLS_META_BW(meta), 64u) + pad16(8ull * n_exc) + 2ull * n_exc;
+        return true;
+      });
+      break;
+    case FLS_S_ALP_RD: {
+      if (t.types[c] != FLS_T_DOUBLE) return bad(g, c, "ALP_RD on a non-double column");
+      if (!need_segs(2)) return bad(g, c, "missing segments");
+      const uint32_t rbw = clamp(k.aux32 & 0xFFu, 63u), lbw = clamp((k.aux32 >> 8) & 0xFFu, 16u);
+      e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
+        const uint32_t n_exc = FLS_META_N(meta);
+        if (n_exc > FLS_VEC) return false;
+        b = 128ull * (rbw + lbw) + pad16(2ull * n_exc) + 2ull * n_exc;
+        return true;
+      });
+      break;
+    }
+    case FLS_S_STR_UNCOMPRESSED:
+      if (wb) return bad(g, c, "string scheme on a fixed-width column");
+      if (!need_segs(3)) return bad(g, c, "missing segments");
+      if (s[2].size < k.aux64[0]) return bad(g, c, "payload segment shorter than the declared payload");
+      e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
+        b = 128u + 128ull * clamp(FLS_META_BW(meta), 32u);
+        return true;
+      });
+      break;
+    case FLS_S_STR_CONSTANT:
+      if (wb) return bad(g, c, "string scheme on a fixed-width column");
+      if (!need_segs(1) || s[0].size < k.aux32) return bad(g, c, "constant shorter than its length");
+      if (k.aux64[0] != (uint64_t)n_vec * FLS_VEC * k.aux32) return bad(g, c, "constant payload size mismatch");
+      break;
+    case FLS_S_STR_DICT:
+    case FLS_S_STR_FSST_DICT: {
+      if (wb) return bad(g, c, "string scheme on a fixed-width column");
+      const bool fsst = k.scheme == FLS_S_STR_FSST_DICT;
+      if (!need_segs(fsst ? 7 : 5)) return bad(g, c, "missing segments");
+      if (k.aux32 == 0) return bad(g, c, "empty dictionary");
+      // dictionary entries: ascending offsets inside the bytes segment (16 bytes of slack behind the last entry:
+      // the table build reads two aligned 8-byte words per piece)
+      if (s[3].size < 16 || !ascending_u32(s[2], k.aux32, s[3].size - 16)) return bad(g, c, "dictionary offsets leave the dictionary");
+      if (fsst) {
+        if (s[5].size < 2048u + 256u) return bad(g, c, "symbol table too short");
+        if (!ascending_u32(s[6], k.aux32, 0xFFFFFFFFull)) return bad(g, c, "decoded dictionary offsets not ascending");
+      }
+      if (!ascending_u32(s[4], n_vec, k.aux64[0])) return bad(g, c, "vector entry points leave the payload");
+      e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
+        b = 128ull * clamp(FLS_META_BW(meta), 32u);
+        return true;
+      });
+      break;
+    }
+    case FLS_S_STR_FSST: {
+      if (wb) return bad(g, c, "string scheme on a fixed-width column");
+      if (!need_segs(6)) return bad(g, c, "missing segments");
+      if (s[4].size < 2048u + 256u) return bad(g, c, "symbol table too short");
+      if (s[5].size < 16 || k.aux64[1] > s[5].size - 16) return bad(g, c, "compressed bytes shorter than declared");
+      auto need = [&](uint32_t, uint32_t meta, uint64_t &b) {
+        b = 128u + 128ull * clamp(FLS_META_BW(meta), 32u);
+        return true;
+      };
+      e = check_stream(s[0], s[1], n_vec, need);
+      if (!e) e = check_stream(s[2], s[3], n_vec, need);
+      break;
+    }
+    default: return bad(g, c, "unknown scheme");
+  }
+  if (e) return bad(g, c, e);
+  return "";
+}

@@ -374,7 +374,40 @@ static double alprd_estimate(const uint64_t *bits, size_t n, uint32_t rbw, std::
   return rbw + lbw + (double)exc * 32.0 / (double)n;
 }
 
+// Test knob (flsw_inject_alprd): the NEXT ALP-RD chunk is assembled from streams another encoder produced — the
+// reference tree's own AlpRD compressor (tests/golden/alprd.npz) — instead of this file's: cut position, dictionary,
+// dictionary indices, right parts and exceptions go into the container verbatim, so a decoder under test consumes
+// bytes the reference wrote.
+struct AlprdInject {
+  uint32_t rbw, lbw, ndict, n_vec;
+  const uint16_t *dict, *left;      // dict[8]; left[n_vec * 1024] = dictionary indices
+  const uint64_t *right;            // right[n_vec * 1024]
+  const uint32_t *nexc;             // per vector
+  const uint16_t *xpos, *xleft;     // per vector: 1024 slots each, the first nexc[v] used
+};
+static thread_local const AlprdInject *tl_alprd_inject = nullptr;
+
+static Chunk enc_alprd_injected(const AlprdInject &in, uint32_t n_vec) {
+  Chunk c; c.scheme = FLS_S_ALP_RD;
+  c.aux32 = in.rbw | (in.lbw << 8) | (in.ndict << 16);
+  uint16_t d8[8] = {0};
+  for (uint32_t i = 0; i < in.ndict && i < 8; ++i) d8[i] = in.dict[i];
+  memcpy(c.aux64, d8, 16);
+  Stream s;
+  for (uint32_t vi = 0; vi < n_vec; ++vi) {
+    const uint32_t src = vi < in.n_vec ? vi : in.n_vec - 1;  // padding vectors repeat the last one
+    s.begin_vec(FLS_META(0, 0, 0, in.nexc[src]), 0);
+    append_packed<uint64_t>(s.data, in.right + (size_t)src * FLS_VEC, in.rbw);
+    append_packed<uint16_t>(s.data, in.left + (size_t)src * FLS_VEC, in.lbw);
+    put_bytes(s.data, in.xleft + (size_t)src * FLS_VEC, in.nexc[src] * 2); pad_to(s.data, 16);
+    put_bytes(s.data, in.xpos + (size_t)src * FLS_VEC, in.nexc[src] * 2); pad_to(s.data, 16);
+  }
+  s.move_into(c);
+  return c;
+}
+
 static Chunk enc_alprd(const double *v, uint32_t n_vec) {
+  if (tl_alprd_inject) { const AlprdInject *in = tl_alprd_inject; tl_alprd_inject = nullptr; return enc_alprd_injected(*in, n_vec); }
   Chunk c; c.scheme = FLS_S_ALP_RD;
   const uint64_t *bits = (const uint64_t *)v;
   std::vector<uint64_t> smp;
@@ -543,21 +576,38 @@ static Chunk enc_str_uncompressed(const uint8_t *bytes, const uint64_t *off, uin
   return c;
 }
 
+// Test knob (flsw_inject_fsst): the NEXT FSST chunk takes its symbol table and compressed bytes from another
+// encoder — libfsst itself (tests/golden/fsst.npz: fsst_create / fsst_compress of the reference tree's
+// duckdb/third_party/fsst) — verbatim; only the offset streams around them are this file's.
+struct FsstInject {
+  const uint8_t *symtab;     // u64 symbol[256] | u8 len[256]
+  const uint8_t *comp;       // compressed bytes of the row group's strings, back to back
+  const uint64_t *comp_off;  // [n_strings + 1]
+  uint32_t n_strings;
+};
+static thread_local const FsstInject *tl_fsst_inject = nullptr;
+
 static Chunk enc_str_fsst(const uint8_t *bytes, const uint64_t *off, uint32_t n_vec) {
   Chunk c; c.scheme = FLS_S_STR_FSST;
   size_t n = (size_t)n_vec * FLS_VEC;
-  Fsst t = fsst_train(bytes, off, n);
+  const FsstInject *inj = tl_fsst_inject;
+  tl_fsst_inject = nullptr;
+  Fsst t;
+  if (!inj) t = fsst_train(bytes, off, n);
   std::vector<uint32_t> dec_ends(n), cmp_ends(n);
   Bytes comp;
   for (size_t i = 0; i < n; ++i) {
-    t.compress(bytes + off[i], off[i + 1] - off[i], comp);
+    if (!inj) t.compress(bytes + off[i], off[i + 1] - off[i], comp);
+    else if (i < inj->n_strings) put_bytes(comp, inj->comp + inj->comp_off[i], inj->comp_off[i + 1] - inj->comp_off[i]);
     dec_ends[i] = (uint32_t)(off[i + 1] - off[0]);
     cmp_ends[i] = (uint32_t)comp.size();
   }
   Stream sd, sc;
   offsets_stream(sd, dec_ends, n_vec); sd.move_into(c);
   offsets_stream(sc, cmp_ends, n_vec); sc.move_into(c);
-  Bytes tb; t.blob(tb); c.segs.push_back(std::move(tb));
+  Bytes tb;
+  if (inj) put_bytes(tb, inj->symtab, 2304); else t.blob(tb);
+  c.segs.push_back(std::move(tb));
   c.aux64[0] = off[n] - off[0];
   c.aux64[1] = comp.size();
   pad_to(comp, 16);
@@ -660,6 +710,8 @@ struct Writer {
   uint64_t n_rows = 0;
   bool last_partial = false, finished = false;
   std::string err;
+  std::map<uint32_t, FsstInject> inject_fsst;    // column -> streams for its next row group (test knobs)
+  std::map<uint32_t, AlprdInject> inject_alprd;
 };
 
 template <typename T>
@@ -684,6 +736,10 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
     Chunk ch;
     int t = w.types[c], f = w.force[c];
     tl_force_alp_ef = c < w.force_ef.size() ? w.force_ef[c] : -1;
+    tl_fsst_inject = nullptr; tl_alprd_inject = nullptr;
+    FsstInject fi; AlprdInject ai;
+    if (w.inject_fsst.count((uint32_t)c)) { fi = w.inject_fsst[(uint32_t)c]; w.inject_fsst.erase((uint32_t)c); tl_fsst_inject = &fi; f = FLS_S_STR_FSST; }
+    if (w.inject_alprd.count((uint32_t)c)) { ai = w.inject_alprd[(uint32_t)c]; w.inject_alprd.erase((uint32_t)c); tl_alprd_inject = &ai; f = FLS_S_ALP_RD; }
     switch (fls_type_bits(t)) {
       case 8: ch = enc_fixed<uint8_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false); break;
       case 16: ch = enc_fixed<uint16_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false); break;
@@ -782,6 +838,25 @@ int flsw_force_alp_ef(flsw_writer *h, uint32_t col, int32_t e, int32_t f) {
   return 0;
 }
 int64_t flsw_alp_encode_value(double v, int32_t e, int32_t f) { return flsw::alp_encode(v, e, f); }
+// Test knobs: the next row group appended for `col` uses these externally produced streams verbatim (the pointers
+// must stay valid until that flsw_append_rowgroup returns).
+int flsw_inject_fsst(flsw_writer *h, uint32_t col, const uint8_t *symtab2304, const uint8_t *comp, const uint64_t *comp_off,
+                     uint32_t n_strings) {
+  flsw::Writer *w = (flsw::Writer *)h;
+  if (col >= w->types.size() || fls_type_bits(w->types[col]) != 0 || !symtab2304 || !comp_off || n_strings > FLS_RG_VECS * FLS_VEC) return 1;
+  w->inject_fsst[col] = flsw::FsstInject{symtab2304, comp, comp_off, n_strings};
+  return 0;
+}
+int flsw_inject_alprd(flsw_writer *h, uint32_t col, uint32_t rbw, uint32_t lbw, uint32_t ndict, const uint16_t *dict8,
+                      uint32_t n_vec, const uint16_t *left, const uint64_t *right, const uint32_t *nexc, const uint16_t *xpos,
+                      const uint16_t *xleft) {
+  flsw::Writer *w = (flsw::Writer *)h;
+  if (col >= w->types.size() || w->types[col] != FLS_T_DOUBLE || rbw == 0 || rbw > 63 || lbw > 16 || ndict > 8 || n_vec == 0 || n_vec > FLS_RG_VECS)
+    return 1;
+  for (uint32_t v = 0; v < n_vec; ++v) if (nexc[v] > FLS_VEC) return 1;
+  w->inject_alprd[col] = flsw::AlprdInject{rbw, lbw, ndict, n_vec, dict8, left, right, nexc, xpos, xleft};
+  return 0;
+}
 
 // Build a new image holding `n_total` row groups by repeating the (full) row groups of `image` round-robin.
 // Every repeat is a separate copy of the bytes.  Returns a finished writer (flsw_data/flsw_size) or NULL.

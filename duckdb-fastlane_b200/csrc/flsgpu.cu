@@ -21,6 +21,7 @@
 #include "../../include/flsgpu.h"
 #include "fls_plan.h"
 #include "fls_strings.cuh"
+#include "fls_validate.h"
 
 // ---------------------------------------------------------------------------------------------------------
 // kernel table
@@ -154,26 +155,32 @@ struct flsgpu {
   std::vector<KStat> kstats;
   std::vector<const char *> name_ptrs;
   std::vector<int32_t> types32;
-  // Plan of the last single-slice resident decode: repeated scans of the same range into the same (pooled)
-  // buffers reuse the descriptors already on the device instead of rebuilding and re-uploading them.
+  std::vector<uint8_t> validated;  // [rg * n_cols + col]: the chunk's footer entry and vector headers passed fls_validate_chunk
+  // Plans of the last single-slice resident decodes: repeated scans of the same range into the same (pooled)
+  // buffers reuse the descriptors already on the device instead of rebuilding and re-uploading them.  A scan that
+  // walks a large table batch by batch (bench.py --scaling strong, the facade's cursor) keeps one plan per batch.
   struct PlanCache {
     bool valid = false;
     uint32_t g0 = 0, g1 = 0;
+    uint64_t stamp = 0;
     std::vector<uint32_t> cols;
     std::vector<const void *> ptrs;
     std::vector<LaunchRec> recs;
     FlsChunkDev *d_desc = nullptr;
-  } plan;
+  };
+  static constexpr size_t MAX_PLANS = 16;
+  std::vector<PlanCache> plans;
+  uint64_t plan_clock = 0;
 
   int fail(int code, const std::string &m) { err = m; return code; }
   int fail_cuda(const char *what, cudaError_t e) {
     err = std::string("CUDA: ") + what + ": " + cudaGetErrorString(e);
     return FLSGPU_E_CUDA;
   }
-  cudaEvent_t ev_get() {
+  cudaEvent_t ev_get() {  // nullptr when the runtime cannot create one (the caller bails)
     if (!ev_free.empty()) { cudaEvent_t e = ev_free.back(); ev_free.pop_back(); return e; }
     cudaEvent_t e = nullptr;
-    cudaEventCreate(&e);
+    if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     return e;
   }
   void *dev_alloc(size_t n) {
@@ -518,11 +525,33 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
   const bool to_host = (flags & FLSGPU_OUT_HOST) != 0;
   memset(&b->tm, 0, sizeof(b->tm));
 
+  // Every exit after this point goes through bail(): work already queued on the handle's streams is drained before
+  // the batch's buffers go back to the pool, and borrowed events go back to the free list.
+  std::vector<cudaEvent_t> used_events;
   auto bail = [&](int code, const std::string &m) {
     cudaDeviceSynchronize();
+    cudaGetLastError();
+    for (auto e : used_events) if (e) h->ev_free.push_back(e);
     flsgpu_batch_release(b);
     return h->fail(code, m);
   };
+#define CKB(call)                                                                                        \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) return bail(FLSGPU_E_CUDA, std::string("CUDA: " #call ": ") + cudaGetErrorString(e_)); \
+  } while (0)
+
+  // ---- the chunks of the range: footer entry + vector headers checked once per handle, before anything derived
+  //      from them (sizes below, device addresses in the kernels) is used
+  if (h->validated.empty()) h->validated.assign((size_t)t.n_rg * t.n_cols, 0);
+  for (uint32_t g = g0; g < g1; ++g)
+    for (uint32_t c : b->cols) {
+      uint8_t &ok = h->validated[(size_t)g * t.n_cols + c];
+      if (ok) continue;
+      const std::string e = fls_validate_chunk(t, g, c, h->image, h->size);
+      if (!e.empty()) return bail(FLSGPU_E_FORMAT, e);
+      ok = 1;
+    }
 
   // ---- output buffers
   b->out.resize(nc); b->dev.resize(nc); b->need.resize(nc);
@@ -581,27 +610,36 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
   uint32_t slice = resident && !to_host ? (g1 - g0) : (h->slice_rgs ? h->slice_rgs : 64u);
   const uint32_t n_slices = (g1 - g0 + slice - 1) / slice;
   // plan cache (single-slice resident decodes only): key = range, columns and every buffer address
-  const bool cacheable = n_slices == 1 && resident && !to_host;
+  const bool cacheable = n_slices == 1 && resident && !to_host && !(h->flags & FLSGPU_OPEN_NO_PLAN_CACHE);
   std::vector<const void *> key_ptrs;
   if (cacheable) {
     key_ptrs.push_back(d_stage); key_ptrs.push_back(d_scratch);
     for (uint32_t i = 0; i < nc; ++i) { key_ptrs.push_back(b->dev[i].data); key_ptrs.push_back(b->dev[i].offsets); key_ptrs.push_back(b->dev[i].payload); }
   }
-  const bool plan_hit = cacheable && h->plan.valid && h->plan.g0 == g0 && h->plan.g1 == g1 && h->plan.cols == b->cols &&
-                        h->plan.ptrs == key_ptrs;
+  flsgpu::PlanCache *plan = nullptr;
+  if (cacheable)
+    for (auto &pc : h->plans)
+      if (pc.valid && pc.g0 == g0 && pc.g1 == g1 && pc.cols == b->cols && pc.ptrs == key_ptrs) { plan = &pc; break; }
+  const bool plan_hit = plan != nullptr;
   // descriptors: at most 2 chunks per (row group, column)
   const size_t desc_cap = (size_t)(g1 - g0) * nc * 2;
   FlsChunkDev *h_desc = nullptr, *d_desc = nullptr;
-  if (plan_hit) d_desc = h->plan.d_desc;
+  if (plan_hit) { d_desc = plan->d_desc; plan->stamp = ++h->plan_clock; }
   else {
     h_desc = (FlsChunkDev *)h->host_alloc(desc_cap * sizeof(FlsChunkDev));
     d_desc = (FlsChunkDev *)h->dev_alloc(desc_cap * sizeof(FlsChunkDev));
     b->host_bufs.push_back(h_desc);
     if (!h_desc || !d_desc) { h->dev_free(d_desc); return bail(FLSGPU_E_NOMEM, "out of memory for chunk descriptors"); }
-    if (cacheable) {  // the cache takes the device descriptors over
-      h->plan.valid = false;
-      h->dev_free(h->plan.d_desc);
-      h->plan.d_desc = d_desc;
+    if (cacheable) {  // the cache takes the device descriptors over (least recently used entry goes)
+      if (h->plans.size() < flsgpu::MAX_PLANS) { h->plans.emplace_back(); plan = &h->plans.back(); }
+      else {
+        plan = &h->plans[0];
+        for (auto &pc : h->plans) if (pc.stamp < plan->stamp) plan = &pc;
+        h->dev_free(plan->d_desc);
+      }
+      plan->valid = false;
+      plan->d_desc = d_desc;
+      plan->stamp = ++h->plan_clock;
     } else b->dev_bufs.push_back(d_desc);
   }
 
@@ -610,14 +648,15 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
   struct KEv { cudaEvent_t a, b; int slot; uint64_t rd, wr, vec; };
   std::vector<KEv> kev;
   const bool time_kernels = (h->flags & FLSGPU_OPEN_TIME_KERNELS) != 0;
-  cudaEvent_t ev_start = h->ev_get(), ev_end = h->ev_get();
-  std::vector<cudaEvent_t> used_events = {ev_start, ev_end};
-  auto ev = [&]() { cudaEvent_t e = h->ev_get(); used_events.push_back(e); return e; };
+  bool ev_fail = false;
+  auto ev = [&]() { cudaEvent_t e = h->ev_get(); if (e) used_events.push_back(e); else ev_fail = true; return e; };
+  cudaEvent_t ev_start = ev(), ev_end = ev();
+  if (ev_fail) return bail(FLSGPU_E_CUDA, "CUDA: cannot create an event");
 
-  CK(cudaEventRecord(ev_start, h->s_h2d));
-  CK(cudaStreamWaitEvent(h->s_k, ev_start, 0));
+  CKB(cudaEventRecord(ev_start, h->s_h2d));
+  CKB(cudaStreamWaitEvent(h->s_k, ev_start, 0));
   for (uint32_t i = 0; i < nc; ++i)
-    if (b->dev[i].offsets) CK(cudaMemsetAsync(b->dev[i].offsets, 0, 4, h->s_k));
+    if (b->dev[i].offsets) CKB(cudaMemsetAsync(b->dev[i].offsets, 0, 4, h->s_k));
 
   size_t desc_used = 0;
   std::vector<uint64_t> pay_done(nc, 0), scratch_done(nc, 0);
@@ -635,7 +674,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     std::vector<FlsLaunch> ls;
     std::vector<LaunchRec> recs;
     std::vector<uint64_t> pay_slice(nc, 0);
-    if (plan_hit) recs = h->plan.recs;
+    if (plan_hit) recs = plan->recs;
     for (uint32_t i = 0; i < nc && perr.empty() && !plan_hit; ++i) {
       const uint32_t c = b->cols[i];
       FlsColOut o = b->dev[i];
@@ -666,26 +705,26 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     }
     if (!perr.empty()) break;
     if (cacheable && !plan_hit) {
-      h->plan.g0 = g0; h->plan.g1 = g1; h->plan.cols = b->cols; h->plan.ptrs = key_ptrs; h->plan.recs = recs;
-      h->plan.valid = true;
+      plan->g0 = g0; plan->g1 = g1; plan->cols = b->cols; plan->ptrs = key_ptrs; plan->recs = recs;
+      plan->valid = true;
     }
     plan_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - plan_t0).count();
     // H2D: compressed bytes (unless resident) + descriptors
     EvPair eh = {ev(), ev()};
-    CK(cudaEventRecord(eh.a, h->s_h2d));
+    CKB(cudaEventRecord(eh.a, h->s_h2d));
     if (!resident) {
-      CK(cudaMemcpyAsync(d_stage + rel, h->image + t.rgs[s0].off, ext, cudaMemcpyHostToDevice, h->s_h2d));
+      CKB(cudaMemcpyAsync(d_stage + rel, h->image + t.rgs[s0].off, ext, cudaMemcpyHostToDevice, h->s_h2d));
       b->tm.h2d_bytes += ext;
     }
     if (!plan_hit)
-      CK(cudaMemcpyAsync(d_desc + desc0, h_desc + desc0, (desc_used - desc0) * sizeof(FlsChunkDev), cudaMemcpyHostToDevice,
+      CKB(cudaMemcpyAsync(d_desc + desc0, h_desc + desc0, (desc_used - desc0) * sizeof(FlsChunkDev), cudaMemcpyHostToDevice,
                          h->s_h2d));
-    CK(cudaEventRecord(eh.b, h->s_h2d));
+    CKB(cudaEventRecord(eh.b, h->s_h2d));
     ev_h2d.push_back(eh);
     // decode
-    CK(cudaStreamWaitEvent(h->s_k, eh.b, 0));
+    CKB(cudaStreamWaitEvent(h->s_k, eh.b, 0));
     EvPair ek = {ev(), ev()};
-    CK(cudaEventRecord(ek.a, h->s_k));
+    CKB(cudaEventRecord(ek.a, h->s_k));
     size_t dpos = desc0;
     // Without per-kernel timing the launches of a slice are independent (different columns) except that a
     // dictionary must be prepared before the gather that reads it: dictprep + str_dict stay on s_k, in order;
@@ -699,12 +738,12 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       if (!time_kernels && recs.size() > 1 && l.kind != FLS_K_STR_FSST_DICTPREP && l.kind != FLS_K_STR_DICT) {
         const uint32_t si = l.kind == FLS_K_STR_FSST ? 0u : 1u + (rr++ & 1u);
         ks = h->s_kx[si];
-        if (!side_used[si]) { CK(cudaStreamWaitEvent(ks, ek.a, 0)); side_used[si] = true; }
+        if (!side_used[si]) { CKB(cudaStreamWaitEvent(ks, ek.a, 0)); side_used[si] = true; }
       }
-      if (time_kernels) { ke.a = ev(); ke.b = ev(); CK(cudaEventRecord(ke.a, ks)); }
+      if (time_kernels) { ke.a = ev(); ke.b = ev(); CKB(cudaEventRecord(ke.a, ks)); }
       if (!launch_kind(l, d_desc + dpos, ks)) { perr = "internal: no kernel for launch kind"; break; }
-      CK(cudaGetLastError());
-      if (time_kernels) CK(cudaEventRecord(ke.b, ks));
+      CKB(cudaGetLastError());
+      if (time_kernels) CKB(cudaEventRecord(ke.b, ks));
       kev.push_back(ke);
       dpos += l.n;
       b->tm.kernel_launches++;
@@ -712,33 +751,33 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     for (uint32_t si = 0; si < 3u; ++si)
       if (side_used[si]) {
         cudaEvent_t je = ev();
-        CK(cudaEventRecord(je, h->s_kx[si]));
-        CK(cudaStreamWaitEvent(h->s_k, je, 0));
+        CKB(cudaEventRecord(je, h->s_kx[si]));
+        CKB(cudaStreamWaitEvent(h->s_k, je, 0));
       }
     if (!perr.empty()) break;
-    CK(cudaEventRecord(ek.b, h->s_k));
+    CKB(cudaEventRecord(ek.b, h->s_k));
     ev_k.push_back(ek);
     // D2H
     if (to_host) {
-      CK(cudaStreamWaitEvent(h->s_d2h, ek.b, 0));
+      CKB(cudaStreamWaitEvent(h->s_d2h, ek.b, 0));
       EvPair ed = {ev(), ev()};
-      CK(cudaEventRecord(ed.a, h->s_d2h));
+      CKB(cudaEventRecord(ed.a, h->s_d2h));
       for (uint32_t i = 0; i < nc; ++i) {
         const uint32_t wb = b->out[i].width;
         if (wb) {
-          CK(cudaMemcpyAsync((uint8_t *)b->out[i].data + rows_done * wb, (uint8_t *)b->dev[i].data + rows_done * wb,
+          CKB(cudaMemcpyAsync((uint8_t *)b->out[i].data + rows_done * wb, (uint8_t *)b->dev[i].data + rows_done * wb,
                              srows * wb, cudaMemcpyDeviceToHost, h->s_d2h));
           b->tm.d2h_bytes += srows * wb;
         } else {
           const uint64_t o0 = rows_done ? rows_done + 1 : 0, o1 = rows_done + srows + 1;
-          CK(cudaMemcpyAsync(b->out[i].offsets + o0, b->dev[i].offsets + o0, (o1 - o0) * 4, cudaMemcpyDeviceToHost, h->s_d2h));
+          CKB(cudaMemcpyAsync(b->out[i].offsets + o0, b->dev[i].offsets + o0, (o1 - o0) * 4, cudaMemcpyDeviceToHost, h->s_d2h));
           if (pay_slice[i])
-            CK(cudaMemcpyAsync(b->out[i].payload + pay_done[i], b->dev[i].payload + pay_done[i], pay_slice[i],
+            CKB(cudaMemcpyAsync(b->out[i].payload + pay_done[i], b->dev[i].payload + pay_done[i], pay_slice[i],
                                cudaMemcpyDeviceToHost, h->s_d2h));
           b->tm.d2h_bytes += (o1 - o0) * 4 + pay_slice[i];
         }
       }
-      CK(cudaEventRecord(ed.b, h->s_d2h));
+      CKB(cudaEventRecord(ed.b, h->s_d2h));
       ev_d2h.push_back(ed);
     }
     for (uint32_t i = 0; i < nc; ++i) pay_done[i] += pay_slice[i];
@@ -746,8 +785,8 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     b->tm.slices++;
   }
   if (!perr.empty()) return bail(FLSGPU_E_FORMAT, perr);
-  if (!ev_k.empty()) CK(cudaStreamWaitEvent(h->s_d2h, ev_k.back().b, 0));
-  CK(cudaEventRecord(ev_end, h->s_d2h));
+  if (!ev_k.empty()) CKB(cudaStreamWaitEvent(h->s_d2h, ev_k.back().b, 0));
+  CKB(cudaEventRecord(ev_end, h->s_d2h));
   cudaError_t se = cudaEventSynchronize(ev_end);
   if (se != cudaSuccess) return bail(FLSGPU_E_CUDA, std::string("CUDA: decode failed: ") + cudaGetErrorString(se));
 
@@ -767,6 +806,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
   b->tm.ms_host_total = (float)std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
   *out = b;
   return FLSGPU_OK;
+#undef CKB
 }
 
 uint32_t flsgpu_batch_num_columns(const flsgpu_batch_t *b) { return (uint32_t)b->out.size(); }

@@ -56,6 +56,9 @@ def lib():
         L.flsw_force_alp_ef.argtypes = [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32]
         L.flsw_alp_encode_value.argtypes = [C.c_double, C.c_int32, C.c_int32]
         L.flsw_alp_encode_value.restype = C.c_int64
+        L.flsw_inject_fsst.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
+        L.flsw_inject_alprd.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.flsw_tile.restype = C.c_void_p
         L.flsw_tile.argtypes = [C.c_void_p, C.c_uint64, C.c_uint32]
         _lib = L
@@ -89,11 +92,14 @@ class StrColumn:
         return StrColumn(self.data, self.offsets[a:b + 1])  # offsets stay absolute into data
 
 
-def write_table(columns, names=None, types=None, force=None, min_bw=None, path=None, alp_ef=None, rg_rows=RG_ROWS) -> np.ndarray:
+def write_table(columns, names=None, types=None, force=None, min_bw=None, path=None, alp_ef=None, rg_rows=RG_ROWS,
+                inject=None) -> np.ndarray:
     """Encode a table into an FLS image (returned as a uint8 array; also written to `path` if given).
 
     columns: list of np.ndarray (fixed width) or StrColumn.   force/min_bw: optional per-column scheme / FFOR width.
     rg_rows: rows per row group, a multiple of 1024 up to 65,536 (what COPY's ROW_GROUP_SIZE sets).
+    inject: {(column, row group index): ("fsst", symtab, comp, comp_off) | ("alprd", rbw, lbw, ndict, dict8, left, right,
+            nexc, xpos, xleft)} — streams another encoder produced, stored verbatim (flsw.h test knobs).
     """
     L = lib()
     n_cols = len(columns)
@@ -134,6 +140,30 @@ def write_table(columns, names=None, types=None, force=None, min_bw=None, path=N
                     keep.append(s)
                     data[i] = s.ctypes.data
                     offs[i] = None
+            for i in range(n_cols):
+                inj = (inject or {}).get((i, r0 // rg_rows))
+                if inj is None:
+                    continue
+                arrs = [np.ascontiguousarray(a) for a in inj[1:] if isinstance(a, np.ndarray)]
+                keep.append(arrs)
+                if inj[0] == "fsst":
+                    sym, comp, coff = (np.ascontiguousarray(a) for a in inj[1:4])
+                    coff = coff.astype(np.uint64)
+                    keep.append((sym, comp, coff))
+                    rc = L.flsw_inject_fsst(w, i, sym.ctypes.data, comp.ctypes.data, coff.ctypes.data, len(coff) - 1)
+                else:
+                    rbw, lbw, ndict = (int(x) for x in inj[1:4])
+                    d8 = np.ascontiguousarray(inj[4], dtype=np.uint16)
+                    left = np.ascontiguousarray(inj[5], dtype=np.uint16).reshape(-1)
+                    right = np.ascontiguousarray(inj[6], dtype=np.uint64).reshape(-1)
+                    nexc = np.ascontiguousarray(np.atleast_1d(inj[7]), dtype=np.uint32)
+                    xpos = np.ascontiguousarray(inj[8], dtype=np.uint16).reshape(-1)
+                    xleft = np.ascontiguousarray(inj[9], dtype=np.uint16).reshape(-1)
+                    keep.append((d8, left, right, nexc, xpos, xleft))
+                    rc = L.flsw_inject_alprd(w, i, rbw, lbw, ndict, d8.ctypes.data, len(nexc), left.ctypes.data,
+                                             right.ctypes.data, nexc.ctypes.data, xpos.ctypes.data, xleft.ctypes.data)
+                if rc:
+                    raise ValueError("bad injected streams for column %d" % i)
             if L.flsw_append_rowgroup(w, r1 - r0, data, offs):
                 raise RuntimeError(L.flsw_error(w).decode())
         if L.flsw_finish(w):

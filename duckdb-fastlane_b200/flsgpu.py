@@ -14,7 +14,7 @@ _ROOT = os.path.dirname(_HERE)
 _lib = None
 
 OK, E_IO, E_FORMAT, E_RANGE, E_CUDA, E_LIMIT, E_NOMEM = range(7)
-OPEN_PINNED_IMAGE, OPEN_NO_PIN, OPEN_TIME_KERNELS = 1, 2, 4
+OPEN_PINNED_IMAGE, OPEN_NO_PIN, OPEN_TIME_KERNELS, OPEN_NO_PLAN_CACHE = 1, 2, 4, 8
 OUT_DEVICE, OUT_HOST = 0, 1
 
 # enum fls_type -> numpy dtype of the decoded column

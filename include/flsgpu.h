@@ -57,6 +57,8 @@ enum flsgpu_type {
 #define FLSGPU_OPEN_PINNED_IMAGE 1u /* open_image: the caller's image is already page-locked */
 #define FLSGPU_OPEN_NO_PIN 2u       /* do not page-lock the image (H2D then goes through the driver's bounce buffer) */
 #define FLSGPU_OPEN_TIME_KERNELS 4u /* record a CUDA-event pair around every kernel launch (flsgpu_kernel_stats) */
+#define FLSGPU_OPEN_NO_PLAN_CACHE 8u /* rebuild and re-upload the chunk descriptors on every decode (what the first
+                                        scan of a range pays; bench.py reports it beside the cached figure) */
 
 /* decode flags */
 #define FLSGPU_OUT_DEVICE 0u /* leave decoded columns in HBM; column pointers are device pointers */

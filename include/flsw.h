@@ -37,6 +37,17 @@ void flsw_destroy(flsw_writer *w);
 int flsw_force_scheme(flsw_writer *w, uint32_t col, int32_t scheme, int32_t min_bw);
 int flsw_force_alp_ef(flsw_writer *w, uint32_t col, int32_t e, int32_t f);
 int64_t flsw_alp_encode_value(double v, int32_t e, int32_t f);
+/* Test knobs for parity against the reference tree's own encoders: the NEXT row group appended for `col` is built
+ * from externally produced streams, verbatim.  FSST: libfsst's symbol table (u64 symbol[256] | u8 len[256]) and
+ * compressed bytes (comp_off[n_strings + 1]); the row group still receives the raw strings (decoded offsets).
+ * ALP-RD: DuckDB's cut position, dictionary, per-value dictionary indices / right parts and exceptions
+ * (per vector: 1024 slots of xpos / xleft, the first nexc[v] used).  Pointers must stay valid until that
+ * flsw_append_rowgroup returns. */
+int flsw_inject_fsst(flsw_writer *w, uint32_t col, const uint8_t *symtab2304, const uint8_t *comp, const uint64_t *comp_off,
+                     uint32_t n_strings);
+int flsw_inject_alprd(flsw_writer *w, uint32_t col, uint32_t rbw, uint32_t lbw, uint32_t ndict, const uint16_t *dict8,
+                      uint32_t n_vec, const uint16_t *left, const uint64_t *right, const uint32_t *nexc, const uint16_t *xpos,
+                      const uint16_t *xleft);
 /* A new finished writer holding n_total row groups: the (full) row groups of `image` repeated round-robin. */
 flsw_writer *flsw_tile(const void *image, uint64_t size, uint32_t n_total);
 

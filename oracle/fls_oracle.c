@@ -115,6 +115,13 @@ uint64_t flso_chunk_bytes(const flso_table *t, uint32_t g, uint32_t c) {
   return s;
 }
 uint64_t flso_chunk_payload(const flso_table *t, uint32_t g, uint32_t c) { return t->rg[g].cols[c].aux64[0]; }
+/* file extent of segment s of a chunk (tests that damage files on purpose); 0 = no such segment */
+int flso_chunk_segment(const flso_table *t, uint32_t g, uint32_t c, uint32_t s, uint64_t *off, uint64_t *size) {
+  const ochunk *k = &t->rg[g].cols[c];
+  if (s >= k->n_seg) return 0;
+  *off = t->rg[g].off + k->seg[s].off; *size = k->seg[s].size;
+  return 1;
+}
 
 /* ---- per-vector primitives, instantiated for T in {u8,u16,u32,u64} ------------------------------------
  * unffor : interleaved bit-unpack + frame of reference: value r of lane l occupies bits

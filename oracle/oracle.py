@@ -38,6 +38,7 @@ def lib():
         L.flso_chunk_scheme.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
         L.flso_chunk_bytes.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
         L.flso_chunk_bytes.restype = C.c_uint64
+        L.flso_chunk_segment.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.flso_range_padded_rows.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32]
         L.flso_range_padded_rows.restype = C.c_uint64
         L.flso_range_payload.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
@@ -87,6 +88,22 @@ class OracleTable:
 
     def chunk_bytes(self, rg, col):
         return lib().flso_chunk_bytes(self.h, rg, col)
+
+    def segments(self):
+        """[(file offset, size, is_vector_header_table)] of every non-empty segment of every chunk."""
+        out = []
+        off, size = C.c_uint64(), C.c_uint64()
+        no_stream = (0, 1, 9)  # UNCOMPRESSED, CONSTANT, STR_CONSTANT: blobs only
+        for g in range(self.n_rg):
+            for c in range(self.n_cols):
+                sch = self.scheme(g, c)
+                hdr_segs = () if sch in no_stream else ((0, 2) if sch == 11 else (0,))
+                for s in range(8):
+                    if not lib().flso_chunk_segment(self.h, g, c, s, C.byref(off), C.byref(size)):
+                        break
+                    if size.value:
+                        out.append((off.value, size.value, s in hdr_segs))
+        return out
 
     def compressed_bytes(self, col, g0=0, g1=None):
         g1 = self.n_rg if g1 is None else g1

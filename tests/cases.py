@@ -216,3 +216,25 @@ def expected_bytes(col):
         pay = col.data[int(col.offsets[0]):int(col.offsets[-1])]
         return off, pay
     return np.ascontiguousarray(col).view(np.uint8)
+
+
+def reference_minted_images():
+    """Tables whose FSST / ALP-RD chunks hold bytes the REFERENCE TREE's encoders produced (tests/golden/*.npz, minted by
+    oracle/ref_twin.cpp from duckdb/third_party/fsst and duckdb's alprd.hpp), stored verbatim by the writer's inject
+    knobs: [(name, image, expected)] with expected = (offsets u64, payload) or the doubles' bit patterns."""
+    import os
+    G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    out = []
+    g = np.load(os.path.join(G, "fsst.npz"))
+    for name in ("comment", "shipinstruct", "user", "binary", "fixture_like"):
+        raw, off = g[name + "_raw"], g[name + "_off"]
+        img = W.write_table([StrColumn(raw, off)],
+                            inject={(0, 0): ("fsst", g[name + "_symtab"], g[name + "_comp"], g[name + "_coff"])})
+        out.append(("libfsst_" + name, img, (off, raw)))
+    g = np.load(os.path.join(G, "alprd.npz"))
+    nv = len(g["in"])
+    inj = {(0, v): ("alprd", g["rbw"][v], g["lbw"][v], g["ndict"][v], g["dict"][v], g["left"][v], g["right"][v],
+                    g["nexc"][v], g["xpos"][v], g["xleft"][v]) for v in range(nv)}
+    img = W.write_table([g["in"].reshape(-1).view(np.float64)], rg_rows=1024, inject=inj)
+    out.append(("duckdb_alprd", img, g["in"].reshape(-1)))
+    return out

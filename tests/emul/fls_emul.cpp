@@ -13,6 +13,7 @@
 
 #include "fls_plan.h"
 #include "fls_strings.cuh"
+#include "fls_validate.h"
 
 static std::string g_err;
 int fls_emul_force_any = 0;
@@ -90,6 +91,10 @@ int emul_decode(const uint8_t *image, uint64_t size, uint32_t col, uint32_t g0, 
   g_err = fls_parse(image, size, t);
   if (!g_err.empty()) return 1;
   if (col >= t.n_cols || g0 > g1 || g1 > t.n_rg) { g_err = "bad range"; return 1; }
+  for (uint32_t g = g0; g < g1; ++g) {  // the same gate libflsgpu applies before a descriptor reaches a kernel
+    g_err = fls_validate_chunk(t, g, col, image, size);
+    if (!g_err.empty()) return 2;
+  }
   FlsColNeed need = fls_column_need(t, col, g0, g1, image);
   std::vector<uint8_t> scratch(need.scratch_bytes + 16);
   FlsColOut out;
@@ -109,6 +114,11 @@ uint64_t emul_need(const uint8_t *image, uint64_t size, uint32_t col, uint32_t g
   FlsTable t;
   g_err = fls_parse(image, size, t);
   if (!g_err.empty()) return 1;
+  if (col >= t.n_cols || g0 > g1 || g1 > t.n_rg) { g_err = "bad range"; return 1; }
+  for (uint32_t g = g0; g < g1; ++g) {
+    g_err = fls_validate_chunk(t, g, col, image, size);
+    if (!g_err.empty()) return 2;
+  }
   FlsColNeed n = fls_column_need(t, col, g0, g1, image);
   out4[0] = n.data_bytes; out4[1] = n.offsets_bytes; out4[2] = n.payload_bytes; out4[3] = n.scratch_bytes;
   return 0;

@@ -92,3 +92,23 @@ def test_fsst_decode_of_libfsst_output(name):
     img = W.write_table([col], force=[W.STR_FSST])
     o, p = oracle.OracleTable(img).decode(0)
     assert np.array_equal(o.astype(np.uint64), off) and np.array_equal(p, raw)
+
+
+def test_reference_minted_streams_decode_through_the_container():
+    """libfsst's symbol table + compressed bytes and DuckDB's ALP-RD streams, stored verbatim in FLS chunks: the oracle
+    and the host emulation of the CUDA kernels (same device source) must both return the reference's input."""
+    import cases
+    import emul
+    for name, img, exp in cases.reference_minted_images():
+        ora = oracle.OracleTable(img)
+        assert ora.scheme(0, 0) == (W.STR_FSST if isinstance(exp, tuple) else W.ALP_RD), name
+        got = ora.decode(0)
+        em = emul.decode(img, 0, ora.types[0], 0, ora.n_rg)
+        if isinstance(exp, tuple):
+            off, raw = exp
+            n = len(off) - 1
+            assert np.array_equal(got[0].astype(np.uint64), off) and np.array_equal(got[1], raw), name
+            assert np.array_equal(em[0][:n + 1].astype(np.uint64), off) and np.array_equal(em[1][:len(raw)], raw), name
+        else:
+            assert np.array_equal(got.view(np.uint64), exp), name
+            assert np.array_equal(em.view(np.uint64)[:len(exp)], exp), name
