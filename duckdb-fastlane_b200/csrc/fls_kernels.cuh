@@ -173,11 +173,7 @@ __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsCh
   for (uint32_t s = 0; s < nseg; ++s) {
     const uint32_t b = s % NB;
     const uint8_t *bsm = tabs + b * BUF;
-#if defined(FLS_EXP) && FLS_EXP == 20
-    const FlsChunkDev &k = chunks[c0 + s];
-#else
     const FlsChunkDev &k = *(const FlsChunkDev *)(bsm + V::BLOCK_SMEM);  // the shared-memory copy
-#endif
     const uint32_t v1 = seg_hi(s);
     if (s >= NB) {
       while (ready[b] != s + 1u) __nanosleep(32);

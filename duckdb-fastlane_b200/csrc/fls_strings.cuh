@@ -9,9 +9,6 @@
 // follow duckdb/third_party/fsst/fsst.h:93-104,162-241 (code<255 -> symbol, 255 -> escaped literal byte).
 #pragma once
 #include "fls_kernels.cuh"
-#ifndef FLS_EXP
-#define FLS_EXP 0  /* timing-only knock-out experiments (profiles/exp.sh); 0 = the product */
-#endif
 
 // ---- contiguous byte writer: head/tail bytes individually, everything between as aligned u64 stores
 struct FlsByteSink {
@@ -121,12 +118,8 @@ struct FlsPush {
   FLS_MEM static void emit(fls_sptr o0, uint32_t Tb, uint32_t Ta, uint32_t pv, uint32_t lo, uint32_t hi) {
     const uint32_t a = Tb >> 5, d = (Ta >> 5) - a;
     const fls_sptr addr = o0 + 4u * a;
-#if FLS_EXP == 1
-    if (d == 77u) fls_sts32_ge<1u>(d, addr, fls_shf_l(pv, lo, Tb) + fls_shf_l(lo, hi, Tb));
-#else
     fls_sts32_ge<1u>(d, addr, fls_shf_l(pv, lo, Tb));       // funnel shifts use T mod 32
     fls_sts32_ge<2u>(d, addr + 4u, fls_shf_l(lo, hi, Tb));
-#endif
   }
   FLS_MEM void push(uint32_t lo, uint32_t hi, uint32_t tail, uint32_t L8) {
     const uint32_t Ta = T + L8;
@@ -461,16 +454,10 @@ struct VecSTRDICT {
           dhi |= (*(const uint32_t *)(tab + ((e + 4u) << sh)) & 0xFFu) << (8u * e);
         }
       }
-#if FLS_EXP == 12
-      return;
-#endif
       for (uint32_t qt = 0; qt < 4u; ++qt) {
         FLS_LANES(t) {
           uint32_t d[8];
           unpack8(idx, bw, 8u * qt + (t >> 2), t, (uint32_t)h.base, n_dict - 1u, d);
-#if FLS_EXP == 11
-          if (d[0] + d[1] + d[2] + d[3] + d[4] + d[5] + d[6] + d[7] != 0x12345u) continue;
-#endif
           const uint32_t s0 = 256u * qt + 8u * t;  // the lane's first string
           const uint32_t start = k.pay_base + vec_ep + s0 * U;
           fls_u4 a, b;
@@ -585,11 +572,7 @@ struct VecSTRDICT {
       }
       if (staged) {
         FLS_LANES(t) { FLS_AT(ps).finish(); }
-#if FLS_EXP == 23
-        FLS_LANES(t) { fls_stage_copy_out(stg, g, hh, qlen, t); }
-#else
         fls_stage_store(w, g, hh, qlen);
-#endif
       }
       qpos += qlen;
     }
@@ -602,9 +585,9 @@ struct VecSTRDICT {
 // The strings of a vector are contiguous in both the compressed and the decoded space.  The vector's compressed
 // bytes are bulk-copied into the warp's window; a vector is decoded in four quarters of 256 strings, lane t
 // owning the 8 consecutive strings 256q + 8t .. +7 = one compressed run -> one output run.  A lane reads its run
-// 8 bytes at a time; every code byte costs one conflict-free 128-bit table load (the block keeps 8 copies of the
+// 16 bytes at a time; every code byte costs one conflict-free 128-bit table load (the block keeps 8 copies of the
 // table, one per 16-byte bank group, lane t uses copy t & 7) and one FlsPush::push.  Escapes (code 255) are rare:
-// a window that holds one, and the partial first/last window of a run, take the byte-by-byte path.
+// a window that holds one takes the variant that patches the literal entries in registers.
 #ifndef FLS_FSST_WARPS
 #define FLS_FSST_WARPS 10
 #define FLS_FSST_COPIES 8
@@ -621,11 +604,15 @@ struct VecSTRFSST {
   static constexpr uint32_t E16N = 1056u;    // 16-bit relative end of every string, padded original order (x2)
   static constexpr uint32_t P1 = 2176u;      // phase 1: each staged offset stream (lane bases + deltas up to 16 bits wide)
   static constexpr uint32_t SMEM = STG + CWIN + 4u * E16N + 256u;
-  // 512 entries (code * 2 + escaped) x COPIES x 16 B, entry i of copy r at (i * COPIES + r) * 16: a lane reads copy
-  // t % COPIES (8 copies: the eight lanes of a 128-bit load phase never share a bank group)
+  // 256 entries (one per code) x COPIES x 16 B, entry c of copy r at (c * COPIES + r) * 16: a lane reads copy
+  // t % COPIES (8 copies: the eight lanes of a 128-bit load phase never share a bank group).  Escaped literals are
+  // not in the table (an escaped byte c is the piece {c}): a window that holds an escape marker takes the ESC
+  // variant, which patches those entries in registers.  Half the size of a table with literal entries, so the block
+  // keeps TWO tables and the next chunk's is built while this one is still in use: nobody waits at a chunk boundary
+  // (with one 64 KB table 13 % of the warps' time was the spin on ready[], profiles/r02_SUMMARY.md).
   static constexpr uint32_t COPIES = FLS_FSST_COPIES, SH = COPIES == 8 ? 7u : COPIES == 4 ? 6u : COPIES == 2 ? 5u : 4u;
-  static constexpr uint32_t BLOCK_SMEM = 512u * 16u * COPIES;
-  static constexpr uint32_t NBUF = 1, CONST_SMEM = 0;
+  static constexpr uint32_t BLOCK_SMEM = 256u * 16u * COPIES;
+  static constexpr uint32_t NBUF = 2, CONST_SMEM = 0;
   static constexpr bool PIPELINED = true;
   FLS_MEM static void const_init(uint8_t *, uint32_t, uint32_t) {}
   static_assert(2u * P1 <= STG + CWIN && 4224u <= STG + CWIN, "phase-1 buffers must fit the staging buffer + window");
@@ -649,11 +636,8 @@ struct VecSTRFSST {
       for (uint32_t j = 0; j < B; ++j) {
         const uint32_t c = c0 + j * nthreads + tid;
         if (c < 256u) {
-          const fls_u4 en = fls_piece_entry(sv[j], lv[j]), el = fls_piece_entry(c, 1u);  // el: escaped byte c, itself
-          for (uint32_t r = 0; r < COPIES; ++r) {
-            *(fls_u4 *)(bsm + (((2u * c) * COPIES + r) << 4)) = en;
-            *(fls_u4 *)(bsm + (((2u * c + 1u) * COPIES + r) << 4)) = el;
-          }
+          const fls_u4 en = fls_piece_entry(sv[j], lv[j]);
+          for (uint32_t r = 0; r < COPIES; ++r) *(fls_u4 *)(bsm + ((c * COPIES + r) << 4)) = en;
         }
       }
     }
@@ -663,65 +647,76 @@ struct VecSTRFSST {
     const uint32_t y = ~x;  // zero byte <=> 0xFF
     return ~(((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y) & 0x80808080u;
   }
-  // NW/2 x eight consecutive compressed bytes (32-bit words w[]) of a lane's run: all table loads in flight, then
-  // all pushes, straight-line.  The table index of byte j is 2 * value + (byte j is an escaped literal).  Byte j is
-  // a literal when byte j-1 is an escape marker (0xFF), `lit` standing for byte -1; that is exact unless two 0xFF
-  // bytes are adjacent (a literal 0xFF), and such a window takes the byte-by-byte path.  The literal flag of byte j
-  // belongs at bit 8j-1, which is the top bit of byte j-1: with the top bits of the odd (even) bytes replaced by
-  // their marker flags, the 9 bits [8j-1, 8j+8) ARE the table index of an even (odd) byte j — one shift and one
-  // mask per byte.  MASK: only bytes [s, e) of the window belong to the run (partial first / last window); the
-  // others are turned into markers that escape nothing.
+  // Escape markers of NW/2 x eight consecutive compressed bytes (32-bit words w[]): ff[k] has 0x80 in every byte of
+  // w[k] that is 0xFF.  MASK: only bytes [s, e) of the window belong to the lane's run (partial first / last
+  // window); the others become 0xFF bytes that are no markers — code 255 is the table's empty entry.
   template <uint32_t NW, bool MASK>
-  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, uint32_t (&w)[NW], uint32_t s, uint32_t e, bool &lit) {
-    uint32_t ff[NW];
+  FLS_MEM static uint32_t markers(uint32_t (&w)[NW], uint32_t (&ff)[NW], uint32_t s, uint32_t e) {
+    uint32_t any = 0;
 #pragma unroll
     for (uint32_t k = 0; k < NW; ++k) ff[k] = ff_bytes(w[k]);
     if (MASK) {
-#pragma unroll
       const uint32_t s8 = 8u * s, e8 = 8u * e;
+#pragma unroll
       for (uint32_t k = 0; k < NW; ++k) {
         // bytes [s, e) of the window that fall into word k: (all ones << bits below s) & ~(all ones << bits below e),
         // the shifts clamped at 32
         const uint32_t vm = fls_shl_c(~0u, fls_max(s8, 32u * k) - 32u * k) & ~fls_shl_c(~0u, fls_max(e8, 32u * k) - 32u * k);
         ff[k] &= vm;
-        w[k] |= ~vm;  // 0xFF and not a marker: the empty entry
+        w[k] |= ~vm;
       }
     }
+#pragma unroll
+    for (uint32_t k = 0; k < NW; ++k) any |= ff[k];
+    return any;
+  }
+  // The window's 4 * NW codes: all table loads in flight, then all pushes, straight-line.  ESC = false: no lane of
+  // the warp has a marker in its window or a literal pending — every byte is a code.  ESC = true: byte j is a literal
+  // when byte j-1 is a marker, `lit` standing for byte -1 (the entry {byte} replaces the loaded one; the marker
+  // itself loads the empty entry); that is exact unless two 0xFF bytes are adjacent (a literal 0xFF), and such a
+  // window goes byte by byte.
+  template <uint32_t NW, bool ESC>
+  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, const uint32_t (&w)[NW], const uint32_t (&ff)[NW], uint32_t s, uint32_t e,
+                             bool &lit) {
     const uint32_t c7 = lit ? 0x80u : 0u;
-    uint32_t adj = ((ff[0] << 8) | c7) & ff[0];
+    if (ESC) {
+      uint32_t adj = ((ff[0] << 8) | c7) & ff[0];
 #pragma unroll
-    for (uint32_t k = 1; k < NW; ++k) adj |= ((ff[k] << 8) | (ff[k - 1u] >> 24)) & ff[k];
-    if (adj) {
-      // adjacent 0xFF bytes: byte by byte
-      for (uint32_t j = 0; j < 4u * NW; ++j) {
-        if (MASK && (j < s || j >= e)) continue;
-        const uint32_t c = (w[j >> 2] >> (8u * (j & 3u))) & 0xFFu;
-        if (lit) { p.push(fls_lds128<fls_u4>(tabr + ((2u * c + 1u) << SH))); lit = false; }
-        else if (c == 255u) lit = true;
-        else p.push(fls_lds128<fls_u4>(tabr + ((2u * c) << SH)));
+      for (uint32_t k = 1; k < NW; ++k) adj |= ((ff[k] << 8) | (ff[k - 1u] >> 24)) & ff[k];
+      if (adj) {
+#pragma unroll
+        for (uint32_t j = 0; j < 4u * NW; ++j) {  // (constant bounds: w[] stays in registers)
+          if (j < s || j >= e) continue;
+          const uint32_t c = (w[j >> 2] >> (8u * (j & 3u))) & 0xFFu;
+          if (lit) { p.push_byte(c); lit = false; }
+          else if (c == 255u) lit = true;
+          else p.push(fls_lds128<fls_u4>(tabr + (c << SH)));
+        }
+        return;
       }
-      return;
+      lit = (ff[NW - 1u] >> 31) != 0u;
     }
-    lit = (ff[NW - 1u] >> 31) != 0u;
-    constexpr uint32_t IM = 0x1FFu << SH;  // the 9 index bits at the entry stride
-    uint32_t ad[4u * NW];  // index << SH
-#pragma unroll
-    for (uint32_t k = 0; k < NW; ++k) {
-      // E: odd bytes carry their marker flag in the top bit (index of the even bytes); O: the other way round
-      const uint32_t E = (w[k] & 0x7FFF7FFFu) | (ff[k] & 0x80008000u), O = (w[k] & 0xFF7FFF7Fu) | (ff[k] & 0x00800080u);
-      const uint32_t below = k ? ((w[k - 1u] & 0x7FFFFFFFu) | (ff[k - 1u] & 0x80000000u)) : 0u;  // E of the word before
-      ad[4u * k] = (k ? fls_shf_r(below, E, 31u - SH) : ((E << (SH + 1u)) | (c7 >> (7u - SH)))) & IM;
-      ad[4u * k + 1u] = (O >> (7u - SH)) & IM;
-      ad[4u * k + 2u] = (E >> (15u - SH)) & IM;
-      ad[4u * k + 3u] = (O >> (23u - SH)) & IM;
-    }
+    constexpr uint32_t IM = 0xFFu << SH;  // the 8 code bits at the entry stride
     fls_u4 en[4u * NW];
 #pragma unroll
-#if FLS_EXP == 2
-    for (uint32_t j = 0; j < 4u * NW; ++j) { en[j].x = ad[j]; en[j].y = 0; en[j].z = ad[j]; en[j].w = (ad[j] & 0x300u) ? 16u : 24u; }
-#else
-    for (uint32_t j = 0; j < 4u * NW; ++j) en[j] = fls_lds128<fls_u4>(tabr + ad[j]);
-#endif
+    for (uint32_t k = 0; k < NW; ++k) {
+      en[4u * k] = fls_lds128<fls_u4>(tabr + ((w[k] << SH) & IM));
+      en[4u * k + 1u] = fls_lds128<fls_u4>(tabr + ((w[k] >> (8u - SH)) & IM));
+      en[4u * k + 2u] = fls_lds128<fls_u4>(tabr + ((w[k] >> (16u - SH)) & IM));
+      en[4u * k + 3u] = fls_lds128<fls_u4>(tabr + ((w[k] >> (24u - SH)) & IM));
+    }
+    if (ESC) {
+#pragma unroll
+      for (uint32_t j = 0; j < 4u * NW; ++j) {
+        const uint32_t k = j >> 2, b = j & 3u;
+        // marker flag of the byte before byte j
+        const uint32_t m = b ? (ff[k] >> (8u * b - 1u)) & 1u : (k ? ff[k - 1u] >> 31 : c7 >> 7);
+        if (m) {
+          const uint32_t c = (w[k] >> (8u * b)) & 0xFFu;
+          en[j].x = c; en[j].y = 0u; en[j].z = c; en[j].w = 8u;
+        }
+      }
+    }
     p.push_all(en);
   }
   // A lane's compressed run = bytes [a, b) of the staged window `cwin`, read 16 bytes at a time (8 at the end).
@@ -730,18 +725,23 @@ struct VecSTRFSST {
     bool lit = false;
     uint32_t i = a >> 3;  // 8-byte unit
     while (8u * i < b) {
-      uint32_t w[4];
-      w[0] = cw[2u * i]; w[1] = cw[2u * i + 1u];
       const uint32_t s = 8u * i < a ? a - 8u * i : 0u, left = b - 8u * i;
-      // the variant is chosen by a vote of the lanes still in the loop, so they stay converged
+      // the variants are chosen by votes of the lanes still in the loop, so they stay converged
       if (FLS_ANY(left > 8u)) {
-        w[2] = cw[2u * i + 2u]; w[3] = cw[2u * i + 3u];  // the window has 16 bytes of slack
-        if (FLS_ANY(s != 0u || left < 16u)) window<4, true>(p, tabr, w, s, fls_min(16u, left), lit);
-        else window<4, false>(p, tabr, w, 0u, 16u, lit);
+        uint32_t w[4] = {cw[2u * i], cw[2u * i + 1u], cw[2u * i + 2u], cw[2u * i + 3u]};  // the window has 16 bytes of slack
+        uint32_t ff[4];
+        const uint32_t e = fls_min(16u, left);
+        const uint32_t any = FLS_ANY(s != 0u || left < 16u) ? markers<4, true>(w, ff, s, e) : markers<4, false>(w, ff, 0u, 16u);
+        if (FLS_ANY(any != 0u || lit)) window<4, true>(p, tabr, w, ff, s, e, lit);
+        else window<4, false>(p, tabr, w, ff, s, e, lit);
         i += 2u;
       } else {
-        uint32_t w2[2] = {w[0], w[1]};
-        window<2, true>(p, tabr, w2, s, fls_min(8u, left), lit);
+        uint32_t w[2] = {cw[2u * i], cw[2u * i + 1u]};
+        uint32_t ff[2];
+        const uint32_t e = fls_min(8u, left);
+        const uint32_t any = markers<2, true>(w, ff, s, e);
+        if (FLS_ANY(any != 0u || lit)) window<2, true>(p, tabr, w, ff, s, e, lit);
+        else window<2, false>(p, tabr, w, ff, s, e, lit);
         i += 1u;
       }
     }
@@ -851,9 +851,6 @@ struct VecSTRFSST {
       return;
     }
     const uint32_t dspan = dv1 - dv0, cspan = cv1 - cv0;
-#if FLS_EXP == 3
-    return;
-#endif
     // ---- phase 2: quarter by quarter (256 strings); the quarter's compressed bytes are split into 32 runs of
     //      (nearly) equal length that start on string boundaries, one per lane; the compressed bytes of quarter
     //      q+1 are bulk-copied into the window as soon as quarter q has been read, while q is copied out
@@ -922,9 +919,7 @@ struct VecSTRFSST {
         if (staged) {
           FlsPush p;
           p.init(stg, hh + (d0 - qd0));
-#if FLS_EXP != 5
           if (c1 > c0) decode_run(p, tab + 16u * (t & (COPIES - 1u)), cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
-#endif
           FLS_AT(ps) = p;
         } else if (c1 > c0) {
           decode_bytes(k, cv0 + c0, cv0 + c1, pay + dv0 + d0, pay + dv0 + qd0 + qlen);
@@ -938,16 +933,10 @@ struct VecSTRFSST {
         windowed = span + 16u <= CWIN && qc0 <= qc1 && qc1 <= cspan;
         if (windowed && span) { w.fence_async(); w.stage(STG, comp + wbase, (span + 15u) & ~15u); }
       }
-#if FLS_EXP != 4
       if (staged) {
         FLS_LANES(t) { FLS_AT(ps).finish(); }
-#if FLS_EXP == 23
-        FLS_LANES(t) { fls_stage_copy_out(stg, g, hh, qlen, t); }
-#else
         fls_stage_store(w, g, hh, qlen);
-#endif
       }
-#endif
     }
   }
 };

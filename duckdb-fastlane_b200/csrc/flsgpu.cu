@@ -13,6 +13,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -39,9 +40,13 @@ template <class V> cudaError_t chunk_attr() {
 }
 // persistent grid: one block per SM (fewer when the launch has fewer than two vectors per warp to hand out)
 int g_num_sms = 148;
-template <class V> void chunk_launch(const FlsChunkDev *d, uint32_t n, cudaStream_t s) {
+// SM partition (0 = off): the FSST grid takes g_split_fsst SMs (a block fills an SM's shared memory, so nothing else
+// lands there) while the bandwidth-bound kernels and then the DICT grid run on the other g_split_dict SMs.
+int g_split_fsst = 0, g_split_dict = 0;
+template <class V> void chunk_launch(const FlsChunkDev *d, uint32_t n, cudaStream_t s, uint32_t cap = 0) {
   const uint32_t slots = n * FLS_RG_VECS;
-  const uint32_t grid = std::max(1u, std::min((uint32_t)g_num_sms, slots / (2u * V::WARPS)));
+  const uint32_t sms = cap ? std::min(cap, (uint32_t)g_num_sms) : (uint32_t)g_num_sms;
+  const uint32_t grid = std::max(1u, std::min(sms, slots / (2u * V::WARPS)));
   fls_chunk_kernel<V><<<grid, V::WARPS * 32, fls_chunk_smem<V>(), s>>>(d, n);
 }
 template <template <typename> class V> cudaError_t vec_attr_all() {
@@ -83,6 +88,8 @@ struct LaunchRec {  // what is needed to (re)issue one launch once its descripto
   int kind, width;
   uint32_t n;
   uint64_t rd, wr, vec;
+  uint32_t cap = 0;  // persistent grids: at most this many blocks (0 = one per SM)
+  size_t doff = 0;   // first descriptor of the launch in the batch's descriptor array
 };
 
 bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
@@ -99,8 +106,8 @@ bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
     case FLS_K_STR_OFFSETS: vec_launch<VecSTROFFS>(d, n, s); return true;
     case FLS_K_STR_COPY: fls_str_copy_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;
     case FLS_K_STR_CONST: vec_launch<VecSTRCONST>(d, n, s); return true;
-    case FLS_K_STR_DICT: chunk_launch<VecSTRDICT>(d, n, s); return true;
-    case FLS_K_STR_FSST: chunk_launch<VecSTRFSST>(d, n, s); return true;
+    case FLS_K_STR_DICT: chunk_launch<VecSTRDICT>(d, n, s, l.cap); return true;
+    case FLS_K_STR_FSST: chunk_launch<VecSTRFSST>(d, n, s, l.cap); return true;
     case FLS_K_STR_FSST_DICTPREP: fls_fsst_dictprep_kernel<<<n * 8, 128, 0, s>>>(d, 8); return true;
   }
   return false;
@@ -235,6 +242,10 @@ int ensure_ready(flsgpu *h) {
   for (auto &sx : h->s_kx) CK(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
   CK(set_kernel_attrs());
   CK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, h->device));
+  if (const char *e = getenv("FLSGPU_SM_SPLIT")) {  // "fsst,dict" SM counts; "0" = no partition
+    g_split_fsst = g_split_dict = 0;
+    sscanf(e, "%d,%d", &g_split_fsst, &g_split_dict);
+  }
   if (!h->image) {  // opened by path: read the file into page-locked memory
     void *p = nullptr;
     const bool pin = !(h->flags & FLSGPU_OPEN_NO_PIN);
@@ -700,8 +711,8 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       if (l.kind == FLS_K_STR_DICT || l.kind == FLS_K_STR_FSST) fls_sort_by_key(l);
       if (desc_used + l.chunks.size() > desc_cap) { perr = "internal: descriptor overflow"; break; }
       memcpy(h_desc + desc_used, l.chunks.data(), l.chunks.size() * sizeof(FlsChunkDev));
+      recs.push_back(LaunchRec{l.kind, l.width, (uint32_t)l.chunks.size(), l.bytes_read, l.bytes_written, l.vectors, 0u, desc_used});
       desc_used += l.chunks.size();
-      recs.push_back(LaunchRec{l.kind, l.width, (uint32_t)l.chunks.size(), l.bytes_read, l.bytes_written, l.vectors});
     }
     if (!perr.empty()) break;
     if (cacheable && !plan_hit) {
@@ -725,27 +736,40 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     CKB(cudaStreamWaitEvent(h->s_k, eh.b, 0));
     EvPair ek = {ev(), ev()};
     CKB(cudaEventRecord(ek.a, h->s_k));
-    size_t dpos = desc0;
     // Without per-kernel timing the launches of a slice are independent (different columns) except that a
     // dictionary must be prepared before the gather that reads it: dictprep + str_dict stay on s_k, in order;
     // the long FSST kernel and the bandwidth-bound kernels go to side streams so that one kernel's tail overlaps
     // the next kernel's start.
     bool side_used[3] = {false, false, false};
     uint32_t rr = 1;
+    // SM partition: FSST on its own SMs (side stream 0); everything else in order on s_k, the DICT grid last
+    bool has_fsst = false, has_other = false;
+    for (auto &l : recs) { if (l.kind == FLS_K_STR_FSST) has_fsst = true; else if (l.kind != FLS_K_STR_FSST_DICTPREP) has_other = true; }
+    const bool split = !time_kernels && g_split_fsst > 0 && has_fsst && has_other;
+    if (split) std::stable_sort(recs.begin(), recs.end(), [](const LaunchRec &a, const LaunchRec &b2) {
+      auto rk = [](int kind) { return kind == FLS_K_STR_FSST ? 0 : kind == FLS_K_STR_FSST_DICTPREP ? 1 : kind == FLS_K_STR_DICT ? 3 : 2; };
+      return rk(a.kind) < rk(b2.kind); });
     for (auto &l : recs) {
       KEv ke = {nullptr, nullptr, l.kind * 5 + width_slot(l.width), l.rd, l.wr, l.vec};
       cudaStream_t ks = h->s_k;
+      l.cap = 0;
+      if (split) {
+        if (l.kind == FLS_K_STR_FSST) {
+          l.cap = (uint32_t)g_split_fsst;
+          ks = h->s_kx[0];
+          if (!side_used[0]) { CKB(cudaStreamWaitEvent(ks, ek.a, 0)); side_used[0] = true; }
+        } else if (l.kind == FLS_K_STR_DICT) l.cap = (uint32_t)g_split_dict;
+      } else
       if (!time_kernels && recs.size() > 1 && l.kind != FLS_K_STR_FSST_DICTPREP && l.kind != FLS_K_STR_DICT) {
         const uint32_t si = l.kind == FLS_K_STR_FSST ? 0u : 1u + (rr++ & 1u);
         ks = h->s_kx[si];
         if (!side_used[si]) { CKB(cudaStreamWaitEvent(ks, ek.a, 0)); side_used[si] = true; }
       }
       if (time_kernels) { ke.a = ev(); ke.b = ev(); CKB(cudaEventRecord(ke.a, ks)); }
-      if (!launch_kind(l, d_desc + dpos, ks)) { perr = "internal: no kernel for launch kind"; break; }
+      if (!launch_kind(l, d_desc + l.doff, ks)) { perr = "internal: no kernel for launch kind"; break; }
       CKB(cudaGetLastError());
       if (time_kernels) CKB(cudaEventRecord(ke.b, ks));
       kev.push_back(ke);
-      dpos += l.n;
       b->tm.kernel_launches++;
     }
     for (uint32_t si = 0; si < 3u; ++si)

@@ -138,7 +138,7 @@ class Batch:
             a = np.ctypeslib.as_array((C.c_uint8 * (n * c.width)).from_address(c.data)).view(dt) if n else np.empty(0, dt)
             return a.copy() if copy else a
         offs = np.ctypeslib.as_array((C.c_uint32 * (n + 1)).from_address(c.offsets))
-        end = int(offs[n])
+        end = min(int(offs[n]), int(c.payload_bytes))  # a damaged file may decode to offsets past the payload buffer
         pay = np.ctypeslib.as_array((C.c_uint8 * end).from_address(c.payload)) if end else np.empty(0, np.uint8)
         return (offs.copy(), pay.copy()) if copy else (offs, pay)
 
@@ -154,7 +154,7 @@ class Batch:
         offs = np.empty(c.padded_rows + 1, dtype=np.uint32)
         pay = np.empty(max(int(c.payload_bytes), 1), dtype=np.uint8)
         self.reader._check(lib().flsgpu_batch_fetch(self.h, i, pay.ctypes.data, offs.ctypes.data))
-        return offs[:n + 1], pay[:int(offs[n])]
+        return offs[:n + 1], pay[:min(int(offs[n]), len(pay))]
 
     def release(self):
         if self.h:

@@ -69,19 +69,19 @@ def _fuzz(img, mode, seed, n):
 
 
 def test_damaged_vector_headers_never_fault(tmp_path):
-    img = np.fromfile(zoo_image(str(tmp_path / "zoo.fls"), n=20_000), dtype=np.uint8)
+    img = np.fromfile(zoo_image(str(tmp_path / "zoo.fls")), dtype=np.uint8)
     ok, refused = _fuzz(img, "hdr", 21, 150)
     assert refused > 0 and ok + refused == 150
 
 
 def test_damaged_segments_never_fault(tmp_path):
-    img = np.fromfile(zoo_image(str(tmp_path / "zoo.fls"), n=20_000), dtype=np.uint8)
+    img = np.fromfile(zoo_image(str(tmp_path / "zoo.fls")), dtype=np.uint8)
     ok, refused = _fuzz(img, "segs", 22, 200)
     assert ok + refused == 200
 
 
 def test_damaged_footer_never_faults(tmp_path):
-    img = np.fromfile(zoo_image(str(tmp_path / "zoo.fls"), n=20_000), dtype=np.uint8)
+    img = np.fromfile(zoo_image(str(tmp_path / "zoo.fls")), dtype=np.uint8)
     ok, refused = _fuzz(img, "footer", 23, 200)
     assert refused > 0
 
