@@ -34,6 +34,7 @@
 struct fls_u4 { uint32_t x, y, z, w; };
 struct fls_ul2 { uint64_t x, y; };
 template <typename T> static inline T fls_ldg(const T *p) { return *p; }
+template <typename T> static inline T fls_ldcg(const T *p) { return *p; }
 static inline uint32_t fls_shf_r(uint32_t lo, uint32_t hi, uint32_t s) {
   s &= 31u;
   return s ? (lo >> s) | (hi << (32u - s)) : lo;
@@ -90,6 +91,8 @@ extern int fls_emul_force_any; /* tests: make every vote succeed, i.e. every lan
 typedef uint4 fls_u4;
 typedef ulonglong2 fls_ul2;
 template <typename T> FLS_DEV T fls_ldg(const T *p) { return __ldg(p); }
+// load through L2 only: data this warp has just written with streaming stores
+template <typename T> FLS_DEV T fls_ldcg(const T *p) { return __ldcg(p); }
 FLS_DEV uint32_t fls_shf_r(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_r(lo, hi, s); }
 FLS_DEV uint32_t fls_shf_l(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_l(lo, hi, s); }
 FLS_DEV uint32_t fls_shf_rc(uint32_t lo, uint32_t hi, uint32_t s) { return __funnelshift_rc(lo, hi, s); }

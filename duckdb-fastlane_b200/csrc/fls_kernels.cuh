@@ -127,12 +127,12 @@ __global__ void __launch_bounds__(FLS_WARPS_PER_BLOCK * 32) fls_vec_kernel(const
 // Each table buffer is followed by a copy of its chunk's descriptor: the decoders read descriptor fields (segment
 // addresses, output addresses) for every vector, and a shared-memory load is an order of magnitude closer than the
 // descriptor array in global memory.
-// Shared memory: [warp slots | constant area (V::CONST_SMEM) | NBUF x (table V::BLOCK_SMEM | descriptor 128 B) |
-//                 mbarriers | control]
+// Shared memory: [warp slots | constant area (V::CONST_SMEM) | tables (V::TABLES_SMEM; buffer b at V::tab_off(b)) |
+//                 NBUF descriptors of 128 B | mbarriers | control]
 #define FLS_DESC_SMEM 128u
 static_assert(sizeof(FlsChunkDev) <= FLS_DESC_SMEM && sizeof(FlsChunkDev) % 4u == 0, "descriptor copy");
 template <class V> constexpr uint32_t fls_chunk_smem() {
-  return V::WARPS * V::SMEM + V::CONST_SMEM + V::NBUF * (V::BLOCK_SMEM + FLS_DESC_SMEM) + V::WARPS * 8u + 64u;
+  return V::WARPS * V::SMEM + V::CONST_SMEM + V::TABLES_SMEM + V::NBUF * FLS_DESC_SMEM + V::WARPS * 8u + 64u;
 }
 template <class V>
 __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t n_chunks) {
@@ -145,11 +145,11 @@ __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsCh
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
   uint8_t *csm = fls_smem + V::WARPS * V::SMEM;
   uint8_t *tabs = csm + V::CONST_SMEM;
-  constexpr uint32_t BUF = V::BLOCK_SMEM + FLS_DESC_SMEM;
-  uint64_t *mbar = (uint64_t *)(tabs + NB * BUF);
+  uint8_t *descs = tabs + V::TABLES_SMEM;
+  uint64_t *mbar = (uint64_t *)(descs + NB * FLS_DESC_SMEM);
   auto copy_desc = [&](uint32_t buf, uint32_t chunk, uint32_t tid) {  // tid: 0 .. 31 at least
     if (tid < sizeof(FlsChunkDev) / 4u)
-      ((uint32_t *)(tabs + buf * BUF + V::BLOCK_SMEM))[tid] = __ldg((const uint32_t *)(chunks + chunk) + tid);
+      ((uint32_t *)(descs + buf * FLS_DESC_SMEM))[tid] = __ldg((const uint32_t *)(chunks + chunk) + tid);
   };
   uint32_t *next = (uint32_t *)(mbar + V::WARPS);  // next[NB]: vector counter of the segment in each buffer
   uint32_t *done = next + NB;                      // done[NB]: warps that have retired from it
@@ -159,8 +159,8 @@ __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsCh
   // prologue: the first NB tables (one table: by the whole block; several: one warp each, so that their
   // global-memory round trips overlap)
   V::const_init(csm, threadIdx.x, V::WARPS * 32u);
-  if (NB == 1u) V::block_init(chunks[c0], tabs, threadIdx.x, V::WARPS * 32u);
-  else if (warp < NB && warp < nseg) V::block_init(chunks[c0 + warp], tabs + warp * BUF, lane, 32u);  // side by side
+  if (NB == 1u) V::block_init(chunks[c0], tabs + V::tab_off(0), threadIdx.x, V::WARPS * 32u);
+  else if (warp < NB && warp < nseg) V::block_init(chunks[c0 + warp], tabs + V::tab_off(warp), lane, 32u);  // side by side
   if (warp < NB && warp < nseg) copy_desc(warp, c0 + warp, lane);
   if (threadIdx.x < NB) {
     next[threadIdx.x] = threadIdx.x < nseg ? seg_lo(threadIdx.x) : 0u;
@@ -172,8 +172,8 @@ __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsCh
   w.init(fls_smem + warp * V::SMEM, mbar + warp);
   for (uint32_t s = 0; s < nseg; ++s) {
     const uint32_t b = s % NB;
-    const uint8_t *bsm = tabs + b * BUF;
-    const FlsChunkDev &k = *(const FlsChunkDev *)(bsm + V::BLOCK_SMEM);  // the shared-memory copy
+    const uint8_t *bsm = tabs + V::tab_off(b);
+    const FlsChunkDev &k = *(const FlsChunkDev *)(descs + b * FLS_DESC_SMEM);  // the shared-memory copy
     const uint32_t v1 = seg_hi(s);
     if (s >= NB) {
       while (ready[b] != s + 1u) __nanosleep(32);
@@ -199,7 +199,7 @@ __global__ void __launch_bounds__(V::WARPS * 32, 1) fls_chunk_kernel(const FlsCh
       }
       if (__shfl_sync(0xFFFFFFFFu, last, 0)) {
         __threadfence_block();
-        V::block_init(chunks[c0 + s + NB], tabs + b * BUF, lane, 32u);
+        V::block_init(chunks[c0 + s + NB], tabs + V::tab_off(b), lane, 32u);
         copy_desc(b, c0 + s + NB, lane);
         if (lane == 0) { next[b] = seg_lo(s + NB); done[b] = 0u; }
         __threadfence_block();

@@ -225,6 +225,8 @@ struct VecSTRDICT {
   static constexpr uint32_t HDRS = TAB + TAB_BYTES, VEP = HDRS + 64u * 16u;
   static constexpr uint32_t BLOCK_SMEM = VEP + 68u * 4u;
   static constexpr uint32_t NBUF = 2, CONST_SMEM = 0;  // two tables per block: the next chunk's is built ahead
+  static constexpr uint32_t TABLES_SMEM = NBUF * BLOCK_SMEM;
+  FLS_MEM static constexpr uint32_t tab_off(uint32_t b) { return b * BLOCK_SMEM; }
   static constexpr bool PIPELINED = true;
   FLS_MEM static void const_init(uint8_t *, uint32_t, uint32_t) {}
   // called by all `nthreads` threads of a group (a whole block, or ONE warp: nthreads == 32)
@@ -586,13 +588,13 @@ struct VecSTRDICT {
 // bytes are bulk-copied into the warp's window; a vector is decoded in four quarters of 256 strings, lane t
 // owning the 8 consecutive strings 256q + 8t .. +7 = one compressed run -> one output run.  A lane reads its run
 // 16 bytes at a time; every code byte costs one conflict-free 128-bit table load (the block keeps 8 copies of the
-// table, one per 16-byte bank group, lane t uses copy t & 7) and one FlsPush::push.  Escapes (code 255) are rare:
-// a window that holds one takes the variant that patches the literal entries in registers.
+// table, one per 16-byte bank group, lane t uses copy t & 7) and one FlsPush::push.  An escaped literal costs the
+// same: its entry sits in a table of its own that the marker flag selects (no branch, no select).
 #ifndef FLS_FSST_WARPS
 #define FLS_FSST_WARPS 10
 #define FLS_FSST_COPIES 8
-#define FLS_FSST_STG 8448
-#define FLS_FSST_CWIN 3584
+#define FLS_FSST_STG 7424
+#define FLS_FSST_CWIN 3456
 #endif
 struct VecSTRFSST {
   // The kernel is bound by instruction issue and latency, not by shared-memory bandwidth (profiles/r01_SUMMARY.md,
@@ -601,23 +603,31 @@ struct VecSTRFSST {
   // A vector is decoded in passes of 256 strings — or 128 / 64 / 32 when a pass of the larger size would not fit:
   static constexpr uint32_t STG = FLS_FSST_STG;      // staging of one pass's output
   static constexpr uint32_t CWIN = FLS_FSST_CWIN;    // compressed bytes of one pass
-  static constexpr uint32_t E16N = 1056u;    // 16-bit relative end of every string, padded original order (x2)
+  static constexpr uint32_t E16N = 1056u;    // 16-bit relative compressed end of every string, padded original order
   static constexpr uint32_t P1 = 2176u;      // phase 1: each staged offset stream (lane bases + deltas up to 16 bits wide)
-  static constexpr uint32_t SMEM = STG + CWIN + 4u * E16N + 256u;
-  // 256 entries (one per code) x COPIES x 16 B, entry c of copy r at (c * COPIES + r) * 16: a lane reads copy
-  // t % COPIES (8 copies: the eight lanes of a 128-bit load phase never share a bank group).  Escaped literals are
-  // not in the table (an escaped byte c is the piece {c}): a window that holds an escape marker takes the ESC
-  // variant, which patches those entries in registers.  Half the size of a table with literal entries, so the block
-  // keeps TWO tables and the next chunk's is built while this one is still in use: nobody waits at a chunk boundary
-  // (with one 64 KB table 13 % of the warps' time was the spin on ready[], profiles/r02_SUMMARY.md).
-  static constexpr uint32_t COPIES = FLS_FSST_COPIES, SH = COPIES == 8 ? 7u : COPIES == 4 ? 6u : COPIES == 2 ? 5u : 4u;
-  static constexpr uint32_t BLOCK_SMEM = 256u * 16u * COPIES;
-  static constexpr uint32_t NBUF = 2, CONST_SMEM = 0;
+  static constexpr uint32_t SMEM = STG + CWIN + 2u * E16N + 320u;  // + DS[40] + LS[40]
+  // Three arrays of 256 entries x COPIES x 16 B (entry c of copy r at (c * COPIES + r) * 16; a lane reads copy
+  // t % COPIES — 8 copies: the eight lanes of a 128-bit load phase never share a bank group):
+  //   [symbols of table A | escaped literals (entry c = the byte c; the same for every chunk) | symbols of table B]
+  // A code byte c that is (is not) an escaped literal reads entry (lit << 8 | c) of the 64 KB that start at table
+  // A — or, for table B, that start at the literals with the `lit` bit flipped.  Two symbol tables: the next
+  // chunk's is built while this one is in use, so nobody waits at a chunk boundary (with ONE 64 KB table holding
+  // symbols and literals 13 % of the warps' time was the spin on ready[], profiles/r02_SUMMARY.md).
+  static constexpr uint32_t COPIES = FLS_FSST_COPIES, SH = 7u;
+  static constexpr uint32_t BLOCK_SMEM = 256u * 16u * COPIES;  // one array
+  static constexpr uint32_t NBUF = 2, CONST_SMEM = 0, TABLES_SMEM = 3u * BLOCK_SMEM;
+  FLS_MEM static constexpr uint32_t tab_off(uint32_t b) { return 2u * b * BLOCK_SMEM; }
   static constexpr bool PIPELINED = true;
-  FLS_MEM static void const_init(uint8_t *, uint32_t, uint32_t) {}
+  static_assert(COPIES == 8u, "the entry stride is 128 bytes");
   static_assert(2u * P1 <= STG + CWIN && 4224u <= STG + CWIN, "phase-1 buffers must fit the staging buffer + window");
   static_assert(SMEM % 128u == 0 && STG % 128u == 0, "warp slots stay 128-byte aligned");
-  static_assert((16u << 0) * COPIES == (1u << SH), "SH = log2 of an entry's stride");
+  // the literals (called once per block, by all its threads; `tabs` = the start of the three arrays)
+  FLS_MEM static void const_init(uint8_t *tabs, uint32_t tid, uint32_t nthreads) {
+    for (uint32_t c = tid; c < 256u; c += nthreads) {
+      const fls_u4 el = fls_piece_entry(c, 1u);
+      for (uint32_t r = 0; r < COPIES; ++r) *(fls_u4 *)(tabs + BLOCK_SMEM + ((c * COPIES + r) << 4)) = el;
+    }
+  }
   // (all of a thread's symbol loads are issued before the first table store: one memory round trip per build)
   FLS_MEM static void block_init(const FlsChunkDev &k, uint8_t *bsm, uint32_t tid, uint32_t nthreads) {
     const uint64_t *sym = (const uint64_t *)k.seg[4];
@@ -647,12 +657,17 @@ struct VecSTRFSST {
     const uint32_t y = ~x;  // zero byte <=> 0xFF
     return ~(((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y) & 0x80808080u;
   }
-  // Escape markers of NW/2 x eight consecutive compressed bytes (32-bit words w[]): ff[k] has 0x80 in every byte of
-  // w[k] that is 0xFF.  MASK: only bytes [s, e) of the window belong to the lane's run (partial first / last
-  // window); the others become 0xFF bytes that are no markers — code 255 is the table's empty entry.
+  // NW/2 x eight consecutive compressed bytes (32-bit words w[]) of a lane's run: all table loads in flight, then
+  // all pushes, straight-line.  Byte j is a literal when byte j-1 is an escape marker (0xFF), `lit` standing for
+  // byte -1; that is exact unless two 0xFF bytes are adjacent (a literal 0xFF), and such a window takes the
+  // byte-by-byte path.  The marker flags shifted up by one bit are the literal flags, each in bit 0 of its own byte;
+  // one byte permute puts {byte j, flags of byte j} side by side, which IS the 9-bit table index of byte j.
+  // MASK: only bytes [s, e) of the window belong to the run (partial first / last window); the others are turned
+  // into 0xFF bytes that are no markers — code 255 is the symbol tables' empty entry.
+  // tabr = the lane's copy inside the 64 KB the index addresses, flip = 0 (table A) or 1 << 15 (table B).
   template <uint32_t NW, bool MASK>
-  FLS_MEM static uint32_t markers(uint32_t (&w)[NW], uint32_t (&ff)[NW], uint32_t s, uint32_t e) {
-    uint32_t any = 0;
+  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, uint32_t flip, uint32_t (&w)[NW], uint32_t s, uint32_t e, bool &lit) {
+    uint32_t ff[NW];
 #pragma unroll
     for (uint32_t k = 0; k < NW; ++k) ff[k] = ff_bytes(w[k]);
     if (MASK) {
@@ -666,82 +681,56 @@ struct VecSTRFSST {
         w[k] |= ~vm;
       }
     }
+    const uint32_t c31 = lit ? 0x80000000u : 0u;  // "the byte before the window is a marker", where a word's last byte has it
+    uint32_t lf[NW];  // literal flags: bit 8j = byte j of the word is a literal
 #pragma unroll
-    for (uint32_t k = 0; k < NW; ++k) any |= ff[k];
-    return any;
-  }
-  // The window's 4 * NW codes: all table loads in flight, then all pushes, straight-line.  ESC = false: no lane of
-  // the warp has a marker in its window or a literal pending — every byte is a code.  ESC = true: byte j is a literal
-  // when byte j-1 is a marker, `lit` standing for byte -1 (the entry {byte} replaces the loaded one; the marker
-  // itself loads the empty entry); that is exact unless two 0xFF bytes are adjacent (a literal 0xFF), and such a
-  // window goes byte by byte.
-  template <uint32_t NW, bool ESC>
-  FLS_MEM static void window(FlsPush &p, const uint8_t *tabr, const uint32_t (&w)[NW], const uint32_t (&ff)[NW], uint32_t s, uint32_t e,
-                             bool &lit) {
-    const uint32_t c7 = lit ? 0x80u : 0u;
-    if (ESC) {
-      uint32_t adj = ((ff[0] << 8) | c7) & ff[0];
+    for (uint32_t k = 0; k < NW; ++k) lf[k] = fls_shf_l(k ? ff[k - 1u] : c31, ff[k], 1u);
+    uint32_t adj = 0;
 #pragma unroll
-      for (uint32_t k = 1; k < NW; ++k) adj |= ((ff[k] << 8) | (ff[k - 1u] >> 24)) & ff[k];
-      if (adj) {
+    for (uint32_t k = 0; k < NW; ++k) adj |= (lf[k] << 7) & ff[k];  // a marker that is itself a literal
+    if (adj) {
+      // adjacent 0xFF bytes: byte by byte
 #pragma unroll
-        for (uint32_t j = 0; j < 4u * NW; ++j) {  // (constant bounds: w[] stays in registers)
-          if (j < s || j >= e) continue;
-          const uint32_t c = (w[j >> 2] >> (8u * (j & 3u))) & 0xFFu;
-          if (lit) { p.push_byte(c); lit = false; }
-          else if (c == 255u) lit = true;
-          else p.push(fls_lds128<fls_u4>(tabr + (c << SH)));
-        }
-        return;
+      for (uint32_t j = 0; j < 4u * NW; ++j) {  // (constant bounds: w[] stays in registers)
+        if (MASK && (j < s || j >= e)) continue;
+        const uint32_t c = (w[j >> 2] >> (8u * (j & 3u))) & 0xFFu;
+        if (lit) { p.push_byte(c); lit = false; }
+        else if (c == 255u) lit = true;
+        else p.push(fls_lds128<fls_u4>(tabr + ((c << SH) ^ flip)));
       }
-      lit = (ff[NW - 1u] >> 31) != 0u;
+      return;
     }
-    constexpr uint32_t IM = 0xFFu << SH;  // the 8 code bits at the entry stride
+    lit = (ff[NW - 1u] >> 31) != 0u;
+    constexpr uint32_t IM = 0x1FFu << SH;  // the 9 index bits at the entry stride
     fls_u4 en[4u * NW];
 #pragma unroll
     for (uint32_t k = 0; k < NW; ++k) {
-      en[4u * k] = fls_lds128<fls_u4>(tabr + ((w[k] << SH) & IM));
-      en[4u * k + 1u] = fls_lds128<fls_u4>(tabr + ((w[k] >> (8u - SH)) & IM));
-      en[4u * k + 2u] = fls_lds128<fls_u4>(tabr + ((w[k] >> (16u - SH)) & IM));
-      en[4u * k + 3u] = fls_lds128<fls_u4>(tabr + ((w[k] >> (24u - SH)) & IM));
-    }
-    if (ESC) {
-#pragma unroll
-      for (uint32_t j = 0; j < 4u * NW; ++j) {
-        const uint32_t k = j >> 2, b = j & 3u;
-        // marker flag of the byte before byte j
-        const uint32_t m = b ? (ff[k] >> (8u * b - 1u)) & 1u : (k ? ff[k - 1u] >> 31 : c7 >> 7);
-        if (m) {
-          const uint32_t c = (w[k] >> (8u * b)) & 0xFFu;
-          en[j].x = c; en[j].y = 0u; en[j].z = c; en[j].w = 8u;
-        }
-      }
+      const uint32_t x01 = fls_prmt(w[k], lf[k], 0x5140u), x23 = fls_prmt(w[k], lf[k], 0x7362u);  // {b0, f0, b1, f1}, {b2, f2, b3, f3}
+      en[4u * k] = fls_lds128<fls_u4>(tabr + (((x01 << SH) & IM) ^ flip));
+      en[4u * k + 1u] = fls_lds128<fls_u4>(tabr + (((x01 >> (16u - SH)) & IM) ^ flip));
+      en[4u * k + 2u] = fls_lds128<fls_u4>(tabr + (((x23 << SH) & IM) ^ flip));
+      en[4u * k + 3u] = fls_lds128<fls_u4>(tabr + (((x23 >> (16u - SH)) & IM) ^ flip));
     }
     p.push_all(en);
   }
   // A lane's compressed run = bytes [a, b) of the staged window `cwin`, read 16 bytes at a time (8 at the end).
-  FLS_MEM static void decode_run(FlsPush &p, const uint8_t *tabr, const uint8_t *cwin, uint32_t a, uint32_t b) {
+  FLS_MEM static void decode_run(FlsPush &p, const uint8_t *tabr, uint32_t flip, const uint8_t *cwin, uint32_t a, uint32_t b) {
     const uint32_t *cw = (const uint32_t *)cwin;
     bool lit = false;
     uint32_t i = a >> 3;  // 8-byte unit
     while (8u * i < b) {
+      uint32_t w[4];
+      w[0] = cw[2u * i]; w[1] = cw[2u * i + 1u];
       const uint32_t s = 8u * i < a ? a - 8u * i : 0u, left = b - 8u * i;
-      // the variants are chosen by votes of the lanes still in the loop, so they stay converged
+      // the variant is chosen by a vote of the lanes still in the loop, so they stay converged
       if (FLS_ANY(left > 8u)) {
-        uint32_t w[4] = {cw[2u * i], cw[2u * i + 1u], cw[2u * i + 2u], cw[2u * i + 3u]};  // the window has 16 bytes of slack
-        uint32_t ff[4];
-        const uint32_t e = fls_min(16u, left);
-        const uint32_t any = FLS_ANY(s != 0u || left < 16u) ? markers<4, true>(w, ff, s, e) : markers<4, false>(w, ff, 0u, 16u);
-        if (FLS_ANY(any != 0u || lit)) window<4, true>(p, tabr, w, ff, s, e, lit);
-        else window<4, false>(p, tabr, w, ff, s, e, lit);
+        w[2] = cw[2u * i + 2u]; w[3] = cw[2u * i + 3u];  // the window has 16 bytes of slack
+        if (FLS_ANY(s != 0u || left < 16u)) window<4, true>(p, tabr, flip, w, s, fls_min(16u, left), lit);
+        else window<4, false>(p, tabr, flip, w, 0u, 16u, lit);
         i += 2u;
       } else {
-        uint32_t w[2] = {cw[2u * i], cw[2u * i + 1u]};
-        uint32_t ff[2];
-        const uint32_t e = fls_min(8u, left);
-        const uint32_t any = markers<2, true>(w, ff, s, e);
-        if (FLS_ANY(any != 0u || lit)) window<2, true>(p, tabr, w, ff, s, e, lit);
-        else window<2, false>(p, tabr, w, ff, s, e, lit);
+        uint32_t w2[2] = {w[0], w[1]};
+        window<2, true>(p, tabr, flip, w2, s, fls_min(8u, left), lit);
         i += 1u;
       }
     }
@@ -769,11 +758,12 @@ struct VecSTRFSST {
   // DELTA u32 chain of lane t over a staged end-offset stream.  Writes {lane base, end 0 .. end 30} + add to the
   // 32 aligned slots line[0..31] (slot i = start of string i; end 31 is the next lane's base) and the 32 ends,
   // relative to `rel0`, as 16-bit values into e16 (padded original order).  Returns the lane's last end.
+  template <bool LINE, bool E16>
   FLS_MEM static uint32_t walk_ends(const uint8_t *stage, uint32_t bw, uint32_t base, uint32_t t, uint32_t add, uint32_t rel0,
                                     uint32_t *line, uint16_t *e16) {
     const uint32_t *bases = (const uint32_t *)stage, *pk = (const uint32_t *)(stage + 128);
     uint32_t acc = bases[t];
-    uint32_t *e16w = (uint32_t *)(e16 + slot16(fls_lane_start(t)));
+    uint32_t *e16w = E16 ? (uint32_t *)(e16 + slot16(fls_lane_start(t))) : nullptr;
     // two groups of four steps per loop iteration: fully unrolled (8) the two walks are 12 KB of straight-line code
     // that the ten warps of a block, each in another phase, keep evicting from the instruction cache
     // (1 / 2 / 8 groups: 1.285 / 1.273 / 1.291 ms on the SF10 launch)
@@ -789,13 +779,15 @@ struct VecSTRFSST {
       for (uint32_t j = 0; j < 4u; ++j)
         x[j + 1u] = x[j] + (bw ? extract32(pk, bw, fls_chain_row<32>(r4 + j), t) : 0u) + base;
       acc = x[4];
-      if (line) {
+      if (LINE) {
         fls_u4 o;
         o.x = x[0] + add; o.y = x[1] + add; o.z = x[2] + add; o.w = x[3] + add;
         fls_st128(line + r4, o);
       }
-      e16w[r4 / 2u] = ((x[1] - rel0) & 0xFFFFu) | ((x[2] - rel0) << 16);
-      e16w[r4 / 2u + 1u] = ((x[3] - rel0) & 0xFFFFu) | ((x[4] - rel0) << 16);
+      if (E16) {
+        e16w[r4 / 2u] = ((x[1] - rel0) & 0xFFFFu) | ((x[2] - rel0) << 16);
+        e16w[r4 / 2u + 1u] = ((x[3] - rel0) & 0xFFFFu) | ((x[4] - rel0) << 16);
+      }
     }
     return acc;
   }
@@ -803,14 +795,21 @@ struct VecSTRFSST {
   FLS_MEM static uint32_t slot16(uint32_t e) { return e + ((e >> 6) << 1); }
   // start offset (relative) of string s: the end of string s - 1
   FLS_MEM static uint32_t start16(const uint16_t *e16, uint32_t s) { return s ? (uint32_t)e16[slot16(s - 1u)] : 0u; }
-  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, uint32_t /*v_next*/, FlsWarp &w, const uint8_t *tab, const uint8_t *) {
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, uint32_t /*v_next*/, FlsWarp &w, const uint8_t *tab, const uint8_t *tabs) {
+    // table A: the 64 KB [symbols A | literals]; table B: [literals | symbols B] with the literal bit flipped
+    const uint32_t flip = tab == tabs ? 0u : 1u << 15;
+    const uint8_t *tab64 = flip ? tabs + BLOCK_SMEM : tabs;
     const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
     uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
     if (bwd > 32u) bwd = 32u;
     if (bwc > 32u) bwc = 32u;
     uint8_t *stg = w.sm;
-    uint16_t *DE = (uint16_t *)(w.sm + STG + CWIN), *CE = DE + E16N;
-    uint32_t *LS = (uint32_t *)(CE + E16N);  // LS[0..32] = first string of each lane, LS[34..37] = vector extents
+    // Compressed ends: 16 bits each, all 1024 (the lanes' run boundaries are searched in them).  Decoded starts: only
+    // of every 32nd string (DS[m] = start of string 32 m, relative to the vector's; every pass boundary is one); the
+    // start of a lane's first string is read back from offsets[], which phase 1 has just written (an L2 hit).
+    uint16_t *CE = (uint16_t *)(w.sm + STG + CWIN);
+    uint32_t *DS = (uint32_t *)(CE + E16N);  // DS[0..32]
+    uint32_t *LS = DS + 40;                  // LS[0..32] = first string of each lane, LS[34..35] = vector extents
     const uint8_t *comp = k.seg[5];
     uint8_t *pay = k.pay + k.pay_base;
     // ---- phase 1: both end-offset streams -> offsets[] (global) and 16-bit relative ends of every string (shared).
@@ -827,15 +826,16 @@ struct VecSTRFSST {
     FLS_VAR(uint32_t, lc0); FLS_VAR(uint32_t, lc1); FLS_VAR(uint32_t, ld0);
     FLS_LANES(t) {
       FLS_AT(ld0) = ((const uint32_t *)w.sm)[t];
-      const uint32_t dend = walk_ends(w.sm, bwd, (uint32_t)hd.base, t, k.pay_base, dv0, offs + fls_lane_start(t), DE);
-      if (t == 31u) { offs[FLS_VEC] = dend + k.pay_base; LS[34] = dend; }  // lane 31 owns the last strings
+      const uint32_t dend = walk_ends<true, false>(w.sm, bwd, (uint32_t)hd.base, t, k.pay_base, dv0, offs + fls_lane_start(t), nullptr);
+      DS[fls_lane_start(t) >> 5] = FLS_AT(ld0) - dv0;  // the lane's 32 strings start at a multiple of 32
+      if (t == 31u) { offs[FLS_VEC] = dend + k.pay_base; LS[34] = dend; DS[32] = dend - dv0; }  // lane 31 owns the last strings
     }
     if (!both) { w.fence_async(); w.stage(0, k.seg[3] + 16ull * hc.ep, 128u + 128u * bwc); w.wait(); }
     const uint8_t *cst = w.sm + (both ? P1 : 0u);
     const uint32_t cv0 = ((const uint32_t *)cst)[0];
     FLS_LANES(t) {
       FLS_AT(lc0) = ((const uint32_t *)cst)[t];
-      const uint32_t cend = walk_ends(cst, bwc, (uint32_t)hc.base, t, 0u, cv0, nullptr, CE);
+      const uint32_t cend = walk_ends<false, true>(cst, bwc, (uint32_t)hc.base, t, 0u, cv0, nullptr, CE);
       FLS_AT(lc1) = cend;
       if (t == 31u) LS[35] = cend;
     }
@@ -863,7 +863,7 @@ struct VecSTRFSST {
       for (uint32_t lv = 0; lv < 3u; ++lv) {
         const uint32_t ps = 256u >> lv;
         if (t < FLS_VEC / ps) {
-          const uint32_t d = start16(DE, (t + 1u) * ps) - start16(DE, t * ps), c = start16(CE, (t + 1u) * ps) - start16(CE, t * ps);
+          const uint32_t d = DS[((t + 1u) * ps) >> 5] - DS[(t * ps) >> 5], c = start16(CE, (t + 1u) * ps) - start16(CE, t * ps);
           if (d + 15u > STG || c + 31u > CWIN) b |= 1u << (8u * lv);
         }
       }
@@ -886,7 +886,7 @@ struct VecSTRFSST {
       const uint32_t cur_wbase = wbase, cur_c0 = qc0, cur_c1 = qc1;
       const bool cur_windowed = windowed;
       const uint32_t S0 = PASS * qt, S1 = S0 + PASS;
-      const uint32_t qd0 = start16(DE, S0), qlen = start16(DE, S1) - qd0;
+      const uint32_t qd0 = DS[S0 >> 5], qlen = DS[S1 >> 5] - qd0;
       uint8_t *g = pay + dv0 + qd0;
       const uint32_t hh = (uint32_t)((uintptr_t)g & 15u);
       // first string of lane t: the first one that starts at or after t/32 of the quarter's compressed bytes
@@ -912,14 +912,15 @@ struct VecSTRFSST {
       w.store_wait();  // the previous pass's bulk copy has read the staging buffer
       FLS_LANES(t) {
         const uint32_t sa = LS[t], sb = LS[t + 1u];
-        uint32_t c0 = start16(CE, sa), c1 = start16(CE, sb), d0 = start16(DE, sa);
+        uint32_t c0 = start16(CE, sa), c1 = start16(CE, sb);
+        uint32_t d0 = fls_ldcg(offs + fls_min(sa, FLS_VEC)) - k.pay_base - dv0;
         // a lane's run lies inside the pass: always true for ascending ends, two compares otherwise
         c0 = fls_max(c0, cur_c0); c1 = fls_min(c1, cur_c1);
         d0 = fls_min(fls_max(d0, qd0), qd0 + qlen);
         if (staged) {
           FlsPush p;
           p.init(stg, hh + (d0 - qd0));
-          if (c1 > c0) decode_run(p, tab + 16u * (t & (COPIES - 1u)), cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
+          if (c1 > c0) decode_run(p, tab64 + 16u * (t & (COPIES - 1u)), flip, cwin, cv0 + c0 - cur_wbase, cv0 + c1 - cur_wbase);
           FLS_AT(ps) = p;
         } else if (c1 > c0) {
           decode_bytes(k, cv0 + c0, cv0 + c1, pay + dv0 + d0, pay + dv0 + qd0 + qlen);

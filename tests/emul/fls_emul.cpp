@@ -22,16 +22,28 @@ template <class V, class = void> struct is_pipelined { static constexpr bool val
 template <class V> struct is_pipelined<V, std::enable_if_t<V::PIPELINED>> { static constexpr bool value = true; };
 
 template <class V> static void run_vectors(const FlsLaunch &l) {
-  std::vector<uint8_t> smem(V::SMEM + V::BLOCK_SMEM + 256);
-  uint8_t *slot = (uint8_t *)(((uintptr_t)smem.data() + 127) & ~(uintptr_t)127);
-  uint8_t *bsm = slot + V::SMEM;
-  for (const FlsChunkDev &k : l.chunks) {
-    if constexpr (V::BLOCK_SMEM != 0) V::block_init(k, bsm, 0, 1);
-    if constexpr (is_pipelined<V>::value) {
-      FlsWarp w;  // one warp decodes the chunk's vectors in order, each call prefetching the next vector
+  if constexpr (is_pipelined<V>::value) {
+    // chunk kernels: [warp slot | constant area | tables | ...] as in fls_chunk_kernel; consecutive chunks alternate
+    // between the table buffers, one warp decodes a chunk's vectors in order, each call prefetching the next vector
+    std::vector<uint8_t> smem(V::SMEM + V::CONST_SMEM + V::TABLES_SMEM + 256);
+    uint8_t *slot = (uint8_t *)(((uintptr_t)smem.data() + 127) & ~(uintptr_t)127);
+    uint8_t *csm = slot + V::SMEM, *tabs = csm + V::CONST_SMEM;
+    V::const_init(csm, 0, 1);
+    uint32_t b = 0;
+    for (const FlsChunkDev &k : l.chunks) {
+      uint8_t *bsm = tabs + V::tab_off(b);
+      b = (b + 1) % V::NBUF;
+      V::block_init(k, bsm, 0, 1);
+      FlsWarp w;
       w.init(slot, nullptr);
-      for (uint32_t v = 0; v < k.n_vec; ++v) V::run(k, v, v + 1 < k.n_vec ? v + 1 : FLS_NO_VECTOR, w, bsm, nullptr);
-    } else {
+      for (uint32_t v = 0; v < k.n_vec; ++v) V::run(k, v, v + 1 < k.n_vec ? v + 1 : FLS_NO_VECTOR, w, bsm, csm);
+    }
+  } else {
+    std::vector<uint8_t> smem(V::SMEM + V::BLOCK_SMEM + 256);
+    uint8_t *slot = (uint8_t *)(((uintptr_t)smem.data() + 127) & ~(uintptr_t)127);
+    uint8_t *bsm = slot + V::SMEM;
+    for (const FlsChunkDev &k : l.chunks) {
+      if constexpr (V::BLOCK_SMEM != 0) V::block_init(k, bsm, 0, 1);
       for (uint32_t v = 0; v < k.n_vec; ++v) {
         FlsWarp w;
         w.init(slot, nullptr);
