@@ -23,6 +23,7 @@
 #include "fls_plan.h"
 #include "fls_strings.cuh"
 #include "fls_validate.h"
+#include "fls_filter.cuh"
 
 // ---------------------------------------------------------------------------------------------------------
 // kernel table
@@ -228,6 +229,10 @@ struct flsgpu_batch {
   std::vector<FlsColNeed> need;
   std::vector<void *> dev_bufs, host_bufs;
   flsgpu_timing tm;
+  // filtered batches: row ids of the surviving rows (device, and host for FLSGPU_OUT_HOST)
+  bool filtered = false;
+  uint64_t *sel_dev = nullptr, *sel_host = nullptr;
+  uint64_t n_sel = 0;
 };
 
 namespace {
@@ -831,6 +836,221 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
   *out = b;
   return FLSGPU_OK;
 #undef CKB
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// filtered decode: decode into HBM, select on the device, compact, and only then copy out
+// ---------------------------------------------------------------------------------------------------------
+int flsgpu_decode_filtered(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, uint32_t n_cols,
+                           const flsgpu_predicate *preds, uint32_t n_preds, uint32_t flags, flsgpu_batch_t **out) {
+  if (!out) return h->fail(FLSGPU_E_RANGE, "null argument");
+  *out = nullptr;
+  const FlsTable &t = h->t;
+  if (n_preds > FLSGPU_MAX_PREDICATES || (n_preds && !preds)) return h->fail(FLSGPU_E_RANGE, "too many predicates");
+  if (g0 > g1 || g1 > t.n_rg) return h->fail(FLSGPU_E_RANGE, "bad row-group range");
+  const auto host_t0 = std::chrono::steady_clock::now();
+  // projected columns first, then the predicate columns that are not projected
+  std::vector<uint32_t> proj;
+  if (cols) proj.assign(cols, cols + n_cols);
+  else for (uint32_t c = 0; c < t.n_cols; ++c) proj.push_back(c);
+  for (uint32_t c : proj) if (c >= t.n_cols) return h->fail(FLSGPU_E_RANGE, "bad column id");
+  std::vector<uint32_t> dcols = proj;
+  std::vector<uint32_t> pred_slot(n_preds);
+  for (uint32_t k = 0; k < n_preds; ++k) {
+    const flsgpu_predicate &p = preds[k];
+    if (p.col >= t.n_cols || p.op > FLSGPU_CMP_GE) return h->fail(FLSGPU_E_RANGE, "bad predicate");
+    const bool is_str = fls_type_bits(t.types[p.col]) == 0;
+    if (is_str && (p.op > FLSGPU_CMP_NE || (p.text_len && !p.text))) return h->fail(FLSGPU_E_RANGE, "string predicates are = and <> only");
+    auto it = std::find(dcols.begin(), dcols.end(), p.col);
+    pred_slot[k] = (uint32_t)(it - dcols.begin());
+    if (it == dcols.end()) dcols.push_back(p.col);
+  }
+  flsgpu_batch_t *b = nullptr;
+  if (int rc = flsgpu_decode(h, g0, g1, dcols.data(), (uint32_t)dcols.size(), FLSGPU_OUT_DEVICE, &b)) return rc;
+  const bool to_host = (flags & FLSGPU_OUT_HOST) != 0;
+  const uint64_t prow = t.padded_rows(g0, g1);
+  const uint32_t n_vec = (uint32_t)(prow / FLS_VEC);
+  auto bail = [&](int code, const std::string &m) {
+    cudaDeviceSynchronize();
+    cudaGetLastError();
+    flsgpu_batch_release(b);
+    return h->fail(code, m);
+  };
+#define CKF(call)                                                                                        \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) return bail(FLSGPU_E_CUDA, std::string("CUDA: " #call ": ") + cudaGetErrorString(e_)); \
+  } while (0)
+  b->filtered = true;
+  b->flags = flags;
+  if (!n_vec) {
+    for (auto &o : b->out) { o.rows = o.padded_rows = 0; }
+    b->out.resize(proj.size()); b->dev.resize(proj.size()); b->cols = proj;
+    *out = b;
+    return FLSGPU_OK;
+  }
+  cudaStream_t s = h->s_k;
+  auto dalloc = [&](size_t n) { void *p = h->dev_alloc(n); if (p) b->dev_bufs.push_back(p); return p; };
+  auto halloc = [&](size_t n) { void *p = h->host_alloc(n); if (p) b->host_bufs.push_back(p); return p; };
+  cudaEvent_t ev0 = h->ev_get(), ev1 = h->ev_get();
+  if (!ev0 || !ev1) return bail(FLSGPU_E_CUDA, "CUDA: cannot create an event");
+  CKF(cudaEventRecord(ev0, s));
+  // ---- per-vector meta: valid rows and the logical row id of the vector's first row; predicate constants
+  const uint32_t n_str = [&] { uint32_t n = 0; for (uint32_t c : proj) n += fls_type_bits(t.types[c]) == 0; return n; }();
+  size_t text_bytes = 0;
+  for (uint32_t k = 0; k < n_preds; ++k) text_bytes += (preds[k].text_len + 15) & ~(uint64_t)15;
+  const size_t meta_bytes = (size_t)n_vec * 16 + text_bytes + 16;
+  uint8_t *h_meta = (uint8_t *)halloc(meta_bytes), *d_meta = (uint8_t *)dalloc(meta_bytes);
+  uint32_t *d_mask = (uint32_t *)dalloc((size_t)n_vec * 128);
+  uint32_t *d_cnt = (uint32_t *)dalloc((size_t)n_vec * 4 * (1 + n_str));
+  uint64_t *d_off = (uint64_t *)dalloc((size_t)n_vec * 8 * (1 + n_str));
+  uint64_t *d_tot = (uint64_t *)dalloc(8 * (1 + n_str)), *h_tot = (uint64_t *)halloc(8 * (1 + n_str));
+  if (!h_meta || !d_meta || !d_mask || !d_cnt || !d_off || !d_tot || !h_tot) return bail(FLSGPU_E_NOMEM, "out of memory for the selection");
+  uint64_t *h_row0 = (uint64_t *)h_meta;
+  uint32_t *h_valid = (uint32_t *)(h_meta + (size_t)n_vec * 8);
+  uint8_t *h_text = h_meta + (size_t)n_vec * 16;
+  {
+    uint64_t v = 0, row = 0;
+    for (uint32_t g = g0; g < g1; ++g) {
+      uint64_t left = t.rgs[g].n_tuples;
+      for (uint32_t i = 0; i < t.rgs[g].n_vec; ++i, ++v) {
+        const uint32_t take = (uint32_t)std::min<uint64_t>(left, FLS_VEC);
+        h_row0[v] = row; h_valid[v] = take;
+        row += take; left -= take;
+      }
+    }
+  }
+  FlsPredSet ps;
+  memset(&ps, 0, sizeof(ps));
+  ps.n = n_preds;
+  size_t tpos = 0;
+  for (uint32_t k = 0; k < n_preds; ++k) {
+    const flsgpu_predicate &p = preds[k];
+    const FlsColOut &d = b->dev[pred_slot[k]];
+    const int ty = t.types[p.col];
+    FlsPredDev &q = ps.p[k];
+    q.data = d.data; q.offsets = d.offsets; q.payload = d.payload;
+    q.width = fls_type_bits(ty) / 8; q.op = p.op; q.i64 = p.i64; q.f64 = p.f64;
+    if (!q.width) {
+      q.kind = 4;
+      if (p.text_len) memcpy(h_text + tpos, p.text, p.text_len);
+      q.text = d_meta + (size_t)n_vec * 16 + tpos; q.text_len = (uint32_t)p.text_len;
+      if (p.text_len >> 32) q.text_len = 0xFFFFFFFFu;  // longer than any string of a batch: never equal
+      tpos += (p.text_len + 15) & ~(uint64_t)15;
+    } else if (ty == FLS_T_FLOAT) q.kind = 2;
+    else if (ty == FLS_T_DOUBLE) q.kind = 3;
+    else if (ty == FLS_T_BOOLEAN || ty == FLS_T_UINT8 || ty == FLS_T_UINT16 || ty == FLS_T_UINT32 || ty == FLS_T_UINT64) q.kind = 1;
+    else q.kind = 0;
+  }
+  CKF(cudaMemcpyAsync(d_meta, h_meta, meta_bytes, cudaMemcpyHostToDevice, s));
+  CKF(cudaMemsetAsync(d_tot, 0, 8 * (1 + n_str), s));
+  const uint64_t *d_row0 = (const uint64_t *)d_meta;
+  const uint32_t *d_valid = (const uint32_t *)(d_meta + (size_t)n_vec * 8);
+  const uint32_t grid = (n_vec + 7) / 8;
+  fls_filter::mask_kernel<<<grid, 256, 0, s>>>(ps, d_valid, n_vec, d_mask, d_cnt);
+  fls_filter::scan_kernel<<<1, 1024, 0, s>>>(d_cnt, n_vec, d_off, d_tot);
+  // string columns: bytes of the surviving strings per vector
+  {
+    uint32_t si = 0;
+    for (size_t i = 0; i < proj.size(); ++i) {
+      if (b->out[i].width) continue;
+      ++si;
+      fls_filter::str_bytes_kernel<<<grid, 256, 0, s>>>(b->dev[i].offsets, d_mask, n_vec, d_cnt + (size_t)si * n_vec);
+      fls_filter::scan_kernel<<<1, 1024, 0, s>>>(d_cnt + (size_t)si * n_vec, n_vec, d_off + (size_t)si * n_vec, d_tot + si);
+    }
+  }
+  CKF(cudaGetLastError());
+  CKF(cudaMemcpyAsync(h_tot, d_tot, 8 * (1 + n_str), cudaMemcpyDeviceToHost, s));
+  CKF(cudaStreamSynchronize(s));
+  const uint64_t n_sel = h_tot[0];
+  // ---- compact every projected column into exactly sized buffers
+  std::vector<flsgpu_column> nout(proj.size());
+  std::vector<FlsColOut> ndev(proj.size());
+  uint64_t d2h = 0;
+  b->n_sel = n_sel;
+  b->sel_dev = (uint64_t *)dalloc(std::max<uint64_t>(n_sel, 1) * 8);
+  if (!b->sel_dev) return bail(FLSGPU_E_NOMEM, "out of device memory");
+  fls_filter::compact_rowid_kernel<<<grid, 256, 0, s>>>(d_row0, d_mask, d_off, n_vec, b->sel_dev);
+  if (to_host) {
+    b->sel_host = (uint64_t *)halloc(std::max<uint64_t>(n_sel, 1) * 8);
+    if (!b->sel_host) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+  }
+  uint32_t si = 0;
+  for (size_t i = 0; i < proj.size(); ++i) {
+    flsgpu_column o = b->out[i];
+    FlsColOut nd;
+    o.rows = o.padded_rows = n_sel;
+    if (o.width) {
+      nd.data = dalloc(std::max<uint64_t>(n_sel, 1) * o.width);
+      if (!nd.data) return bail(FLSGPU_E_NOMEM, "out of device memory");
+      switch (o.width) {
+        case 1: fls_filter::compact_fixed_kernel<uint8_t><<<grid, 256, 0, s>>>((const uint8_t *)b->dev[i].data, d_mask, d_off, n_vec, (uint8_t *)nd.data); break;
+        case 2: fls_filter::compact_fixed_kernel<uint16_t><<<grid, 256, 0, s>>>((const uint16_t *)b->dev[i].data, d_mask, d_off, n_vec, (uint16_t *)nd.data); break;
+        case 4: fls_filter::compact_fixed_kernel<uint32_t><<<grid, 256, 0, s>>>((const uint32_t *)b->dev[i].data, d_mask, d_off, n_vec, (uint32_t *)nd.data); break;
+        default: fls_filter::compact_fixed_kernel<uint64_t><<<grid, 256, 0, s>>>((const uint64_t *)b->dev[i].data, d_mask, d_off, n_vec, (uint64_t *)nd.data); break;
+      }
+      o.data = nd.data;
+      o.decoded_bytes = n_sel * o.width;
+      if (to_host) {
+        if (!(o.data = halloc(std::max<uint64_t>(n_sel, 1) * o.width))) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+        if (n_sel) CKF(cudaMemcpyAsync(o.data, nd.data, n_sel * o.width, cudaMemcpyDeviceToHost, s));
+        d2h += n_sel * o.width;
+      }
+    } else {
+      ++si;
+      const uint64_t pay = h_tot[si];
+      if (pay >> 32) return bail(FLSGPU_E_LIMIT, "string payload of one batch must stay below 4 GiB; split the row-group range");
+      nd.offsets = (uint32_t *)dalloc((n_sel + 1) * 4);
+      nd.payload = (uint8_t *)dalloc(pay + 16);
+      if (!nd.offsets || !nd.payload) return bail(FLSGPU_E_NOMEM, "out of device memory");
+      CKF(cudaMemsetAsync(nd.offsets, 0, 4, s));
+      fls_filter::compact_str_kernel<<<grid, 256, 0, s>>>(b->dev[i].offsets, b->dev[i].payload, d_mask, d_off, d_off + (size_t)si * n_vec,
+                                                         n_vec, nd.offsets, nd.payload);
+      o.offsets = nd.offsets; o.payload = nd.payload; o.payload_bytes = pay;
+      o.decoded_bytes = (n_sel + 1) * 4 + pay;
+      if (to_host) {
+        o.offsets = (uint32_t *)halloc((n_sel + 1) * 4);
+        o.payload = (uint8_t *)halloc(pay + 16);
+        if (!o.offsets || !o.payload) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+        CKF(cudaMemcpyAsync(o.offsets, nd.offsets, (n_sel + 1) * 4, cudaMemcpyDeviceToHost, s));
+        if (pay) CKF(cudaMemcpyAsync(o.payload, nd.payload, pay, cudaMemcpyDeviceToHost, s));
+        d2h += (n_sel + 1) * 4 + pay;
+      }
+    }
+    nout[i] = o; ndev[i] = nd;
+  }
+  if (to_host && n_sel) { CKF(cudaMemcpyAsync(b->sel_host, b->sel_dev, n_sel * 8, cudaMemcpyDeviceToHost, s)); d2h += n_sel * 8; }
+  CKF(cudaGetLastError());
+  CKF(cudaEventRecord(ev1, s));
+  CKF(cudaEventSynchronize(ev1));
+  float ms = 0;
+  cudaEventElapsedTime(&ms, ev0, ev1);
+  h->ev_free.push_back(ev0); h->ev_free.push_back(ev1);
+  b->tm.ms_total += ms; b->tm.ms_kernels += ms; b->tm.d2h_bytes = d2h;
+  b->tm.kernel_launches += 3 + (uint32_t)proj.size() + 2 * n_str;
+  b->tm.ms_host_total = (float)std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
+  // the full-size decode buffers go back to the pool now; the batch keeps the compacted ones
+  {
+    std::vector<void *> keep;
+    for (void *p : b->dev_bufs) {
+      bool full = false;
+      for (auto &d : b->dev) full = full || p == d.data || p == (void *)d.offsets || p == (void *)d.payload;
+      if (full) h->dev_free(p); else keep.push_back(p);
+    }
+    b->dev_bufs.swap(keep);
+  }
+  b->out.swap(nout); b->dev.swap(ndev); b->cols = proj;
+  b->need.resize(proj.size());
+  *out = b;
+  return FLSGPU_OK;
+#undef CKF
+}
+int flsgpu_batch_selection(const flsgpu_batch_t *b, const uint64_t **ids, uint64_t *n) {
+  if (!b || !ids || !n) return FLSGPU_E_RANGE;
+  if (!b->filtered) { *ids = nullptr; *n = b->out.empty() ? 0 : b->out[0].rows; return FLSGPU_OK; }
+  *ids = (b->flags & FLSGPU_OUT_HOST) ? b->sel_host : b->sel_dev;
+  *n = b->n_sel;
+  return FLSGPU_OK;
 }
 
 uint32_t flsgpu_batch_num_columns(const flsgpu_batch_t *b) { return (uint32_t)b->out.size(); }

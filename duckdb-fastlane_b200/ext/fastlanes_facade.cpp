@@ -6,6 +6,8 @@
 #include <cstring>
 
 #include "duckdb/common/types/vector.hpp"
+#include "duckdb/common/types/vector_buffer.hpp"
+#include "utf8proc_wrapper.hpp"
 #include "fls_scan.hpp"
 
 namespace duckdb {
@@ -82,6 +84,14 @@ idx_t FastLanesFacade::pruneRowGroups(const std::vector<flsgpu_host::ZonePredica
 	return pImpl->scanner.pruneRowGroups(predicates);
 }
 
+bool FastLanesFacade::setDeviceFilter(const std::vector<flsgpu_host::ZonePredicate> &predicates) {
+	if (!pImpl->scanner.setDeviceFilter(predicates)) {
+		pImpl->error = pImpl->scanner.error();
+		return false;
+	}
+	return true;
+}
+
 template <class T>
 static void CopyFixed(Vector &out, const flsgpu_host::ColumnSlice &s, idx_t rows) {
 	memcpy(FlatVector::GetData<T>(out), s.data, rows * sizeof(T));
@@ -104,7 +114,14 @@ bool FastLanesFacade::readNextChunk(DataChunk &result) {
 		auto &out = result.data[c];
 		out.SetVectorType(VectorType::FLAT_VECTOR);
 		switch (s.type) {
-		case FLSGPU_T_BOOLEAN:
+		case FLSGPU_T_BOOLEAN: { // bytes come from a file: anything non-zero is true
+			auto dst = FlatVector::GetData<bool>(out);
+			auto src = (const uint8_t *)s.data;
+			for (idx_t r = 0; r < rows; r++) {
+				dst[r] = src[r] != 0;
+			}
+			break;
+		}
 		case FLSGPU_T_INT8:
 		case FLSGPU_T_UINT8: CopyFixed<uint8_t>(out, s, rows); break;
 		case FLSGPU_T_INT16:
@@ -118,12 +135,43 @@ bool FastLanesFacade::readNextChunk(DataChunk &result) {
 		case FLSGPU_T_DOUBLE: CopyFixed<uint64_t>(out, s, rows); break;
 		case FLSGPU_T_STR:
 		case FLSGPU_T_BYTE_ARRAY: {
-			// strings <= 12 bytes are inlined in string_t; longer ones are copied into the vector's heap, so the
-			// chunk stays valid after the scanner recycles its pinned batch buffers
+			// strings <= 12 bytes are inlined in string_t; longer ones are copied into the vector's heap in ONE
+			// allocation per chunk (the chunk stays valid after the scanner recycles its pinned batch buffers).
+			// The offsets come from a file: they are checked before they address anything, and VARCHAR bytes are
+			// validated as UTF-8 like the reference's Value(std::string) does (src/fastlanes_facade.cpp:157-172).
 			auto dst = FlatVector::GetData<string_t>(out);
+			const uint32_t first = s.offsets[0], last = s.offsets[rows];
+			bool ok = first <= last;
+			for (idx_t r = 0; ok && r < rows; r++) {
+				ok = s.offsets[r] <= s.offsets[r + 1];
+			}
+			if (!ok) {
+				pImpl->error = "FastLanes file is damaged: string offsets of a chunk are not ascending";
+				return false;
+			}
+			if (s.type == FLSGPU_T_STR && last > first &&
+			    Utf8Proc::Analyze(const_char_ptr_cast(s.payload + first), last - first) == UnicodeType::INVALID) {
+				pImpl->error = "FastLanes file holds a VARCHAR value that is not valid UTF-8";
+				return false;
+			}
+			idx_t long_bytes = 0;
 			for (idx_t r = 0; r < rows; r++) {
-				const uint32_t a = s.offsets[r], b = s.offsets[r + 1];
-				dst[r] = StringVector::AddStringOrBlob(out, const_char_ptr_cast(s.payload + a), b - a);
+				const uint32_t len = s.offsets[r + 1] - s.offsets[r];
+				long_bytes += len > string_t::INLINE_LENGTH ? len : 0;
+			}
+			char *heap = nullptr;
+			if (long_bytes) {
+				heap = char_ptr_cast(StringVector::GetStringBuffer(out).AllocateShrinkableBuffer(long_bytes));
+			}
+			for (idx_t r = 0; r < rows; r++) {
+				const uint32_t a = s.offsets[r], len = s.offsets[r + 1] - a;
+				if (len <= string_t::INLINE_LENGTH) {
+					dst[r] = string_t(const_char_ptr_cast(s.payload + a), len);
+				} else {
+					memcpy(heap, s.payload + a, len);
+					dst[r] = string_t(heap, len);
+					heap += len;
+				}
 			}
 			break;
 		}

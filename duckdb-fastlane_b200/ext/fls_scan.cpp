@@ -36,11 +36,19 @@ struct FlsScanner::Impl {
   uint32_t next_g = 0;             // first row group not yet handed to the worker
 
   // Runs on the worker thread; it is the only caller of the handle while it runs (flsgpu.h: one caller at a time).
+  std::vector<ZonePredicate> filt_src;   // keeps the predicates' text alive
+  std::vector<flsgpu_predicate> filt;    // device filter (flsgpu_decode_filtered); empty = plain decode
+  uint64_t f_row = 0;                    // filtered batches: next row of the batch to serve
+  uint64_t scanned = 0, filtered_out = 0;
   Decoded decode(flsgpu_batch_t *release_first, uint32_t g0, uint32_t g1) {
     if (release_first) flsgpu_batch_release(release_first);
     Decoded d;
     d.g0 = g0; d.g1 = g1;
-    d.rc = flsgpu_decode(h, g0, g1, proj.empty() ? nullptr : proj.data(), (uint32_t)proj.size(), FLSGPU_OUT_HOST, &d.batch);
+    const uint32_t *pc = proj.empty() ? nullptr : proj.data();
+    if (!filt.empty())
+      d.rc = flsgpu_decode_filtered(h, g0, g1, pc, (uint32_t)proj.size(), filt.data(), (uint32_t)filt.size(), FLSGPU_OUT_HOST, &d.batch);
+    else
+      d.rc = flsgpu_decode(h, g0, g1, pc, (uint32_t)proj.size(), FLSGPU_OUT_HOST, &d.batch);
     if (d.rc) d.err = flsgpu_last_error(h);
     return d;
   }
@@ -73,6 +81,9 @@ struct FlsScanner::Impl {
     cur = Decoded();
     if (!ahead.valid()) {
       if (old) flsgpu_batch_release(old);
+      if (!filt.empty() && getenv("FLS_SCAN_TRACE"))
+        fprintf(stderr, "fls_filter: device filter kept %llu of %llu rows\n", (unsigned long long)(scanned - filtered_out),
+                (unsigned long long)scanned);
       return false;
     }
     Decoded d = ahead.get();
@@ -85,7 +96,13 @@ struct FlsScanner::Impl {
     const uint32_t nc = flsgpu_batch_num_columns(cur.batch);
     cols.resize(nc);
     for (uint32_t i = 0; i < nc; ++i) flsgpu_batch_column(cur.batch, i, &cols[i]);
-    rg = cur.g0; rg_row = 0; rg_base = 0;
+    rg = cur.g0; rg_row = 0; rg_base = 0; f_row = 0;
+    if (!filt.empty()) {
+      uint64_t in = 0;
+      for (uint32_t g = cur.g0; g < cur.g1; ++g) in += flsgpu_rowgroup_rows(h, g);
+      scanned += in;
+      filtered_out += in - (nc ? cols[0].rows : 0);
+    }
     launch_ahead(old);
     return true;
   }
@@ -120,6 +137,7 @@ bool FlsScanner::open(const std::string &path, int device, uint32_t batch_rowgro
   p->started = false;
   p->served = 0;
   p->skip.clear(); p->n_skipped = 0;
+  p->filt.clear(); p->filt_src.clear(); p->scanned = p->filtered_out = 0;
   return true;
 }
 
@@ -167,6 +185,7 @@ uint32_t FlsScanner::pruneRowGroups(const std::vector<ZonePredicate> &preds) {
     for (const ZonePredicate &z : preds) {
       int64_t mn = 0, mx = 0;
       int32_t known = 0;
+      if (z.is_double) continue;  // floating-point chunks carry no bounds
       if (z.is_text) {
         int32_t found = 0;
         if (z.op != ZONE_EQ || z.col >= p->names.size() ||
@@ -202,6 +221,28 @@ uint32_t FlsScanner::pruneRowGroups(const std::vector<ZonePredicate> &preds) {
 }
 uint32_t FlsScanner::rowGroupsSkipped() const { return p->n_skipped; }
 
+bool FlsScanner::setDeviceFilter(const std::vector<ZonePredicate> &preds) {
+  if (!p->h || p->started) { p->err = "the device filter must be set on an open scanner before the first chunk"; return false; }
+  p->filt.clear();
+  p->filt_src = preds;
+  for (const ZonePredicate &z : p->filt_src) {
+    if (p->filt.size() == FLSGPU_MAX_PREDICATES) break;
+    if (z.col >= p->names.size()) continue;
+    const int32_t ty = p->types[z.col];
+    const bool str_col = ty == FLSGPU_T_STR || ty == FLSGPU_T_BYTE_ARRAY, fp_col = ty == FLSGPU_T_FLOAT || ty == FLSGPU_T_DOUBLE;
+    if (z.is_text != str_col || z.is_double != fp_col) continue;           // constant of another kind: leave it to the caller
+    if (z.is_text && z.op != ZONE_EQ && z.op != ZONE_NE) continue;
+    if (ty == FLSGPU_T_UINT64 && z.value < 0) continue;                    // (an i64 constant cannot say what it means here)
+    flsgpu_predicate q = {};
+    q.col = z.col; q.op = (uint32_t)z.op;  // ZoneOp and flsgpu_cmp share their order
+    q.i64 = z.value; q.f64 = z.dvalue;
+    q.text = (const uint8_t *)z.text.data(); q.text_len = z.text.size();
+    p->filt.push_back(q);
+  }
+  return true;
+}
+uint64_t FlsScanner::rowsFilteredOut() const { return p->filtered_out; }
+
 bool FlsScanner::next(uint64_t max_rows, uint64_t &rows, std::vector<ColumnSlice> &out) {
   rows = 0;
   if (!p->h || !max_rows) return false;
@@ -213,6 +254,26 @@ bool FlsScanner::next(uint64_t max_rows, uint64_t &rows, std::vector<ColumnSlice
   }
   for (;;) {
     if (!p->cur.batch) return false;
+    if (!p->filt.empty()) {  // a filtered batch is one run of surviving rows, no padding, no row-group structure
+      const uint64_t have = p->cols.empty() ? 0 : p->cols[0].rows;
+      if (p->f_row >= have) {
+        if (!p->advance_batch()) return false;
+        continue;
+      }
+      rows = std::min<uint64_t>(max_rows, have - p->f_row);
+      out.resize(p->cols.size());
+      for (size_t i = 0; i < p->cols.size(); ++i) {
+        const flsgpu_column &c = p->cols[i];
+        ColumnSlice &s = out[i];
+        s.type = c.type; s.width = c.width;
+        s.data = c.width ? (const uint8_t *)c.data + p->f_row * c.width : nullptr;
+        s.offsets = c.width ? nullptr : c.offsets + p->f_row;
+        s.payload = c.width ? nullptr : c.payload;
+      }
+      p->f_row += rows;
+      p->served += rows;
+      return true;
+    }
     if (p->rg >= p->cur.g1) {
       if (!p->advance_batch()) return false;
       continue;

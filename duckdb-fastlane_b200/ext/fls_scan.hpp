@@ -34,9 +34,13 @@ struct ZonePredicate {
   uint32_t col = 0;  // file column id
   ZoneOp op = ZONE_EQ;
   int64_t value = 0;
-  // string columns: `column = text` against the row group's dictionary (flsgpu_rowgroup_dict_contains); op is ZONE_EQ
+  // string columns: `column = text` against the row group's dictionary (flsgpu_rowgroup_dict_contains); pruning
+  // uses ZONE_EQ only, the device filter ZONE_EQ and ZONE_NE
   bool is_text = false;
   std::string text;
+  // FLOAT / DOUBLE columns: device filter only (their chunks carry no bounds)
+  bool is_double = false;
+  double dvalue = 0;
 };
 
 class FlsScanner {
@@ -72,6 +76,12 @@ class FlsScanner {
   // setRowGroupRange / before the first next().  Returns the number of row groups skipped.
   uint32_t pruneRowGroups(const std::vector<ZonePredicate> &preds);
   uint32_t rowGroupsSkipped() const;
+  // Late materialisation (same SURVEY row, second half): the conjunction is evaluated on the GPU after the decode
+  // (flsgpu_decode_filtered) and only the rows that pass are copied to the host and served by next() — the runs it
+  // returns then hold no row that fails a predicate, and may span row groups.  At most FLSGPU_MAX_PREDICATES
+  // predicates are taken (the first ones); the caller may re-apply all of them.  Before the first next().
+  bool setDeviceFilter(const std::vector<ZonePredicate> &preds);
+  uint64_t rowsFilteredOut() const;
 
   // Next run of at most max_rows rows (never crossing a row-group boundary).  Returns false at the end of the
   // scan or on error (error() non-empty).  out[i] describes projected column i.

@@ -46,6 +46,9 @@ public:
 	//! Skip the row groups whose FFOR / DELTA bounds rule out `column <op> constant` (a conjunction); returns how
 	//! many were skipped.  The engine keeps the filters: this only avoids decoding what cannot match.
 	idx_t pruneRowGroups(const std::vector<flsgpu_host::ZonePredicate> &predicates);
+	//! Evaluate the conjunction on the GPU and serve only the rows that pass (flsgpu_decode_filtered); the engine
+	//! keeps the filters.  Call between openFile and the first readNextChunk.
+	bool setDeviceFilter(const std::vector<flsgpu_host::ZonePredicate> &predicates);
 	//! Fills `result` with the next <= STANDARD_VECTOR_SIZE rows; false at the end of the file or on error.
 	bool readNextChunk(DataChunk &result);
 	void closeFile();

@@ -15,9 +15,14 @@
 //   * comparisons `column <op> constant` on integer / DATE columns are looked at (pushdown_complex_filter) and used
 //     to skip row groups whose FFOR / DELTA vector headers rule them out — the filters stay in the plan, only the
 //     decode of row groups that cannot match is saved (the reference leaves its filter flags
-//     off, /root/reference/src/scanner/scan_fastlanes.cpp:154-155).
+//     off, /root/reference/src/scanner/scan_fastlanes.cpp:154-155);
+//   * the same comparisons (plus FLOAT / DOUBLE / BOOLEAN constants and `column <> 'text'`) are evaluated on the GPU
+//     after the decode and only the rows that pass are copied back and served (late materialisation,
+//     flsgpu_decode_filtered); DuckDB still applies its own filter on top, so results cannot differ.
 // MaxThreads stays 1 like the reference: the parallelism is on the GPU, behind the facade.
 #include "scan_fastlanes.hpp"
+
+#include <cstdlib>
 
 #include "duckdb/common/exception.hpp"
 #include "duckdb/common/string_util.hpp"
@@ -77,6 +82,13 @@ static bool OpenNext(FastLanesScanState &state, const FastLanesBindData &bind, s
 		}
 		if (!bind.zone_predicates.empty()) {
 			facade->pruneRowGroups(bind.zone_predicates);
+			// late materialisation: the same conjunction runs on the GPU, only the rows that pass come back
+			// (FLS_SCAN_NO_DEVICE_FILTER=1 keeps the row-group skipping alone, for A/B timing)
+			const char *off = getenv("FLS_SCAN_NO_DEVICE_FILTER");
+			if (!(off && *off == '1') && !facade->setDeviceFilter(bind.zone_predicates)) {
+				err = facade->lastError();
+				return false;
+			}
 		}
 		state.facade = std::move(facade);
 		return true;
@@ -220,6 +232,15 @@ static bool ZoneOperand(const LogicalGet &get, const FastLanesBindData &bind_dat
 	case LogicalTypeId::USMALLINT:
 	case LogicalTypeId::UINTEGER: z.value = v.GetValue<int64_t>(); return true;
 	case LogicalTypeId::DATE: z.value = DateValue::Get(v).days; return true;
+	case LogicalTypeId::BOOLEAN: z.value = BooleanValue::Get(v) ? 1 : 0; return true;
+	case LogicalTypeId::FLOAT: // device filter only: floating-point chunks carry no bounds to prune by
+		z.is_double = true;
+		z.dvalue = FloatValue::Get(v);
+		return true;
+	case LogicalTypeId::DOUBLE:
+		z.is_double = true;
+		z.dvalue = DoubleValue::Get(v);
+		return true;
 	case LogicalTypeId::VARCHAR:  // `column = 'text'` is checked against the row group's dictionary
 		z.is_text = true;
 		z.text = StringValue::Get(v);
@@ -268,7 +289,7 @@ static void FastLanesComplexFilter(ClientContext &context, LogicalGet &get, Func
 		case ExpressionType::COMPARE_GREATERTHANOREQUALTO: z.op = flsgpu_host::ZONE_GE; break;
 		default: continue;
 		}
-		if (z.is_text && z.op != flsgpu_host::ZONE_EQ) {
+		if (z.is_text && z.op != flsgpu_host::ZONE_EQ && z.op != flsgpu_host::ZONE_NE) {
 			continue;
 		}
 		bind_data.zone_predicates.push_back(z);

@@ -16,6 +16,7 @@ _lib = None
 OK, E_IO, E_FORMAT, E_RANGE, E_CUDA, E_LIMIT, E_NOMEM = range(7)
 OPEN_PINNED_IMAGE, OPEN_NO_PIN, OPEN_TIME_KERNELS, OPEN_NO_PLAN_CACHE = 1, 2, 4, 8
 OUT_DEVICE, OUT_HOST = 0, 1
+CMP = {"=": 0, "==": 0, "!=": 1, "<>": 1, "<": 2, "<=": 3, ">": 4, ">=": 5}
 
 # enum fls_type -> numpy dtype of the decoded column
 DTYPES = {1: np.uint8, 2: np.int8, 3: np.int16, 4: np.int32, 5: np.int64, 6: np.uint8, 7: np.uint16, 8: np.uint32,
@@ -39,6 +40,11 @@ class Timing(C.Structure):
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("compressed_bytes", C.c_uint64),
                 ("decoded_bytes", C.c_uint64), ("kernel_launches", C.c_uint32), ("slices", C.c_uint32),
                 ("ms_host_plan", C.c_float), ("ms_host_total", C.c_float)]
+
+
+class Predicate(C.Structure):
+    _fields_ = [("col", C.c_uint32), ("op", C.c_uint32), ("i64", C.c_int64), ("f64", C.c_double),
+                ("text", C.c_char_p), ("text_len", C.c_uint64)]
 
 
 class KernelStat(C.Structure):
@@ -89,6 +95,8 @@ def lib():
     L.flsgpu_rowgroup_dict_contains.argtypes = [vp, u32, u32, C.c_char_p, C.c_uint64, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.flsgpu_make_resident.argtypes = [vp, u32, u32]
     L.flsgpu_decode.argtypes = [vp, u32, u32, C.POINTER(u32), u32, u32, C.POINTER(vp)]
+    L.flsgpu_decode_filtered.argtypes = [vp, u32, u32, C.POINTER(u32), u32, C.POINTER(Predicate), u32, u32, C.POINTER(vp)]
+    L.flsgpu_batch_selection.argtypes = [vp, C.POINTER(C.POINTER(u64)), C.POINTER(u64)]
     L.flsgpu_batch_num_columns.argtypes = [vp]
     L.flsgpu_batch_num_columns.restype = u32
     L.flsgpu_batch_column.argtypes = [vp, u32, C.POINTER(Column)]
@@ -155,6 +163,15 @@ class Batch:
         pay = np.empty(max(int(c.payload_bytes), 1), dtype=np.uint8)
         self.reader._check(lib().flsgpu_batch_fetch(self.h, i, pay.ctypes.data, offs.ctypes.data))
         return offs[:n + 1], pay[:min(int(offs[n]), len(pay))]
+
+    def selection(self):
+        """Row ids of a filtered host batch (None for an unfiltered one)."""
+        ids, n = C.POINTER(C.c_uint64)(), C.c_uint64()
+        lib().flsgpu_batch_selection(self.h, C.byref(ids), C.byref(n))
+        if not ids:
+            return None
+        assert self.to_host
+        return np.ctypeslib.as_array(ids, shape=(n.value,)).copy() if n.value else np.empty(0, np.uint64)
 
     def release(self):
         if self.h:
@@ -251,6 +268,33 @@ class Reader:
             arr, n = (C.c_uint32 * len(cols))(*cols), len(cols)
         self._check(lib().flsgpu_decode(self.h, g0, g1, arr, n, OUT_HOST if to_host else OUT_DEVICE, C.byref(b)))
         return Batch(self, b, to_host)
+
+    def decode_filtered_batch(self, preds, g0=0, g1=None, cols=None, to_host=True) -> Batch:
+        """flsgpu_decode_filtered: preds = [(column id, "<" | "<=" | "=" | ..., constant)], a conjunction; the batch
+        holds only the rows that pass.  The constant is an int, a float (FLOAT / DOUBLE columns) or bytes (strings)."""
+        g1 = self.n_rowgroups if g1 is None else g1
+        ps = (Predicate * max(len(preds), 1))()
+        for i, (col, op, val) in enumerate(preds):
+            ps[i].col, ps[i].op = col, CMP[op] if isinstance(op, str) else op
+            if isinstance(val, (bytes, bytearray)):
+                ps[i].text, ps[i].text_len = bytes(val), len(val)
+            elif self.types[col] in (10, 11):
+                ps[i].f64 = float(val)
+            else:
+                ps[i].i64 = int(val) if int(val) < (1 << 63) else int(val) - (1 << 64)
+        b = C.c_void_p()
+        if cols is None:
+            arr, n = None, 0
+        else:
+            arr, n = (C.c_uint32 * len(cols))(*cols), len(cols)
+        self._check(lib().flsgpu_decode_filtered(self.h, g0, g1, arr, n, ps, len(preds), OUT_HOST if to_host else OUT_DEVICE,
+                                                 C.byref(b)))
+        return Batch(self, b, to_host)
+
+    def decode_filtered(self, preds, g0=0, g1=None, cols=None):
+        """Host copies of the surviving rows: (row ids, [ndarray | (offsets, payload)])."""
+        with self.decode_filtered_batch(preds, g0, g1, cols, to_host=True) as b:
+            return b.selection(), [b.numpy(i) for i in range(b.n)]
 
     def decode(self, g0=0, g1=None, cols=None, to_host=True, padded=False):
         """Decode and return host copies: list of ndarray / (offsets, payload)."""

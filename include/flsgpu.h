@@ -156,6 +156,33 @@ int flsgpu_batch_fetch(const flsgpu_batch_t *b, uint32_t i, void *values, uint32
 /* Returns the batch's buffers to the handle's pool. */
 void flsgpu_batch_release(flsgpu_batch_t *b);
 
+/* ---- filtered decode (late materialisation) -------------------------------------------------------------
+ * SURVEY.md section 8f rank 3, second half.  The reference declares filter pushdown and leaves it switched off
+ * (src/scanner/scan_fastlanes.cpp:154-155); DuckDB's hooks are table_function.hpp:377-379,414-422.
+ * flsgpu_decode_filtered decodes the predicate columns and the projected columns of [g0,g1) into HBM, evaluates the
+ * conjunction preds[0..n_preds) there, and hands back only the rows that pass, in row order: every column of the
+ * batch has rows == padded_rows == the number of surviving rows, strings are re-based (offsets[0] = 0).  With
+ * FLSGPU_OUT_HOST only the survivors cross PCIe.  Comparison semantics are DuckDB's: integers and DATE by value
+ * (signed or unsigned as the column type says; the constant is i64, reinterpreted for UINT64), FLOAT / DOUBLE in
+ * DuckDB's total order (NaN = NaN, NaN greater than everything else; the constant is f64), strings byte-wise for
+ * EQ / NE only.  A predicate column need not be projected.  At most FLSGPU_MAX_PREDICATES predicates. */
+enum flsgpu_cmp { FLSGPU_CMP_EQ = 0, FLSGPU_CMP_NE, FLSGPU_CMP_LT, FLSGPU_CMP_LE, FLSGPU_CMP_GT, FLSGPU_CMP_GE };
+#define FLSGPU_MAX_PREDICATES 8
+typedef struct {
+  uint32_t col;         /* file column id */
+  uint32_t op;          /* enum flsgpu_cmp */
+  int64_t i64;          /* constant for integer / BOOLEAN / DATE columns */
+  double f64;           /* constant for FLOAT / DOUBLE columns */
+  const uint8_t *text;  /* constant for STR / BYTE_ARRAY columns (EQ / NE) */
+  uint64_t text_len;
+} flsgpu_predicate;
+int flsgpu_decode_filtered(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, uint32_t n_cols,
+                           const flsgpu_predicate *preds, uint32_t n_preds, uint32_t flags, flsgpu_batch_t **out);
+/* Row ids (positions in the unpadded row range of [g0,g1)) of a filtered batch's rows: *n entries, host memory for
+ * FLSGPU_OUT_HOST batches and device memory otherwise; valid until the batch is released.  *ids = NULL, *n = the
+ * batch's row count for an unfiltered batch. */
+int flsgpu_batch_selection(const flsgpu_batch_t *b, const uint64_t **ids, uint64_t *n);
+
 /* ---- instrumentation ---------------------------------------------------------------------------------- */
 /* Per-kernel-family accumulators (needs FLSGPU_OPEN_TIME_KERNELS).  i in [0, flsgpu_num_kernel_stats). */
 uint32_t flsgpu_num_kernel_stats(const flsgpu_t *h);

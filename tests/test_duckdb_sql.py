@@ -23,8 +23,9 @@ CHECK = os.path.join(EXT, "duckdb_sql_check")
 pytestmark = pytest.mark.skipif(not os.path.exists(CHECK), reason="ext/duckdb_sql_check not built (needs the DuckDB sources)")
 
 
-def sql(*stmts, trace=None):
+def sql(*stmts, trace=None, env_extra=None):
     env = dict(os.environ)
+    env.update(env_extra or {})
     if trace is not None:
         env["FLS_SCAN_TRACE"] = "1"
     env["LD_LIBRARY_PATH"] = os.path.join(EXT, "_duckdb") + ":" + os.path.join(ROOT, "duckdb-fastlane_b200") + ":" + \
@@ -33,7 +34,7 @@ def sql(*stmts, trace=None):
     out = [json.loads(line) for line in r.stdout.strip().splitlines() if line.startswith("{")]
     assert len(out) == len(stmts), r.stdout + r.stderr
     if trace is not None:
-        trace.extend(line for line in r.stderr.splitlines() if line.startswith("fls_scan:"))
+        trace.extend(line for line in r.stderr.splitlines() if line.startswith(("fls_scan:", "fls_filter:")))
     return out
 
 
@@ -191,8 +192,8 @@ def test_row_groups_are_skipped_by_their_compressed_bounds(tmp_path):
     assert res[1]["rows"] == res[2]["rows"] and res[1]["rows"][0][0] == "20000"
     assert res[3]["rows"] == res[4]["rows"] and res[3]["rows"][0][0] == "4096"
     assert res[5]["rows"] == [["400"]] and res[6]["rows"] == [["0"]]
-    skipped = [int(t.split()[2]) for t in trace]
-    total = [int(t.split()[4]) for t in trace]
+    skipped = [int(t.split()[2]) for t in trace if t.startswith("fls_scan:")]
+    total = [int(t.split()[4]) for t in trace if t.startswith("fls_scan:")]
     assert total == [25, 25, 25, 25] and skipped == [23, 24, 0, 25], trace
 
 
@@ -211,7 +212,7 @@ def test_row_groups_are_skipped_by_their_dictionaries(tmp_path):
               "SELECT count(*) FROM read_fls('%s') WHERE mode = 'NOPE'" % path,
               "SELECT count(*) FROM read_fls('%s') WHERE 'AIR' = mode AND k < 60000" % path,
               "SELECT count(*) FROM (%s) WHERE 'AIR' = mode AND k < 60000" % src,
-              "SELECT count(*) FROM read_fls('%s') WHERE mode <> 'SHIP'" % path,     # not an equality: no pruning pass at all
+              "SELECT count(*) FROM read_fls('%s') WHERE mode <> 'SHIP'" % path,     # not an equality: nothing to prune by
               "SELECT count(*) FROM (%s) WHERE mode <> 'SHIP'" % src,
               trace=trace)
     assert res[1]["rows"] == res[2]["rows"] and int(res[1]["rows"][0][0]) > 0
@@ -225,6 +226,36 @@ def test_row_groups_are_skipped_by_their_dictionaries(tmp_path):
     n_rg = (400000 + 16383) // 16384
     want_ship = sum(not holds(g, 3) for g in range(n_rg))
     want_air = sum((not holds(g, 1)) or 16384 * g >= 60000 for g in range(n_rg))
-    skipped = [int(t.split()[2]) for t in trace]
-    assert skipped == [want_ship, n_rg, want_air], (trace, want_ship, want_air)
+    skipped = [int(t.split()[2]) for t in trace if t.startswith("fls_scan:")]
+    assert skipped == [want_ship, n_rg, want_air, 0], (trace, want_ship, want_air)
     assert 0 < want_ship < n_rg and 0 < want_air < n_rg and int(res[4]["rows"][0][0]) > 0
+
+
+@pytest.mark.gpu
+def test_device_filter_serves_only_surviving_rows(tmp_path):
+    """SURVEY.md section 8f rank 3, second half (late materialisation): `column <op> constant` conjunctions run on the
+    GPU after the decode (flsgpu_decode_filtered) and only the rows that pass are copied back; DuckDB re-applies the
+    filter, so the answers equal the source query's and those of a scan with the device filter switched off."""
+    path = str(tmp_path / "f.fls")
+    src = ("SELECT i::BIGINT AS k, ((i * 7919) % 1000)::INTEGER AS m, DATE '2020-01-01' + ((i * 31) % 700)::INTEGER AS d, "
+           "round(((i * 37) % 10007) * 0.01, 2)::DOUBLE AS price, (['AIR', 'RAIL', 'SHIP', 'TRUCK'])[1 + (i * 13) % 4] AS mode, "
+           "'row_' || i AS s, (i % 3 = 0) AS flag FROM range(0, 300000) t(i)")
+    qs = ["WHERE m < 10", "WHERE d BETWEEN DATE '2020-03-01' AND DATE '2020-03-07' AND mode = 'SHIP'",
+          "WHERE price >= 99.5 AND mode <> 'AIR'", "WHERE flag = true AND k >= 299000", "WHERE m = 5000", "WHERE 17.25 = price"]
+    agg = "count(*), sum(k), sum(m), min(s), max(s), sum(price), count(*) FILTER (flag)"
+    stm = ["COPY (%s) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 32768)" % (src, path)]
+    for q in qs:
+        stm += ["SELECT %s FROM read_fls('%s') %s" % (agg, path, q), "SELECT %s FROM (%s) %s" % (agg, src, q)]
+    trace = []
+    res = sql(*stm, trace=trace)
+    assert all("error" not in r for r in res), res
+    for i in range(len(qs)):
+        assert res[1 + 2 * i]["rows"] == res[2 + 2 * i]["rows"], (qs[i], res[1 + 2 * i], res[2 + 2 * i])
+    assert int(res[1]["rows"][0][0]) == 3000
+    kept = [(int(t.split()[4]), int(t.split()[6])) for t in trace if t.startswith("fls_filter:")]
+    assert len(kept) == len(qs) and kept[0] == (3000, 300000), trace       # the device handed back exactly the survivors
+    counts = [int(res[1 + 2 * i]["rows"][0][0]) for i in range(len(qs))]
+    assert all(k >= c for (k, _n), c in zip(kept, counts)), (kept, counts)   # a conjunct DuckDB keeps to itself may remain
+    assert [k for k, _n in kept[:3]] == counts[:3] and min(counts[:4]) > 0, (kept, counts)
+    off = sql(*[stm[0]] + stm[1::2], env_extra={"FLS_SCAN_NO_DEVICE_FILTER": "1"})
+    assert [r["rows"] for r in off[1:]] == [res[1 + 2 * i]["rows"] for i in range(len(qs))]
