@@ -16,6 +16,7 @@ struct FlsPredDev {
   const void *data;         // fixed width: decoded values (padded rows)
   const uint32_t *offsets;  // strings
   const uint8_t *payload;
+  const uint32_t *validity; // bit per padded row (null: no NULLs); a NULL value fails every comparison
   const uint8_t *text;      // strings: the constant's bytes (device)
   uint32_t text_len;
   int32_t kind;             // 0 signed int, 1 unsigned int, 2 f32, 3 f64, 4 string
@@ -56,6 +57,7 @@ template <typename F> __device__ __forceinline__ bool cmp_fp(F a, F b, uint32_t 
   }
 }
 __device__ __forceinline__ bool eval(const FlsPredDev &p, uint64_t row) {
+  if (p.validity && !((p.validity[row >> 5] >> (row & 31u)) & 1u)) return false;
   switch (p.kind) {
     case 0: {
       int64_t v;
@@ -127,14 +129,6 @@ __global__ void __launch_bounds__(1024) scan_kernel(const uint32_t *__restrict__
   if (tid == 1023u) total[0] += part[1023];
 }
 
-// rank of row (j, lane) among the vector's selected rows, for the lanes whose bit is set; all lanes hold the
-// vector's 32 mask words (lane l holds word l)
-__device__ __forceinline__ uint32_t words_before(uint32_t mine, uint32_t j) {
-  uint32_t before = 0;
-  for (uint32_t q = 0; q < j; ++q) before += __popc(__shfl_sync(0xFFFFFFFFu, mine, q));
-  return before;
-}
-
 template <typename T>
 __global__ void __launch_bounds__(256) compact_fixed_kernel(const T *__restrict__ in, const uint32_t *__restrict__ mask,
                                                             const uint64_t *__restrict__ voff, uint32_t n_vec, T *__restrict__ out) {
@@ -146,6 +140,25 @@ __global__ void __launch_bounds__(256) compact_fixed_kernel(const T *__restrict_
     const uint32_t w = __shfl_sync(0xFFFFFFFFu, mine, j);
     if (!w) continue;  // warp-uniform
     if ((w >> lane) & 1u) out[dst + __popc(w & ((1u << lane) - 1u))] = in[(size_t)v * 1024u + 32u * j + lane];
+    dst += __popc(w);
+  }
+}
+
+// validity bits of the selected rows (out zeroed by the caller)
+__global__ void __launch_bounds__(256) compact_validity_kernel(const uint32_t *__restrict__ valid, const uint32_t *__restrict__ mask,
+                                                               const uint64_t *__restrict__ voff, uint32_t n_vec,
+                                                               unsigned long long *__restrict__ out) {
+  const uint32_t v = blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+  if (v >= n_vec) return;
+  const uint32_t mine = mask[(size_t)v * 32u + lane], vmine = valid[(size_t)v * 32u + lane];
+  uint64_t dst = voff[v];
+  for (uint32_t j = 0; j < 32u; ++j) {
+    const uint32_t w = __shfl_sync(0xFFFFFFFFu, mine, j), vw = __shfl_sync(0xFFFFFFFFu, vmine, j);
+    if (!w) continue;
+    if ((w >> lane) & (vw >> lane) & 1u) {
+      const uint64_t at = dst + __popc(w & ((1u << lane) - 1u));
+      atomicOr(out + (at >> 6), 1ull << (at & 63u));
+    }
     dst += __popc(w);
   }
 }

@@ -100,6 +100,10 @@ typedef struct {
   uint64_t size;
 } fls_seg;
 
+// fls_colchunk.flags
+#define FLS_CHUNK_VALIDITY 1u  // the chunk's LAST segment is a validity bitmap: 128 bytes per vector, bit r of the vector
+                               // (LSB first) = row r holds a value; NULL rows keep a filler in the value streams
+
 typedef struct {
   uint8_t scheme;   // enum fls_scheme
   uint8_t n_seg;

@@ -221,6 +221,14 @@ __global__ void __launch_bounds__(256) fls_copy_kernel(const FlsChunkDev *__rest
   for (uint64_t i = bx * (uint64_t)blockDim.x + threadIdx.x; i < n16; i += (uint64_t)bpc * blockDim.x)
     __stcs(dst + i, __ldg(src + i));
 }
+// validity bitmaps: 128 bytes per vector, copied from the chunk's bitmap segment or set to all ones
+__global__ void __launch_bounds__(256) fls_validity_kernel(const FlsChunkDev *__restrict__ chunks) {
+  const FlsChunkDev &k = chunks[blockIdx.x];
+  const uint4 *src = (const uint4 *)k.seg[0];
+  uint4 *dst = (uint4 *)k.out;
+  for (uint32_t i = threadIdx.x; i < k.n_vec * 8u; i += blockDim.x)
+    dst[i] = src ? __ldg(src + i) : make_uint4(~0u, ~0u, ~0u, ~0u);
+}
 // CONSTANT: fill n_vec*1024 values of width aux32 bytes with aux64[0].
 __global__ void __launch_bounds__(256) fls_fill_kernel(const FlsChunkDev *__restrict__ chunks, uint32_t bpc) {
   const FlsChunkDev &k = chunks[blockIdx.x / bpc];

@@ -20,6 +20,7 @@ enum FlsKernelKind {
   FLS_K_STR_DICT,
   FLS_K_STR_FSST,
   FLS_K_STR_FSST_DICTPREP,  // decode an FSST-compressed dictionary into scratch
+  FLS_K_VALIDITY,           // validity bitmap of a chunk (copied, or all ones) -> the column's bitmap
   FLS_K_N
 };
 
@@ -54,11 +55,13 @@ struct FlsColOut {
   uint32_t *offsets = nullptr; // strings: padded_rows + 1
   uint8_t *payload = nullptr;  // strings: sum of row-group payload bytes (+16 slack)
   uint8_t *scratch = nullptr;  // strings (FSST_DICT): decoded dictionaries
+  uint8_t *validity = nullptr; // 128 bytes per vector of the range, or null when no chunk of the range has NULLs
   uint64_t pay_base0 = 0;      // strings: payload bytes that precede row group g0 in `payload` (pipeline slices)
 };
 
 struct FlsColNeed {  // sizes the caller must provide for a column over a row-group range
   uint64_t data_bytes = 0, offsets_bytes = 0, payload_bytes = 0, scratch_bytes = 0;
+  uint64_t validity_bytes = 0;    // 128 per vector when some chunk of the range carries a validity bitmap, else 0
   uint64_t compressed_bytes = 0;  // segment bytes read
   uint64_t decoded_bytes = 0;     // algorithmic bytes written (values, or offsets + payload)
 };
@@ -81,6 +84,7 @@ static inline FlsColNeed fls_column_need(const FlsTable &t, uint32_t col, uint32
   for (uint32_t g = g0; g < g1; ++g) {
     const fls_colchunk &k = t.chunk(g, col);
     for (uint32_t s = 0; s < k.n_seg; ++s) n.compressed_bytes += k.seg[s].size;
+    if (k.flags & FLS_CHUNK_VALIDITY) n.validity_bytes = rows / 8;
     if (!wb) {
       n.payload_bytes += k.aux64[0];
       if (k.scheme == FLS_S_STR_FSST_DICT && host_image) {
@@ -122,6 +126,15 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
     uint64_t rd = 0;
     for (uint32_t s = 0; s < k.n_seg; ++s) rd += k.seg[s].size;
     const uint64_t vals = (uint64_t)rg.n_vec * FLS_VEC;
+    if (out.validity) {  // seg[0] = the chunk's bitmap, or null: all rows hold values
+      FlsChunkDev vd;
+      memset(&vd, 0, sizeof(vd));
+      vd.n_vec = rg.n_vec;
+      const bool hv = (k.flags & FLS_CHUNK_VALIDITY) && k.n_seg;
+      vd.seg[0] = hv ? d.seg[k.n_seg - 1u] : nullptr;
+      vd.out = out.validity + row_base / 8;
+      fls_launch_for(ls, FLS_K_VALIDITY, 0).add(vd, hv ? 128ull * rg.n_vec : 0, 128ull * rg.n_vec);
+    }
     if (wb) {
       const uint64_t wr = vals * wb;
       d.out = (uint8_t *)out.data + row_base * wb;

@@ -87,7 +87,9 @@ static inline std::string fls_validate_chunk(const FlsTable &t, uint32_t g, uint
   SegView s[FLS_MAX_SEGS];
   for (uint32_t i = 0; i < k.n_seg; ++i)
     if (!seg_view(rg, k, i, image, image_size, s[i])) return bad(g, c, "segment leaves its row group");
-  auto need_segs = [&](uint32_t n) { return k.n_seg >= n; };
+  const bool has_valid = (k.flags & FLS_CHUNK_VALIDITY) != 0;
+  if (has_valid && (k.n_seg == 0 || s[k.n_seg - 1u].size < 128ull * n_vec)) return bad(g, c, "validity bitmap shorter than its vectors");
+  auto need_segs = [&](uint32_t n) { return k.n_seg - (has_valid ? 1u : 0u) >= n; };
   const char *e = nullptr;
   auto clamp = [](uint32_t x, uint32_t hi) { return x > hi ? hi : x; };
   switch (k.scheme) {

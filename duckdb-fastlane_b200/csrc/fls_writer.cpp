@@ -714,16 +714,26 @@ struct Writer {
   std::map<uint32_t, AlprdInject> inject_alprd;
 };
 
+static inline bool bit_at(const uint64_t *bits, size_t r) { return (bits[r >> 6] >> (r & 63u)) & 1u; }
+
 template <typename T>
-static Chunk enc_fixed(const void *src, uint32_t n_rows, uint32_t n_vec, int force, int force_bw, bool is_double) {
+static Chunk enc_fixed(const void *src, uint32_t n_rows, uint32_t n_vec, int force, int force_bw, bool is_double,
+                       const uint64_t *valid = nullptr) {
   std::vector<T> v((size_t)n_vec * FLS_VEC);
   memcpy(v.data(), src, (size_t)n_rows * sizeof(T));
+  if (valid) {  // NULL rows take the value before them (the first non-NULL value for leading NULLs): cheap to encode
+    size_t first = 0;
+    while (first < n_rows && !bit_at(valid, first)) ++first;
+    T prev = first < n_rows ? v[first] : T();
+    for (size_t i = 0; i < n_rows; ++i) { if (bit_at(valid, i)) prev = v[i]; else v[i] = prev; }
+  }
   for (size_t i = n_rows; i < v.size(); ++i) v[i] = v[n_rows - 1];  // pad the tail vector
   if (is_double) return enc_double_auto((const double *)v.data(), n_vec, force);
   return enc_int_auto<T>(v.data(), n_vec, force, force_bw);
 }
 
-static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_data, const uint64_t *const *str_off) {
+static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_data, const uint64_t *const *str_off,
+                           const uint64_t *const *validity = nullptr) {
   if (w.finished) { w.err = "writer already finished"; return 1; }
   if (w.last_partial) { w.err = "only the last row group may end in a partial vector (rows not a multiple of 1024)"; return 1; }
   if (n_rows == 0 || n_rows > FLS_RG_VECS * FLS_VEC) { w.err = "row group must hold 1..65536 rows"; return 1; }
@@ -735,16 +745,22 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
   for (size_t c = 0; c < w.types.size(); ++c) {
     Chunk ch;
     int t = w.types[c], f = w.force[c];
+    const uint64_t *vb = validity ? validity[c] : nullptr;
+    if (vb) {  // a bitmap without a cleared bit is not stored
+      bool all = true;
+      for (uint32_t r = 0; all && r < n_rows; ++r) all = bit_at(vb, r);
+      if (all) vb = nullptr;
+    }
     tl_force_alp_ef = c < w.force_ef.size() ? w.force_ef[c] : -1;
     tl_fsst_inject = nullptr; tl_alprd_inject = nullptr;
     FsstInject fi; AlprdInject ai;
     if (w.inject_fsst.count((uint32_t)c)) { fi = w.inject_fsst[(uint32_t)c]; w.inject_fsst.erase((uint32_t)c); tl_fsst_inject = &fi; f = FLS_S_STR_FSST; }
     if (w.inject_alprd.count((uint32_t)c)) { ai = w.inject_alprd[(uint32_t)c]; w.inject_alprd.erase((uint32_t)c); tl_alprd_inject = &ai; f = FLS_S_ALP_RD; }
     switch (fls_type_bits(t)) {
-      case 8: ch = enc_fixed<uint8_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false); break;
-      case 16: ch = enc_fixed<uint16_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false); break;
-      case 32: ch = enc_fixed<uint32_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false); break;
-      case 64: ch = enc_fixed<uint64_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], t == FLS_T_DOUBLE); break;
+      case 8: ch = enc_fixed<uint8_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false, vb); break;
+      case 16: ch = enc_fixed<uint16_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false, vb); break;
+      case 32: ch = enc_fixed<uint32_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false, vb); break;
+      case 64: ch = enc_fixed<uint64_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], t == FLS_T_DOUBLE, vb); break;
       default: {
         if (t != FLS_T_STR && t != FLS_T_BYTE_ARRAY) { w.err = "unsupported column type"; return 1; }
         std::vector<uint64_t> off((size_t)n_vec * FLS_VEC + 1);
@@ -754,8 +770,14 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
         ch = enc_str_auto((const uint8_t *)col_data[c], off.data(), n_vec, f, w.force_bw[c]);
       }
     }
+    if (vb) {  // validity bitmap: the chunk's last segment, 128 bytes per vector, padding rows cleared
+      Bytes bm((size_t)n_vec * 128, 0);
+      for (uint32_t r = 0; r < n_rows; ++r)
+        if (bit_at(vb, r)) bm[r >> 3] |= (uint8_t)(1u << (r & 7u));
+      ch.segs.push_back(std::move(bm));
+    }
     if (ch.segs.size() > FLS_MAX_SEGS) { w.err = "internal: too many segments"; return 1; }
-    put<uint8_t>(cc, ch.scheme); put<uint8_t>(cc, (uint8_t)ch.segs.size()); put<uint16_t>(cc, 0);
+    put<uint8_t>(cc, ch.scheme); put<uint8_t>(cc, (uint8_t)ch.segs.size()); put<uint16_t>(cc, vb ? FLS_CHUNK_VALIDITY : 0);
     put<uint32_t>(cc, ch.aux32); put<uint64_t>(cc, ch.aux64[0]); put<uint64_t>(cc, ch.aux64[1]);
     for (auto &sg : ch.segs) {
       pad_to(w.file, FLS_SEG_ALIGN);
@@ -813,6 +835,10 @@ int flsw_force_scheme(flsw_writer *h, uint32_t col, int32_t scheme, int32_t min_
 }
 int flsw_append_rowgroup(flsw_writer *h, uint32_t n_rows, const void *const *col_data, const uint64_t *const *str_off) {
   return flsw::append_rowgroup(*(flsw::Writer *)h, n_rows, col_data, str_off);
+}
+int flsw_append_rowgroup_v(flsw_writer *h, uint32_t n_rows, const void *const *col_data, const uint64_t *const *str_off,
+                           const uint64_t *const *validity) {
+  return flsw::append_rowgroup(*(flsw::Writer *)h, n_rows, col_data, str_off, validity);
 }
 int flsw_finish(flsw_writer *h) { return flsw::finish(*(flsw::Writer *)h); }
 const void *flsw_data(flsw_writer *h) { return ((flsw::Writer *)h)->file.data(); }

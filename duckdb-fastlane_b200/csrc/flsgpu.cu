@@ -83,7 +83,7 @@ cudaError_t set_kernel_attrs() {
 
 const char *const kKindName[FLS_K_N] = {"ffor",     "delta",     "rle",      "dict",     "alp",  "alp_rd", "copy",
                                         "fill",     "str_offsets", "str_copy", "str_const", "str_dict", "str_fsst",
-                                        "fsst_dictprep"};
+                                        "fsst_dictprep", "validity"};
 
 struct LaunchRec {  // what is needed to (re)issue one launch once its descriptors are on the device
   int kind, width;
@@ -110,6 +110,7 @@ bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
     case FLS_K_STR_DICT: chunk_launch<VecSTRDICT>(d, n, s, l.cap); return true;
     case FLS_K_STR_FSST: chunk_launch<VecSTRFSST>(d, n, s, l.cap); return true;
     case FLS_K_STR_FSST_DICTPREP: fls_fsst_dictprep_kernel<<<n * 8, 128, 0, s>>>(d, 8); return true;
+    case FLS_K_VALIDITY: fls_validity_kernel<<<n, 256, 0, s>>>(d); return true;
   }
   return false;
 }
@@ -605,6 +606,11 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       }
       scratch_total += n.scratch_bytes;
     }
+    if (n.validity_bytes) {
+      if (!(d.validity = (uint8_t *)dalloc(n.validity_bytes + 16))) return bail(FLSGPU_E_NOMEM, "out of device memory");
+      o.validity = (uint64_t *)d.validity;
+      if (to_host && !(o.validity = (uint64_t *)halloc(n.validity_bytes + 16))) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+    }
   }
   if (g1 == g0) { *out = b; return FLSGPU_OK; }
 
@@ -630,7 +636,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
   std::vector<const void *> key_ptrs;
   if (cacheable) {
     key_ptrs.push_back(d_stage); key_ptrs.push_back(d_scratch);
-    for (uint32_t i = 0; i < nc; ++i) { key_ptrs.push_back(b->dev[i].data); key_ptrs.push_back(b->dev[i].offsets); key_ptrs.push_back(b->dev[i].payload); }
+    for (uint32_t i = 0; i < nc; ++i) { key_ptrs.push_back(b->dev[i].data); key_ptrs.push_back(b->dev[i].offsets); key_ptrs.push_back(b->dev[i].payload); key_ptrs.push_back(b->dev[i].validity); }
   }
   flsgpu::PlanCache *plan = nullptr;
   if (cacheable)
@@ -695,6 +701,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       const uint32_t c = b->cols[i];
       FlsColOut o = b->dev[i];
       const uint32_t wb = b->out[i].width;
+      if (o.validity) o.validity += rows_done / 8;
       if (wb) o.data = (uint8_t *)o.data + rows_done * wb;
       else {
         o.offsets += rows_done;
@@ -793,6 +800,11 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       CKB(cudaEventRecord(ed.a, h->s_d2h));
       for (uint32_t i = 0; i < nc; ++i) {
         const uint32_t wb = b->out[i].width;
+        if (b->dev[i].validity) {
+          CKB(cudaMemcpyAsync((uint8_t *)b->out[i].validity + rows_done / 8, b->dev[i].validity + rows_done / 8, srows / 8,
+                             cudaMemcpyDeviceToHost, h->s_d2h));
+          b->tm.d2h_bytes += srows / 8;
+        }
         if (wb) {
           CKB(cudaMemcpyAsync((uint8_t *)b->out[i].data + rows_done * wb, (uint8_t *)b->dev[i].data + rows_done * wb,
                              srows * wb, cudaMemcpyDeviceToHost, h->s_d2h));
@@ -930,6 +942,7 @@ int flsgpu_decode_filtered(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t
     const int ty = t.types[p.col];
     FlsPredDev &q = ps.p[k];
     q.data = d.data; q.offsets = d.offsets; q.payload = d.payload;
+    q.validity = (const uint32_t *)d.validity;  // a comparison with NULL is not true: the row goes
     q.width = fls_type_bits(ty) / 8; q.op = p.op; q.i64 = p.i64; q.f64 = p.f64;
     if (!q.width) {
       q.kind = 4;
@@ -980,6 +993,19 @@ int flsgpu_decode_filtered(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t
     flsgpu_column o = b->out[i];
     FlsColOut nd;
     o.rows = o.padded_rows = n_sel;
+    if (b->dev[i].validity) {
+      const size_t vb = (n_sel + 63) / 64 * 8 + 16;
+      if (!(nd.validity = (uint8_t *)dalloc(vb))) return bail(FLSGPU_E_NOMEM, "out of device memory");
+      CKF(cudaMemsetAsync(nd.validity, 0, vb, s));
+      fls_filter::compact_validity_kernel<<<grid, 256, 0, s>>>((const uint32_t *)b->dev[i].validity, d_mask, d_off, n_vec,
+                                                              (unsigned long long *)nd.validity);
+      o.validity = (uint64_t *)nd.validity;
+      if (to_host) {
+        if (!(o.validity = (uint64_t *)halloc(vb))) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+        CKF(cudaMemcpyAsync(o.validity, nd.validity, vb - 16, cudaMemcpyDeviceToHost, s));
+        d2h += vb - 16;
+      }
+    }
     if (o.width) {
       nd.data = dalloc(std::max<uint64_t>(n_sel, 1) * o.width);
       if (!nd.data) return bail(FLSGPU_E_NOMEM, "out of device memory");
@@ -1034,7 +1060,7 @@ int flsgpu_decode_filtered(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t
     std::vector<void *> keep;
     for (void *p : b->dev_bufs) {
       bool full = false;
-      for (auto &d : b->dev) full = full || p == d.data || p == (void *)d.offsets || p == (void *)d.payload;
+      for (auto &d : b->dev) full = full || p == d.data || p == (void *)d.offsets || p == (void *)d.payload || p == (void *)d.validity;
       if (full) h->dev_free(p); else keep.push_back(p);
     }
     b->dev_bufs.swap(keep);
@@ -1076,6 +1102,13 @@ int flsgpu_batch_fetch(const flsgpu_batch_t *b, uint32_t i, void *values, uint32
     if (offsets) CK(cudaMemcpy(offsets, d.offsets, (o.padded_rows + 1) * 4, cudaMemcpyDeviceToHost));
     if (values && o.payload_bytes) CK(cudaMemcpy(values, d.payload, o.payload_bytes, cudaMemcpyDeviceToHost));
   }
+  return FLSGPU_OK;
+}
+int flsgpu_batch_fetch_validity(const flsgpu_batch_t *b, uint32_t i, uint64_t *bits) {
+  flsgpu *h = b->h;
+  if (i >= b->out.size() || !bits || !b->dev[i].validity) return h->fail(FLSGPU_E_RANGE, "column has no validity bitmap");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpy(bits, b->dev[i].validity, (b->out[i].padded_rows + 63) / 64 * 8, cudaMemcpyDeviceToHost));
   return FLSGPU_OK;
 }
 void flsgpu_batch_release(flsgpu_batch_t *b) {

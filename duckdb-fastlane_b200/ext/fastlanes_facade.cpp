@@ -180,6 +180,15 @@ bool FastLanesFacade::readNextChunk(DataChunk &result) {
 				FlatVector::SetNull(out, r, true);
 			}
 		}
+		if (s.validity) { // NULLs: the batch's bitmap, from bit validity_bit0 on, into the vector's validity mask
+			auto &mask = FlatVector::Validity(out);
+			for (idx_t r = 0; r < rows; r++) {
+				const uint64_t bit = s.validity_bit0 + r;
+				if (!((s.validity[bit >> 6] >> (bit & 63)) & 1)) {
+					mask.SetInvalid(r);
+				}
+			}
+		}
 	}
 	return true;
 }

@@ -269,6 +269,7 @@ bool FlsScanner::next(uint64_t max_rows, uint64_t &rows, std::vector<ColumnSlice
         s.data = c.width ? (const uint8_t *)c.data + p->f_row * c.width : nullptr;
         s.offsets = c.width ? nullptr : c.offsets + p->f_row;
         s.payload = c.width ? nullptr : c.payload;
+        s.validity = c.validity; s.validity_bit0 = p->f_row;
       }
       p->f_row += rows;
       p->served += rows;
@@ -300,6 +301,7 @@ bool FlsScanner::next(uint64_t max_rows, uint64_t &rows, std::vector<ColumnSlice
         s.offsets = c.offsets + at;
         s.payload = c.payload;
       }
+      s.validity = c.validity; s.validity_bit0 = at;
     }
     p->rg_row += rows;
     p->served += rows;

@@ -25,6 +25,10 @@ struct ColumnSlice {
   const void *data = nullptr;          // fixed width: `rows` values
   const uint32_t *offsets = nullptr;   // strings: rows + 1 offsets into payload (offsets[0] need not be 0)
   const uint8_t *payload = nullptr;
+  // NULLs: bit (validity_bit0 + r) of `validity` (64 rows per word, LSB first) = row r of the run holds a value;
+  // null pointer = the column has no NULLs in this batch
+  const uint64_t *validity = nullptr;
+  uint64_t validity_bit0 = 0;
 };
 
 // A comparison `column <op> constant` on an integer / DATE column, used to skip row groups whose bounds

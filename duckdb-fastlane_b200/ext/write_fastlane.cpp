@@ -82,6 +82,8 @@ struct FastlaneWriteGlobalState : public GlobalFunctionData {
 	idx_t rows = 0; // rows buffered for the current row group
 	vector<vector<uint8_t>> data;   // per column: values / string payload
 	vector<vector<uint64_t>> offs;  // per string column: offsets[rows + 1]
+	vector<vector<uint64_t>> valid; // per column: validity bitmap of the buffered rows (bit = holds a value)
+	vector<bool> has_null;          // per column: a NULL was buffered for the current row group
 	~FastlaneWriteGlobalState() override {
 		if (writer) {
 			flsw_destroy(writer);
@@ -150,6 +152,8 @@ unique_ptr<GlobalFunctionData> FastlaneWriteInitializeGlobal(ClientContext &, Fu
 	result->file_path = file_path;
 	result->data.resize(names.size());
 	result->offs.resize(names.size());
+	result->valid.resize(names.size());
+	result->has_null.assign(names.size(), false);
 	for (idx_t c = 0; c < names.size(); c++) {
 		if (WidthOf(bind_data.fls_types[c]) == 0) {
 			result->offs[c].push_back(0);
@@ -167,19 +171,22 @@ void FlushRowGroup(FastlaneWriteGlobalState &g, const FastlaneWriteBindData &bin
 		return;
 	}
 	vector<const void *> cols;
-	vector<const uint64_t *> offs;
+	vector<const uint64_t *> offs, valid;
 	for (idx_t c = 0; c < g.data.size(); c++) {
+		valid.push_back(g.has_null[c] ? g.valid[c].data() : nullptr);
 		const bool str = WidthOf(bind_data.fls_types[c]) == 0;
 		static const uint8_t empty = 0;
 		cols.push_back(g.data[c].empty() ? (const void *)&empty : (const void *)g.data[c].data());
 		offs.push_back(str ? g.offs[c].data() : nullptr);
 	}
-	if (flsw_append_rowgroup(g.writer, (uint32_t)g.rows, cols.data(), offs.data())) {
+	if (flsw_append_rowgroup_v(g.writer, (uint32_t)g.rows, cols.data(), offs.data(), valid.data())) {
 		throw IOException("Failed to write FastLanes rowgroup: %s", flsw_error(g.writer));
 	}
 	g.rows = 0;
 	for (idx_t c = 0; c < g.data.size(); c++) {
 		g.data[c].clear();
+		g.valid[c].clear();
+		g.has_null[c] = false;
 		if (!g.offs[c].empty()) {
 			g.offs[c].assign(1, 0);
 		}
@@ -193,12 +200,20 @@ void AppendRows(FastlaneWriteGlobalState &g, const FastlaneWriteBindData &bind_d
 		UnifiedVectorFormat fmt;
 		cols[c]->ToUnifiedFormat(input.size(), fmt);
 		const idx_t wb = WidthOf(bind_data.fls_types[c]);
+		g.valid[c].resize((g.rows + n + 63) / 64, 0);
 		for (idx_t i = from; i < from + n; i++) {
 			const idx_t idx = fmt.sel->get_index(i);
-			if (!fmt.validity.RowIsValid(idx)) {
-				throw InvalidInputException("FastLanes writer: NULL in column \"%s\" — the FLS reader has no null map "
-				                            "(use COALESCE)", bind_data.column_names[c]);
+			const idx_t row = g.rows + (i - from);
+			if (!fmt.validity.RowIsValid(idx)) { // a NULL: a filler value / an empty string, the validity bit stays 0
+				g.has_null[c] = true;
+				if (wb) {
+					g.data[c].insert(g.data[c].end(), wb, 0);
+				} else {
+					g.offs[c].push_back(g.data[c].size());
+				}
+				continue;
 			}
+			g.valid[c][row >> 6] |= uint64_t(1) << (row & 63);
 			if (wb) {
 				const auto *src = fmt.data + idx * wb;
 				g.data[c].insert(g.data[c].end(), src, src + wb);

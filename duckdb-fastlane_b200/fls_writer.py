@@ -44,6 +44,8 @@ def lib():
         L.flsw_create.argtypes = [C.c_uint32, C.POINTER(C.c_char_p), C.POINTER(C.c_int32)]
         L.flsw_force_scheme.argtypes = [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32]
         L.flsw_append_rowgroup.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.flsw_append_rowgroup_v.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                             C.POINTER(C.c_void_p)]
         L.flsw_finish.argtypes = [C.c_void_p]
         L.flsw_data.restype = C.c_void_p
         L.flsw_data.argtypes = [C.c_void_p]
@@ -93,10 +95,11 @@ class StrColumn:
 
 
 def write_table(columns, names=None, types=None, force=None, min_bw=None, path=None, alp_ef=None, rg_rows=RG_ROWS,
-                inject=None) -> np.ndarray:
+                inject=None, validity=None) -> np.ndarray:
     """Encode a table into an FLS image (returned as a uint8 array; also written to `path` if given).
 
     columns: list of np.ndarray (fixed width) or StrColumn.   force/min_bw: optional per-column scheme / FFOR width.
+    validity: optional per-column bool arrays (True = the row holds a value) or None: NULLs (flsw_append_rowgroup_v).
     rg_rows: rows per row group, a multiple of 1024 up to 65,536 (what COPY's ROW_GROUP_SIZE sets).
     inject: {(column, row group index): ("fsst", symtab, comp, comp_off) | ("alprd", rbw, lbw, ndict, dict8, left, right,
             nexc, xpos, xleft)} — streams another encoder produced, stored verbatim (flsw.h test knobs).
@@ -164,7 +167,21 @@ def write_table(columns, names=None, types=None, force=None, min_bw=None, path=N
                                              right.ctypes.data, nexc.ctypes.data, xpos.ctypes.data, xleft.ctypes.data)
                 if rc:
                     raise ValueError("bad injected streams for column %d" % i)
-            if L.flsw_append_rowgroup(w, r1 - r0, data, offs):
+            vptr = None
+            if validity and any(v is not None for v in validity):
+                vptr = (C.c_void_p * n_cols)()
+                for i, v in enumerate(validity):
+                    if v is None:
+                        continue
+                    words = np.zeros((r1 - r0 + 63) // 64 * 8, dtype=np.uint8)
+                    pk = np.packbits(np.asarray(v[r0:r1], dtype=bool), bitorder="little")
+                    words[:len(pk)] = pk
+                    keep.append(words)
+                    vptr[i] = words.ctypes.data
+            if vptr is not None:
+                if L.flsw_append_rowgroup_v(w, r1 - r0, data, offs, vptr):
+                    raise RuntimeError(L.flsw_error(w).decode())
+            elif L.flsw_append_rowgroup(w, r1 - r0, data, offs):
                 raise RuntimeError(L.flsw_error(w).decode())
         if L.flsw_finish(w):
             raise RuntimeError(L.flsw_error(w).decode())

@@ -32,7 +32,7 @@ class Opts(C.Structure):
 class Column(C.Structure):
     _fields_ = [("type", C.c_int32), ("width", C.c_uint32), ("rows", C.c_uint64), ("padded_rows", C.c_uint64),
                 ("data", C.c_void_p), ("offsets", C.c_void_p), ("payload", C.c_void_p), ("payload_bytes", C.c_uint64),
-                ("compressed_bytes", C.c_uint64), ("decoded_bytes", C.c_uint64)]
+                ("compressed_bytes", C.c_uint64), ("decoded_bytes", C.c_uint64), ("validity", C.c_void_p)]
 
 
 class Timing(C.Structure):
@@ -102,6 +102,7 @@ def lib():
     L.flsgpu_batch_column.argtypes = [vp, u32, C.POINTER(Column)]
     L.flsgpu_batch_timing.argtypes = [vp, C.POINTER(Timing)]
     L.flsgpu_batch_fetch.argtypes = [vp, u32, vp, vp]
+    L.flsgpu_batch_fetch_validity.argtypes = [vp, u32, vp]
     L.flsgpu_batch_release.argtypes = [vp]
     L.flsgpu_batch_release.restype = None
     L.flsgpu_num_kernel_stats.argtypes = [vp]
@@ -163,6 +164,20 @@ class Batch:
         pay = np.empty(max(int(c.payload_bytes), 1), dtype=np.uint8)
         self.reader._check(lib().flsgpu_batch_fetch(self.h, i, pay.ctypes.data, offs.ctypes.data))
         return offs[:n + 1], pay[:min(int(offs[n]), len(pay))]
+
+    def validity(self, i, padded=False):
+        """bool per row of column i (True = holds a value), or None when the column has no validity bitmap."""
+        c = self.columns[i]
+        if not c.validity:
+            return None
+        nb = (c.padded_rows + 63) // 64 * 8
+        if self.to_host:
+            bits = np.ctypeslib.as_array((C.c_uint8 * nb).from_address(c.validity)).copy() if nb else np.empty(0, np.uint8)
+        else:
+            bits = np.empty(nb, dtype=np.uint8)
+            self.reader._check(lib().flsgpu_batch_fetch_validity(self.h, i, bits.ctypes.data))
+        v = np.unpackbits(bits, bitorder="little").astype(bool)
+        return v[:c.padded_rows if padded else c.rows]
 
     def selection(self):
         """Row ids of a filtered host batch (None for an unfiltered one)."""

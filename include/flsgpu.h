@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define FLSGPU_ABI_VERSION 1
+#define FLSGPU_ABI_VERSION 2
 
 enum flsgpu_status {
   FLSGPU_OK = 0,
@@ -85,6 +85,10 @@ typedef struct {
   uint64_t payload_bytes; /* strings: bytes of payload in use */
   uint64_t compressed_bytes; /* algorithmic bytes read: segment bytes of this column in [g0,g1) */
   uint64_t decoded_bytes;    /* algorithmic bytes written: values, or offsets + payload */
+  uint64_t *validity;     /* NULL: every row holds a value.  Else a bitmap over the padded rows, bit r (LSB first, 64
+                             rows per word, DuckDB's ValidityMask layout) = row r is not NULL; a NULL row's value /
+                             string is a filler.  The reference ignores FastLanes' null maps
+                             (src/fastlanes_facade.cpp:113-118,173-181 emit NULL only for unknown columns). */
 } flsgpu_column;
 
 typedef struct {
@@ -153,6 +157,8 @@ int flsgpu_batch_timing(const flsgpu_batch_t *b, flsgpu_timing *out);
 /* Copy column i of a FLSGPU_OUT_DEVICE batch to caller memory: `values` receives padded_rows * width bytes
  * (fixed width) or payload_bytes bytes (strings); `offsets` (strings only) receives padded_rows + 1 entries. */
 int flsgpu_batch_fetch(const flsgpu_batch_t *b, uint32_t i, void *values, uint32_t *offsets);
+/* The same for column i's validity bitmap: (padded_rows + 63) / 64 words; FLSGPU_E_RANGE when the column has none. */
+int flsgpu_batch_fetch_validity(const flsgpu_batch_t *b, uint32_t i, uint64_t *bits);
 /* Returns the batch's buffers to the handle's pool. */
 void flsgpu_batch_release(flsgpu_batch_t *b);
 

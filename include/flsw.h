@@ -24,6 +24,11 @@ flsw_writer *flsw_create(uint32_t n_cols, const char *const *names, const int32_
  * elements of the type's width; strings: the payload bytes), str_off[c] = u64 offsets[n_rows + 1] for string columns
  * (NULL for fixed width).  Returns 0, or 1 with flsw_error(). */
 int flsw_append_rowgroup(flsw_writer *w, uint32_t n_rows, const void *const *col_data, const uint64_t *const *str_off);
+/* The same with NULLs: validity[c] = bitmap of column c (bit r of word r / 64, LSB first = row r holds a value; DuckDB's
+ * ValidityMask layout) or NULL for a column without NULLs; `validity` itself may be NULL.  The values / strings at NULL
+ * rows are ignored (strings: the offsets must still ascend). */
+int flsw_append_rowgroup_v(flsw_writer *w, uint32_t n_rows, const void *const *col_data, const uint64_t *const *str_off,
+                           const uint64_t *const *validity);
 /* finalizeFile: write the footer (flsw_finish) / the whole image to `path` (finishes first if needed). */
 int flsw_finish(flsw_writer *w);
 int flsw_write_file(flsw_writer *w, const char *path);

@@ -33,7 +33,7 @@ enum { S_UNCOMP = 0, S_CONST, S_FFOR, S_DELTA, S_RLE, S_DICT, S_ALP, S_ALPRD,
 static const uint8_t ORDER[8] = {0, 4, 2, 6, 1, 5, 3, 7};
 
 typedef struct { uint64_t off, size; } oseg;
-typedef struct { uint8_t scheme, n_seg; uint32_t aux32; uint64_t aux64[2]; oseg seg[8]; } ochunk;
+typedef struct { uint8_t scheme, n_seg; uint16_t flags; uint32_t aux32; uint64_t aux64[2]; oseg seg[8]; } ochunk;
 typedef struct { uint64_t off, size; uint32_t n_vec, n_tuples; ochunk *cols; } org;
 typedef struct {
   const uint8_t *img; uint64_t size;
@@ -85,7 +85,7 @@ int flso_open(const void *image, uint64_t size, flso_table **out) {
     r->cols = (ochunk *)calloc(t->n_cols, sizeof(ochunk));
     for (uint32_t c = 0; c < t->n_cols; ++c) {
       ochunk *k = &r->cols[c];
-      k->scheme = p[0]; k->n_seg = p[1];
+      k->scheme = p[0]; k->n_seg = p[1]; k->flags = RD(uint16_t, p + 2);
       k->aux32 = RD(uint32_t, p + 4); k->aux64[0] = RD(uint64_t, p + 8); k->aux64[1] = RD(uint64_t, p + 16);
       p += 24;
       for (uint32_t s = 0; s < k->n_seg; ++s) { k->seg[s].off = RD(uint64_t, p); k->seg[s].size = RD(uint64_t, p + 8); p += 16; }
@@ -407,6 +407,22 @@ static int par_for(uint32_t g0, uint32_t g1, int threads, rg_fn fn, void *ctx) {
 /* ---- public decode entry points.  Output convention (identical to libflsgpu's):
  *   fixed width : out[(sum of n_vec over the range) * 1024] values, tail vectors padded
  *   strings     : offsets[rows_padded + 1] (u32, relative to payload[0]) + payload bytes */
+/* Validity (FORMAT.md, chunk flag 1: the chunk's last segment is a bitmap, 128 bytes per vector, bit r = row r holds a
+ * value).  out = padded rows / 8 bytes; chunks without a bitmap contribute all ones.  Returns 1 when some chunk of the
+ * range has a bitmap, else 0.  The reference has no twin: it never reads FastLanes' null maps
+ * (fastlanes_facade.cpp:113-118,173-181). */
+int flso_decode_validity(const flso_table *t, uint32_t c, uint32_t g0, uint32_t g1, uint8_t *out) {
+  int any = 0;
+  uint64_t at = 0;
+  for (uint32_t g = g0; g < g1; ++g) {
+    const ochunk *k = &t->rg[g].cols[c];
+    const uint64_t nb = 128ull * t->rg[g].n_vec;
+    if ((k->flags & 1) && k->n_seg) { memcpy(out + at, t->img + t->rg[g].off + k->seg[k->n_seg - 1].off, nb); any = 1; }
+    else memset(out + at, 0xFF, nb);
+    at += nb;
+  }
+  return any;
+}
 uint64_t flso_range_padded_rows(const flso_table *t, uint32_t g0, uint32_t g1) {
   uint64_t n = 0;
   for (uint32_t g = g0; g < g1; ++g) n += (uint64_t)t->rg[g].n_vec * O_VEC;

@@ -43,6 +43,7 @@ def lib():
         L.flso_range_padded_rows.restype = C.c_uint64
         L.flso_range_payload.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]
         L.flso_range_payload.restype = C.c_uint64
+        L.flso_decode_validity.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]
         L.flso_decode_fixed.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int]
         L.flso_decode_str.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
         L.flso_alp_decode_value.argtypes = [C.c_int64, C.c_uint, C.c_uint]
@@ -116,6 +117,17 @@ class OracleTable:
     def rows(self, g0=0, g1=None):
         g1 = self.n_rg if g1 is None else g1
         return sum(lib().flso_rowgroup_rows(self.h, g) for g in range(g0, g1))
+
+    def validity(self, col, g0=0, g1=None, padded=False):
+        """bool per row (True = holds a value), or None when no chunk of the range carries a validity bitmap."""
+        L = lib()
+        g1 = self.n_rg if g1 is None else g1
+        n_pad = L.flso_range_padded_rows(self.h, g0, g1)
+        bits = np.empty(n_pad // 8, dtype=np.uint8)
+        if not L.flso_decode_validity(self.h, col, g0, g1, bits.ctypes.data):
+            return None
+        v = np.unpackbits(bits, bitorder="little").astype(bool)
+        return v if padded else v[:self.rows(g0, g1)]
 
     def decode(self, col, g0=0, g1=None, threads=1, padded=False):
         """Fixed width -> np.ndarray; strings -> (offsets u32[n+1], payload u8)."""

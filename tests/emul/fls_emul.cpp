@@ -87,6 +87,12 @@ static bool run_launch(const FlsLaunch &l) {
     case FLS_K_STR_FSST_DICTPREP:
       for (auto &k : l.chunks) fls_fsst_dictprep_chunk_host(k);
       return true;
+    case FLS_K_VALIDITY:
+      for (auto &k : l.chunks) {
+        if (k.seg[0]) memcpy(k.out, k.seg[0], 128ull * k.n_vec);
+        else memset(k.out, 0xFF, 128ull * k.n_vec);
+      }
+      return true;
   }
   return false;
 }

@@ -17,7 +17,7 @@ def test_exports_every_declared_symbol():
     L = C.CDLL(flsgpu.lib_path())
     for s in syms:
         assert hasattr(L, s), s
-    assert flsgpu.lib().flsgpu_abi_version() == 1
+    assert flsgpu.lib().flsgpu_abi_version() == 2
 
 
 def test_missing_file_error_text_matches_reference():

@@ -150,12 +150,12 @@ def test_copy_to_fls_options_and_errors(tmp_path):
     p = str(tmp_path / "x.fls")
     res = sql("COPY (SELECT 1 AS a) TO '%s' (FORMAT FLS, FOO 3)" % p,
               "COPY (SELECT 1 AS a) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 2048, ROW_GROUP_SIZE_BYTES '1MB')" % p,
-              "COPY (SELECT NULL::INTEGER AS a) TO '%s' (FORMAT FLS)" % p,
+              "COPY (SELECT NULL::INTEGER AS a) TO '%s' (FORMAT FLS)" % p,                 # NULLs are written (validity bitmap)
               "COPY (SELECT 42 AS a) TO '%s'" % str(tmp_path / "y.fastlane"),      # format from the file extension
               "COPY (SELECT 42 AS a) TO '%s' (FORMAT FLS, CHUNK_SIZE 4096, ROW_GROUPS_PER_FILE 10)" % p)
     assert "Unknown option for FastLanes: FOO" in res[0]["error"]                  # write_fastlane_stream.cpp:104
     assert "mutually exclusive" in res[1]["error"]                                 # :85-87
-    assert "NULL in column" in res[2]["error"]
+    assert res[2]["rows"] == [["1"]]
     assert res[3]["rows"] == [["1"]] and res[4]["rows"] == [["1"]]
 
 
@@ -259,3 +259,28 @@ def test_device_filter_serves_only_surviving_rows(tmp_path):
     assert [k for k, _n in kept[:3]] == counts[:3] and min(counts[:4]) > 0, (kept, counts)
     off = sql(*[stm[0]] + stm[1::2], env_extra={"FLS_SCAN_NO_DEVICE_FILTER": "1"})
     assert [r["rows"] for r in off[1:]] == [res[1 + 2 * i]["rows"] for i in range(len(qs))]
+
+
+@pytest.mark.gpu
+def test_nulls_round_trip_through_copy_and_read_fls(tmp_path):
+    """NULLs written by COPY (validity bitmap, FORMAT.md) come back as NULLs: every aggregate that looks at them agrees
+    with the source query, with and without the device filter."""
+    path = str(tmp_path / "nulls.fls")
+    src = ("SELECT i::BIGINT AS k, CASE WHEN i % 7 = 0 THEN NULL ELSE (i % 1000)::INTEGER END AS m, "
+           "CASE WHEN i % 3 = 0 THEN NULL ELSE round(i * 0.25, 2)::DOUBLE END AS price, "
+           "CASE WHEN i % 11 = 0 THEN NULL ELSE 'row_' || (i % 5000) END AS s, "
+           "CASE WHEN i > 100000 AND i % 2 = 0 THEN NULL ELSE DATE '2021-01-01' + (i % 400)::INTEGER END AS d "
+           "FROM range(0, 200000) t(i)")
+    agg = ("count(*), count(m), count(price), count(s), count(d), sum(m), sum(price), min(s), max(s), max(d), "
+           "count(*) FILTER (m IS NULL AND s IS NULL)")
+    qs = ["", "WHERE m < 100", "WHERE s = 'row_77' OR m IS NULL", "WHERE price > 40000.0 AND d >= DATE '2021-06-01'", "WHERE m IS NULL"]
+    stm = ["COPY (%s) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 40960)" % (src, path)]
+    for q in qs:
+        stm += ["SELECT %s FROM read_fls('%s') %s" % (agg, path, q), "SELECT %s FROM (%s) %s" % (agg, src, q)]
+    stm += ["SELECT count(*) FROM (SELECT * FROM (%s) EXCEPT SELECT * FROM read_fls('%s'))" % (src, path)]
+    res = sql(*stm)
+    assert all("error" not in r for r in res), res
+    for i in range(len(qs)):
+        assert res[1 + 2 * i]["rows"] == res[2 + 2 * i]["rows"], (qs[i], res[1 + 2 * i], res[2 + 2 * i])
+    assert res[-1]["rows"] == [["0"]]
+    assert res[1]["rows"][0][1] != res[1]["rows"][0][0]       # there are NULLs
