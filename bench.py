@@ -50,6 +50,9 @@ def parse_args():
     ap.add_argument("--distinct", type=int, default=64, help="distinct row groups generated+encoded, then repeated")
     ap.add_argument("--e2e-steps", type=int, default=0, help="timed end-to-end steps (0 = min(steps, 5))")
     ap.add_argument("--cpu-sample-rowgroups", type=int, default=0, help="0 = auto (about 10-30 s of CPU work)")
+    ap.add_argument("--inproc", action="store_true",
+                    help="ONE process, --gpus devices behind one scan cursor (ext/fls_scan.cpp, the table function's `gpus := [..]`): "
+                         "end-to-end line only, pinned host -> host through FlsScanner")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", action="store_true", help="skip the bit-exactness checks around the timed loops")
     a = ap.parse_args()
@@ -612,6 +615,41 @@ def run_ours(args, rank, world, local, dist):
         raise SystemExit(3)
 
 
+def run_inproc(args):
+    """In-process multi-GPU: the scan cursor the DuckDB table function sits on (FlsScanner, `gpus := [0, .., N-1]`),
+    driven by ext/fls_scan_check --bench.  Strong scaling of one SF10 table (916 row groups) unless --rowgroups says
+    otherwise: the file is written to /dev/shm, opened once per device (each handle pins its own mapping), batches of
+    --batch-rowgroups (capped at 64) row groups go to the devices round-robin and come back in file order."""
+    import synth
+    import fls_writer as W
+    n_rg = 916 if args.rowgroups in (0, 9156) else args.rowgroups   # one SF10 table unless --rowgroups names a size
+    small = synth.lineitem_image(min(args.distinct, n_rg), seed=7)
+    img = W.tile_rowgroups(small, n_rg) if min(args.distinct, n_rg) < n_rg else small
+    path = "/dev/shm/flsgpu_bench_%d.fls" % os.getpid()
+    img.tofile(path)
+    try:
+        check = os.path.join(ROOT, "duckdb-fastlane_b200", "ext", "fls_scan_check")
+        batch = min(args.batch_rowgroups, 64)
+        r = subprocess.run([check, path, "--gpus", ",".join(str(i) for i in range(args.gpus)), "--batch", str(batch),
+                            "--chunk", "65536", "--bench", str(max(args.steps, 1))], capture_output=True, text=True, timeout=3000)
+        out = json.loads(r.stdout.strip().splitlines()[-1])
+        if "error" in out:
+            raise SystemExit("bench.py --inproc: " + out["error"])
+    finally:
+        os.unlink(path)
+    v = out["decoded_bytes"] / out["sec_mean"] / GB
+    emit({"metric": "read_fls decoded GB/s", "value": v, "unit": "GB/s", "n_gpus": args.gpus, "steps": out["passes"], "warmup": 1,
+          "ms_per_step": out["sec_mean"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+          "dtype": "int64/f64/u8", "data": "synthetic", "mode": "inproc",
+          "config": {"workload": "lineitem-shaped synthetic, ONE table of %d row groups x 65536 rows x 16 columns scanned through "
+                                 "FlsScanner (the table function's cursor) with %d device(s) behind it; file in /dev/shm, "
+                                 "host -> H2D -> decode -> D2H -> pinned host, every served run touched" % (n_rg, args.gpus),
+                     "rowgroups_total": n_rg, "rowgroups_per_decode_call": batch, "parallelism": "batches round-robin over devices"},
+          "e2e": {"value": v, "unit": "GB/s", "ms_per_step": out["sec_mean"] * 1e3, "best_ms": out["sec_best"] * 1e3,
+                  "h2d_bytes_per_step": int(img.size), "d2h_bytes_per_step": int(out["decoded_bytes"])},
+          "rows_per_s": out["rows"] / out["sec_mean"], "gpu_launches": None})
+
+
 _RESULT = sys.stdout
 
 
@@ -636,6 +674,9 @@ def main():
         run_reference(args, int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), None)
         return
     g.build()
+    if args.inproc:
+        run_inproc(args)
+        return
     rank, world, local, dist = dist_setup(args)
     run_ours(args, rank, world, local, dist)
 

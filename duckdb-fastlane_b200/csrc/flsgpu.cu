@@ -6,7 +6,9 @@
 // cudaMemcpyAsync (pipelined in slices: H2D | decode | D2H on three streams) and runs one kernel launch per
 // (scheme, width) family per slice.  No CPU decode exists in this library.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 #include <fcntl.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
@@ -16,7 +18,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/flsgpu.h"
@@ -135,6 +139,50 @@ struct BufPool {  // size-keyed free lists; buffers live until the handle closes
   }
 };
 
+// Process-wide cache of the buffers closed handles leave behind: a query opens a handle, scans and closes it, and the
+// next query's handle would otherwise pay cudaHostAlloc again (about 0.3 s per GB of page-locked memory — more than
+// the scan itself).  Bounded (FLSGPU_CACHE_HOST_MB, default 8192; FLSGPU_CACHE_DEV_MB, default 32768);
+// flsgpu_trim_cache() frees it.
+struct GlobalCache {
+  std::mutex mu;
+  std::multimap<size_t, void *> host;
+  std::map<int, std::multimap<size_t, void *>> dev;
+  size_t host_bytes = 0, dev_bytes = 0;
+  static size_t cap_mb(const char *name, size_t dflt) { const char *e = getenv(name); return (e ? strtoull(e, nullptr, 10) : dflt) << 20; }
+  void *take_host(size_t n, size_t *got) {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = host.lower_bound(n);
+    if (it == host.end() || it->first > n + n / 4 + 4096) return nullptr;
+    void *p = it->second;
+    *got = it->first; host_bytes -= it->first;
+    host.erase(it);
+    return p;
+  }
+  void *take_dev(int device, size_t n, size_t *got) {
+    std::lock_guard<std::mutex> g(mu);
+    auto &fl = dev[device];
+    auto it = fl.lower_bound(n);
+    if (it == fl.end() || it->first > n + n / 4 + 4096) return nullptr;
+    void *p = it->second;
+    *got = it->first; dev_bytes -= it->first;
+    fl.erase(it);
+    return p;
+  }
+  bool give_host(void *p, size_t n) {
+    std::lock_guard<std::mutex> g(mu);
+    if (host_bytes + n > cap_mb("FLSGPU_CACHE_HOST_MB", 8192)) return false;
+    host.emplace(n, p); host_bytes += n;
+    return true;
+  }
+  bool give_dev(int device, void *p, size_t n) {
+    std::lock_guard<std::mutex> g(mu);
+    if (dev_bytes + n > cap_mb("FLSGPU_CACHE_DEV_MB", 32768)) return false;
+    dev[device].emplace(n, p); dev_bytes += n;
+    return true;
+  }
+};
+GlobalCache g_cache;
+
 struct KStat {
   std::string name;
   uint64_t launches = 0, rd = 0, wr = 0, vectors = 0;
@@ -151,6 +199,9 @@ struct flsgpu {
   const uint8_t *image = nullptr;  // host image (whole file)
   uint64_t size = 0;
   bool image_owned = false, image_registered = false, cuda_ready = false;
+  bool image_mapped = false;  // opened by path: `image` is a read-only mapping of the file (pageable)
+  int fd = -1;
+  void *gds = nullptr;        // cuFile state (FLSGPU_OPEN_GDS)
   cudaStream_t s_h2d = nullptr, s_k = nullptr, s_d2h = nullptr;
   cudaStream_t s_kx[3] = {nullptr, nullptr, nullptr};  // side streams: independent kernels of a slice overlap
   uint8_t *d_res = nullptr;  // resident compressed row groups [res_g0, res_g1)
@@ -197,6 +248,8 @@ struct flsgpu {
     if (!n) n = 256;
     void *p = pool.get(pool.free_dev, n);
     if (p) return p;
+    size_t got = 0;
+    if ((p = g_cache.take_dev(device, n, &got))) { dev_size[p] = got; return p; }
     if (cudaMalloc(&p, n) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     dev_size[p] = n;
     return p;
@@ -206,7 +259,9 @@ struct flsgpu {
     if (!n) n = 4096;
     void *p = pool.get(pool.free_host, n);
     if (p) return p;
-    if (cudaHostAlloc(&p, n, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    size_t got = 0;
+    if ((p = g_cache.take_host(n, &got))) { host_size[p] = got; return p; }
+    if (cudaHostAlloc(&p, n, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     host_size[p] = n;
     return p;
   }
@@ -238,6 +293,96 @@ struct flsgpu_batch {
 
 namespace {
 
+// ---- GPUDirect Storage (cuFile), bound at run time: libflsgpu.so does not link libcufile ------------------------
+// The handful of declarations used, as in cufile.h (CUDA 12.9): CUfileError_t {err, cu_err}; CU_FILE_SUCCESS = 0;
+// descriptor type CU_FILE_HANDLE_TYPE_OPAQUE_FD = 1.
+struct GdsApi {
+  struct Err { int err; int cu_err; };
+  struct Descr { int type; union { int fd; void *handle; } h; const void *fs_ops; };
+  void *lib = nullptr, *fh = nullptr;
+  Err (*DriverOpen)() = nullptr;
+  Err (*HandleRegister)(void **, Descr *) = nullptr;
+  void (*HandleDeregister)(void *) = nullptr;
+  Err (*BufRegister)(const void *, size_t, int) = nullptr;
+  Err (*BufDeregister)(const void *) = nullptr;
+  ssize_t (*Read)(void *, void *, size_t, off_t, off_t) = nullptr;
+};
+int gds_open(flsgpu *h) {
+  // Without the nvidia-fs kernel driver cuFile can only run its compatibility mode (POSIX reads into a bounce buffer:
+  // what the mapped path already does, on more threads) — and on the B200 boxes of this pool, which have no
+  // nvidia-fs, cuFileDriverOpen / cuFileRead did not return at all.  So: no driver, no GDS, said loudly.
+  // FLSGPU_GDS_COMPAT=1 tries cuFile anyway.
+  struct stat st;
+  const char *force = getenv("FLSGPU_GDS_COMPAT");
+  if (stat("/proc/driver/nvidia-fs", &st) != 0 && !(force && *force == '1'))
+    return h->fail(FLSGPU_E_IO, "FLSGPU_OPEN_GDS: the nvidia-fs kernel driver is not loaded (no /proc/driver/nvidia-fs): "
+                                "GPUDirect Storage is unavailable on this box; open without the flag");
+  GdsApi *g = new GdsApi();
+  g->lib = dlopen("libcufile.so.0", RTLD_NOW | RTLD_LOCAL);
+  if (!g->lib) g->lib = dlopen("libcufile.so", RTLD_NOW | RTLD_LOCAL);
+  if (!g->lib) { std::string m = std::string("FLSGPU_OPEN_GDS: cannot load libcufile: ") + dlerror(); delete g; return h->fail(FLSGPU_E_IO, m); }
+  g->DriverOpen = (GdsApi::Err(*)())dlsym(g->lib, "cuFileDriverOpen");
+  g->HandleRegister = (GdsApi::Err(*)(void **, GdsApi::Descr *))dlsym(g->lib, "cuFileHandleRegister");
+  g->HandleDeregister = (void (*)(void *))dlsym(g->lib, "cuFileHandleDeregister");
+  g->BufRegister = (GdsApi::Err(*)(const void *, size_t, int))dlsym(g->lib, "cuFileBufRegister");
+  g->BufDeregister = (GdsApi::Err(*)(const void *))dlsym(g->lib, "cuFileBufDeregister");
+  g->Read = (ssize_t(*)(void *, void *, size_t, off_t, off_t))dlsym(g->lib, "cuFileRead");
+  if (!g->DriverOpen || !g->HandleRegister || !g->HandleDeregister || !g->Read) {
+    dlclose(g->lib); delete g;
+    return h->fail(FLSGPU_E_IO, "FLSGPU_OPEN_GDS: libcufile lacks the cuFile entry points");
+  }
+  GdsApi::Err e = g->DriverOpen();
+  if (e.err != 0) {
+    const int code = e.err;
+    dlclose(g->lib); delete g;
+    return h->fail(FLSGPU_E_IO, "FLSGPU_OPEN_GDS: cuFileDriverOpen failed (CUfileOpError " + std::to_string(code) + "): no GPUDirect Storage on this box");
+  }
+  GdsApi::Descr d;
+  memset(&d, 0, sizeof(d));
+  d.type = 1;
+  d.h.fd = h->fd;
+  e = g->HandleRegister(&g->fh, &d);
+  if (e.err != 0) {
+    const int code = e.err;
+    dlclose(g->lib); delete g;
+    return h->fail(FLSGPU_E_IO, "FLSGPU_OPEN_GDS: cuFileHandleRegister failed (CUfileOpError " + std::to_string(code) + ") for " + h->path);
+  }
+  h->gds = g;
+  return 0;
+}
+void gds_close(flsgpu *h) {
+  GdsApi *g = (GdsApi *)h->gds;
+  if (!g) return;
+  if (g->fh) g->HandleDeregister(g->fh);
+  dlclose(g->lib);
+  delete g;
+  h->gds = nullptr;
+}
+// file bytes [off, off + n) -> device memory at dst (synchronous: cuFileRead returns when the bytes are there)
+int gds_read(flsgpu *h, void *dst, uint64_t off, uint64_t n) {
+  GdsApi *g = (GdsApi *)h->gds;
+  uint64_t done = 0;
+  while (done < n) {
+    const ssize_t r = g->Read(g->fh, dst, (size_t)(n - done), (off_t)(off + done), (off_t)done);
+    if (r <= 0) return h->fail(FLSGPU_E_IO, "cuFileRead failed (" + std::to_string((long long)r) + ") on " + h->path);
+    done += (uint64_t)r;
+  }
+  return 0;
+}
+// pageable bytes -> page-locked bounce buffer, on a few threads (one thread copies out of the page cache at a fraction
+// of what the PCIe link takes)
+void parallel_copy(void *dst, const void *src, uint64_t n) {
+  const uint64_t chunk = 8ull << 20;
+  const unsigned nt = (unsigned)std::min<uint64_t>(4, (n + chunk - 1) / chunk);
+  if (nt <= 1) { memcpy(dst, src, n); return; }
+  std::vector<std::thread> th;
+  for (unsigned i = 0; i < nt; ++i) {
+    const uint64_t a = n * i / nt, b = n * (i + 1) / nt;
+    th.emplace_back([=] { memcpy((uint8_t *)dst + a, (const uint8_t *)src + a, b - a); });
+  }
+  for (auto &t : th) t.join();
+}
+
 // Bring CUDA up for this handle and make the whole host image available (page-locked unless told otherwise).
 int ensure_ready(flsgpu *h) {
   if (h->cuda_ready) { CK(cudaSetDevice(h->device)); return 0; }
@@ -252,7 +397,21 @@ int ensure_ready(flsgpu *h) {
     g_split_fsst = g_split_dict = 0;
     sscanf(e, "%d,%d", &g_split_fsst, &g_split_dict);
   }
-  if (!h->image) {  // opened by path: read the file into page-locked memory
+  if (!h->image && !(h->flags & FLSGPU_OPEN_LOAD_FILE)) {
+    // opened by path: map the file.  Footer, vector headers and dictionaries are read through the mapping (page
+    // cache); the compressed bytes of each pipeline slice are copied into a page-locked bounce buffer right before
+    // their H2D copy (stage_slice) — or read by cuFile straight into HBM — so a scan never waits for the whole file.
+    h->fd = open(h->path.c_str(), O_RDONLY);
+    void *p = h->fd >= 0 ? mmap(nullptr, h->size, PROT_READ, MAP_SHARED, h->fd, 0) : MAP_FAILED;
+    if (p == MAP_FAILED) {
+      if (h->fd >= 0) close(h->fd);
+      h->fd = -1;
+      return h->fail(FLSGPU_E_IO, "Failed to open FastLanes file: " + h->path);
+    }
+    h->image = (const uint8_t *)p;
+    h->image_mapped = true;
+    if (h->flags & FLSGPU_OPEN_GDS) { if (int rc = gds_open(h)) return rc; }
+  } else if (!h->image) {  // FLSGPU_OPEN_LOAD_FILE: read the whole file into page-locked memory
     void *p = nullptr;
     const bool pin = !(h->flags & FLSGPU_OPEN_NO_PIN);
     if (pin) CK(cudaHostAlloc(&p, h->size, cudaHostAllocDefault));
@@ -356,12 +515,18 @@ void flsgpu_close(flsgpu_t *h) {
   if (h->cuda_ready) {
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
-    for (auto &kv : h->dev_size) cudaFree(kv.first);
+    // the pooled buffers go to the process-wide cache (up to its bounds) for the next handle
+    for (auto &kv : h->pool.free_dev) { h->dev_size.erase(kv.second); if (!g_cache.give_dev(h->device, kv.second, kv.first)) cudaFree(kv.second); }
+    for (auto &kv : h->pool.free_host) { h->host_size.erase(kv.second); if (!g_cache.give_host(kv.second, kv.first)) cudaFreeHost(kv.second); }
+    for (auto &kv : h->dev_size) cudaFree(kv.first);       // (buffers of batches the caller never released)
     for (auto &kv : h->host_size) cudaFreeHost(kv.first);
     if (h->d_res) cudaFree(h->d_res);
     if (h->d_flush) cudaFree(h->d_flush);
     for (auto e : h->ev_free) cudaEventDestroy(e);
     if (h->image_registered) cudaHostUnregister((void *)h->image);
+    gds_close(h);
+    if (h->image_mapped) munmap((void *)h->image, h->size);
+    if (h->fd >= 0) close(h->fd);
     if (h->image_owned) { if (h->flags & FLSGPU_OPEN_NO_PIN) free((void *)h->image); else cudaFreeHost((void *)h->image); }
     cudaStreamDestroy(h->s_h2d);
     cudaStreamDestroy(h->s_k);
@@ -369,6 +534,20 @@ void flsgpu_close(flsgpu_t *h) {
     for (auto sx : h->s_kx) cudaStreamDestroy(sx);
   }
   delete h;
+}
+
+void flsgpu_trim_cache(void) {
+  std::lock_guard<std::mutex> g(g_cache.mu);
+  for (auto &kv : g_cache.host) cudaFreeHost(kv.second);
+  g_cache.host.clear(); g_cache.host_bytes = 0;
+  int cur = 0;
+  cudaGetDevice(&cur);
+  for (auto &d : g_cache.dev) {
+    cudaSetDevice(d.first);
+    for (auto &kv : d.second) cudaFree(kv.second);
+  }
+  cudaSetDevice(cur);
+  g_cache.dev.clear(); g_cache.dev_bytes = 0;
 }
 
 const char *flsgpu_last_error(const flsgpu_t *h) { return h ? h->err.c_str() : g_open_err.c_str(); }
@@ -514,7 +693,8 @@ int flsgpu_make_resident(flsgpu_t *h, uint32_t g0, uint32_t g1) {
   const uint64_t bytes = range_extent(h->t, g0, g1);
   if (!bytes) return FLSGPU_OK;
   CK(cudaMalloc((void **)&h->d_res, bytes));
-  CK(cudaMemcpyAsync(h->d_res, h->image + h->t.rgs[g0].off, bytes, cudaMemcpyHostToDevice, h->s_h2d));
+  if (h->gds) { if (int rc = gds_read(h, h->d_res, h->t.rgs[g0].off, bytes)) return rc; }
+  else CK(cudaMemcpyAsync(h->d_res, h->image + h->t.rgs[g0].off, bytes, cudaMemcpyHostToDevice, h->s_h2d));
   CK(cudaStreamSynchronize(h->s_h2d));
   h->res_bytes = bytes;
   h->res_g0 = g0;
@@ -736,7 +916,17 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     EvPair eh = {ev(), ev()};
     CKB(cudaEventRecord(eh.a, h->s_h2d));
     if (!resident) {
-      CKB(cudaMemcpyAsync(d_stage + rel, h->image + t.rgs[s0].off, ext, cudaMemcpyHostToDevice, h->s_h2d));
+      if (h->gds) {  // GPUDirect Storage: file -> HBM, no host bounce (cuFileRead is synchronous)
+        if (int rc = gds_read(h, d_stage + rel, t.rgs[s0].off, ext)) { const std::string m = h->err; return bail(rc, m); }
+      } else if (h->image_mapped) {  // mapped file: page cache -> page-locked bounce buffer -> HBM
+        void *bounce = h->host_alloc(ext);
+        if (!bounce) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+        b->host_bufs.push_back(bounce);
+        parallel_copy(bounce, h->image + t.rgs[s0].off, ext);
+        CKB(cudaMemcpyAsync(d_stage + rel, bounce, ext, cudaMemcpyHostToDevice, h->s_h2d));
+      } else {
+        CKB(cudaMemcpyAsync(d_stage + rel, h->image + t.rgs[s0].off, ext, cudaMemcpyHostToDevice, h->s_h2d));
+      }
       b->tm.h2d_bytes += ext;
     }
     if (!plan_hit)

@@ -8,6 +8,7 @@
 // (dev container only; the binary and the library travel to the GPU box with the snapshot) and libflsgpu.so.
 //
 //   duckdb_sql_check "SELECT count(*) FROM read_fls('x.fls')" ["SELECT ..."]...
+#include <chrono>
 #include <cstdio>
 #include <string>
 
@@ -43,8 +44,11 @@ int main(int argc, char **argv) {
 	duckdb::Connection con(db);
 	int rc = 0;
 	for (int i = 1; i < argc; i++) {
+		fprintf(stderr, "sql_check: statement %d\n", i - 1);
+		const auto t0 = std::chrono::steady_clock::now();
 		auto res = con.Query(argv[i]);
-		printf("{\"sql\": \"%s\", ", esc(argv[i]).c_str());
+		const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+		printf("{\"sql\": \"%s\", \"ms\": %.3f, ", esc(argv[i]).c_str(), ms);
 		if (res->HasError()) {
 			printf("\"error\": \"%s\"}\n", esc(res->GetError()).c_str());
 			rc = 1;

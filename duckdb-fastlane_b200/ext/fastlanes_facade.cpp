@@ -48,8 +48,12 @@ FastLanesFacade::~FastLanesFacade() {
 }
 
 bool FastLanesFacade::openFile(const std::string &file_path) {
+	return openFile(file_path, std::vector<int>());
+}
+
+bool FastLanesFacade::openFile(const std::string &file_path, const std::vector<int> &devices) {
 	closeFile();
-	if (!pImpl->scanner.open(file_path)) {
+	if (!pImpl->scanner.open(file_path, devices)) {
 		pImpl->error = pImpl->scanner.error();
 		return false;
 	}
@@ -78,6 +82,19 @@ bool FastLanesFacade::setProjection(const std::vector<idx_t> &column_ids) {
 	}
 	pImpl->projection = column_ids;
 	return true;
+}
+
+bool FastLanesFacade::setRowGroupRange(idx_t g0, idx_t g1) {
+	pImpl->scanner.rewind();
+	if (!pImpl->scanner.setRowGroupRange((uint32_t)g0, (uint32_t)g1)) {
+		pImpl->error = pImpl->scanner.error();
+		return false;
+	}
+	pImpl->error.clear();
+	return true;
+}
+idx_t FastLanesFacade::rowGroupCount() const {
+	return pImpl->scanner.rowGroupCount();
 }
 
 idx_t FastLanesFacade::pruneRowGroups(const std::vector<flsgpu_host::ZonePredicate> &predicates) {

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <deque>
 #include <future>
 
 namespace flsgpu_host {
@@ -11,14 +12,21 @@ namespace flsgpu_host {
 namespace {
 struct Decoded {
   flsgpu_batch_t *batch = nullptr;
-  uint32_t g0 = 0, g1 = 0;
+  uint32_t g0 = 0, g1 = 0, lane = 0;
   int rc = 0;
   std::string err;
 };
 }  // namespace
 
 struct FlsScanner::Impl {
-  flsgpu_t *h = nullptr;
+  flsgpu_t *h = nullptr;  // lane 0's handle: schema, row counts, pruning
+  // One lane per device of the scan: its own handle (streams, buffer pools, pinned image) and at most ONE decode in
+  // flight, so no handle ever has two callers.  Batches go to the lanes round-robin and come back in order: with N
+  // devices, N batches are being decoded while the caller consumes one (one host thread +
+  // context per device feeding one ordered queue).
+  std::vector<flsgpu_t *> lanes;
+  std::vector<std::vector<flsgpu_batch_t *>> to_release;  // per lane: served batches, released by the lane's next task
+  uint32_t next_lane = 0;
   std::string err;
   std::vector<std::string> names;
   std::vector<int32_t> types;
@@ -32,7 +40,6 @@ struct FlsScanner::Impl {
   uint32_t rg = 0;                 // row group being served (absolute)
   uint64_t rg_row = 0;             // next row inside it
   uint64_t rg_base = 0;            // padded row index of the row group's first row inside the batch
-  std::future<Decoded> ahead;      // batch being decoded by the worker
   uint32_t next_g = 0;             // first row group not yet handed to the worker
 
   // Runs on the worker thread; it is the only caller of the handle while it runs (flsgpu.h: one caller at a time).
@@ -40,10 +47,11 @@ struct FlsScanner::Impl {
   std::vector<flsgpu_predicate> filt;    // device filter (flsgpu_decode_filtered); empty = plain decode
   uint64_t f_row = 0;                    // filtered batches: next row of the batch to serve
   uint64_t scanned = 0, filtered_out = 0;
-  Decoded decode(flsgpu_batch_t *release_first, uint32_t g0, uint32_t g1) {
-    if (release_first) flsgpu_batch_release(release_first);
+  Decoded decode(uint32_t lane, std::vector<flsgpu_batch_t *> release_first, uint32_t g0, uint32_t g1) {
+    flsgpu_t *h = lanes[lane];  // (shadows the member: this task's handle)
+    for (auto *b : release_first) flsgpu_batch_release(b);
     Decoded d;
-    d.g0 = g0; d.g1 = g1;
+    d.g0 = g0; d.g1 = g1; d.lane = lane;
     const uint32_t *pc = proj.empty() ? nullptr : proj.data();
     if (!filt.empty())
       d.rc = flsgpu_decode_filtered(h, g0, g1, pc, (uint32_t)proj.size(), filt.data(), (uint32_t)filt.size(), FLSGPU_OUT_HOST, &d.batch);
@@ -55,41 +63,51 @@ struct FlsScanner::Impl {
   std::vector<uint8_t> skip;       // per row group: pruned by a zone predicate
   uint32_t n_skipped = 0;
   bool skipped(uint32_t g) const { return g < skip.size() && skip[g]; }
-  void launch_ahead(flsgpu_batch_t *release_first) {
-    while (next_g < g_end && skipped(next_g)) ++next_g;
-    if (next_g >= g_end) {
-      if (release_first) flsgpu_batch_release(release_first);
-      return;
+  std::deque<std::future<Decoded>> queue;  // decodes in flight, in scan order; at most one per lane
+  // hand the next batches to the idle lanes (a served batch `old` of lane `old_lane` is released by that lane's next task)
+  void launch_ahead(flsgpu_batch_t *old, uint32_t old_lane) {
+    if (old) to_release[old_lane].push_back(old);
+    while (queue.size() < lanes.size()) {
+      while (next_g < g_end && skipped(next_g)) ++next_g;
+      if (next_g >= g_end) break;
+      // the next contiguous run of row groups that survive pruning, at most one batch long
+      const uint32_t g0 = next_g;
+      uint32_t g1 = g0 + 1;
+      while (g1 < g_end && g1 - g0 < batch_rgs && !skipped(g1)) ++g1;
+      next_g = g1;
+      const uint32_t lane = next_lane;
+      next_lane = (next_lane + 1) % (uint32_t)lanes.size();
+      std::vector<flsgpu_batch_t *> rel;
+      rel.swap(to_release[lane]);
+      queue.push_back(std::async(std::launch::async, [this, lane, rel, g0, g1] { return decode(lane, rel, g0, g1); }));
     }
-    // the next contiguous run of row groups that survive pruning, at most one batch long
-    const uint32_t g0 = next_g;
-    uint32_t g1 = g0 + 1;
-    while (g1 < g_end && g1 - g0 < batch_rgs && !skipped(g1)) ++g1;
-    next_g = g1;
-    ahead = std::async(std::launch::async, [this, release_first, g0, g1] { return decode(release_first, g0, g1); });
   }
   void drain() {
-    if (ahead.valid()) {
-      Decoded d = ahead.get();
+    while (!queue.empty()) {
+      Decoded d = queue.front().get();
+      queue.pop_front();
       if (d.batch) flsgpu_batch_release(d.batch);
     }
     if (cur.batch) { flsgpu_batch_release(cur.batch); cur.batch = nullptr; }
+    for (auto &v : to_release) { for (auto *b : v) flsgpu_batch_release(b); v.clear(); }
   }
   // make `cur` the next batch; false at the end or on error
   bool advance_batch() {
     flsgpu_batch_t *old = cur.batch;
+    const uint32_t old_lane = cur.lane;
     cur = Decoded();
-    if (!ahead.valid()) {
+    if (queue.empty()) {
       if (old) flsgpu_batch_release(old);
       if (!filt.empty() && getenv("FLS_SCAN_TRACE"))
         fprintf(stderr, "fls_filter: device filter kept %llu of %llu rows\n", (unsigned long long)(scanned - filtered_out),
                 (unsigned long long)scanned);
       return false;
     }
-    Decoded d = ahead.get();
+    Decoded d = queue.front().get();
+    queue.pop_front();
     if (d.rc) {
       err = d.err;
-      if (old) flsgpu_batch_release(old);
+      if (old) to_release[old_lane].push_back(old);
       return false;
     }
     cur = d;
@@ -103,7 +121,7 @@ struct FlsScanner::Impl {
       scanned += in;
       filtered_out += in - (nc ? cols[0].rows : 0);
     }
-    launch_ahead(old);
+    launch_ahead(old, old_lane);
     return true;
   }
 };
@@ -112,15 +130,28 @@ FlsScanner::FlsScanner() : p(new Impl()) {}
 FlsScanner::~FlsScanner() { close(); }
 
 bool FlsScanner::open(const std::string &path, int device, uint32_t batch_rowgroups) {
+  return open(path, std::vector<int>(1, device), batch_rowgroups);
+}
+
+bool FlsScanner::open(const std::string &path, const std::vector<int> &devices, uint32_t batch_rowgroups) {
   close();
-  flsgpu_opts o = {};
-  o.device = device;
-  const int rc = flsgpu_open(path.c_str(), &o, &p->h);
-  if (rc != FLSGPU_OK) {
-    p->err = flsgpu_last_error(nullptr);
-    p->h = nullptr;
-    return false;
+  for (int device : devices.empty() ? std::vector<int>(1, 0) : devices) {
+    flsgpu_opts o = {};
+    o.device = device;
+    flsgpu_t *lane = nullptr;
+    const int rc = flsgpu_open(path.c_str(), &o, &lane);
+    if (rc != FLSGPU_OK) {
+      p->err = flsgpu_last_error(nullptr);
+      for (auto *l : p->lanes) flsgpu_close(l);
+      p->lanes.clear();
+      p->h = nullptr;
+      return false;
+    }
+    p->lanes.push_back(lane);
   }
+  p->h = p->lanes[0];
+  p->to_release.assign(p->lanes.size(), {});
+  p->next_lane = 0;
   p->err.clear();
   uint32_t nc = 0;
   const char *const *names = nullptr;
@@ -144,13 +175,15 @@ bool FlsScanner::open(const std::string &path, int device, uint32_t batch_rowgro
 void FlsScanner::close() {
   if (!p->h) return;
   p->drain();
-  flsgpu_close(p->h);
+  for (auto *l : p->lanes) flsgpu_close(l);
+  p->lanes.clear();
   p->h = nullptr;
   p->names.clear(); p->types.clear(); p->proj.clear();
   p->n_rg = 0; p->n_rows = 0; p->served = 0; p->started = false;
 }
 
 bool FlsScanner::isOpen() const { return p->h != nullptr; }
+uint32_t FlsScanner::deviceCount() const { return (uint32_t)p->lanes.size(); }
 const std::string &FlsScanner::error() const { return p->err; }
 uint32_t FlsScanner::columnCount() const { return (uint32_t)p->names.size(); }
 uint64_t FlsScanner::rowCount() const { return p->n_rows; }
@@ -166,6 +199,19 @@ bool FlsScanner::setProjection(const std::vector<uint32_t> &cols) {
     if (c >= p->names.size()) { p->err = "bad column id"; return false; }
   p->proj = cols;
   return true;
+}
+
+void FlsScanner::rewind() {
+  if (!p->h) return;
+  p->drain();
+  p->cur = Decoded();
+  p->started = false;
+  p->err.clear();
+  p->g_begin = 0; p->g_end = p->n_rg;
+  p->rows_in_range = p->n_rows;
+  p->skip.clear(); p->n_skipped = 0;
+  p->next_lane = 0;
+  p->scanned = p->filtered_out = 0; p->served = 0;
 }
 
 bool FlsScanner::setRowGroupRange(uint32_t g0, uint32_t g1) {
@@ -249,7 +295,7 @@ bool FlsScanner::next(uint64_t max_rows, uint64_t &rows, std::vector<ColumnSlice
   if (!p->started) {
     p->started = true;
     p->next_g = p->g_begin;
-    p->launch_ahead(nullptr);
+    p->launch_ahead(nullptr, 0);
     if (!p->advance_batch()) return false;
   }
   for (;;) {

@@ -58,6 +58,11 @@ class FlsScanner {
   // On failure returns false and error() holds the text the reference's bind raises
   // ("Failed to open FastLanes file: <path>", /root/reference/src/scan_fastlanes.cpp:42).
   bool open(const std::string &path, int device = 0, uint32_t batch_rowgroups = 0);
+  // Several GPUs behind one cursor (`gpus := [0, 1, ..]` on the table function): one handle and
+  // one decode in flight per device, batches of row groups dealt to the devices round-robin and served in file order.
+  // A device may be listed twice (two decodes in flight on it).
+  bool open(const std::string &path, const std::vector<int> &devices, uint32_t batch_rowgroups = 0);
+  uint32_t deviceCount() const;
   void close();
   bool isOpen() const;
   const std::string &error() const;
@@ -73,6 +78,9 @@ class FlsScanner {
   bool setProjection(const std::vector<uint32_t> &cols);
   // Restrict the scan to row groups [g0, g1) — one shard of a multi-GPU / multi-thread scan.
   bool setRowGroupRange(uint32_t g0, uint32_t g1);
+  // After a scan has ended (or before it began): back to the state right after open(), handles and their buffer pools
+  // kept, so that setRowGroupRange / pruneRowGroups can aim the cursor at another shard.  Projection and device filter stay.
+  void rewind();
 
   // Row-group skipping: a row group is dropped from the scan when one of the predicates
   // (a conjunction) is false for every value its bounds allow.  The caller still applies the predicates to the rows

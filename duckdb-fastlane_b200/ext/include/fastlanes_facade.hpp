@@ -39,6 +39,9 @@ public:
 
 	// Reading operations
 	bool openFile(const std::string &file_path);
+	//! The same on several GPUs (CUDA device ordinals): batches of row groups are decoded on the devices in turn and
+	//! served in file order.  An empty list means device 0.
+	bool openFile(const std::string &file_path, const std::vector<int> &devices);
 	std::vector<LogicalType> getColumnTypes();
 	std::vector<std::string> getColumnNames();
 	//! Projected file column ids, in output order; call between openFile and the first readNextChunk.
@@ -49,6 +52,10 @@ public:
 	//! Evaluate the conjunction on the GPU and serve only the rows that pass (flsgpu_decode_filtered); the engine
 	//! keeps the filters.  Call between openFile and the first readNextChunk.
 	bool setDeviceFilter(const std::vector<flsgpu_host::ZonePredicate> &predicates);
+	//! One shard of a parallel scan: aim the (possibly finished) reader at row groups [g0, g1) of the open file.
+	//! Projection and device filter stay; row-group pruning must be asked for again.
+	bool setRowGroupRange(idx_t g0, idx_t g1);
+	idx_t rowGroupCount() const;
 	//! Fills `result` with the next <= STANDARD_VECTOR_SIZE rows; false at the end of the file or on error.
 	bool readNextChunk(DataChunk &result);
 	void closeFile();

@@ -19,10 +19,16 @@
 //   * the same comparisons (plus FLOAT / DOUBLE / BOOLEAN constants and `column <> 'text'`) are evaluated on the GPU
 //     after the decode and only the rows that pass are copied back and served (late materialisation,
 //     flsgpu_decode_filtered); DuckDB still applies its own filter on top, so results cannot differ.
-// MaxThreads stays 1 like the reference: the parallelism is on the GPU, behind the facade.
+// The scan is dealt out in shards of row groups to as many threads as DuckDB gives it (the reference's MaxThreads is 1):
+// the decode runs on the GPU behind every thread's reader, the copy-out into vectors and the rest of the pipeline on
+// the host threads; batch indices keep file order where a plan needs it.  `gpus := [0, 1, ..]` / `device := n` name
+// the CUDA devices.
 #include "scan_fastlanes.hpp"
 
+#include <algorithm>
+#include <atomic>
 #include <cstdlib>
+#include <mutex>
 
 #include "duckdb/common/exception.hpp"
 #include "duckdb/common/string_util.hpp"
@@ -37,7 +43,9 @@
 #include "duckdb/planner/expression/bound_columnref_expression.hpp"
 #include "duckdb/planner/expression/bound_comparison_expression.hpp"
 #include "duckdb/planner/expression/bound_constant_expression.hpp"
+#include "duckdb/parallel/task_scheduler.hpp"
 #include "duckdb/planner/operator/logical_get.hpp"
+#include "duckdb/execution/partition_info.hpp"
 #include "duckdb/storage/statistics/node_statistics.hpp"
 #include "fastlanes_facade.hpp"
 
@@ -48,53 +56,125 @@ struct FastLanesBindData : public TableFunctionData {
 	vector<LogicalType> return_types;
 	vector<string> return_names;
 	idx_t total_rows = 0;
+	idx_t total_rowgroups = 0;
 	vector<flsgpu_host::ZonePredicate> zone_predicates; // from pushdown_complex_filter; file column ids
+	std::vector<int> devices; // `gpus := [0, 1, ..]` / `device := n`; empty = device 0
 };
 
+// A scan is dealt out in SHARDS of consecutive row groups.  Every DuckDB thread that scans owns a reader (its own
+// libflsgpu handle: streams, buffer pools, one decode in flight per listed device) and asks the global state for the
+// next shard when its reader runs dry — so the copy-out into DuckDB vectors and everything downstream of the scan run
+// on as many threads as DuckDB gives the pipeline, while the shards' batch indices keep the rows in file order where
+// the plan needs it.  (The reference scans on one thread, MaxThreads() == 1, /root/reference/src/scan_fastlanes.cpp:30.)
 struct FastLanesScanState : public GlobalTableFunctionState {
-	unique_ptr<FastLanesFacade> facade; // reader of files[current_file]
-	idx_t current_file = 0;
+	std::mutex lock;
+	idx_t current_file = 0; // file the next shard comes from
+	idx_t next_rowgroup = 0;
+	idx_t file_rowgroups = 0; // row groups of files[current_file]; 0 = not looked at yet
+	idx_t next_batch_index = 0;
+	idx_t shard_rowgroups = 8;
+	idx_t max_threads = 1;
 	vector<idx_t> projection; // file column id per output column
-	bool has_rowid_only = false;
-	idx_t rows_done = 0; // rows of the files already finished
+	std::atomic<idx_t> rows_done {0};
 	bool initialized = false;
 
 	idx_t MaxThreads() const override {
-		return 1;
+		return max_threads;
 	}
 };
 
-static bool OpenNext(FastLanesScanState &state, const FastLanesBindData &bind, string &err) {
-	while (state.current_file < bind.files.size()) {
-		auto facade = make_uniq<FastLanesFacade>();
-		const auto &path = bind.files[state.current_file];
-		if (!facade->openFile(path)) {
-			err = "Failed to open FastLanes file: " + path;
-			return false;
-		}
-		if (facade->getColumnTypes() != std::vector<LogicalType>(bind.return_types.begin(), bind.return_types.end())) {
-			err = "FastLanes file " + path + " does not have the schema of " + bind.files[0];
-			return false;
-		}
-		if (!state.projection.empty() && !facade->setProjection(state.projection)) {
+struct FastLanesLocalState : public LocalTableFunctionState {
+	unique_ptr<FastLanesFacade> facade;
+	idx_t file = DConstants::INVALID_INDEX; // index of the file `facade` has open
+	idx_t batch_index = 0;
+	idx_t thread_no = 0;
+	bool active = false; // a shard is being served
+};
+
+static bool OpenFile(FastLanesLocalState &local, const FastLanesScanState &state, const FastLanesBindData &bind, idx_t file,
+                     string &err) {
+	auto facade = make_uniq<FastLanesFacade>();
+	const auto &path = bind.files[file];
+	// several devices: every thread's reader starts its round-robin on another one
+	std::vector<int> devices = bind.devices;
+	if (devices.size() > 1) {
+		std::rotate(devices.begin(), devices.begin() + (local.thread_no % devices.size()), devices.end());
+	}
+	if (!facade->openFile(path, devices)) {
+		err = facade->lastError().empty() ? "Failed to open FastLanes file: " + path : facade->lastError();
+		return false;
+	}
+	if (facade->getColumnTypes() != std::vector<LogicalType>(bind.return_types.begin(), bind.return_types.end())) {
+		err = "FastLanes file " + path + " does not have the schema of " + bind.files[0];
+		return false;
+	}
+	if (facade->getColumnNames() != std::vector<std::string>(bind.return_names.begin(), bind.return_names.end())) {
+		err = "FastLanes file " + path + " does not have the column names of " + bind.files[0];
+		return false;
+	}
+	if (!state.projection.empty() && !facade->setProjection(state.projection)) {
+		err = facade->lastError();
+		return false;
+	}
+	if (!bind.zone_predicates.empty()) {
+		// late materialisation: the conjunction runs on the GPU, only the rows that pass come back
+		// (FLS_SCAN_NO_DEVICE_FILTER=1 keeps the row-group skipping alone, for A/B timing)
+		const char *off = getenv("FLS_SCAN_NO_DEVICE_FILTER");
+		if (!(off && *off == '1') && !facade->setDeviceFilter(bind.zone_predicates)) {
 			err = facade->lastError();
 			return false;
 		}
-		if (!bind.zone_predicates.empty()) {
-			facade->pruneRowGroups(bind.zone_predicates);
-			// late materialisation: the same conjunction runs on the GPU, only the rows that pass come back
-			// (FLS_SCAN_NO_DEVICE_FILTER=1 keeps the row-group skipping alone, for A/B timing)
-			const char *off = getenv("FLS_SCAN_NO_DEVICE_FILTER");
-			if (!(off && *off == '1') && !facade->setDeviceFilter(bind.zone_predicates)) {
-				err = facade->lastError();
+	}
+	local.facade = std::move(facade);
+	local.file = file;
+	return true;
+}
+
+// Aim the thread's reader at the next shard; false (and no error) at the end of the scan.
+static bool NextShard(FastLanesLocalState &local, FastLanesScanState &state, const FastLanesBindData &bind, string &err) {
+	for (;;) {
+		idx_t file, g0, g1;
+		{
+			std::lock_guard<std::mutex> guard(state.lock);
+			if (state.current_file >= bind.files.size()) {
 				return false;
 			}
+			file = state.current_file;
+			if (state.file_rowgroups == 0) { // first look at this file: any reader can tell its row-group count
+				if (local.file != file) {
+					if (!OpenFile(local, state, bind, file, err)) {
+						return false;
+					}
+				}
+				state.file_rowgroups = local.facade->rowGroupCount();
+				state.next_rowgroup = 0;
+				if (state.file_rowgroups == 0) { // an empty file
+					state.current_file++;
+					continue;
+				}
+			}
+			g0 = state.next_rowgroup;
+			g1 = MinValue<idx_t>(g0 + state.shard_rowgroups, state.file_rowgroups);
+			state.next_rowgroup = g1;
+			local.batch_index = state.next_batch_index++;
+			if (g1 >= state.file_rowgroups) {
+				state.current_file++;
+				state.file_rowgroups = 0;
+			}
 		}
-		state.facade = std::move(facade);
+		if (local.file != file && !OpenFile(local, state, bind, file, err)) {
+			return false;
+		}
+		if (!local.facade->setRowGroupRange(g0, g1)) {
+			err = local.facade->lastError();
+			return false;
+		}
+		local.active = true;
+		if (!bind.zone_predicates.empty()) {
+			local.facade->pruneRowGroups(bind.zone_predicates);
+		}
 		return true;
 	}
-	state.facade.reset();
-	return true;
 }
 
 static unique_ptr<FunctionData> FastLanesBind(ClientContext &context, TableFunctionBindInput &input,
@@ -116,6 +196,21 @@ static unique_ptr<FunctionData> FastLanesBind(ClientContext &context, TableFunct
 	} else {
 		throw BinderException("scan_fastlanes file path must be a string");
 	}
+	// `gpus := [0, 1]`: decode on several devices behind this one scan; `device := n`: on another device than 0
+	for (auto &kv : input.named_parameters) {
+		if (kv.first == "gpus") {
+			for (auto &v : ListValue::GetChildren(kv.second)) {
+				result->devices.push_back(v.GetValue<int32_t>());
+			}
+		} else if (kv.first == "device") {
+			result->devices.assign(1, kv.second.GetValue<int32_t>());
+		}
+	}
+	for (auto d : result->devices) {
+		if (d < 0) {
+			throw BinderException("scan_fastlanes: CUDA device ordinals are not negative");
+		}
+	}
 	// schema from the first file's footer; every file is opened once here so a bad path fails at bind, as in
 	// the reference — without decoding a single value
 	for (idx_t i = 0; i < result->files.size(); i++) {
@@ -132,6 +227,7 @@ static unique_ptr<FunctionData> FastLanesBind(ClientContext &context, TableFunct
 			}
 		}
 		result->total_rows += facade.rowCount();
+		result->total_rowgroups += facade.rowGroupCount();
 	}
 	return_types = result->return_types;
 	return_names = result->return_names;
@@ -145,7 +241,6 @@ static unique_ptr<GlobalTableFunctionState> FastLanesInitGlobal(ClientContext &c
 	// (count(*)) gets the row-id pseudo column only -> decode the narrowest thing we can: column 0
 	for (auto col : input.column_ids) {
 		if (IsRowIdColumnId(col)) {
-			result->has_rowid_only = true;
 			continue;
 		}
 		result->projection.push_back(col);
@@ -153,37 +248,67 @@ static unique_ptr<GlobalTableFunctionState> FastLanesInitGlobal(ClientContext &c
 	if (result->projection.empty()) {
 		result->projection.push_back(0);
 	}
-	string err;
-	if (!OpenNext(*result, bind_data, err)) {
-		throw IOException(err);
+	// at most 16 scanning threads (every thread holds a handle with its page-locked buffers) and about four shards per
+	// thread, each of 8 to 64 row groups: long enough to keep a reader's H2D / decode / D2H pipeline full, short enough
+	// to balance the threads
+	idx_t threads = MinValue<idx_t>(16, NumericCast<idx_t>(TaskScheduler::GetScheduler(context).NumberOfThreads()));
+	if (const char *e = getenv("FLS_SCAN_THREADS")) { // A/B timing: FLS_SCAN_THREADS=1 is the reference's single-threaded scan
+		threads = (idx_t)atoi(e);
 	}
+	threads = MaxValue<idx_t>(1, threads);
+	result->shard_rowgroups = MinValue<idx_t>(64, MaxValue<idx_t>(8, bind_data.total_rowgroups / (4 * threads)));
+	const idx_t shards = (bind_data.total_rowgroups + result->shard_rowgroups - 1) / result->shard_rowgroups;
+	result->max_threads = MaxValue<idx_t>(1, MinValue<idx_t>(threads, shards));
 	result->initialized = true;
+	return std::move(result);
+}
+
+static unique_ptr<LocalTableFunctionState> FastLanesInitLocal(ExecutionContext &context, TableFunctionInitInput &input,
+                                                              GlobalTableFunctionState *global_state) {
+	auto &state = global_state->Cast<FastLanesScanState>();
+	auto result = make_uniq<FastLanesLocalState>();
+	std::lock_guard<std::mutex> guard(state.lock);
+	static std::atomic<idx_t> thread_counter {0};
+	result->thread_no = thread_counter++;
 	return std::move(result);
 }
 
 static void FastLanesScan(ClientContext &context, TableFunctionInput &data_p, DataChunk &output) {
 	auto &state = data_p.global_state->Cast<FastLanesScanState>();
+	auto &local = data_p.local_state->Cast<FastLanesLocalState>();
 	auto &bind_data = data_p.bind_data->Cast<FastLanesBindData>();
 	if (!state.initialized) {
 		output.SetCardinality(0);
 		return;
 	}
-	while (state.facade) {
-		if (state.facade->readNextChunk(output)) {
-			return;
+	for (;;) {
+		if (local.active) {
+			if (local.facade->readNextChunk(output)) {
+				return;
+			}
+			if (!local.facade->lastError().empty()) {
+				throw IOException(local.facade->lastError());
+			}
+			// end of this shard
+			state.rows_done += local.facade->rowCount();
+			local.active = false;
 		}
-		if (!state.facade->lastError().empty()) {
-			throw IOException(state.facade->lastError());
-		}
-		// end of this file: move to the next one
-		state.rows_done += state.facade->rowsRead();
-		state.current_file++;
 		string err;
-		if (!OpenNext(state, bind_data, err)) {
-			throw IOException(err);
+		if (!NextShard(local, state, bind_data, err)) {
+			if (!err.empty()) {
+				throw IOException(err);
+			}
+			break;
 		}
 	}
 	output.SetCardinality(0);
+}
+
+static OperatorPartitionData FastLanesGetPartitionData(ClientContext &context, TableFunctionGetPartitionInput &input) {
+	if (input.partition_info.RequiresPartitionColumns()) {
+		throw InternalException("scan_fastlanes: partition columns are not supported");
+	}
+	return OperatorPartitionData(input.local_state->Cast<FastLanesLocalState>().batch_index);
 }
 
 static unique_ptr<NodeStatistics> FastLanesCardinality(ClientContext &context, const FunctionData *bind_data_p) {
@@ -198,8 +323,7 @@ static double FastLanesProgress(ClientContext &context, const FunctionData *bind
 	if (bind_data.total_rows == 0) {
 		return 100.0;
 	}
-	const idx_t done = state.rows_done + (state.facade ? state.facade->rowsRead() : 0);
-	return 100.0 * double(done) / double(bind_data.total_rows);
+	return MinValue(100.0, 100.0 * double(state.rows_done.load()) / double(bind_data.total_rows));
 }
 
 // `column <op> constant` (and `column BETWEEN a AND b`, which is what the optimizer makes of a two-sided range) with
@@ -312,8 +436,11 @@ static unique_ptr<TableRef> FastLanesReplacementScan(ClientContext &context, Rep
 
 void ScanFastLanes::Register(DatabaseInstance &db) {
 	for (auto name : {"scan_fastlanes", "read_fls"}) {
-		TableFunction fn(name, {LogicalType::VARCHAR}, FastLanesScan, FastLanesBind, FastLanesInitGlobal);
+		TableFunction fn(name, {LogicalType::VARCHAR}, FastLanesScan, FastLanesBind, FastLanesInitGlobal, FastLanesInitLocal);
+		fn.get_partition_data = FastLanesGetPartitionData;
 		fn.named_parameters["file"] = LogicalType::VARCHAR;
+		fn.named_parameters["gpus"] = LogicalType::LIST(LogicalType::INTEGER);
+		fn.named_parameters["device"] = LogicalType::INTEGER;
 		fn.projection_pushdown = true;
 		fn.cardinality = FastLanesCardinality;
 		fn.table_scan_progress = FastLanesProgress;

@@ -14,7 +14,7 @@ _ROOT = os.path.dirname(_HERE)
 _lib = None
 
 OK, E_IO, E_FORMAT, E_RANGE, E_CUDA, E_LIMIT, E_NOMEM = range(7)
-OPEN_PINNED_IMAGE, OPEN_NO_PIN, OPEN_TIME_KERNELS, OPEN_NO_PLAN_CACHE = 1, 2, 4, 8
+OPEN_PINNED_IMAGE, OPEN_NO_PIN, OPEN_TIME_KERNELS, OPEN_NO_PLAN_CACHE, OPEN_LOAD_FILE, OPEN_GDS = 1, 2, 4, 8, 16, 32
 OUT_DEVICE, OUT_HOST = 0, 1
 CMP = {"=": 0, "==": 0, "!=": 1, "<>": 1, "<": 2, "<=": 3, ">": 4, ">=": 5}
 
@@ -80,6 +80,8 @@ def lib():
     L.flsgpu_open_image.argtypes = [vp, u64, C.POINTER(Opts), C.POINTER(vp)]
     L.flsgpu_close.argtypes = [vp]
     L.flsgpu_close.restype = None
+    L.flsgpu_trim_cache.argtypes = []
+    L.flsgpu_trim_cache.restype = None
     L.flsgpu_last_error.argtypes = [vp]
     L.flsgpu_last_error.restype = C.c_char_p
     for f in ("flsgpu_num_columns", "flsgpu_num_rowgroups"):

@@ -57,6 +57,13 @@ enum flsgpu_type {
 #define FLSGPU_OPEN_PINNED_IMAGE 1u /* open_image: the caller's image is already page-locked */
 #define FLSGPU_OPEN_NO_PIN 2u       /* do not page-lock the image (H2D then goes through the driver's bounce buffer) */
 #define FLSGPU_OPEN_TIME_KERNELS 4u /* record a CUDA-event pair around every kernel launch (flsgpu_kernel_stats) */
+#define FLSGPU_OPEN_LOAD_FILE 16u /* flsgpu_open: read the whole file into page-locked memory at the first decode (the
+                                     round-1 behaviour) instead of mapping it and staging each pipeline slice through a
+                                     page-locked bounce buffer */
+#define FLSGPU_OPEN_GDS 32u       /* flsgpu_open: read each slice's compressed bytes straight from the file into HBM with
+                                     cuFile (GPUDirect Storage; SURVEY.md section 8f rank 4, no reference twin).  Fails
+                                     with FLSGPU_E_IO and the cuFile error text when libcufile or the driver is not
+                                     available — never silently falls back */
 #define FLSGPU_OPEN_NO_PLAN_CACHE 8u /* rebuild and re-upload the chunk descriptors on every decode (what the first
                                         scan of a range pays; bench.py reports it beside the cached figure) */
 
@@ -117,6 +124,10 @@ int flsgpu_open(const char *path, const flsgpu_opts *opts, flsgpu_t **out);
 /* The image must stay valid until flsgpu_close. */
 int flsgpu_open_image(const void *image, uint64_t size, const flsgpu_opts *opts, flsgpu_t **out);
 void flsgpu_close(flsgpu_t *h);
+/* Closed handles leave their pooled device and page-locked host buffers in a bounded process-wide cache for the next
+ * handle (a query = open + scan + close; FLSGPU_CACHE_HOST_MB / FLSGPU_CACHE_DEV_MB set the bounds, 0 = keep nothing).
+ * This frees the cache. */
+void flsgpu_trim_cache(void);
 /* Error text of the last failing call on `h`; with h == NULL, of the last failing open on this thread. */
 const char *flsgpu_last_error(const flsgpu_t *h);
 int flsgpu_abi_version(void);

@@ -99,3 +99,26 @@ def test_projection_and_rowgroup_range(small_table):
     assert out["digests"] == [expected_digest(ora, c, 1, 3) for c in (4, 0, 4)]
     rc, out = run_check(path, "--cols", "99")
     assert rc == 1 and "bad column" in out["error"]
+
+
+@pytest.mark.gpu
+def test_several_devices_behind_one_cursor_serve_the_same_rows_in_order(small_table):
+    """SURVEY.md section 8e / `gpus := [..]`: one handle and one decode in flight per listed device, batches dealt
+    round-robin and served in file order.  On a one-GPU box the device is listed twice (two lanes, two handles)."""
+    import flsgpu
+    path, ora, _ = small_table
+    want = [expected_digest(ora, c) for c in range(ora.n_cols)]
+    n_dev = 1
+    try:
+        import torch
+        n_dev = max(1, torch.cuda.device_count())
+    except Exception:
+        pass
+    lists = ["0,0", "0,0,0"] + (["0,1", ",".join(str(i) for i in range(n_dev))] if n_dev > 1 else [])
+    for gpus in lists:
+        for batch in ("1", "2"):
+            rc, out = run_check(path, "--gpus", gpus, "--batch", batch)
+            assert rc == 0 and out["rows"] == ora.n_rows, (gpus, out)
+            assert out["digests"] == want, gpus
+    rc, out = run_check(path, "--gpus", "0,99", "--batch", "1")   # the second batch goes to the device that does not exist
+    assert rc == 1 and "error" in out
