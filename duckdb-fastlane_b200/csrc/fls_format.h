@@ -59,6 +59,11 @@ enum fls_scheme {
   FLS_S_STR_FSST = 11,         // S dec end-offsets(DELTA u32) + S cmp end-offsets(DELTA u32) + B symtab + B bytes
   FLS_S_STR_FSST_DICT = 12,    // S idx + B dict_cmp_offsets(u32 x (n+1)) + B dict_cmp_bytes + B vec_ep + B symtab
                                //   + B dict_dec_offsets(u32 x (n+1))
+  FLS_S_FFOR_PATCH = 13,   // S   FFOR + exception list (FastLanes SLPATCH; with bw = 0 it is FREQUENCY: the base is the
+                           //     vector's most frequent value and every other value an exception)
+  FLS_S_CROSS_RLE = 14,    // B run values (aux32 x T) + B run ends (aux32 x u32, cumulative, in padded rows of the row
+                           //     group): runs span vectors
+  FLS_S_EQUAL = 15,        // the chunk equals column aux32's chunk of the same row group (no segments)
   FLS_S_N
 };
 
@@ -89,6 +94,7 @@ typedef struct {
 //   DELTA   : [lane bases 128 B = L x T/8][packed 128*bw]          (deltas are FFOR'd: + base)
 //   RLE     : [run values n x T/8, pad16][idx lane bases 64 x u16][idx packed 128*bw, bw in {0,1}]
 //   ALP     : [packed 128*bw][exc values n x f64, pad16][exc positions n x u16, pad16]
+//   FFOR_PATCH : [packed 128*bw][exc values n x T, pad16][exc positions n x u16, pad16]   (exception slots pack 0)
 //   ALP_RD  : [right packed 128*rbw][left packed 128*lbw][exc left n x u16, pad16][exc pos n x u16, pad16]
 
 // Unified transposed layout.

@@ -61,6 +61,52 @@ template <typename T> struct VecDICT {
                     (T *)k.out + (size_t)v * FLS_VEC);
   }
 };
+// FFOR + exception list (SLPATCH; FREQUENCY when bw = 0): FFOR, then the listed positions take their own values
+template <typename T> struct VecFFORPATCH {
+  static constexpr uint32_t SMEM = DecFFOR<T>::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    uint32_t bw = FLS_META_BW(h.meta);
+    if (bw > sizeof(T) * 8u) bw = (uint32_t)sizeof(T) * 8u;
+    const uint32_t n_exc = FLS_META_N(h.meta);
+    const uint8_t *in = k.seg[1] + 16ull * h.ep;
+    T *out = (T *)k.out + (size_t)v * FLS_VEC;
+    DecFFOR<T>::run(w, in, bw, h.base, out);
+    if (n_exc) {  // patches land after the region barrier of the decode, so they win over the unpacked values
+      const T *xv = (const T *)(in + 128ull * bw);
+      const uint16_t *xp = (const uint16_t *)(in + 128ull * bw + (((uint64_t)n_exc * sizeof(T) + 15u) & ~15ull));
+      FLS_LANES(t) {
+        for (uint32_t i = t; i < n_exc; i += 32u) out[fls_ldg(xp + i) & 1023u] = fls_ldg(xv + i);
+      }
+    }
+  }
+};
+// CROSS_RLE: seg[0] = run values (aux32 x T), seg[1] = cumulative run ends u32 (padded rows of the row group); the
+// run of position p is the first one whose end is > p (binary search; the ends are L1 / L2 resident)
+template <typename T> struct VecCROSSRLE {
+  static constexpr uint32_t SMEM = 16, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &, const uint8_t *) {
+    const T *vals = (const T *)k.seg[0];
+    const uint32_t *ends = (const uint32_t *)k.seg[1];
+    const uint32_t n = k.aux32;
+    T *out = (T *)k.out + (size_t)v * FLS_VEC;
+    FLS_LANES(t) {
+      // lane t owns the 32 consecutive positions 32 t .. 32 t + 31: one search, then a walk along the runs
+      const uint32_t p0 = v * FLS_VEC + 32u * t;
+      uint32_t lo = 0, hi = n ? n - 1u : 0u;
+      while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (fls_ldg(ends + mid) > p0) hi = mid; else lo = mid + 1u;
+      }
+      uint32_t r = lo, end = n ? fls_ldg(ends + r) : 0u;
+      T val = n ? fls_ldg(vals + r) : (T)0;
+      for (uint32_t j = 0; j < 32u; ++j) {
+        while (p0 + j >= end && r + 1u < n) { ++r; end = fls_ldg(ends + r); val = fls_ldg(vals + r); }
+        out[32u * t + j] = val;
+      }
+    }
+  }
+};
 struct VecALP {
   static constexpr uint32_t SMEM = DecALP::SMEM, BLOCK_SMEM = 0;
   FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {

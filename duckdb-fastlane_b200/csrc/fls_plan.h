@@ -21,6 +21,7 @@ enum FlsKernelKind {
   FLS_K_STR_FSST,
   FLS_K_STR_FSST_DICTPREP,  // decode an FSST-compressed dictionary into scratch
   FLS_K_VALIDITY,           // validity bitmap of a chunk (copied, or all ones) -> the column's bitmap
+  FLS_K_FFOR_PATCH, FLS_K_CROSS_RLE,
   FLS_K_N
 };
 
@@ -113,7 +114,13 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
   uint64_t row_base = 0, pay_base = out.pay_base0, scratch_off = 0;
   for (uint32_t g = g0; g < g1; ++g) {
     const fls_rowgroup &rg = t.rgs[g];
-    const fls_colchunk &k = t.chunk(g, col);
+    const fls_colchunk &k0 = t.chunk(g, col);
+    // EQUAL: the chunk is column aux32's chunk of this row group, decoded into this column's buffers
+    const bool eq = k0.scheme == FLS_S_EQUAL;
+    if (eq && (k0.aux32 >= t.n_cols || t.chunk(g, k0.aux32).scheme == FLS_S_EQUAL ||
+               fls_type_bits(t.types[k0.aux32]) != fls_type_bits(t.types[col]) || !wb))
+      return "EQUAL chunk does not name a fixed-width column of the same width";
+    const fls_colchunk &k = eq ? t.chunk(g, k0.aux32) : k0;
     FlsChunkDev d;
     memset(&d, 0, sizeof(d));
     const uint8_t *rgp = stage_base + (rg.off - t.rgs[g0].off);
@@ -138,17 +145,18 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
     if (wb) {
       const uint64_t wr = vals * wb;
       d.out = (uint8_t *)out.data + row_base * wb;
-      const bool is_dbl = t.types[col] == FLS_T_DOUBLE;
       switch (k.scheme) {
         case FLS_S_FFOR: fls_launch_for(ls, FLS_K_FFOR, wb).add(d, rd, wr); break;
         case FLS_S_DELTA: fls_launch_for(ls, FLS_K_DELTA, wb).add(d, rd, wr); break;
         case FLS_S_RLE: fls_launch_for(ls, FLS_K_RLE, wb).add(d, rd, wr); break;
+        case FLS_S_FFOR_PATCH: fls_launch_for(ls, FLS_K_FFOR_PATCH, wb).add(d, rd, wr); break;
+        case FLS_S_CROSS_RLE: fls_launch_for(ls, FLS_K_CROSS_RLE, wb).add(d, rd, wr); break;
         case FLS_S_DICT: fls_launch_for(ls, FLS_K_DICT, wb).add(d, rd, wr); break;
         case FLS_S_ALP:
-          if (!is_dbl) return "ALP on a non-double column";
+          if (!(t.types[eq ? k0.aux32 : col] == FLS_T_DOUBLE)) return "ALP on a non-double column";
           fls_launch_for(ls, FLS_K_ALP, wb).add(d, rd, wr); break;
         case FLS_S_ALP_RD:
-          if (!is_dbl) return "ALP_RD on a non-double column";
+          if (!(t.types[eq ? k0.aux32 : col] == FLS_T_DOUBLE)) return "ALP_RD on a non-double column";
           fls_launch_for(ls, FLS_K_ALPRD, wb).add(d, rd, wr); break;
         case FLS_S_UNCOMPRESSED:
           d.aux64[1] = (uint64_t)rg.n_vec * FLS_VEC * wb;

@@ -109,6 +109,26 @@ static inline std::string fls_validate_chunk(const FlsTable &t, uint32_t g, uint
         return true;
       });
       break;
+    case FLS_S_FFOR_PATCH:
+      if (!wb) return bad(g, c, "fixed-width scheme on a string column");
+      if (!need_segs(2)) return bad(g, c, "missing segments");
+      e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
+        const uint32_t n_exc = FLS_META_N(meta);
+        if (n_exc > FLS_VEC) return false;
+        b = 128ull * clamp(FLS_META_BW(meta), tb) + pad16((uint64_t)n_exc * wb) + pad16((uint64_t)n_exc * 2u);
+        return true;
+      });
+      break;
+    case FLS_S_CROSS_RLE:
+      if (!wb) return bad(g, c, "fixed-width scheme on a string column");
+      if (!need_segs(2) || k.aux32 == 0 || s[0].size < (uint64_t)k.aux32 * wb || s[1].size < 4ull * k.aux32)
+        return bad(g, c, "run segments shorter than their run count");
+      break;
+    case FLS_S_EQUAL:
+      if (!wb || k.aux32 >= t.n_cols || k.aux32 == c || t.chunk(g, k.aux32).scheme == FLS_S_EQUAL ||
+          fls_type_bits(t.types[k.aux32]) != tb)
+        return bad(g, c, "EQUAL chunk does not name a fixed-width column of the same width");
+      return fls_validate_chunk(t, g, k.aux32, image, image_size);
     case FLS_S_RLE:
       if (!wb) return bad(g, c, "fixed-width scheme on a string column");
       if (!need_segs(2)) return bad(g, c, "missing segments");

@@ -195,6 +195,70 @@ static bool enc_dict(const T *v, uint32_t n_vec, uint32_t max_dict, Chunk &c) {
   return true;
 }
 
+// FFOR_PATCH (SLPATCH / FREQUENCY): per vector the frame [lo, lo + 2^W) that makes 128 W + exceptions x (sizeof T + 2)
+// smallest; values outside the frame go to the exception list and pack as 0.
+template <typename T>
+static Chunk enc_ffor_patch(const T *v, uint32_t n_vec) {
+  Chunk c; c.scheme = FLS_S_FFOR_PATCH;
+  Stream s;
+  constexpr uint32_t TB = sizeof(T) * 8;
+  for (uint32_t i = 0; i < n_vec; ++i) {
+    const T *x = v + i * FLS_VEC;
+    std::vector<T> srt(x, x + FLS_VEC);
+    std::sort(srt.begin(), srt.end());
+    uint64_t best_cost = ~0ull;
+    uint32_t best_w = TB;
+    T best_lo = srt[0];
+    for (uint32_t W = 0; W <= TB; ++W) {
+      // widest coverage of a window of 2^W consecutive values over the sorted vector (two pointers)
+      uint32_t cover = 0, at = 0;
+      for (uint32_t a = 0, b = 0; a < FLS_VEC; ++a) {
+        if (b < a) b = a;
+        while (b < FLS_VEC && (W >= TB || (T)(srt[b] - srt[a]) <= (T)(((T)1 << W) - 1))) ++b;
+        if (b - a > cover) { cover = b - a; at = a; }
+        if (b == FLS_VEC) break;
+      }
+      const uint64_t cost = 128ull * W + (uint64_t)(FLS_VEC - cover) * (sizeof(T) + 2);
+      if (cost < best_cost) { best_cost = cost; best_w = W; best_lo = srt[at]; }
+    }
+    T tmp[FLS_VEC];
+    std::vector<T> xv;
+    std::vector<uint16_t> xp;
+    for (uint32_t j = 0; j < FLS_VEC; ++j) {
+      const T d = (T)(x[j] - best_lo);
+      const bool in = best_w >= TB || d <= (T)(((T)1 << best_w) - 1);
+      tmp[j] = in ? d : (T)0;
+      if (!in) { xv.push_back(x[j]); xp.push_back((uint16_t)j); }
+    }
+    s.begin_vec(FLS_META(best_w, 0, 0, xv.size()), (uint64_t)best_lo);
+    append_packed<T>(s.data, tmp, best_w);
+    put_bytes(s.data, xv.data(), xv.size() * sizeof(T)); pad_to(s.data, 16);
+    put_bytes(s.data, xp.data(), xp.size() * 2); pad_to(s.data, 16);
+  }
+  s.move_into(c);
+  return c;
+}
+
+// CROSS_RLE: runs over the whole row group (they span vectors): values + cumulative ends.
+template <typename T>
+static Chunk enc_cross_rle(const T *v, uint32_t n_vec) {
+  Chunk c; c.scheme = FLS_S_CROSS_RLE;
+  const size_t n = (size_t)n_vec * FLS_VEC;
+  std::vector<T> vals;
+  std::vector<uint32_t> ends;
+  for (size_t i = 0; i < n; ++i) {
+    if (i == 0 || v[i] != v[i - 1]) { if (i) ends.push_back((uint32_t)i); vals.push_back(v[i]); }
+  }
+  ends.push_back((uint32_t)n);
+  c.aux32 = (uint32_t)vals.size();
+  Bytes a, b;
+  put_bytes(a, vals.data(), vals.size() * sizeof(T));
+  put_bytes(b, ends.data(), ends.size() * 4);
+  c.segs.push_back(std::move(a));
+  c.segs.push_back(std::move(b));
+  return c;
+}
+
 template <typename T>
 static Chunk enc_uncompressed(const T *v, uint32_t n_vec) {
   Chunk c; c.scheme = FLS_S_UNCOMPRESSED;
@@ -221,8 +285,13 @@ static Chunk enc_int_auto(const T *v, uint32_t n_vec, int force, int force_bw) {
   if (force == FLS_S_RLE) return enc_rle<T>(v, n_vec);
   if (force == FLS_S_DICT) { if (enc_dict<T>(v, n_vec, 1u << 20, c)) return c; return enc_ffor<T>(v, n_vec, -1); }
   if (force == FLS_S_CONSTANT) { if (enc_constant<T>(v, n_vec, c)) return c; return enc_ffor<T>(v, n_vec, -1); }
+  if (force == FLS_S_FFOR_PATCH) return enc_ffor_patch<T>(v, n_vec);
+  if (force == FLS_S_CROSS_RLE) return enc_cross_rle<T>(v, n_vec);
   if (enc_constant<T>(v, n_vec, c)) return c;
   Chunk best = enc_ffor<T>(v, n_vec, -1);
+  // (the exception list and row-group-wide runs are taken only when they pay clearly: their decoders do more work per value)
+  { Chunk p = enc_ffor_patch<T>(v, n_vec); if (p.bytes() + p.bytes() / 4 < best.bytes()) best = std::move(p); }
+  { Chunk r = enc_cross_rle<T>(v, n_vec); if (2 * r.bytes() < best.bytes()) best = std::move(r); }
   { Chunk d = enc_delta<T>(v, n_vec); if (d.bytes() < best.bytes()) best = std::move(d); }
   { Chunk r = enc_rle<T>(v, n_vec); if (r.bytes() < best.bytes()) best = std::move(r); }
   { Chunk d; if (enc_dict<T>(v, n_vec, 4096, d) && d.bytes() < best.bytes()) best = std::move(d); }
@@ -710,6 +779,7 @@ struct Writer {
   uint64_t n_rows = 0;
   bool last_partial = false, finished = false;
   std::string err;
+  std::vector<int> rg_schemes;                   // schemes chosen for the columns of the row group being appended
   std::map<uint32_t, FsstInject> inject_fsst;    // column -> streams for its next row group (test knobs)
   std::map<uint32_t, AlprdInject> inject_alprd;
 };
@@ -742,6 +812,7 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
   pad_to(w.file, FLS_RG_ALIGN);
   uint64_t rg_off = w.file.size();
   Bytes cc;  // column-chunk records
+  w.rg_schemes.clear();
   for (size_t c = 0; c < w.types.size(); ++c) {
     Chunk ch;
     int t = w.types[c], f = w.force[c];
@@ -756,11 +827,22 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
     FsstInject fi; AlprdInject ai;
     if (w.inject_fsst.count((uint32_t)c)) { fi = w.inject_fsst[(uint32_t)c]; w.inject_fsst.erase((uint32_t)c); tl_fsst_inject = &fi; f = FLS_S_STR_FSST; }
     if (w.inject_alprd.count((uint32_t)c)) { ai = w.inject_alprd[(uint32_t)c]; w.inject_alprd.erase((uint32_t)c); tl_alprd_inject = &ai; f = FLS_S_ALP_RD; }
+    // EQUAL: a fixed-width column whose values (and NULLs) repeat an earlier column of the same type in this row group
+    int equal_to = -1;
+    if (fls_type_bits(t) && (f < 0 || f == FLS_S_EQUAL) && !vb)
+      for (size_t e = 0; e < c && equal_to < 0; ++e)
+        if (w.types[e] == t && !(validity && validity[e]) &&
+            memcmp(col_data[e], col_data[c], (size_t)n_rows * fls_type_bits(t) / 8) == 0)
+          equal_to = (int)e;
+    if (equal_to >= 0 && w.rg_schemes.size() > (size_t)equal_to && w.rg_schemes[equal_to] != FLS_S_EQUAL) {
+      ch.scheme = FLS_S_EQUAL;
+      ch.aux32 = (uint32_t)equal_to;
+    } else
     switch (fls_type_bits(t)) {
-      case 8: ch = enc_fixed<uint8_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false, vb); break;
-      case 16: ch = enc_fixed<uint16_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false, vb); break;
-      case 32: ch = enc_fixed<uint32_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], false, vb); break;
-      case 64: ch = enc_fixed<uint64_t>(col_data[c], n_rows, n_vec, f, w.force_bw[c], t == FLS_T_DOUBLE, vb); break;
+      case 8: ch = enc_fixed<uint8_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], false, vb); break;
+      case 16: ch = enc_fixed<uint16_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], false, vb); break;
+      case 32: ch = enc_fixed<uint32_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], false, vb); break;
+      case 64: ch = enc_fixed<uint64_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], t == FLS_T_DOUBLE, vb); break;
       default: {
         if (t != FLS_T_STR && t != FLS_T_BYTE_ARRAY) { w.err = "unsupported column type"; return 1; }
         std::vector<uint64_t> off((size_t)n_vec * FLS_VEC + 1);
@@ -777,6 +859,7 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
       ch.segs.push_back(std::move(bm));
     }
     if (ch.segs.size() > FLS_MAX_SEGS) { w.err = "internal: too many segments"; return 1; }
+    w.rg_schemes.push_back(ch.scheme);
     put<uint8_t>(cc, ch.scheme); put<uint8_t>(cc, (uint8_t)ch.segs.size()); put<uint16_t>(cc, vb ? FLS_CHUNK_VALIDITY : 0);
     put<uint32_t>(cc, ch.aux32); put<uint64_t>(cc, ch.aux64[0]); put<uint64_t>(cc, ch.aux64[1]);
     for (auto &sg : ch.segs) {

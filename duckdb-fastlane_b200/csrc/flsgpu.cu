@@ -77,6 +77,8 @@ cudaError_t set_kernel_attrs() {
   if ((e = vec_attr_all<VecDELTA>()) != cudaSuccess) return e;
   if ((e = vec_attr_all<VecRLE>()) != cudaSuccess) return e;
   if ((e = vec_attr_all<VecDICT>()) != cudaSuccess) return e;
+  if ((e = vec_attr_all<VecFFORPATCH>()) != cudaSuccess) return e;
+  if ((e = vec_attr_all<VecCROSSRLE>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecALP>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecALPRD>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecSTROFFS>()) != cudaSuccess) return e;
@@ -87,7 +89,7 @@ cudaError_t set_kernel_attrs() {
 
 const char *const kKindName[FLS_K_N] = {"ffor",     "delta",     "rle",      "dict",     "alp",  "alp_rd", "copy",
                                         "fill",     "str_offsets", "str_copy", "str_const", "str_dict", "str_fsst",
-                                        "fsst_dictprep", "validity"};
+                                        "fsst_dictprep", "validity", "ffor_patch", "cross_rle"};
 
 struct LaunchRec {  // what is needed to (re)issue one launch once its descriptors are on the device
   int kind, width;
@@ -104,6 +106,8 @@ bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
     case FLS_K_DELTA: return vec_launch_w<VecDELTA>(l.width, d, n, s);
     case FLS_K_RLE: return vec_launch_w<VecRLE>(l.width, d, n, s);
     case FLS_K_DICT: return vec_launch_w<VecDICT>(l.width, d, n, s);
+    case FLS_K_FFOR_PATCH: return vec_launch_w<VecFFORPATCH>(l.width, d, n, s);
+    case FLS_K_CROSS_RLE: return vec_launch_w<VecCROSSRLE>(l.width, d, n, s);
     case FLS_K_ALP: vec_launch<VecALP>(d, n, s); return true;
     case FLS_K_ALPRD: vec_launch<VecALPRD>(d, n, s); return true;
     case FLS_K_COPY: fls_copy_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;
@@ -469,6 +473,11 @@ int width_slot(int width) { return width == 1 ? 1 : width == 2 ? 2 : width == 4 
 extern "C" {
 
 int flsgpu_abi_version(void) { return FLSGPU_ABI_VERSION; }
+int flsgpu_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
 
 int flsgpu_open(const char *path, const flsgpu_opts *opts, flsgpu_t **out) {
   if (!out || !path) { g_open_err = "null argument"; return FLSGPU_E_RANGE; }
@@ -792,7 +801,15 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       if (to_host && !(o.validity = (uint64_t *)halloc(n.validity_bytes + 16))) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
     }
   }
-  if (g1 == g0) { *out = b; return FLSGPU_OK; }
+  if (g1 == g0) {  // an empty range: nothing to decode, but offsets[0] of a string column is still 0
+    for (uint32_t i = 0; i < nc; ++i) {
+      if (!b->dev[i].offsets) continue;
+      CKB(cudaMemset(b->dev[i].offsets, 0, 4));
+      if (to_host) b->out[i].offsets[0] = 0;
+    }
+    *out = b;
+    return FLSGPU_OK;
+  }
 
   // ---- compressed bytes: resident, or staged slice by slice
   const bool resident = h->d_res && g0 >= h->res_g0 && g1 <= h->res_g1;

@@ -135,6 +135,14 @@ bool FlsScanner::open(const std::string &path, int device, uint32_t batch_rowgro
 
 bool FlsScanner::open(const std::string &path, const std::vector<int> &devices, uint32_t batch_rowgroups) {
   close();
+  if (devices.size() > 1 || (devices.size() == 1 && devices[0] != 0)) {  // named devices must exist (the default, device 0,
+    const int n = flsgpu_device_count();                                  // is left to the first decode: bind needs no GPU)
+    for (int d : devices)
+      if (d < 0 || d >= n) {
+        p->err = "CUDA device " + std::to_string(d) + " does not exist (" + std::to_string(n) + " visible)";
+        return false;
+      }
+  }
   for (int device : devices.empty() ? std::vector<int>(1, 0) : devices) {
     flsgpu_opts o = {};
     o.device = device;

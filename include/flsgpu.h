@@ -131,6 +131,8 @@ void flsgpu_trim_cache(void);
 /* Error text of the last failing call on `h`; with h == NULL, of the last failing open on this thread. */
 const char *flsgpu_last_error(const flsgpu_t *h);
 int flsgpu_abi_version(void);
+/* CUDA devices visible to the process (0 when there is none or no driver). */
+int flsgpu_device_count(void);
 
 /* ---- schema ------------------------------------------------------------------------------------------- */
 uint32_t flsgpu_num_columns(const flsgpu_t *h);

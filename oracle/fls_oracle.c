@@ -28,7 +28,8 @@
 
 enum { T_BOOL = 1, T_I8, T_I16, T_I32, T_I64, T_U8, T_U16, T_U32, T_U64, T_FLT, T_DBL, T_STR, T_DATE, T_BYTES };
 enum { S_UNCOMP = 0, S_CONST, S_FFOR, S_DELTA, S_RLE, S_DICT, S_ALP, S_ALPRD,
-       S_STR_UNCOMP, S_STR_CONST, S_STR_DICT, S_STR_FSST, S_STR_FSST_DICT };
+       S_STR_UNCOMP, S_STR_CONST, S_STR_DICT, S_STR_FSST, S_STR_FSST_DICT,
+       S_FFOR_PATCH, S_CROSS_RLE, S_EQUAL };
 
 static const uint8_t ORDER[8] = {0, 4, 2, 6, 1, 5, 3, 7};
 
@@ -199,6 +200,25 @@ typedef struct { uint32_t ep, meta; uint64_t base; } ovhdr;
           for (unsigned i = 0; i < O_VEC; ++i) out[v * O_VEC + i] = runs[idx[i]];                         \
         }                                                                                                 \
         return 0;                                                                                         \
+      case S_FFOR_PATCH: /* SLPATCH / FREQUENCY: unffor, then the exception list overwrites */ \
+        for (uint32_t v = 0; v < n_vec; ++v) {                                                            \
+          const uint8_t *p = data + 16ull * h[v].ep;                                                      \
+          const uint32_t bw = M_BW(h[v].meta), nx = M_N(h[v].meta);                                       \
+          unffor_##TB((const T *)p, bw, (T)h[v].base, out + v * O_VEC);                                   \
+          const T *xv = (const T *)(p + 128ull * bw);                                                     \
+          const uint16_t *xp = (const uint16_t *)(p + 128ull * bw + PAD16((uint64_t)nx * sizeof(T)));     \
+          for (uint32_t i = 0; i < nx; ++i) out[v * O_VEC + (xp[i] & 1023u)] = xv[i];                     \
+        }                                                                                                 \
+        return 0;                                                                                         \
+      case S_CROSS_RLE: { /* runs over the whole row group: values + cumulative ends */                   \
+        const T *vals = (const T *)(rgp + k->seg[0].off);                                                 \
+        const uint32_t *ends = (const uint32_t *)(rgp + k->seg[1].off);                                   \
+        size_t at = 0, n = (size_t)n_vec * O_VEC;                                                         \
+        for (uint32_t r = 0; r < k->aux32 && at < n; ++r)                                                 \
+          for (; at < ends[r] && at < n; ++at) out[at] = vals[r];                                         \
+        for (; at < n; ++at) out[at] = k->aux32 ? vals[k->aux32 - 1] : (T)0;                              \
+        return 0;                                                                                         \
+      }                                                                                                   \
       case S_DICT: {                                                                                      \
         const T *dict = (const T *)(rgp + k->seg[2].off);                                                 \
         uint32_t idx[O_VEC];                                                                              \
@@ -438,6 +458,10 @@ static int decode_fixed_rg(const flso_table *t, uint32_t c, uint32_t g, void *ds
   const org *r = &t->rg[g];
   const ochunk *k = &r->cols[c];
   const uint8_t *rgp = t->img + r->off;
+  if (k->scheme == S_EQUAL) { /* the chunk equals another column's chunk of the same row group */
+    if (k->aux32 >= t->n_cols || r->cols[k->aux32].scheme == S_EQUAL || type_bits(t->types[k->aux32]) != type_bits(t->types[c])) return 13;
+    k = &r->cols[k->aux32];
+  }
   if (k->scheme == S_ALP) return chunk_alp(rgp, k, r->n_vec, (double *)dst);
   if (k->scheme == S_ALPRD) return chunk_alprd(rgp, k, r->n_vec, (uint64_t *)dst);
   switch (type_bits(t->types[c])) {

@@ -102,6 +102,36 @@ def misc_fixed_cases(n=70_000):
     return out
 
 
+def variant_cases(n=70_000):
+    """FFOR_PATCH (FastLanes SLPATCH; FREQUENCY when the frame is one value), CROSS_RLE and EQUAL."""
+    r = rng(15)
+    out = []
+    for bits in (8, 16, 32, 64):
+        dt = INT_DTYPES[bits]
+        v = r.integers(0, 50, n).astype(np.int64)
+        pos = r.integers(0, n, n // 100)
+        v[pos] = r.integers(-2 ** (bits - 1), 2 ** (bits - 1) - 1, len(pos), dtype=np.int64)     # 1 % outliers, full width
+        out.append(("slpatch_i%d" % bits, [v.astype(dt)], None, [W.FFOR_PATCH], None))
+        f = np.full(n, -7, dtype=np.int64)
+        pos = r.integers(0, n, n // 50)
+        f[pos] = r.integers(0, 100, len(pos))                                                       # one frequent value
+        out.append(("frequency_i%d" % bits, [f.astype(dt)], None, [W.FFOR_PATCH], None))
+        runs = r.integers(1, 9000, 64)
+        vals = r.integers(-100, 100, len(runs))
+        c = np.repeat(vals, runs)[:n]
+        c = np.concatenate([c, np.full(max(0, n - len(c)), 3)])
+        out.append(("cross_rle_i%d" % bits, [c.astype(dt)], None, [W.CROSS_RLE], None))
+    out.append(("slpatch_auto_pick", [np.where(r.random(n) < 0.002, 2 ** 40, r.integers(0, 9, n)).astype(np.int64)], None, None, None))
+    out.append(("cross_rle_single_run", [np.full(n, 9, dtype=np.int32)], None, [W.CROSS_RLE], None))
+    out.append(("cross_rle_f64", [np.repeat(r.normal(size=40), 2000)[:n]], None, [W.CROSS_RLE], None))
+    out.append(("slpatch_all_exceptions_w0", [r.integers(-2 ** 62, 2 ** 62, 2048).astype(np.int64)], None, [W.FFOR_PATCH], None))
+    a = r.integers(0, 1000, n).astype(np.int32)
+    d = np.round(r.uniform(0, 100, n), 2)
+    out.append(("equal_columns", [a, d, a.copy(), d.copy(), a.copy()], None, None, None))
+    out.append(("equal_first_column_has_no_twin", [a, a.copy()], None, None, None))
+    return out
+
+
 SPECIALS = np.array([np.nan, np.inf, -np.inf, -0.0, 1e300, 0.1 + 0.2, 5e-324, -1e-310, 1.7976931348623157e308])
 
 
@@ -200,7 +230,7 @@ def string_cases(n=70_000):
 
 
 def all_cases():
-    return (all_ffor_cases() + delta_cases() + rle_cases() + dict_cases() + misc_fixed_cases() + alp_cases() +
+    return (all_ffor_cases() + delta_cases() + rle_cases() + dict_cases() + misc_fixed_cases() + variant_cases() + alp_cases() +
             string_cases())
 
 

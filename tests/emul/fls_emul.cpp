@@ -68,6 +68,8 @@ static bool run_launch(const FlsLaunch &l) {
     case FLS_K_DELTA: return run_by_width<VecDELTA>(l);
     case FLS_K_RLE: return run_by_width<VecRLE>(l);
     case FLS_K_DICT: return run_by_width<VecDICT>(l);
+    case FLS_K_FFOR_PATCH: return run_by_width<VecFFORPATCH>(l);
+    case FLS_K_CROSS_RLE: return run_by_width<VecCROSSRLE>(l);
     case FLS_K_ALP: run_vectors<VecALP>(l); return true;
     case FLS_K_ALPRD: run_vectors<VecALPRD>(l); return true;
     case FLS_K_COPY:
