@@ -593,7 +593,11 @@ int flsgpu_rowgroup_minmax(flsgpu_t *h, uint32_t rg, uint32_t col, int64_t *mn, 
   const bool is_signed = type == FLS_T_INT8 || type == FLS_T_INT16 || type == FLS_T_INT32 || type == FLS_T_INT64 || type == FLS_T_DATE;
   const bool is_unsigned = type == FLS_T_UINT8 || type == FLS_T_UINT16 || type == FLS_T_UINT32 || type == FLS_T_UINT64 || type == FLS_T_BOOLEAN;
   if (!tb || !(is_signed || is_unsigned)) return FLSGPU_OK;
-  const fls_colchunk &k = h->t.chunk(rg, col);
+  const fls_colchunk &k0 = h->t.chunk(rg, col);
+  // EQUAL: the bounds of the chunk it repeats (same width; read in this column's own signedness)
+  const bool alias = k0.scheme == FLS_S_EQUAL && k0.aux32 < h->t.n_cols && h->t.chunk(rg, k0.aux32).scheme != FLS_S_EQUAL &&
+                     fls_type_bits(h->t.types[k0.aux32]) == tb;
+  const fls_colchunk &k = alias ? h->t.chunk(rg, k0.aux32) : k0;
   const fls_rowgroup &r = h->t.rgs[rg];
   const uint64_t tmask = tb == 64 ? ~0ull : ((1ull << tb) - 1ull);
   auto as_i64 = [&](uint64_t v, int64_t *o) {  // value of the column's type -> int64; false if it does not fit
@@ -608,8 +612,7 @@ int flsgpu_rowgroup_minmax(flsgpu_t *h, uint32_t rg, uint32_t col, int64_t *mn, 
     *mn = *mx = v; *known = 1;
     return FLSGPU_OK;
   }
-  const bool delta = k.scheme == FLS_S_DELTA;
-  if ((k.scheme != FLS_S_FFOR && !delta) || k.n_seg < 2 || k.seg[0].size < 16ull * r.n_vec) return FLSGPU_OK;
+  const bool delta = k.scheme == FLS_S_DELTA, patch = k.scheme == FLS_S_FFOR_PATCH;
   int fd = -1;
   auto read_at = [&](uint64_t off, void *dst, size_t n) {  // bytes of the file: the host image, or the file itself
     if (h->image) { memcpy(dst, h->image + off, n); return true; }
@@ -617,6 +620,23 @@ int flsgpu_rowgroup_minmax(flsgpu_t *h, uint32_t rg, uint32_t col, int64_t *mn, 
     return fd >= 0 && pread(fd, dst, n, (off_t)off) == (ssize_t)n;
   };
   struct Closer { int &fd; ~Closer() { if (fd >= 0) close(fd); } } closer{fd};
+  if (k.scheme == FLS_S_CROSS_RLE) {  // the run values are the column's distinct neighbours: their min / max are exact
+    const uint64_t n = k.aux32;
+    if (k.n_seg < 2 || !n || n > (1u << 22) || k.seg[0].size < n * (tb / 8)) return FLSGPU_OK;
+    std::vector<uint8_t> vals(n * (tb / 8));
+    if (!read_at(r.off + k.seg[0].off, vals.data(), vals.size())) return h->fail(FLSGPU_E_IO, "cannot read the run values");
+    int64_t lo = INT64_MAX, hi = INT64_MIN;
+    for (uint64_t i = 0; i < n; ++i) {
+      uint64_t b = 0;
+      memcpy(&b, vals.data() + i * (tb / 8), tb / 8);
+      int64_t a;
+      if (!as_i64(b, &a)) return FLSGPU_OK;
+      lo = std::min(lo, a); hi = std::max(hi, a);
+    }
+    *mn = lo; *mx = hi; *known = 1;
+    return FLSGPU_OK;
+  }
+  if ((k.scheme != FLS_S_FFOR && !delta && !patch) || k.n_seg < 2 || k.seg[0].size < 16ull * r.n_vec) return FLSGPU_OK;
   std::vector<uint64_t> hdr(2ull * r.n_vec);
   if (!read_at(r.off + k.seg[0].off, hdr.data(), hdr.size() * 8)) return h->fail(FLSGPU_E_IO, "cannot read vector headers");
   const int64_t tmax = is_signed ? (tb == 64 ? INT64_MAX : (int64_t)((1ull << (tb - 1)) - 1)) : (tb == 64 ? INT64_MAX : (int64_t)tmask);
@@ -632,6 +652,20 @@ int flsgpu_rowgroup_minmax(flsgpu_t *h, uint32_t rg, uint32_t col, int64_t *mn, 
       if (!as_i64(base, &a)) return FLSGPU_OK;
       lo = std::min<__int128>(lo, a);
       hi = std::max<__int128>(hi, (__int128)a + span);
+      if (patch) {  // ... and the exception values, wherever they lie
+        const uint32_t ep = (uint32_t)hdr[2 * v], nx = FLS_META_N((uint32_t)(hdr[2 * v] >> 32));
+        const uint64_t at = 16ull * ep + 128ull * bw, nb = (uint64_t)nx * (tb / 8);
+        if (nx > FLS_VEC || k.seg[1].size < at + nb) return FLSGPU_OK;
+        std::vector<uint8_t> xv(nb);
+        if (nb && !read_at(r.off + k.seg[1].off + at, xv.data(), nb)) return FLSGPU_OK;
+        for (uint32_t i = 0; i < nx; ++i) {
+          uint64_t b = 0;
+          memcpy(&b, xv.data() + (size_t)i * (tb / 8), tb / 8);
+          int64_t x;
+          if (!as_i64(b, &x)) return FLSGPU_OK;
+          lo = std::min<__int128>(lo, x); hi = std::max<__int128>(hi, x);
+        }
+      }
     } else {
       // DELTA: element r (1..T) of a lane = lane base + r deltas, every delta in [dmin, dmin + span] (signed)
       const uint32_t ep = (uint32_t)hdr[2 * v];

@@ -146,3 +146,27 @@ def test_rowgroup_dict_contains_without_a_gpu():
         assert rd.rowgroup_dict_contains(2, 1, b"MAIL") is True and rd.rowgroup_dict_contains(2, 1, b"AIR") is False
         assert rd.rowgroup_dict_contains(2, 1, b"") is False
         assert rd.chunk_info(0, 2)[0] == W.STR_FSST and rd.rowgroup_dict_contains(0, 2, b"x") is None
+
+
+def test_rowgroup_minmax_of_patched_run_length_and_aliased_chunks():
+    """Zone maps of the operator variants: FFOR_PATCH = the frame plus the exception values, CROSS_RLE = min / max of the
+    run values (exact), EQUAL = the bounds of the chunk it repeats."""
+    import numpy as np
+    import flsgpu
+    import fls_writer as W
+    r = np.random.default_rng(8)
+    n = 70_000
+    p = r.integers(100, 150, n).astype(np.int64)
+    p[r.integers(0, n, 300)] = -(2 ** 40)
+    p[r.integers(0, n, 300)] = 2 ** 41
+    runs = np.repeat(r.integers(-500, 500, 200), 400)[:n].astype(np.int32)
+    img = W.write_table([p, runs, p.copy()], force=[W.FFOR_PATCH, W.CROSS_RLE, None])
+    with flsgpu.Reader.from_image(img) as rd:
+        assert [rd.chunk_info(0, c)[0] for c in range(3)] == [W.FFOR_PATCH, W.CROSS_RLE, W.EQUAL]
+        for g in range(rd.n_rowgroups):
+            sl = slice(g * 65536, (g + 1) * 65536)
+            for c, src in enumerate((p, runs, p)):
+                b = rd.rowgroup_minmax(g, c)
+                assert b is not None and b[0] <= src[sl].min() and src[sl].max() <= b[1], (g, c, b)
+            assert rd.rowgroup_minmax(g, 1) == (int(runs[sl].min()), int(runs[sl].max()))
+            assert rd.rowgroup_minmax(g, 2) == rd.rowgroup_minmax(g, 0)
