@@ -10,6 +10,7 @@
 //   duckdb_sql_check "SELECT count(*) FROM read_fls('x.fls')" ["SELECT ..."]...
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 
 #include "duckdb.hpp"
@@ -38,10 +39,25 @@ static std::string esc(const std::string &s) {
 }
 
 int main(int argc, char **argv) {
-	duckdb::DuckDB db(nullptr);
-	duckdb::ScanFastLanes::Register(*db.instance);
-	duckdb::ext_fastlane::RegisterFastlaneStreamCopyFunction(*db.instance);
+	// FLS_SQL_CHECK_LOAD=<path of fastlane.duckdb_extension>: nothing is registered statically, the functions come from
+	// LOAD '<path>' (an unsigned extension), i.e. through DuckDB's own extension loader
+	const char *load = getenv("FLS_SQL_CHECK_LOAD");
+	duckdb::DBConfig config;
+	if (load) {
+		config.options.allow_unsigned_extensions = true;
+	}
+	duckdb::DuckDB db(nullptr, &config);
 	duckdb::Connection con(db);
+	if (load) {
+		auto res = con.Query(std::string("LOAD '") + load + "'");
+		if (res->HasError()) {
+			printf("{\"sql\": \"LOAD\", \"error\": \"%s\"}\n", esc(res->GetError()).c_str());
+			return 1;
+		}
+	} else {
+		duckdb::ScanFastLanes::Register(*db.instance);
+		duckdb::ext_fastlane::RegisterFastlaneStreamCopyFunction(*db.instance);
+	}
 	int rc = 0;
 	for (int i = 1; i < argc; i++) {
 		fprintf(stderr, "sql_check: statement %d\n", i - 1);

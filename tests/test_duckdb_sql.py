@@ -344,3 +344,41 @@ def test_gpus_and_device_named_parameters(tmp_path):
     assert "error" not in res[0] and same_rows(res[0]["rows"], res[1]["rows"]) and same_rows(res[0]["rows"], res[2]["rows"]), res[:3]
     assert [r[0] for r in res[3]["rows"]] == ["1", "50001", "100001", "150001"]
     assert "error" in res[4] and "error" in res[5]
+
+
+# ------------------------------------------------------------------------------------------- the loadable extension
+# fastlane.duckdb_extension (reference: CMakeLists.txt:32-33 build_loadable_extension): here the functions are NOT
+# registered by the check driver — DuckDB's own loader opens the file, checks its metadata footer and calls fastlane_init.
+EXTENSION = os.path.join(EXT, "fastlane.duckdb_extension")
+needs_extension = pytest.mark.skipif(not os.path.exists(EXTENSION), reason="ext/fastlane.duckdb_extension not built")
+
+
+@needs_extension
+def test_load_extension_registers_the_functions(tmp_path):
+    cols, names = synth.basic_usage(3000, seed=1)
+    path = str(tmp_path / "b.fls")
+    synth.encode(cols, names, types=synth.basic_usage_types(), path=path)
+    res = sql("SELECT extension_name, loaded, extension_version FROM duckdb_extensions() WHERE extension_name = 'fastlane'",
+              "SELECT * FROM scan_fastlanes('nonexistent.fls') LIMIT 0",                 # fastlane.test:9-12
+              "DESCRIBE SELECT * FROM read_fls('%s')" % path,
+              "COPY (SELECT 42 AS a) TO '%s' (FORMAT FLS)" % str(tmp_path / "x.fls"),
+              env_extra={"FLS_SQL_CHECK_LOAD": EXTENSION})
+    assert res[0]["rows"] == [["fastlane", "true", "b200-r02"]]
+    assert "Failed to open FastLanes file: nonexistent.fls" in res[1]["error"]
+    assert [r[1] for r in res[2]["rows"]] == ["INTEGER", "BIGINT", "DOUBLE", "DOUBLE", "VARCHAR", "BOOLEAN", "DATE"]
+    assert res[3]["rows"] == [["1"]]
+
+
+@needs_extension
+@pytest.mark.gpu
+def test_loaded_extension_scans_on_the_gpu(tmp_path):
+    path = str(tmp_path / "users.fls")
+    agg = "count(*), sum(id), sum(big), min(username), max(username), count(*) FILTER (is_active), max(join_date)"
+    res = sql("COPY (%s) TO '%s' (FORMAT FLS, ROW_GROUP_SIZE 20480)" % (_COPY_SRC, path),
+              "SELECT %s FROM (%s)" % (agg, _COPY_SRC),
+              "SELECT %s FROM read_fls('%s')" % (agg, path),
+              "SELECT %s FROM '%s' WHERE id < 1000" % (agg, path),
+              "SELECT %s FROM (%s) WHERE id < 1000" % (agg, _COPY_SRC),
+              env_extra={"FLS_SQL_CHECK_LOAD": EXTENSION})
+    assert all("error" not in r for r in res), res
+    assert res[1]["rows"] == res[2]["rows"] and res[3]["rows"] == res[4]["rows"]
