@@ -145,7 +145,7 @@ struct BufPool {  // size-keyed free lists; buffers live until the handle closes
 
 // Process-wide cache of the buffers closed handles leave behind: a query opens a handle, scans and closes it, and the
 // next query's handle would otherwise pay cudaHostAlloc again (about 0.3 s per GB of page-locked memory — more than
-// the scan itself).  Bounded (FLSGPU_CACHE_HOST_MB, default 8192; FLSGPU_CACHE_DEV_MB, default 32768);
+// the scan itself).  Bounded (FLSGPU_CACHE_HOST_MB, default 24576; FLSGPU_CACHE_DEV_MB, default 32768);
 // flsgpu_trim_cache() frees it.
 struct GlobalCache {
   std::mutex mu;
@@ -174,7 +174,7 @@ struct GlobalCache {
   }
   bool give_host(void *p, size_t n) {
     std::lock_guard<std::mutex> g(mu);
-    if (host_bytes + n > cap_mb("FLSGPU_CACHE_HOST_MB", 8192)) return false;
+    if (host_bytes + n > cap_mb("FLSGPU_CACHE_HOST_MB", 24576)) return false;
     host.emplace(n, p); host_bytes += n;
     return true;
   }

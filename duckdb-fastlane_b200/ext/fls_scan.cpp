@@ -146,6 +146,8 @@ bool FlsScanner::open(const std::string &path, const std::vector<int> &devices, 
   for (int device : devices.empty() ? std::vector<int>(1, 0) : devices) {
     flsgpu_opts o = {};
     o.device = device;
+    // four pipeline slices per batch: the H2D copy, the kernels and the D2H copy of one batch overlap each other
+    o.slice_rowgroups = std::max(1u, (batch_rowgroups ? batch_rowgroups : p->batch_rgs) / 4u);
     flsgpu_t *lane = nullptr;
     const int rc = flsgpu_open(path.c_str(), &o, &lane);
     if (rc != FLSGPU_OK) {

@@ -31,7 +31,7 @@ int main(int argc, char **argv) {
   uint64_t chunk = 2048;
   uint32_t batch = 0, g0 = 0, g1 = 0;
   bool have_range = false;
-  int device = 0, bench = 0;
+  int device = 0, bench = 0, lanes = 1;  // --lanes n: every device listed n times = n decodes in flight on it
   std::vector<int> gpus;
   for (int i = 2; i + 1 < argc; i += 2) {
     const std::string k = argv[i];
@@ -41,10 +41,16 @@ int main(int argc, char **argv) {
     else if (k == "--batch") batch = (uint32_t)strtoul(v, nullptr, 10);
     else if (k == "--device") device = atoi(v);
     else if (k == "--bench") bench = atoi(v);
+    else if (k == "--lanes") lanes = atoi(v);
     else if (k == "--gpus") { for (const char *s = v; *s;) { gpus.push_back((int)strtol(s, (char **)&s, 10)); if (*s == ',') ++s; } }
     else if (k == "--range") { char *e; g0 = (uint32_t)strtoul(v, &e, 10); g1 = (uint32_t)strtoul(e + 1, nullptr, 10); have_range = true; }
   }
   if (gpus.empty()) gpus.push_back(device);
+  if (lanes > 1) {
+    std::vector<int> rep;
+    for (int l = 0; l < lanes; ++l) rep.insert(rep.end(), gpus.begin(), gpus.end());
+    gpus.swap(rep);
+  }
   if (bench > 0) {
     double best = 1e30, sum = 0;
     uint64_t bytes = 0, total = 0;
