@@ -277,6 +277,55 @@ struct DecALP {
   }
 };
 
+// ===================================================================== ALP (f32)
+// payload: [packed 128*bw (u32 lanes)][exc values n x f32, pad16][exc positions n x u16, pad16]
+// value = (float)(int64)(bits + for) * (float)FACT[f] * FRAC[e] in float arithmetic (AlpTypedConstants<float>,
+// alp_constants.hpp:66-83; DecodeValue alp.hpp:129-134): one int64 -> float conversion, two separately rounded multiplies.
+FLS_CONST_TABLE float fls_alpf_frac[11] = {1.0F, 0.1F, 0.01F, 0.001F, 0.0001F, 0.00001F, 0.000001F, 0.0000001F, 0.00000001F,
+                                           0.000000001F, 0.0000000001F};
+FLS_DEV uint32_t fls_alpf_value(int64_t n, float fact, float frac) {
+#ifdef FLS_HOST_EMUL
+  volatile float a = (float)n * fact;
+  volatile float b = a * frac;
+  float r = b;
+  uint32_t u;
+  memcpy(&u, &r, 4);
+  return u;
+#else
+  return (uint32_t)__float_as_int(__fmul_rn(__fmul_rn(__ll2float_rn((long long)n), fact), frac));
+#endif
+}
+struct DecALP32 {
+  static constexpr uint32_t SMEM = 4096u;
+  FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint32_t e, uint32_t f, uint32_t n_exc,
+                          int64_t base, float *out) {
+    const float fact = (float)fls_alp_fact[f < 19u ? f : 18u], frac = fls_alpf_frac[e < 11u ? e : 10u];
+    if (bw) { w.stage(0, in, 128u * bw); w.wait(); }
+    FLS_LANES(t) {
+      const uint32_t q = t & 7u, g = t >> 3;
+#pragma unroll 4
+      for (uint32_t j = 0; j < 8u; ++j) {
+        const uint32_t row = g * 8u + j;
+        fls_u4 v;
+        if (bw) v = fls_unpack32_row(w.sm, bw, row, q, 0u);
+        else { v.x = 0; v.y = 0; v.z = 0; v.w = 0; }
+        v.x = fls_alpf_value(base + (int64_t)v.x, fact, frac);
+        v.y = fls_alpf_value(base + (int64_t)v.y, fact, frac);
+        v.z = fls_alpf_value(base + (int64_t)v.z, fact, frac);
+        v.w = fls_alpf_value(base + (int64_t)v.w, fact, frac);
+        fls_st128((uint8_t *)out + row * 128u + q * 16u, v);
+      }
+    }
+    if (n_exc) {  // patches land after the region barrier above, so they win over the decoded values
+      const uint32_t *xv = (const uint32_t *)(in + 128ull * bw);
+      const uint16_t *xp = (const uint16_t *)(in + 128ull * bw + (((uint64_t)n_exc * 4u + 15u) & ~15ull));
+      FLS_LANES(t) {
+        for (uint32_t i = t; i < n_exc; i += 32u) ((uint32_t *)out)[fls_ldg(xp + i) & 1023u] = fls_ldg(xv + i);
+      }
+    }
+  }
+};
+
 // ===================================================================== ALP-RD (f64 bit patterns)
 // payload: [right packed 128*rbw (u64 lanes)][left packed 128*lbw (u16 lanes)][exc left n x u16, pad16]
 //          [exc pos n x u16, pad16];  out = (dict[left] << rbw) | right; exceptions replace the left part.

@@ -116,6 +116,15 @@ struct VecALP {
                 FLS_META_N(h.meta), h.base, (double *)k.out + (size_t)v * FLS_VEC);
   }
 };
+struct VecALP32 {
+  static constexpr uint32_t SMEM = DecALP32::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    const uint32_t bw = FLS_META_BW(h.meta);
+    DecALP32::run(w, k.seg[1] + 16ull * h.ep, bw > 32u ? 32u : bw, FLS_META_E(h.meta), FLS_META_F(h.meta),
+                  FLS_META_N(h.meta), (int64_t)h.base, (float *)k.out + (size_t)v * FLS_VEC);
+  }
+};
 struct VecALPRD {
   static constexpr uint32_t SMEM = DecALPRD::SMEM, BLOCK_SMEM = 0;
   FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {

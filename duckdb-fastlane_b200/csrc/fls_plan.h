@@ -153,7 +153,7 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
         case FLS_S_CROSS_RLE: fls_launch_for(ls, FLS_K_CROSS_RLE, wb).add(d, rd, wr); break;
         case FLS_S_DICT: fls_launch_for(ls, FLS_K_DICT, wb).add(d, rd, wr); break;
         case FLS_S_ALP:
-          if (!(t.types[eq ? k0.aux32 : col] == FLS_T_DOUBLE)) return "ALP on a non-double column";
+          if (t.types[eq ? k0.aux32 : col] != FLS_T_DOUBLE && t.types[eq ? k0.aux32 : col] != FLS_T_FLOAT) return "ALP on a column that is neither DOUBLE nor FLOAT";
           fls_launch_for(ls, FLS_K_ALP, wb).add(d, rd, wr); break;
         case FLS_S_ALP_RD:
           if (!(t.types[eq ? k0.aux32 : col] == FLS_T_DOUBLE)) return "ALP_RD on a non-double column";

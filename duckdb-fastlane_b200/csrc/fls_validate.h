@@ -149,12 +149,12 @@ static inline std::string fls_validate_chunk(const FlsTable &t, uint32_t g, uint
       });
       break;
     case FLS_S_ALP:
-      if (t.types[c] != FLS_T_DOUBLE) return bad(g, c, "ALP on a non-double column");
+      if (t.types[c] != FLS_T_DOUBLE && t.types[c] != FLS_T_FLOAT) return bad(g, c, "ALP on a column that is neither DOUBLE nor FLOAT");
       if (!need_segs(2)) return bad(g, c, "missing segments");
       e = check_stream(s[0], s[1], n_vec, [&](uint32_t, uint32_t meta, uint64_t &b) {
         const uint32_t n_exc = FLS_META_N(meta);
         if (n_exc > FLS_VEC) return false;
-        b = 128ull * clamp(FLS_META_BW(meta), 64u) + pad16(8ull * n_exc) + 2ull * n_exc;
+        b = 128ull * clamp(FLS_META_BW(meta), tb) + pad16((uint64_t)wb * n_exc) + 2ull * n_exc;
         return true;
       });
       break;

@@ -426,6 +426,110 @@ static Chunk enc_alp(const double *v, uint32_t n_vec) {
   return c;
 }
 
+// ------------------------------------------------------------------ ALP (floats)
+// DuckDB's AlpTypedConstants<float> (alp_constants.hpp:66-83): float arithmetic throughout, magic number 2^22 + 2^23,
+// exponents 0..10; decode = (float)n * (float)FACT[f] * FRAC[e], two float multiplies (alp.hpp:129-134).  The encoded
+// integers of a vector's non-exceptions differ by less than 2^32 (a float holds 24 bits), so the stream is u32 FFOR.
+static const float ALPF_EXP[] = {1.0F, 10.0F, 100.0F, 1000.0F, 10000.0F, 100000.0F, 1000000.0F, 10000000.0F, 100000000.0F,
+                                 1000000000.0F, 10000000000.0F};
+static const float ALPF_FRAC[] = {1.0F, 0.1F, 0.01F, 0.001F, 0.0001F, 0.00001F, 0.000001F, 0.0000001F, 0.00000001F,
+                                  0.000000001F, 0.0000000001F};
+static const float ALPF_MAGIC = 12582912.0F;
+static const int ALPF_MAX_E = 10;
+static inline int64_t alpf_encode(float v, int e, int f) {
+  float t = v * ALPF_EXP[e] * ALPF_FRAC[f];
+  if (!std::isfinite(t) || std::isnan(t) || t > ALP_LIMIT || t < -ALP_LIMIT || (t == 0.0f && std::signbit(t))) return (int64_t)ALP_LIMIT;
+  t = t + ALPF_MAGIC - ALPF_MAGIC;
+  return (int64_t)t;
+}
+static inline float alpf_decode(int64_t n, int e, int f) { return (float)n * (float)ALP_FACT[f] * ALPF_FRAC[e]; }
+static inline bool same_bits32(float a, float b) { return memcmp(&a, &b, 4) == 0; }
+static uint64_t alpf_estimate(const std::vector<float> &smp, int e, int f, bool penalize) {
+  uint64_t exc = 0, ok = 0;
+  int64_t mn = INT64_MAX, mx = INT64_MIN;
+  for (float v : smp) {
+    int64_t n = alpf_encode(v, e, f);
+    if (alpf_decode(n, e, f) == v) { ++ok; mn = std::min(mn, n); mx = std::max(mx, n); }
+    else ++exc;
+  }
+  if (penalize && ok < 2) return UINT64_MAX;
+  uint64_t delta = ok ? (uint64_t)mx - (uint64_t)mn : 0;
+  return smp.size() * bits_needed<uint64_t>(delta) + exc * (32 + 16);
+}
+static std::vector<AlpCombo> alpf_topk(const float *v, uint32_t n_vec) {
+  std::map<std::pair<int, int>, uint64_t> votes;
+  uint32_t step = std::max(1u, n_vec / 8);
+  for (uint32_t vi = 0; vi < n_vec; vi += step) {
+    std::vector<float> smp;
+    for (uint32_t j = 0; j < FLS_VEC; j += 32) smp.push_back(v[vi * FLS_VEC + j]);
+    AlpCombo best = {ALPF_MAX_E, ALPF_MAX_E, 0, UINT64_MAX};
+    bool have = false;
+    for (int e = ALPF_MAX_E; e >= 0; --e)
+      for (int f = e; f >= 0; --f) {
+        AlpCombo c = {e, f, 0, alpf_estimate(smp, e, f, true)};
+        if (!have || alp_better(c, best)) { best = c; have = true; }
+      }
+    votes[{best.e, best.f}]++;
+  }
+  std::vector<AlpCombo> out;
+  for (auto &kv : votes) out.push_back({kv.first.first, kv.first.second, kv.second, 0});
+  std::sort(out.begin(), out.end(), alp_better);
+  if (out.size() > 5) out.resize(5);
+  return out;
+}
+// false: some vector's encoded range does not fit 32 bits (then the column takes another scheme)
+static bool enc_alp_f32(const float *v, uint32_t n_vec, Chunk &c) {
+  c = Chunk(); c.scheme = FLS_S_ALP;
+  Stream s;
+  std::vector<AlpCombo> topk = alpf_topk(v, n_vec);
+  if (tl_force_alp_ef >= 0) topk.assign(1, AlpCombo{std::min(tl_force_alp_ef / 32, ALPF_MAX_E), std::min(tl_force_alp_ef % 32, ALPF_MAX_E), 1, 0});
+  for (uint32_t vi = 0; vi < n_vec; ++vi) {
+    const float *x = v + vi * FLS_VEC;
+    int e = topk[0].e, f = topk[0].f;
+    if (topk.size() > 1) {
+      std::vector<float> smp;
+      for (uint32_t j = 0; j < FLS_VEC; j += 32) smp.push_back(x[j]);
+      uint64_t best = UINT64_MAX; int worse = 0;
+      for (auto &cb : topk) {
+        uint64_t sz = alpf_estimate(smp, cb.e, cb.f, false);
+        if (sz >= best) { if (++worse == 2) break; continue; }
+        best = sz; e = cb.e; f = cb.f; worse = 0;
+      }
+    }
+    int64_t enc[FLS_VEC];
+    std::vector<uint16_t> pos; std::vector<float> exc;
+    for (uint32_t i = 0; i < FLS_VEC; ++i) {
+      enc[i] = alpf_encode(x[i], e, f);
+      if (!same_bits32(alpf_decode(enc[i], e, f), x[i])) { pos.push_back((uint16_t)i); exc.push_back(x[i]); }
+    }
+    int64_t filler = 0;
+    { size_t k = 0;
+      for (uint32_t i = 0; i < FLS_VEC; ++i) { if (k < pos.size() && pos[k] == i) { ++k; continue; } filler = enc[i]; break; } }
+    for (uint16_t p : pos) enc[p] = filler;
+    int64_t mn = enc[0], mx = enc[0];
+    for (uint32_t i = 1; i < FLS_VEC; ++i) { mn = std::min(mn, enc[i]); mx = std::max(mx, enc[i]); }
+    if ((uint64_t)mx - (uint64_t)mn > 0xFFFFFFFFull || mn < INT32_MIN || mn > INT32_MAX) return false;
+    uint32_t tmp[FLS_VEC];
+    for (uint32_t i = 0; i < FLS_VEC; ++i) tmp[i] = (uint32_t)((uint64_t)enc[i] - (uint64_t)mn);
+    uint32_t W = bits_needed<uint32_t>((uint32_t)((uint64_t)mx - (uint64_t)mn));
+    s.begin_vec(FLS_META(W, e, f, pos.size()), (uint64_t)(int64_t)mn);  // base: the frame of reference, sign-extended
+    append_packed<uint32_t>(s.data, tmp, W);
+    put_bytes(s.data, exc.data(), exc.size() * 4); pad_to(s.data, 16);
+    put_bytes(s.data, pos.data(), pos.size() * 2); pad_to(s.data, 16);
+  }
+  s.move_into(c);
+  return true;
+}
+static Chunk enc_float_auto(const float *v, uint32_t n_vec, int force, int force_bw) {
+  const uint32_t *bits = (const uint32_t *)v;
+  Chunk a;
+  if (force == FLS_S_ALP) { if (enc_alp_f32(v, n_vec, a)) return a; return enc_int_auto<uint32_t>(bits, n_vec, -1, -1); }
+  if (force >= 0) return enc_int_auto<uint32_t>(bits, n_vec, force, force_bw);
+  Chunk best = enc_int_auto<uint32_t>(bits, n_vec, -1, force_bw);
+  if (best.scheme != FLS_S_CONSTANT && enc_alp_f32(v, n_vec, a) && a.bytes() < best.bytes()) best = std::move(a);
+  return best;
+}
+
 // ------------------------------------------------------------------ ALP-RD (doubles, "real doubles")
 // Split each 64-bit pattern at rbw: right part bit-packed as u64, left part (<=16 bits) dictionary-coded
 // with <=8 entries / <=3 bits, misses stored as (u16 left, u16 pos) exceptions.  alprd.hpp:70-199.
@@ -798,7 +902,8 @@ static Chunk enc_fixed(const void *src, uint32_t n_rows, uint32_t n_vec, int for
     for (size_t i = 0; i < n_rows; ++i) { if (bit_at(valid, i)) prev = v[i]; else v[i] = prev; }
   }
   for (size_t i = n_rows; i < v.size(); ++i) v[i] = v[n_rows - 1];  // pad the tail vector
-  if (is_double) return enc_double_auto((const double *)v.data(), n_vec, force);
+  if (is_double) return sizeof(T) == 8 ? enc_double_auto((const double *)v.data(), n_vec, force)
+                                       : enc_float_auto((const float *)v.data(), n_vec, force, force_bw);  // (is_double: floating point)
   return enc_int_auto<T>(v.data(), n_vec, force, force_bw);
 }
 
@@ -841,7 +946,7 @@ static int append_rowgroup(Writer &w, uint32_t n_rows, const void *const *col_da
     switch (fls_type_bits(t)) {
       case 8: ch = enc_fixed<uint8_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], false, vb); break;
       case 16: ch = enc_fixed<uint16_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], false, vb); break;
-      case 32: ch = enc_fixed<uint32_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], false, vb); break;
+      case 32: ch = enc_fixed<uint32_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], t == FLS_T_FLOAT, vb); break;
       case 64: ch = enc_fixed<uint64_t>(col_data[c], n_rows, n_vec, f == FLS_S_EQUAL ? -1 : f, w.force_bw[c], t == FLS_T_DOUBLE, vb); break;
       default: {
         if (t != FLS_T_STR && t != FLS_T_BYTE_ARRAY) { w.err = "unsupported column type"; return 1; }
@@ -947,6 +1052,7 @@ int flsw_force_alp_ef(flsw_writer *h, uint32_t col, int32_t e, int32_t f) {
   return 0;
 }
 int64_t flsw_alp_encode_value(double v, int32_t e, int32_t f) { return flsw::alp_encode(v, e, f); }
+int64_t flsw_alpf_encode_value(float v, int32_t e, int32_t f) { return flsw::alpf_encode(v, e, f); }
 // Test knobs: the next row group appended for `col` uses these externally produced streams verbatim (the pointers
 // must stay valid until that flsw_append_rowgroup returns).
 int flsw_inject_fsst(flsw_writer *h, uint32_t col, const uint8_t *symtab2304, const uint8_t *comp, const uint64_t *comp_off,

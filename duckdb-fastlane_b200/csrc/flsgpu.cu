@@ -80,6 +80,7 @@ cudaError_t set_kernel_attrs() {
   if ((e = vec_attr_all<VecFFORPATCH>()) != cudaSuccess) return e;
   if ((e = vec_attr_all<VecCROSSRLE>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecALP>()) != cudaSuccess) return e;
+  if ((e = vec_attr<VecALP32>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecALPRD>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecSTROFFS>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecSTRCONST>()) != cudaSuccess) return e;
@@ -108,7 +109,9 @@ bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
     case FLS_K_DICT: return vec_launch_w<VecDICT>(l.width, d, n, s);
     case FLS_K_FFOR_PATCH: return vec_launch_w<VecFFORPATCH>(l.width, d, n, s);
     case FLS_K_CROSS_RLE: return vec_launch_w<VecCROSSRLE>(l.width, d, n, s);
-    case FLS_K_ALP: vec_launch<VecALP>(d, n, s); return true;
+    case FLS_K_ALP:
+      if (l.width == 4) vec_launch<VecALP32>(d, n, s); else vec_launch<VecALP>(d, n, s);
+      return true;
     case FLS_K_ALPRD: vec_launch<VecALPRD>(d, n, s); return true;
     case FLS_K_COPY: fls_copy_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;
     case FLS_K_FILL: fls_fill_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;

@@ -58,6 +58,8 @@ def lib():
         L.flsw_force_alp_ef.argtypes = [C.c_void_p, C.c_uint32, C.c_int32, C.c_int32]
         L.flsw_alp_encode_value.argtypes = [C.c_double, C.c_int32, C.c_int32]
         L.flsw_alp_encode_value.restype = C.c_int64
+        L.flsw_alpf_encode_value.argtypes = [C.c_float, C.c_int32, C.c_int32]
+        L.flsw_alpf_encode_value.restype = C.c_int64
         L.flsw_inject_fsst.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
         L.flsw_inject_alprd.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32,
                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

@@ -42,6 +42,7 @@ void flsw_destroy(flsw_writer *w);
 int flsw_force_scheme(flsw_writer *w, uint32_t col, int32_t scheme, int32_t min_bw);
 int flsw_force_alp_ef(flsw_writer *w, uint32_t col, int32_t e, int32_t f);
 int64_t flsw_alp_encode_value(double v, int32_t e, int32_t f);
+int64_t flsw_alpf_encode_value(float v, int32_t e, int32_t f); /* FLOAT columns: float arithmetic, e, f <= 10 */
 /* Test knobs for parity against the reference tree's own encoders: the NEXT row group appended for `col` is built
  * from externally produced streams, verbatim.  FSST: libfsst's symbol table (u64 symbol[256] | u8 len[256]) and
  * compressed bytes (comp_off[n_strings + 1]); the row group still receives the raw strings (decoded offsets).

@@ -271,6 +271,33 @@ static int chunk_alp(const uint8_t *rgp, const ochunk *k, uint32_t n_vec, double
   return 0;
 }
 
+/* ---- ALP on FLOAT columns: AlpTypedConstants<float> (alp_constants.hpp:66-83) — float arithmetic, exponents 0..10;
+ *      decode = (float)(int64)n * (float)FACT[f] * FRAC[e] (alp.hpp:129-134 with T = float).  The stream is u32 FFOR,
+ *      the vector header's base the (sign-extended) frame of reference. */
+static const float AF_FRAC[] = {1.0F, 0.1F, 0.01F, 0.001F, 0.0001F, 0.00001F, 0.000001F, 0.0000001F, 0.00000001F,
+                                0.000000001F, 0.0000000001F};
+float flso_alpf_decode_value(int64_t n, unsigned e, unsigned f) {
+  volatile float a = (float)n * (float)A_FACT[f > 18 ? 18 : f];
+  volatile float b = a * AF_FRAC[e > 10 ? 10 : e];
+  return b;
+}
+static int chunk_alp32(const uint8_t *rgp, const ochunk *k, uint32_t n_vec, float *out) {
+  const ovhdr *h = (const ovhdr *)(rgp + k->seg[0].off);
+  const uint8_t *data = rgp + k->seg[1].off;
+  uint32_t tmp[O_VEC];
+  for (uint32_t v = 0; v < n_vec; ++v) {
+    uint32_t m = h[v].meta, W = M_BW(m), e = M_E(m), f = M_F(m), nx = M_N(m);
+    const uint8_t *p = data + 16ull * h[v].ep;
+    unffor_32((const uint32_t *)p, W, 0, tmp);
+    float *o = out + (size_t)v * O_VEC;
+    for (unsigned i = 0; i < O_VEC; ++i) o[i] = flso_alpf_decode_value((int64_t)h[v].base + (int64_t)tmp[i], e, f);
+    const float *xv = (const float *)(p + 128ull * W);
+    const uint16_t *xp = (const uint16_t *)(p + 128ull * W + PAD16((uint64_t)nx * 4));
+    for (uint32_t i = 0; i < nx; ++i) o[xp[i] & 1023u] = xv[i];
+  }
+  return 0;
+}
+
 /* ---- ALP-RD: out = (dict[left] << rbw) | right, then patch left-part exceptions.
  *      duckdb/.../alprd/algorithm/alprd.hpp:206-233. */
 void flso_alprd_decode(const uint16_t *dict, const uint16_t *left, const uint64_t *right, uint32_t rbw, uint32_t n,
@@ -462,6 +489,7 @@ static int decode_fixed_rg(const flso_table *t, uint32_t c, uint32_t g, void *ds
     if (k->aux32 >= t->n_cols || r->cols[k->aux32].scheme == S_EQUAL || type_bits(t->types[k->aux32]) != type_bits(t->types[c])) return 13;
     k = &r->cols[k->aux32];
   }
+  if (k->scheme == S_ALP && type_bits(t->types[c]) == 32) return chunk_alp32(rgp, k, r->n_vec, (float *)dst);
   if (k->scheme == S_ALP) return chunk_alp(rgp, k, r->n_vec, (double *)dst);
   if (k->scheme == S_ALPRD) return chunk_alprd(rgp, k, r->n_vec, (uint64_t *)dst);
   switch (type_bits(t->types[c])) {

@@ -48,6 +48,8 @@ def lib():
         L.flso_decode_str.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int]
         L.flso_alp_decode_value.argtypes = [C.c_int64, C.c_uint, C.c_uint]
         L.flso_alp_decode_value.restype = C.c_double
+        L.flso_alpf_decode_value.argtypes = [C.c_int64, C.c_uint, C.c_uint]
+        L.flso_alpf_decode_value.restype = C.c_float
         L.flso_fsst_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.flso_fsst_decode.restype = C.c_uint64
         L.flso_alprd_decode.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p,

@@ -49,6 +49,29 @@ double twin_alp_decode(int64_t n, uint8_t e, uint8_t f) {
   return alp::AlpCompression<double, true>::DecodeValue(n, idx);
 }
 
+// The same for FLOAT columns (AlpTypedConstants<float>: float arithmetic, exponents 0..10).
+int64_t twin_alpf_encode(float v, uint8_t e, uint8_t f) {
+  alp::AlpEncodingIndices idx(e, f);
+  return alp::AlpCompression<float, true>::EncodeValue(v, idx);
+}
+float twin_alpf_decode(int64_t n, uint8_t e, uint8_t f) {
+  alp::AlpEncodingIndices idx(e, f);
+  return alp::AlpCompression<float, true>::DecodeValue(n, idx);
+}
+// DuckDB's sampler + Compress + Decompress on one float vector: decoded floats, chosen (e, f), exception count
+int twin_alpf_roundtrip(const float *in, uint32_t n, float *out, uint8_t *e, uint8_t *f) {
+  alp::AlpCompressionState<float, false> st;
+  duckdb::vector<duckdb::vector<float>> samples; samples.emplace_back(in, in + n);
+  alp::AlpCompression<float, false>::FindTopKCombinations(samples, st);
+  alp::AlpCompression<float, false>::Compress(in, n, st);
+  alp::AlpDecompression<float>::Decompress(st.values_encoded, out, n, st.vector_encoding_indices.factor,
+                                           st.vector_encoding_indices.exponent, st.exceptions_count, st.exceptions,
+                                           st.exceptions_positions, st.frame_of_reference, (uint8_t)st.bit_width);
+  *e = st.vector_encoding_indices.exponent;
+  *f = st.vector_encoding_indices.factor;
+  return st.exceptions_count;
+}
+
 // One ALP vector through DuckDB's sampler + compressor.  Outputs: chosen (e,f), FOR base, bit width,
 // FOR-subtracted encoded integers, exceptions.  Returns the exception count.
 int twin_alp_compress(const double *in, uint32_t n, uint8_t *e, uint8_t *f, uint64_t *frame, uint8_t *bw,

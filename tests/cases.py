@@ -162,6 +162,19 @@ def alp_cases(n=70_000):
     v = synth.alp_entropy(n)
     v[r.choice(n, 500, replace=False)] = SPECIALS[r.integers(0, len(SPECIALS), 500)]
     out.append(("alprd_with_specials", [v], None, [W.ALP_RD], None))
+    # FLOAT columns: ALP in float arithmetic (AlpTypedConstants<float>), u32 stream
+    f32 = np.float32
+    out.append(("alpf_prices_2dec", [np.round(r.uniform(1, 1000, n), 2).astype(f32)], None, [W.ALP], None))
+    out.append(("alpf_1dec_signed", [np.round(r.uniform(-500, 500, n), 1).astype(f32)], None, [W.ALP], None))
+    out.append(("alpf_integers", [r.integers(-10 ** 5, 10 ** 5, n).astype(f32)], None, [W.ALP], None))
+    v = np.round(r.uniform(0, 100, n), 2).astype(f32)
+    sp = np.array([np.nan, np.inf, -np.inf, -0.0, 1e30, 0.1 + 0.2, 1e-45, 3.4e38], dtype=f32)
+    v[r.choice(n, n // 4, replace=False)] = sp[r.integers(0, len(sp), n // 4)]
+    out.append(("alpf_many_exceptions", [v], None, [W.ALP], None))
+    out.append(("alpf_all_nan", [np.full(n, np.nan, dtype=f32)], None, [W.ALP], None))
+    out.append(("alpf_constant_w0", [np.full(n, 2.5, dtype=f32)], None, [W.ALP], None))
+    out.append(("float_auto_entropy", [r.normal(size=n).astype(f32)], None, None, None))   # (ALP does not pay: another scheme)
+    out.append(("float_auto_prices", [np.round(r.uniform(1, 1000, n), 2).astype(f32)], None, None, None))
     out.append(("double_auto_prices", [prices], None, None, None))
     out.append(("double_auto_entropy", [synth.alp_entropy(n)], None, None, None))
     return out

@@ -70,7 +70,9 @@ static bool run_launch(const FlsLaunch &l) {
     case FLS_K_DICT: return run_by_width<VecDICT>(l);
     case FLS_K_FFOR_PATCH: return run_by_width<VecFFORPATCH>(l);
     case FLS_K_CROSS_RLE: return run_by_width<VecCROSSRLE>(l);
-    case FLS_K_ALP: run_vectors<VecALP>(l); return true;
+    case FLS_K_ALP:
+      if (l.width == 4) run_vectors<VecALP32>(l); else run_vectors<VecALP>(l);
+      return true;
     case FLS_K_ALPRD: run_vectors<VecALPRD>(l); return true;
     case FLS_K_COPY:
       for (auto &k : l.chunks) memcpy(k.out, k.seg[0], k.aux64[1]);

@@ -77,6 +77,46 @@ def alp():
     np.savez_compressed(os.path.join(HERE, "alp.npz"), **dec, **enc, **vec)
 
 
+def alpf():
+    """ALP on FLOAT columns: DuckDB's AlpCompression<float> (alp.hpp with AlpTypedConstants<float>)."""
+    L.twin_alpf_encode.argtypes = [C.c_float, C.c_uint8, C.c_uint8]
+    L.twin_alpf_encode.restype = C.c_int64
+    L.twin_alpf_decode.argtypes = [C.c_int64, C.c_uint8, C.c_uint8]
+    L.twin_alpf_decode.restype = C.c_float
+    L.twin_alpf_roundtrip.argtypes = [vp, C.c_uint32, vp, vp, vp]
+    r = np.random.Generator(np.random.PCG64(2025))
+    es, fs, ns, ds = [], [], [], []
+    for e in range(11):
+        for f in range(e + 1):
+            mags = r.integers(0, 40, 64)
+            n = (r.integers(0, 2 ** 40, 64) >> (39 - mags)) * r.choice([-1, 1], 64)
+            n[:4] = [0, 1, -1, 1234567]
+            for x in n:
+                es.append(e); fs.append(f); ns.append(int(x)); ds.append(L.twin_alpf_decode(int(x), e, f))
+    dec = dict(dec_e=np.array(es, np.uint8), dec_f=np.array(fs, np.uint8), dec_n=np.array(ns, np.int64),
+               dec_bits=np.array(ds, np.float32).view(np.uint32))
+    vals = np.concatenate([np.round(r.uniform(-1e4, 1e4, 400), 2), np.round(r.uniform(0, 1, 200), 4),
+                           r.integers(-10 ** 6, 10 ** 6, 200).astype(np.float64), r.uniform(0, 1, 100),
+                           np.array([np.nan, np.inf, -np.inf, -0.0, 0.0, 1e30, -1e30, 0.1 + 0.2, 1e-45, 9.2e18])]).astype(np.float32)
+    ee, ff, vv, nn = [], [], [], []
+    for v in vals:
+        for (e, f) in ((2, 0), (6, 0), (10, 8), (10, 10), (0, 0), (7, 5), (4, 1)):
+            ee.append(e); ff.append(f); vv.append(v); nn.append(L.twin_alpf_encode(float(v), e, f))
+    enc = dict(enc_e=np.array(ee, np.uint8), enc_f=np.array(ff, np.uint8), enc_v=np.array(vv, np.float32).view(np.uint32),
+               enc_n=np.array(nn, np.int64))
+    vecs = [np.round(r.uniform(1, 1000, 1024), 2), np.round(r.uniform(0, 100, 1024), 1), r.integers(0, 50, 1024).astype(np.float64),
+            np.where(r.random(1024) < 0.05, r.normal(size=1024), np.round(r.uniform(0, 10, 1024), 3)), r.normal(size=1024)]
+    vin, vout, ve, vf, vn = [], [], [], [], []
+    for v in vecs:
+        v = np.ascontiguousarray(v.astype(np.float32))
+        out = np.empty(1024, np.float32)
+        e, f = np.zeros(1, np.uint8), np.zeros(1, np.uint8)
+        nx = L.twin_alpf_roundtrip(p(v), 1024, p(out), p(e), p(f))
+        vin.append(v.view(np.uint32)); vout.append(out.view(np.uint32)); ve.append(e[0]); vf.append(f[0]); vn.append(nx)
+    vec = dict(vec_in=np.array(vin), vec_out=np.array(vout), vec_e=np.array(ve), vec_f=np.array(vf), vec_nexc=np.array(vn))
+    np.savez_compressed(os.path.join(HERE, "alpf.npz"), **dec, **enc, **vec)
+
+
 def alprd():
     r = np.random.Generator(np.random.PCG64(2025))
     vecs = [synth.alp_entropy(1024, seed=9), r.uniform(0, 1000, 1024), r.normal(size=1024) * 1e-3,
@@ -123,6 +163,6 @@ def fsst():
 
 
 if __name__ == "__main__":
-    alp(); alprd(); fsst()
-    for f in ("alp.npz", "alprd.npz", "fsst.npz"):
+    alp(); alpf(); alprd(); fsst()
+    for f in ("alp.npz", "alpf.npz", "alprd.npz", "fsst.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")

@@ -173,6 +173,30 @@ def test_alp_kernel_against_reference_golden_every_exponent_factor():
         assert np.array_equal(got[c].view(np.uint64), bits), efs[c]
 
 
+def test_alpf_kernel_against_reference_golden_every_exponent_factor():
+    # tests/golden/alpf.npz: DuckDB's own AlpCompression<float>::DecodeValue(n, e, f) for all 66 (e, f) pairs, f <= e <= 10
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "alpf.npz"))
+    cols, efs, want = [], [], []
+    for e in range(11):
+        for f in range(e + 1):
+            m = (g["dec_e"] == e) & (g["dec_f"] == f)
+            bits = g["dec_bits"][m]
+            cols.append(bits.view(np.float32)); efs.append((e, f)); want.append(bits)
+    img = W.write_table(cols, force=[W.ALP] * len(cols), alp_ef=efs)
+    ora = oracle.OracleTable(img)
+    assert all(ora.scheme(0, c) == W.ALP for c in range(len(cols)))
+    with flsgpu.Reader.from_image(img) as rd:
+        got = rd.decode()
+    for c, bits in enumerate(want):
+        assert np.array_equal(got[c].view(np.uint32), bits), efs[c]
+    # whole vectors DuckDB's sampler + Compress + Decompress returned unchanged
+    for bits in g["vec_in"]:
+        img = W.write_table([bits.view(np.float32)], force=[W.ALP])
+        with flsgpu.Reader.from_image(img) as rd:
+            assert np.array_equal(rd.decode()[0].view(np.uint32), bits)
+
+
 def test_fsst_kernel_on_reference_golden_strings():
     import os
     g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fsst.npz"))

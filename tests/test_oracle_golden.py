@@ -112,3 +112,39 @@ def test_reference_minted_streams_decode_through_the_container():
         else:
             assert np.array_equal(got.view(np.uint64), exp), name
             assert np.array_equal(em.view(np.uint64)[:len(exp)], exp), name
+
+
+# ------------------------------------------------------------------------------------------------- ALP on FLOAT columns
+def test_alpf_decode_value_every_exponent_factor():
+    g = np.load(os.path.join(G, "alpf.npz"))
+    L = oracle.lib()
+    assert len(g["dec_n"]) == 66 * 64          # f <= e <= 10
+    for n, e, f, bits in zip(g["dec_n"], g["dec_e"], g["dec_f"], g["dec_bits"]):
+        got = np.float32(L.flso_alpf_decode_value(int(n), int(e), int(f))).view(np.uint32)
+        assert got == bits, (n, e, f)
+
+
+def test_alpf_encode_value_matches_reference():
+    g = np.load(os.path.join(G, "alpf.npz"))
+    L = W.lib()
+    for v, e, f, n in zip(g["enc_v"].view(np.float32), g["enc_e"], g["enc_f"], g["enc_n"]):
+        assert L.flsw_alpf_encode_value(float(v), int(e), int(f)) == int(n), (v, e, f)
+
+
+def test_alpf_vectors_roundtrip_like_reference():
+    import emul
+    g = np.load(os.path.join(G, "alpf.npz"))
+    assert np.array_equal(g["vec_in"], g["vec_out"])     # DuckDB's Compress + Decompress returns the input bits
+    for i, bits in enumerate(g["vec_in"]):
+        v = bits.view(np.float32)
+        e, f = int(g["vec_e"][i]), int(g["vec_f"][i])
+        for ef in (None, (e, f)):                         # own sampler, then DuckDB's chosen (e, f)
+            img = W.write_table([v], force=[W.ALP], alp_ef=[ef])
+            ora = oracle.OracleTable(img)
+            assert ora.scheme(0, 0) == W.ALP
+            assert np.array_equal(ora.decode(0).view(np.uint32), bits)
+            assert np.array_equal(emul.decode(img, 0, ora.types[0], 0, 1)[:1024].view(np.uint32), bits)
+        # with DuckDB's (e, f) the exception count is DuckDB's too
+        enc = np.array([W.lib().flsw_alpf_encode_value(float(x), e, f) for x in v], dtype=np.int64)
+        dec = np.array([oracle.lib().flso_alpf_decode_value(int(n), e, f) for n in enc], dtype=np.float32)
+        assert int((dec.view(np.uint32) != bits).sum()) == int(g["vec_nexc"][i])
