@@ -508,7 +508,7 @@ static bool enc_alp_f32(const float *v, uint32_t n_vec, Chunk &c) {
     for (uint16_t p : pos) enc[p] = filler;
     int64_t mn = enc[0], mx = enc[0];
     for (uint32_t i = 1; i < FLS_VEC; ++i) { mn = std::min(mn, enc[i]); mx = std::max(mx, enc[i]); }
-    if ((uint64_t)mx - (uint64_t)mn > 0xFFFFFFFFull || mn < INT32_MIN || mn > INT32_MAX) return false;
+    if ((uint64_t)mx - (uint64_t)mn > 0xFFFFFFFFull) return false;
     uint32_t tmp[FLS_VEC];
     for (uint32_t i = 0; i < FLS_VEC; ++i) tmp[i] = (uint32_t)((uint64_t)enc[i] - (uint64_t)mn);
     uint32_t W = bits_needed<uint32_t>((uint32_t)((uint64_t)mx - (uint64_t)mn));

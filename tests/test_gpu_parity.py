@@ -181,8 +181,15 @@ def test_alpf_kernel_against_reference_golden_every_exponent_factor():
     for e in range(11):
         for f in range(e + 1):
             m = (g["dec_e"] == e) & (g["dec_f"] == f)
-            bits = g["dec_bits"][m]
-            cols.append(bits.view(np.float32)); efs.append((e, f)); want.append(bits)
+            order = np.argsort(g["dec_n"][m])
+            ns, bits = g["dec_n"][m][order], g["dec_bits"][m][order]
+            # a FLOAT vector's encoded integers must span less than 2^32: one column per run of close-by integers
+            start = 0
+            for i in range(1, len(ns) + 1):
+                if i == len(ns) or int(ns[i]) - int(ns[start]) >= 2 ** 31:
+                    grp = np.concatenate([bits[start:i], np.full(64 - (i - start), bits[i - 1], dtype=np.uint32)])  # 64 rows each
+                    cols.append(grp.view(np.float32)); efs.append((e, f)); want.append(grp)
+                    start = i
     img = W.write_table(cols, force=[W.ALP] * len(cols), alp_ef=efs)
     ora = oracle.OracleTable(img)
     assert all(ora.scheme(0, c) == W.ALP for c in range(len(cols)))
