@@ -126,6 +126,11 @@ bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
   return false;
 }
 
+// out[j] = base + in[j]: a part's 32-bit string offsets, relative to the part's first payload byte, as 64-bit offsets
+__global__ void fls_widen_offsets_kernel(const uint32_t *__restrict__ in, uint64_t *__restrict__ out, uint64_t n, uint64_t base) {
+  for (uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; j < n; j += (uint64_t)gridDim.x * blockDim.x)
+    out[j] = base + in[j];
+}
 __global__ void fls_flush_kernel(uint4 *p, uint64_t n16, uint32_t v) {
   for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x)
     p[i] = make_uint4(v, v, v, v);
@@ -292,6 +297,13 @@ struct flsgpu_batch {
   std::vector<FlsColNeed> need;
   std::vector<void *> dev_bufs, host_bufs;
   flsgpu_timing tm;
+  // string columns whose payload reaches 4 GiB are decoded in PARTS of less than 4 GiB: inside a part the kernels'
+  // 32-bit offsets are relative to the part's first payload byte (part k's offsets live 4 k entries further on in the
+  // device array, so that a part's first entry can be 0 while the previous part's last end stays); a last kernel
+  // widens them into the 64-bit offsets the caller sees
+  struct StrPart { uint32_t g_first; uint64_t row_base, pay_base; };
+  std::vector<std::vector<StrPart>> parts;   // per column; empty = not wide
+  std::vector<uint64_t *> off64_dev;
   // filtered batches: row ids of the surviving rows (device, and host for FLSGPU_OUT_HOST)
   bool filtered = false;
   uint64_t *sel_dev = nullptr, *sel_host = nullptr;
@@ -797,14 +809,13 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     }
 
   // ---- output buffers
-  b->out.resize(nc); b->dev.resize(nc); b->need.resize(nc);
+  b->out.resize(nc); b->dev.resize(nc); b->need.resize(nc); b->parts.resize(nc); b->off64_dev.assign(nc, nullptr);
   const uint64_t rows = t.rows(g0, g1), prow = t.padded_rows(g0, g1);
   uint64_t scratch_total = 0;
   for (uint32_t i = 0; i < nc; ++i) {
     const uint32_t c = b->cols[i];
     FlsColNeed n = fls_column_need(t, c, g0, g1, h->image);
     b->need[i] = n;
-    if (n.payload_bytes >= (1ull << 32)) return bail(FLSGPU_E_LIMIT, "string payload of one batch must stay below 4 GiB; split the row-group range");
     flsgpu_column &o = b->out[i];
     memset(&o, 0, sizeof(o));
     o.type = t.types[c];
@@ -820,15 +831,31 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       o.data = d.data;
       if (to_host && !(o.data = halloc(n.data_bytes))) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
     } else {
-      d.offsets = (uint32_t *)dalloc(n.offsets_bytes);
+      // 4 GiB of payload and more: parts of less than 4 GiB each, 64-bit offsets for the caller
+      std::vector<flsgpu_batch::StrPart> &parts = b->parts[i];
+      if (n.payload_bytes >= (1ull << 32)) {
+        uint64_t in_part = 0, pay = 0, row = 0;
+        for (uint32_t g = g0; g < g1; ++g) {
+          const uint64_t rp = t.chunk(g, c).aux64[0];
+          if (g == g0 || in_part + rp > 0xFFFF0000ull) { parts.push_back({g, row, pay}); in_part = 0; }
+          in_part += rp; pay += rp;
+          row += (uint64_t)t.rgs[g].n_vec * FLS_VEC;
+        }
+      }
+      d.offsets = (uint32_t *)dalloc(n.offsets_bytes + 16 * parts.size());
       d.payload = (uint8_t *)dalloc(n.payload_bytes);
       if (!d.offsets || !d.payload) return bail(FLSGPU_E_NOMEM, "out of device memory");
       o.offsets = d.offsets; o.payload = d.payload;
       o.payload_bytes = n.payload_bytes - 16;
+      if (!parts.empty()) {
+        if (!(b->off64_dev[i] = (uint64_t *)dalloc((prow + 1) * 8))) return bail(FLSGPU_E_NOMEM, "out of device memory");
+        o.offsets = nullptr; o.offsets64 = b->off64_dev[i];
+      }
       if (to_host) {
-        o.offsets = (uint32_t *)halloc(n.offsets_bytes);
+        if (parts.empty()) o.offsets = (uint32_t *)halloc(n.offsets_bytes);
+        else o.offsets64 = (uint64_t *)halloc((prow + 1) * 8);
         o.payload = (uint8_t *)halloc(n.payload_bytes);
-        if (!o.offsets || !o.payload) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+        if (!(o.offsets || o.offsets64) || !o.payload) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
       }
       scratch_total += n.scratch_bytes;
     }
@@ -842,7 +869,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     for (uint32_t i = 0; i < nc; ++i) {
       if (!b->dev[i].offsets) continue;
       CKB(cudaMemset(b->dev[i].offsets, 0, 4));
-      if (to_host) b->out[i].offsets[0] = 0;
+      if (to_host && b->out[i].offsets) b->out[i].offsets[0] = 0;
     }
     *out = b;
     return FLSGPU_OK;
@@ -938,10 +965,30 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       if (o.validity) o.validity += rows_done / 8;
       if (wb) o.data = (uint8_t *)o.data + rows_done * wb;
       else {
-        o.offsets += rows_done;
-        o.pay_base0 = pay_done[i];
         FlsColNeed sn = fls_column_need(t, c, s0, s1, h->image);
         pay_slice[i] = sn.payload_bytes - 16;
+        const auto &parts = b->parts[i];
+        if (!parts.empty()) {  // a wide column: one planner call per (slice x part), each with its own 32-bit base
+          for (size_t pk = 0; pk < parts.size() && perr.empty(); ++pk) {
+            const uint32_t pa = std::max(s0, parts[pk].g_first), pb = std::min(s1, pk + 1 < parts.size() ? parts[pk + 1].g_first : g1);
+            if (pa >= pb) continue;
+            FlsColOut o2 = o;
+            const uint64_t row_a = t.padded_rows(g0, pa);
+            o2.offsets = b->dev[i].offsets + row_a + 4 * pk;  // (the kernels store offsets 16 bytes at a time: parts keep that alignment)
+            o2.payload = b->dev[i].payload + parts[pk].pay_base;
+            o2.pay_base0 = 0;
+            for (uint32_t g = parts[pk].g_first; g < pa; ++g) o2.pay_base0 += t.chunk(g, c).aux64[0];
+            if (o.validity) o2.validity = b->dev[i].validity + row_a / 8;
+            FlsColNeed pn = fls_column_need(t, c, pa, pb, h->image);
+            o2.scratch = d_scratch ? d_scratch + scratch_col_base[i] + scratch_done[i] : nullptr;
+            scratch_done[i] += pn.scratch_bytes;
+            if (pa == parts[pk].g_first) CKB(cudaMemsetAsync(o2.offsets, 0, 4, h->s_h2d));  // (ordered before the slice's kernels)
+            perr = fls_plan_column(t, c, pa, pb, d_stage + (t.rgs[pa].off - t.rgs[g0].off), h->image, o2, ls);
+          }
+          continue;
+        }
+        o.offsets += rows_done;
+        o.pay_base0 = pay_done[i];
         o.scratch = d_scratch ? d_scratch + scratch_col_base[i] + scratch_done[i] : nullptr;
         scratch_done[i] += sn.scratch_bytes;
       }
@@ -1035,6 +1082,19 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
         CKB(cudaStreamWaitEvent(h->s_k, je, 0));
       }
     if (!perr.empty()) break;
+    // wide string columns: the parts' 32-bit offsets -> the caller's 64-bit offsets
+    for (uint32_t i = 0; i < nc; ++i) {
+      const auto &parts = b->parts[i];
+      for (size_t pk = 0; pk < parts.size(); ++pk) {
+        const uint32_t pa = std::max(s0, parts[pk].g_first), pb = std::min(s1, pk + 1 < parts.size() ? parts[pk + 1].g_first : g1);
+        if (pa >= pb) continue;
+        const uint64_t row_a = t.padded_rows(g0, pa), n = t.padded_rows(pa, pb) + 1;
+        fls_widen_offsets_kernel<<<(unsigned)std::min<uint64_t>((n + 255) / 256, 148 * 16), 256, 0, h->s_k>>>(
+            b->dev[i].offsets + row_a + 4 * pk, b->off64_dev[i] + row_a, n, parts[pk].pay_base);
+        b->tm.kernel_launches++;
+      }
+    }
+    CKB(cudaGetLastError());
     CKB(cudaEventRecord(ek.b, h->s_k));
     ev_k.push_back(ek);
     // D2H
@@ -1055,6 +1115,9 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
           b->tm.d2h_bytes += srows * wb;
         } else {
           const uint64_t o0 = rows_done ? rows_done + 1 : 0, o1 = rows_done + srows + 1;
+          if (b->off64_dev[i])
+            CKB(cudaMemcpyAsync(b->out[i].offsets64 + o0, b->off64_dev[i] + o0, (o1 - o0) * 8, cudaMemcpyDeviceToHost, h->s_d2h));
+          else
           CKB(cudaMemcpyAsync(b->out[i].offsets + o0, b->dev[i].offsets + o0, (o1 - o0) * 4, cudaMemcpyDeviceToHost, h->s_d2h));
           if (pay_slice[i])
             CKB(cudaMemcpyAsync(b->out[i].payload + pay_done[i], b->dev[i].payload + pay_done[i], pay_slice[i],
@@ -1137,6 +1200,8 @@ int flsgpu_decode_filtered(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t
     cudaError_t e_ = (call);                                                                             \
     if (e_ != cudaSuccess) return bail(FLSGPU_E_CUDA, std::string("CUDA: " #call ": ") + cudaGetErrorString(e_)); \
   } while (0)
+  for (auto &pp : b->parts)
+    if (!pp.empty()) return bail(FLSGPU_E_LIMIT, "a filtered decode cannot take a string column with 4 GiB of payload or more; split the row-group range");
   b->filtered = true;
   b->flags = flags;
   if (!n_vec) {
@@ -1343,9 +1408,17 @@ int flsgpu_batch_fetch(const flsgpu_batch_t *b, uint32_t i, void *values, uint32
   if (o.width) {
     if (values) CK(cudaMemcpy(values, d.data, o.padded_rows * o.width, cudaMemcpyDeviceToHost));
   } else {
+    if (offsets && i < b->off64_dev.size() && b->off64_dev[i]) return h->fail(FLSGPU_E_RANGE, "the column's offsets are 64-bit: flsgpu_batch_fetch_offsets64");
     if (offsets) CK(cudaMemcpy(offsets, d.offsets, (o.padded_rows + 1) * 4, cudaMemcpyDeviceToHost));
     if (values && o.payload_bytes) CK(cudaMemcpy(values, d.payload, o.payload_bytes, cudaMemcpyDeviceToHost));
   }
+  return FLSGPU_OK;
+}
+int flsgpu_batch_fetch_offsets64(const flsgpu_batch_t *b, uint32_t i, uint64_t *offsets64) {
+  flsgpu *h = b->h;
+  if (i >= b->out.size() || !offsets64 || i >= b->off64_dev.size() || !b->off64_dev[i]) return h->fail(FLSGPU_E_RANGE, "column has no 64-bit offsets");
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpy(offsets64, b->off64_dev[i], (b->out[i].padded_rows + 1) * 8, cudaMemcpyDeviceToHost));
   return FLSGPU_OK;
 }
 int flsgpu_batch_fetch_validity(const flsgpu_batch_t *b, uint32_t i, uint64_t *bits) {

@@ -114,6 +114,14 @@ struct FlsScanner::Impl {
     const uint32_t nc = flsgpu_batch_num_columns(cur.batch);
     cols.resize(nc);
     for (uint32_t i = 0; i < nc; ++i) flsgpu_batch_column(cur.batch, i, &cols[i]);
+    for (uint32_t i = 0; i < nc; ++i)
+      if (!cols[i].width && !cols[i].offsets) {  // a batch with 4 GiB of strings in one column: the cursor serves 32-bit offsets
+        err = "a batch of row groups holds 4 GiB or more of one string column: open the scanner with fewer row groups per batch";
+        to_release[cur.lane].push_back(cur.batch);
+        cur = Decoded();
+        if (old) to_release[old_lane].push_back(old);
+        return false;
+      }
     rg = cur.g0; rg_row = 0; rg_base = 0; f_row = 0;
     if (!filt.empty()) {
       uint64_t in = 0;

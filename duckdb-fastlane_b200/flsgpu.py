@@ -32,7 +32,7 @@ class Opts(C.Structure):
 class Column(C.Structure):
     _fields_ = [("type", C.c_int32), ("width", C.c_uint32), ("rows", C.c_uint64), ("padded_rows", C.c_uint64),
                 ("data", C.c_void_p), ("offsets", C.c_void_p), ("payload", C.c_void_p), ("payload_bytes", C.c_uint64),
-                ("compressed_bytes", C.c_uint64), ("decoded_bytes", C.c_uint64), ("validity", C.c_void_p)]
+                ("compressed_bytes", C.c_uint64), ("decoded_bytes", C.c_uint64), ("offsets64", C.c_void_p), ("validity", C.c_void_p)]
 
 
 class Timing(C.Structure):
@@ -105,6 +105,7 @@ def lib():
     L.flsgpu_batch_timing.argtypes = [vp, C.POINTER(Timing)]
     L.flsgpu_batch_fetch.argtypes = [vp, u32, vp, vp]
     L.flsgpu_batch_fetch_validity.argtypes = [vp, u32, vp]
+    L.flsgpu_batch_fetch_offsets64.argtypes = [vp, u32, vp]
     L.flsgpu_batch_release.argtypes = [vp]
     L.flsgpu_batch_release.restype = None
     L.flsgpu_num_kernel_stats.argtypes = [vp]
@@ -148,7 +149,10 @@ class Batch:
             dt = np.dtype(DTYPES[c.type])
             a = np.ctypeslib.as_array((C.c_uint8 * (n * c.width)).from_address(c.data)).view(dt) if n else np.empty(0, dt)
             return a.copy() if copy else a
-        offs = np.ctypeslib.as_array((C.c_uint32 * (n + 1)).from_address(c.offsets))
+        if c.offsets64:   # 4 GiB of payload or more in this batch: 64-bit offsets
+            offs = np.ctypeslib.as_array((C.c_uint64 * (n + 1)).from_address(c.offsets64))
+        else:
+            offs = np.ctypeslib.as_array((C.c_uint32 * (n + 1)).from_address(c.offsets))
         end = min(int(offs[n]), int(c.payload_bytes))  # a damaged file may decode to offsets past the payload buffer
         pay = np.ctypeslib.as_array((C.c_uint8 * end).from_address(c.payload)) if end else np.empty(0, np.uint8)
         return (offs.copy(), pay.copy()) if copy else (offs, pay)
@@ -162,8 +166,13 @@ class Batch:
             rc = lib().flsgpu_batch_fetch(self.h, i, a.ctypes.data, None)
             self.reader._check(rc)
             return a[:n]
-        offs = np.empty(c.padded_rows + 1, dtype=np.uint32)
         pay = np.empty(max(int(c.payload_bytes), 1), dtype=np.uint8)
+        if c.offsets64:
+            offs = np.empty(c.padded_rows + 1, dtype=np.uint64)
+            self.reader._check(lib().flsgpu_batch_fetch(self.h, i, pay.ctypes.data, None))
+            self.reader._check(lib().flsgpu_batch_fetch_offsets64(self.h, i, offs.ctypes.data))
+            return offs[:n + 1], pay[:min(int(offs[n]), len(pay))]
+        offs = np.empty(c.padded_rows + 1, dtype=np.uint32)
         self.reader._check(lib().flsgpu_batch_fetch(self.h, i, pay.ctypes.data, offs.ctypes.data))
         return offs[:n + 1], pay[:min(int(offs[n]), len(pay))]
 

@@ -41,7 +41,7 @@ enum flsgpu_status {
   FLSGPU_E_FORMAT = 2,  /* not an FLS file, or corrupt footer */
   FLSGPU_E_RANGE = 3,   /* bad row-group range / column id / argument */
   FLSGPU_E_CUDA = 4,    /* CUDA runtime failure (message in flsgpu_last_error) */
-  FLSGPU_E_LIMIT = 5,   /* batch exceeds a format limit (e.g. > 4 GiB string payload per batch) */
+  FLSGPU_E_LIMIT = 5,   /* batch exceeds a limit (a filtered decode over a string column with >= 4 GiB of payload) */
   FLSGPU_E_NOMEM = 6
 };
 
@@ -92,6 +92,8 @@ typedef struct {
   uint64_t payload_bytes; /* strings: bytes of payload in use */
   uint64_t compressed_bytes; /* algorithmic bytes read: segment bytes of this column in [g0,g1) */
   uint64_t decoded_bytes;    /* algorithmic bytes written: values, or offsets + payload */
+  uint64_t *offsets64;    /* strings whose payload in this batch reaches 4 GiB: `offsets` is NULL and this holds
+                             padded_rows + 1 64-bit offsets instead (NULL otherwise) */
   uint64_t *validity;     /* NULL: every row holds a value.  Else a bitmap over the padded rows, bit r (LSB first, 64
                              rows per word, DuckDB's ValidityMask layout) = row r is not NULL; a NULL row's value /
                              string is a filler.  The reference ignores FastLanes' null maps
@@ -170,6 +172,8 @@ int flsgpu_batch_timing(const flsgpu_batch_t *b, flsgpu_timing *out);
 /* Copy column i of a FLSGPU_OUT_DEVICE batch to caller memory: `values` receives padded_rows * width bytes
  * (fixed width) or payload_bytes bytes (strings); `offsets` (strings only) receives padded_rows + 1 entries. */
 int flsgpu_batch_fetch(const flsgpu_batch_t *b, uint32_t i, void *values, uint32_t *offsets);
+/* The same for a column that carries offsets64: padded_rows + 1 entries. */
+int flsgpu_batch_fetch_offsets64(const flsgpu_batch_t *b, uint32_t i, uint64_t *offsets64);
 /* The same for column i's validity bitmap: (padded_rows + 63) / 64 words; FLSGPU_E_RANGE when the column has none. */
 int flsgpu_batch_fetch_validity(const flsgpu_batch_t *b, uint32_t i, uint64_t *bits);
 /* Returns the batch's buffers to the handle's pool. */
