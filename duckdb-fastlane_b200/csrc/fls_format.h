@@ -64,6 +64,10 @@ enum fls_scheme {
   FLS_S_CROSS_RLE = 14,    // B run values (aux32 x T) + B run ends (aux32 x u32, cumulative, in padded rows of the row
                            //     group): runs span vectors
   FLS_S_EQUAL = 15,        // the chunk equals column aux32's chunk of the same row group (no segments)
+  FLS_S_STR_FSST12 = 16,   // FSST with 12-bit codes: S dec end-offsets + S cmp end-offsets (both DELTA u32) + B symbol table
+                           //   (aux32 = n symbols <= 4096: u64 symbol[n] | u8 len[n]; codes 0..255 are the bytes themselves,
+                           //   there is no escape) + B compressed bytes (+16 slack).  A string's codes are packed LSB first,
+                           //   12 bits each, padded to whole bytes: L compressed bytes hold floor(2 L / 3) codes
   FLS_S_N
 };
 

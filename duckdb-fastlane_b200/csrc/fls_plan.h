@@ -21,7 +21,7 @@ enum FlsKernelKind {
   FLS_K_STR_FSST,
   FLS_K_STR_FSST_DICTPREP,  // decode an FSST-compressed dictionary into scratch
   FLS_K_VALIDITY,           // validity bitmap of a chunk (copied, or all ones) -> the column's bitmap
-  FLS_K_FFOR_PATCH, FLS_K_CROSS_RLE,
+  FLS_K_FFOR_PATCH, FLS_K_CROSS_RLE, FLS_K_STR_FSST12,
   FLS_K_N
 };
 
@@ -182,6 +182,7 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
         case FLS_S_STR_CONSTANT: fls_launch_for(ls, FLS_K_STR_CONST, 0).add(d, rd, wr); break;
         case FLS_S_STR_DICT: fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, rd, wr, g); break;
         case FLS_S_STR_FSST: fls_launch_for(ls, FLS_K_STR_FSST, 0).add(d, rd, wr, g); break;
+        case FLS_S_STR_FSST12: fls_launch_for(ls, FLS_K_STR_FSST12, 0).add(d, rd, wr); break;
         case FLS_S_STR_FSST_DICT: {
           if (!host_image) return "FSST_DICT planning needs the host image";
           uint32_t sz;

@@ -75,6 +75,53 @@ struct VecSTRCONST {
   }
 };
 
+// ===================================================================== FSST12 strings (12-bit codes, up to 4096 symbols)
+// chunk: seg[0]/[1] = decoded end-offset stream, seg[2]/[3] = compressed end-offset stream (both DELTA u32),
+//        seg[4] = symbol table (u64 symbol[aux32] | u8 len[aux32]; codes 0..255 = the bytes themselves, no escape),
+//        seg[5] = compressed bytes.  A string's codes are packed LSB first, two per three bytes.
+// The plain decoder: one warp per vector, both offset streams walked into the warp's tile one after the other, then
+// every lane decodes every 32nd string byte-wise with the 36 KB table read through L1 / L2.  (The 8-bit FSST kernel
+// keeps its table in shared memory; a 4096-entry table does not fit its replicated layout.  FSST12 chunks are written
+// only on request, the lineitem shape has none.)
+struct VecSTRFSST12 {
+  static constexpr uint32_t SMEM = DecDELTA<uint32_t>::SMEM, BLOCK_SMEM = 0;
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
+    uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
+    if (bwd > 32u) bwd = 32u;
+    if (bwc > 32u) bwc = 32u;
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i, offs[i + 1] its end
+    const uint32_t *tile = (const uint32_t *)(w.sm + DecDELTA<uint32_t>::STAGE);
+    DecDELTA<uint32_t>::to_tile(w, k.seg[1] + 16ull * hd.ep, bwd, hd.base);
+    const uint32_t dv0 = ((const uint32_t *)w.sm)[0];  // lane 0's base = the vector's first decoded start
+    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + DecDELTA<uint32_t>::STAGE, offs + 1, t, k.pay_base); }
+    DecDELTA<uint32_t>::to_tile(w, k.seg[3] + 16ull * hc.ep, bwc, hc.base);
+    const uint32_t cv0 = ((const uint32_t *)w.sm)[0];
+    const uint64_t *sym = (const uint64_t *)k.seg[4];
+    const uint32_t n_sym = k.aux32 < 4096u ? k.aux32 : 4096u;
+    const uint8_t *len = k.seg[4] + 8ull * k.aux32, *comp = k.seg[5];
+    uint8_t *pay = k.pay + k.pay_base;
+    FLS_LANES(t) {
+      for (uint32_t i = t; i < FLS_VEC; i += 32u) {
+        const uint32_t c0 = i ? tile[fls_tile_slot<uint32_t>(i - 1u)] : cv0, c1 = tile[fls_tile_slot<uint32_t>(i)];
+        // decoded extent of the string: what phase 1 has just written (read back through L2), bounded by the row group's payload
+        uint64_t d0 = (i ? fls_ldcg(offs + i) - k.pay_base : dv0), d1 = fls_ldcg(offs + i + 1u) - k.pay_base;
+        if (c1 < c0 || c1 > k.aux64[1] || d1 < d0 || d1 > k.aux64[0]) continue;  // damaged offsets: nothing is written
+        const uint32_t n_codes = 2u * (c1 - c0) / 3u;
+        const uint8_t *in = comp + c0;
+        for (uint32_t q = 0; q < n_codes && d0 < d1; ++q) {
+          const uint8_t *p = in + 3u * (q >> 1);
+          uint32_t c = (q & 1u) ? ((uint32_t)fls_ldg(p + 1) >> 4) | ((uint32_t)fls_ldg(p + 2) << 4)
+                                : (uint32_t)fls_ldg(p) | (((uint32_t)fls_ldg(p + 1) & 15u) << 8);
+          if (c >= n_sym) c = 0;
+          uint64_t s = fls_ldg(sym + c);
+          for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(len + c)); b && d0 < d1; --b) { pay[d0++] = (uint8_t)s; s >>= 8; }
+        }
+      }
+    }
+  }
+};
+
 // ---- staged word writer.  A lane appends pieces of <= 8 bytes to ONE contiguous run inside the warp's shared
 // staging buffer.  State: `o` = 4-aligned address of the word being filled, `n8` = 8 * (bytes pending in that
 // word, 0..3), `prev` = a word whose TOP n8/8 bytes are the pending bytes.  A piece comes as a 16-byte table

@@ -217,6 +217,19 @@ static inline std::string fls_validate_chunk(const FlsTable &t, uint32_t g, uint
       if (!e) e = check_stream(s[2], s[3], n_vec, need);
       break;
     }
+    case FLS_S_STR_FSST12: {
+      if (wb) return bad(g, c, "string scheme on a fixed-width column");
+      if (!need_segs(6)) return bad(g, c, "missing segments");
+      if (k.aux32 < 256u || k.aux32 > 4096u || s[4].size < 9ull * k.aux32) return bad(g, c, "symbol table does not hold its symbol count");
+      if (s[5].size < 16 || k.aux64[1] > s[5].size - 16) return bad(g, c, "compressed bytes shorter than declared");
+      auto need = [&](uint32_t, uint32_t meta, uint64_t &b) {
+        b = 128u + 128ull * clamp(FLS_META_BW(meta), 32u);
+        return true;
+      };
+      e = check_stream(s[0], s[1], n_vec, need);
+      if (!e) e = check_stream(s[2], s[3], n_vec, need);
+      break;
+    }
     default: return bad(g, c, "unknown scheme");
   }
   if (e) return bad(g, c, e);

@@ -789,6 +789,71 @@ static Chunk enc_str_fsst(const uint8_t *bytes, const uint64_t *off, uint32_t n_
   return c;
 }
 
+// FSST12: up to 4096 symbols, 12-bit codes, codes 0..255 = the bytes themselves (no escape).  The table here is the
+// 3840 substrings of 2..8 bytes with the largest count x (length - 1) in a sample; compression is greedy longest match.
+static Chunk enc_str_fsst12(const uint8_t *bytes, const uint64_t *off, uint32_t n_vec) {
+  Chunk c; c.scheme = FLS_S_STR_FSST12;
+  const size_t n = (size_t)n_vec * FLS_VEC;
+  struct Key { uint64_t s; uint32_t l; bool operator==(const Key &o) const { return s == o.s && l == o.l; } };
+  struct KeyHash { size_t operator()(const Key &k) const { return (size_t)((k.s * 0x9E3779B97F4A7C15ull) ^ (k.l * 0xC2B2AE3D27D4EB4Full)); } };
+  auto key_at = [](const uint8_t *p, uint32_t l) { uint64_t s = 0; memcpy(&s, p, l); return Key{s, l}; };
+  std::unordered_map<Key, uint64_t, KeyHash> cnt;
+  const size_t total = off[n] - off[0], step = std::max<size_t>(1, total / 65536);
+  for (size_t i = 0; i < n; i += step) {
+    const uint8_t *p = bytes + off[i];
+    const size_t len = off[i + 1] - off[i];
+    for (size_t a = 0; a < len; ++a)
+      for (uint32_t l = 2; l <= 8 && a + l <= len; ++l) cnt[key_at(p + a, l)]++;
+  }
+  std::vector<std::pair<uint64_t, Key>> cand;
+  for (auto &kv : cnt) if (kv.second > 1) cand.push_back({kv.second * (kv.first.l - 1), kv.first});
+  std::sort(cand.begin(), cand.end(), [](const std::pair<uint64_t, Key> &a, const std::pair<uint64_t, Key> &b) {
+    return a.first != b.first ? a.first > b.first : (a.second.l != b.second.l ? a.second.l > b.second.l : a.second.s < b.second.s); });
+  if (cand.size() > 4096 - 256) cand.resize(4096 - 256);
+  std::vector<uint64_t> sym(256 + cand.size());
+  std::vector<uint8_t> slen(256 + cand.size());
+  std::unordered_map<Key, uint32_t, KeyHash> code;
+  for (uint32_t b = 0; b < 256; ++b) { sym[b] = b; slen[b] = 1; }
+  for (size_t k = 0; k < cand.size(); ++k) { sym[256 + k] = cand[k].second.s; slen[256 + k] = (uint8_t)cand[k].second.l; code[cand[k].second] = (uint32_t)(256 + k); }
+  std::vector<uint32_t> dec_ends(n), cmp_ends(n);
+  Bytes comp;
+  for (size_t i = 0; i < n; ++i) {
+    const uint8_t *p = bytes + off[i];
+    const size_t len = off[i + 1] - off[i];
+    std::vector<uint32_t> codes;
+    for (size_t a = 0; a < len;) {
+      uint32_t cd = p[a], adv = 1;
+      for (uint32_t l = (uint32_t)std::min<size_t>(8, len - a); l >= 2; --l) {
+        auto it = code.find(key_at(p + a, l));
+        if (it != code.end()) { cd = it->second; adv = l; break; }
+      }
+      codes.push_back(cd);
+      a += adv;
+    }
+    for (size_t k = 0; k + 1 < codes.size(); k += 2) {  // two codes in three bytes, LSB first
+      const uint32_t w = codes[k] | (codes[k + 1] << 12);
+      comp.push_back((uint8_t)w); comp.push_back((uint8_t)(w >> 8)); comp.push_back((uint8_t)(w >> 16));
+    }
+    if (codes.size() & 1) { const uint32_t w = codes.back(); comp.push_back((uint8_t)w); comp.push_back((uint8_t)(w >> 8)); }
+    dec_ends[i] = (uint32_t)(off[i + 1] - off[0]);
+    cmp_ends[i] = (uint32_t)comp.size();
+  }
+  Stream sd, sc;
+  offsets_stream(sd, dec_ends, n_vec); sd.move_into(c);
+  offsets_stream(sc, cmp_ends, n_vec); sc.move_into(c);
+  Bytes tb;
+  put_bytes(tb, sym.data(), sym.size() * 8);
+  put_bytes(tb, slen.data(), slen.size());
+  c.segs.push_back(std::move(tb));
+  c.aux32 = (uint32_t)sym.size();
+  c.aux64[0] = off[n] - off[0];
+  c.aux64[1] = comp.size();
+  pad_to(comp, 16);
+  comp.resize(comp.size() + 16, 0);
+  c.segs.push_back(std::move(comp));
+  return c;
+}
+
 static bool enc_str_dict(const uint8_t *bytes, const uint64_t *off, uint32_t n_vec, uint32_t max_dict, bool fsst,
                          Chunk &c, int force_bw = -1) {
   size_t n = (size_t)n_vec * FLS_VEC;
@@ -845,6 +910,7 @@ static Chunk enc_str_auto(const uint8_t *bytes, const uint64_t *off, uint32_t n_
   Chunk c;
   if (force == FLS_S_STR_UNCOMPRESSED) return enc_str_uncompressed(bytes, off, n_vec);
   if (force == FLS_S_STR_FSST) return enc_str_fsst(bytes, off, n_vec);
+  if (force == FLS_S_STR_FSST12) return enc_str_fsst12(bytes, off, n_vec);
   if (force == FLS_S_STR_DICT || force == FLS_S_STR_FSST_DICT) {
     if (enc_str_dict(bytes, off, n_vec, 1u << 20, force == FLS_S_STR_FSST_DICT, c, force_bw)) return c;
     return enc_str_fsst(bytes, off, n_vec);
@@ -866,6 +932,7 @@ static Chunk enc_str_auto(const uint8_t *bytes, const uint64_t *off, uint32_t n_
     return best;
   }
   best = enc_str_fsst(bytes, off, n_vec);
+  // (FSST12 is written only on request — flsw_force_scheme — so that the lineitem-shaped benchmark keeps its FSST column)
   { Chunk u = enc_str_uncompressed(bytes, off, n_vec); if (u.bytes() < best.bytes()) best = std::move(u); }
   return best;
 }

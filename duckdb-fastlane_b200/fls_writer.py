@@ -15,9 +15,9 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 BOOLEAN, INT8, INT16, INT32, INT64, UINT8, UINT16, UINT32, UINT64, FLOAT, DOUBLE, STR, DATE, BYTE_ARRAY = range(1, 15)
 # enum fls_scheme
 (UNCOMPRESSED, CONSTANT, FFOR, DELTA, RLE, DICT, ALP, ALP_RD,
- STR_UNCOMPRESSED, STR_CONSTANT, STR_DICT, STR_FSST, STR_FSST_DICT, FFOR_PATCH, CROSS_RLE, EQUAL) = range(16)
+ STR_UNCOMPRESSED, STR_CONSTANT, STR_DICT, STR_FSST, STR_FSST_DICT, FFOR_PATCH, CROSS_RLE, EQUAL, STR_FSST12) = range(17)
 SCHEME_NAMES = ["UNCOMPRESSED", "CONSTANT", "FFOR", "DELTA", "RLE", "DICT", "ALP", "ALP_RD",
-                "STR_UNCOMPRESSED", "STR_CONSTANT", "STR_DICT", "STR_FSST", "STR_FSST_DICT", "FFOR_PATCH", "CROSS_RLE", "EQUAL"]
+                "STR_UNCOMPRESSED", "STR_CONSTANT", "STR_DICT", "STR_FSST", "STR_FSST_DICT", "FFOR_PATCH", "CROSS_RLE", "EQUAL", "STR_FSST12"]
 
 TYPE_OF_DTYPE = {
     np.dtype(np.bool_): BOOLEAN, np.dtype(np.int8): INT8, np.dtype(np.int16): INT16, np.dtype(np.int32): INT32,

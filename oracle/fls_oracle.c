@@ -29,7 +29,7 @@
 enum { T_BOOL = 1, T_I8, T_I16, T_I32, T_I64, T_U8, T_U16, T_U32, T_U64, T_FLT, T_DBL, T_STR, T_DATE, T_BYTES };
 enum { S_UNCOMP = 0, S_CONST, S_FFOR, S_DELTA, S_RLE, S_DICT, S_ALP, S_ALPRD,
        S_STR_UNCOMP, S_STR_CONST, S_STR_DICT, S_STR_FSST, S_STR_FSST_DICT,
-       S_FFOR_PATCH, S_CROSS_RLE, S_EQUAL };
+       S_FFOR_PATCH, S_CROSS_RLE, S_EQUAL, S_STR_FSST12 };
 
 static const uint8_t ORDER[8] = {0, 4, 2, 6, 1, 5, 3, 7};
 
@@ -341,6 +341,24 @@ uint64_t flso_fsst_decode(const uint8_t *symtab, const uint8_t *in, uint64_t n_i
   return o;
 }
 
+/* ---- FSST12 (upstream libfsst's fsst12.h is not in the reference tree: restated, UNVERIFIED): 12-bit
+ *      codes packed LSB first, two codes per three bytes; L compressed bytes hold floor(2 L / 3) codes; code c expands to
+ *      symbol[c] (len[c] bytes); codes 0..255 are the bytes themselves, there is no escape.  Table blob: u64 symbol[n] | u8
+ *      len[n]. */
+uint64_t flso_fsst12_decode(const uint8_t *symtab, uint32_t n_sym, const uint8_t *in, uint64_t n_in, uint8_t *out) {
+  const uint64_t *sym = (const uint64_t *)symtab;
+  const uint8_t *len = symtab + 8ull * n_sym;
+  uint64_t o = 0, n_codes = 2 * n_in / 3;
+  for (uint64_t k = 0; k < n_codes; ++k) {
+    const uint8_t *p = in + 3 * (k / 2);
+    uint32_t c = (k & 1) ? ((uint32_t)p[1] >> 4) | ((uint32_t)p[2] << 4) : (uint32_t)p[0] | (((uint32_t)p[1] & 15u) << 8);
+    if (c >= n_sym) c = 0;
+    uint64_t s = sym[c];
+    for (unsigned b = 0; b < len[c] && b < 8; ++b) out[o++] = (uint8_t)(s >> (8 * b));
+  }
+  return o;
+}
+
 /* offsets stream: DELTA u32 over END offsets -> ends[n_vec*1024] */
 static void ends_stream(const uint8_t *rgp, const ochunk *k, unsigned s0, uint32_t n_vec, uint32_t *ends) {
   const ovhdr *h = (const ovhdr *)(rgp + k->seg[s0].off);
@@ -382,6 +400,20 @@ static int chunk_str(const uint8_t *rgp, const ochunk *k, uint32_t n_vec, uint32
         uint32_t cs = i ? ce[i - 1] : 0, ds = i ? de[i - 1] : 0;
         uint64_t got = flso_fsst_decode(symtab, comp + cs, ce[i] - cs, pay + ds);
         if (got != de[i] - ds) { free(de); free(ce); return 21; }
+        offs[i + 1] = base + de[i];
+      }
+      free(de); free(ce);
+      return 0;
+    }
+    case S_STR_FSST12: {
+      uint32_t *de = (uint32_t *)malloc(n * 4), *ce = (uint32_t *)malloc(n * 4);
+      ends_stream(rgp, k, 0, n_vec, de);
+      ends_stream(rgp, k, 2, n_vec, ce);
+      const uint8_t *symtab = rgp + k->seg[4].off, *comp = rgp + k->seg[5].off;
+      for (size_t i = 0; i < n; ++i) {
+        uint32_t cs = i ? ce[i - 1] : 0, ds = i ? de[i - 1] : 0;
+        uint64_t got = flso_fsst12_decode(symtab, k->aux32, comp + cs, ce[i] - cs, pay + ds);
+        if (got != de[i] - ds) { free(de); free(ce); return 23; }
         offs[i + 1] = base + de[i];
       }
       free(de); free(ce);

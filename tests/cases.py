@@ -224,6 +224,12 @@ def string_cases(n=70_000):
                 [W.STR_DICT], None))
     out.append(("str_dict_3000_entries_bw23", [StrColumn.from_list([big[i] for i in r.integers(0, len(big), n)])], None,
                 [W.STR_DICT], [23]))
+    # FSST12: 12-bit codes, up to 4096 symbols, no escape
+    out.append(("str_fsst12_comment", [li[15]], None, [W.STR_FSST12], None))
+    out.append(("str_fsst12_shipinstruct", [li[13]], None, [W.STR_FSST12], None))
+    out.append(("str_fsst12_random_0_40", [_rand_strings(r, n, 0, 40)], None, [W.STR_FSST12], None))
+    out.append(("str_fsst12_binary", [_rand_strings(r, 5000, 0, 90, alphabet=bytes(range(256)))], None, [W.STR_FSST12], None))
+    out.append(("str_fsst12_all_empty", [StrColumn.from_list([b""] * 3000)], None, [W.STR_FSST12], None))
     # compressed bytes of one vector exceed the kernel's shared-memory window -> streaming fallback path
     out.append(("str_fsst_long_fallback", [_rand_strings(r, 9000, 60, 200)], None, [W.STR_FSST], None))
     # pass sizes 128 / 64 / 32 strings (a pass of 256 would not fit the staging buffer), and a mix within one column

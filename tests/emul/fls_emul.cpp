@@ -86,6 +86,7 @@ static bool run_launch(const FlsLaunch &l) {
       for (auto &k : l.chunks) fls_str_copy_chunk_host(k);
       return true;
     case FLS_K_STR_CONST: run_vectors<VecSTRCONST>(l); return true;
+    case FLS_K_STR_FSST12: run_vectors<VecSTRFSST12>(l); return true;
     case FLS_K_STR_DICT: run_vectors<VecSTRDICT>(l); return true;
     case FLS_K_STR_FSST: run_vectors<VecSTRFSST>(l); return true;
     case FLS_K_STR_FSST_DICTPREP:
