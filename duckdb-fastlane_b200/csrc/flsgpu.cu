@@ -1430,6 +1430,54 @@ int flsgpu_batch_fetch_validity(const flsgpu_batch_t *b, uint32_t i, uint64_t *b
   CK(cudaMemcpy(bits, b->dev[i].validity, (b->out[i].padded_rows + 63) / 64 * 8, cudaMemcpyDeviceToHost));
   return FLSGPU_OK;
 }
+// Result gather over NVLink (optional; the reference merges per-thread DataChunks on the host,
+// /root/reference/src/scanner/scan_fastlanes.cpp:89-120).  Peer access is switched on once per (source, destination)
+// pair; without it cudaMemcpyPeerAsync stages through the host and still completes.
+int flsgpu_batch_copy_to_device(const flsgpu_batch_t *b, uint32_t i, int32_t dst_device, void *dst_values, void *dst_offsets,
+                                float *ms) {
+  flsgpu *h = b->h;
+  if (i >= b->out.size()) return h->fail(FLSGPU_E_RANGE, "bad column index");
+  if (dst_device < 0 || dst_device >= flsgpu_device_count()) return h->fail(FLSGPU_E_RANGE, "no such destination device");
+  const flsgpu_column &o = b->out[i];
+  const FlsColOut &d = b->dev[i];
+  if (!d.data && !d.offsets) return h->fail(FLSGPU_E_RANGE, "the batch holds no device copy of this column");
+  CK(cudaSetDevice(h->device));
+  if (dst_device != h->device) {
+    int can = 0;
+    CK(cudaDeviceCanAccessPeer(&can, h->device, dst_device));
+    if (can) {
+      const cudaError_t e = cudaDeviceEnablePeerAccess(dst_device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CK(e);
+      (void)cudaGetLastError();
+    }
+  }
+  cudaEvent_t ea = nullptr, eb = nullptr;
+  if (ms) {
+    CK(cudaEventCreate(&ea));
+    CK(cudaEventCreate(&eb));
+    CK(cudaEventRecord(ea, h->s_d2h));
+  }
+  auto push = [&](void *dst, const void *src, size_t n) -> cudaError_t {
+    if (!dst || !n) return cudaSuccess;
+    return cudaMemcpyPeerAsync(dst, dst_device, src, h->device, n, h->s_d2h);
+  };
+  cudaError_t e = cudaSuccess;
+  if (o.width) {
+    e = push(dst_values, d.data, (size_t)o.padded_rows * o.width);
+  } else {
+    const bool wide = i < b->off64_dev.size() && b->off64_dev[i];
+    e = wide ? push(dst_offsets, b->off64_dev[i], (size_t)(o.padded_rows + 1) * 8)
+             : push(dst_offsets, d.offsets, (size_t)(o.padded_rows + 1) * 4);
+    if (e == cudaSuccess) e = push(dst_values, d.payload, (size_t)o.payload_bytes);
+  }
+  if (e == cudaSuccess && ms) e = cudaEventRecord(eb, h->s_d2h);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(h->s_d2h);
+  if (e == cudaSuccess && ms) e = cudaEventElapsedTime(ms, ea, eb);
+  if (ea) cudaEventDestroy(ea);
+  if (eb) cudaEventDestroy(eb);
+  CK(e);
+  return FLSGPU_OK;
+}
 void flsgpu_batch_release(flsgpu_batch_t *b) {
   if (!b) return;
   for (void *p : b->dev_bufs) b->h->dev_free(p);

@@ -106,6 +106,7 @@ def lib():
     L.flsgpu_batch_fetch.argtypes = [vp, u32, vp, vp]
     L.flsgpu_batch_fetch_validity.argtypes = [vp, u32, vp]
     L.flsgpu_batch_fetch_offsets64.argtypes = [vp, u32, vp]
+    L.flsgpu_batch_copy_to_device.argtypes = [vp, u32, C.c_int32, vp, vp, C.POINTER(C.c_float)]
     L.flsgpu_batch_release.argtypes = [vp]
     L.flsgpu_batch_release.restype = None
     L.flsgpu_num_kernel_stats.argtypes = [vp]
@@ -198,6 +199,13 @@ class Batch:
             return None
         assert self.to_host
         return np.ctypeslib.as_array(ids, shape=(n.value,)).copy() if n.value else np.empty(0, np.uint64)
+
+    def copy_to_device(self, i, dst_device, dst_values, dst_offsets=None):
+        """flsgpu_batch_copy_to_device: column i of a device-output batch into caller buffers (raw device pointers) on
+        `dst_device`.  Returns the copies' device time in ms."""
+        ms = C.c_float()
+        self.reader._check(lib().flsgpu_batch_copy_to_device(self.h, i, dst_device, dst_values, dst_offsets, C.byref(ms)))
+        return float(ms.value)
 
     def release(self):
         if self.h:

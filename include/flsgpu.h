@@ -176,6 +176,14 @@ int flsgpu_batch_fetch(const flsgpu_batch_t *b, uint32_t i, void *values, uint32
 int flsgpu_batch_fetch_offsets64(const flsgpu_batch_t *b, uint32_t i, uint64_t *offsets64);
 /* The same for column i's validity bitmap: (padded_rows + 63) / 64 words; FLSGPU_E_RANGE when the column has none. */
 int flsgpu_batch_fetch_validity(const flsgpu_batch_t *b, uint32_t i, uint64_t *bits);
+/* Optional result gather (the reference merges its threads' DataChunks on the host,
+ * src/scanner/scan_fastlanes.cpp:89-120): copy column i of a batch that holds device buffers (FLSGPU_OUT_DEVICE) into
+ * buffers the caller owns on device `dst_device` — NVLink peer copies when the two GPUs can reach each other,
+ * staged through the host by the driver otherwise.  Sizes are those of flsgpu_batch_fetch; `dst_offsets` receives
+ * 32-bit entries, or 64-bit ones when the column carries offsets64.  NULL destinations are skipped.  Returns when
+ * the copies are complete; *ms (may be NULL) = their device time. */
+int flsgpu_batch_copy_to_device(const flsgpu_batch_t *b, uint32_t i, int32_t dst_device, void *dst_values,
+                                void *dst_offsets, float *ms);
 /* Returns the batch's buffers to the handle's pool. */
 void flsgpu_batch_release(flsgpu_batch_t *b);
 
