@@ -1514,3 +1514,104 @@ int flsgpu_flush_l2(flsgpu_t *h, uint64_t bytes) {
 }
 
 }  // extern "C"
+
+// ---- selection without allocation (include/flsgpu.h: flsgpu_select_fixed_noalloc) ---------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc.  The selection kernels of flsgpu_decode_filtered run with their scratch in this file-scope array, which
+// every GPU that loads the library holds until exit (FLSGPU_NOALLOC_SCRATCH_BYTES = 608.25 KiB).  In host code the
+// array's NAME is a host-side stand-in, not a device address: the address each device gave it comes from
+// cudaGetSymbolAddress, once per device with that device current, and that is what the kernels get.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[FLSGPU_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr uint32_t kNoallocMaxVec = FLSGPU_NOALLOC_MAX_ROWS / FLS_VEC;
+// layout of g_noalloc_scratch (bytes); every part starts on a 256-byte boundary
+constexpr size_t kNaTotal = 0;                                        // uint64: running total of the scan
+constexpr size_t kNaValid = 256;                                      // uint32[n_vec]: real rows of each vector
+constexpr size_t kNaCnt = kNaValid + (size_t)kNoallocMaxVec * 4;      // uint32[n_vec]: survivors of each vector
+constexpr size_t kNaOff = kNaCnt + (size_t)kNoallocMaxVec * 4;        // uint64[n_vec]: exclusive scan of the counts
+constexpr size_t kNaRow0 = kNaOff + (size_t)kNoallocMaxVec * 8;       // uint64[n_vec]: first row of each vector
+constexpr size_t kNaMask = kNaRow0 + (size_t)kNoallocMaxVec * 8;      // uint32[n_vec * 32]: one bit per row
+static_assert(kNaMask + (size_t)kNoallocMaxVec * 128 == FLSGPU_NOALLOC_SCRATCH_BYTES, "scratch layout and header disagree");
+static_assert(kNaCnt % 256 == 0 && kNaOff % 256 == 0 && kNaRow0 % 256 == 0 && kNaMask % 256 == 0, "scratch parts are 256-byte aligned");
+
+constexpr int kNaMaxDev = 64;
+std::mutex g_na_mu;
+unsigned char *g_na_ptr[kNaMaxDev];  // device address of g_noalloc_scratch on each device (null: not resolved yet)
+
+// valid[v] = real rows of vector v, row0[v] = index of its first row
+__global__ void __launch_bounds__(256) noalloc_meta_kernel(uint64_t n_rows, uint32_t n_vec, uint32_t *__restrict__ valid,
+                                                           uint64_t *__restrict__ row0) {
+  const uint32_t v = blockIdx.x * 256u + threadIdx.x;
+  if (v >= n_vec) return;
+  const uint64_t first = (uint64_t)v * FLS_VEC;
+  valid[v] = (uint32_t)(n_rows - first < FLS_VEC ? n_rows - first : FLS_VEC);
+  row0[v] = first;
+}
+__global__ void noalloc_count_kernel(const uint64_t *__restrict__ total, uint64_t *__restrict__ out) { *out = *total; }
+
+int na_fail(int code, const std::string &m) { g_open_err = m; return code; }
+}  // namespace
+
+extern "C" int flsgpu_select_fixed_noalloc(int32_t device, const void *values, int32_t type, uint64_t n_rows, uint32_t op,
+                                           int64_t i64, double f64, void *out_values, uint64_t *out_row_ids,
+                                           uint64_t *out_count, void *stream) {
+#define CKN(call)                                                                                   \
+  do {                                                                                              \
+    cudaError_t e_ = (call);                                                                        \
+    if (e_ != cudaSuccess) return na_fail(FLSGPU_E_CUDA, std::string("CUDA: " #call ": ") + cudaGetErrorString(e_)); \
+  } while (0)
+  if (device < 0 || device >= kNaMaxDev) return na_fail(FLSGPU_E_RANGE, "flsgpu_select_fixed_noalloc: no such device");
+  if (n_rows > FLSGPU_NOALLOC_MAX_ROWS)
+    return na_fail(FLSGPU_E_LIMIT, "flsgpu_select_fixed_noalloc: " + std::to_string(n_rows) + " rows exceed FLSGPU_NOALLOC_MAX_ROWS (" +
+                                       std::to_string(FLSGPU_NOALLOC_MAX_ROWS) + "): the scratch array is fixed; split the range");
+  const uint32_t width = type > FLS_T_INVALID && type < FLS_T_N ? fls_type_bits(type) / 8 : 0;
+  if (!width) return na_fail(FLSGPU_E_RANGE, "flsgpu_select_fixed_noalloc: not a fixed-width type");
+  if (op > FLSGPU_CMP_GE) return na_fail(FLSGPU_E_RANGE, "flsgpu_select_fixed_noalloc: bad comparison");
+  if (!out_count || (n_rows && !values)) return na_fail(FLSGPU_E_RANGE, "flsgpu_select_fixed_noalloc: null argument");
+  CKN(cudaSetDevice(device));
+  unsigned char *base;
+  {
+    std::lock_guard<std::mutex> lk(g_na_mu);
+    if (!g_na_ptr[device]) {
+      void *p = nullptr;
+      CKN(cudaGetSymbolAddress(&p, g_noalloc_scratch));  // this device's copy: the current device is `device`
+      g_na_ptr[device] = (unsigned char *)p;
+    }
+    base = g_na_ptr[device];
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  uint64_t *d_tot = (uint64_t *)(base + kNaTotal);
+  uint32_t *d_valid = (uint32_t *)(base + kNaValid), *d_cnt = (uint32_t *)(base + kNaCnt), *d_mask = (uint32_t *)(base + kNaMask);
+  uint64_t *d_off = (uint64_t *)(base + kNaOff), *d_row0 = (uint64_t *)(base + kNaRow0);
+  // the scan adds to the total: it is the one word that must start at zero; everything else the kernels read they wrote
+  // in this call (valid / row0 / cnt / off / mask entries [0, n_vec))
+  CKN(cudaMemsetAsync(d_tot, 0, 8, s));
+  const uint32_t n_vec = (uint32_t)((n_rows + FLS_VEC - 1) / FLS_VEC);
+  if (n_vec) {
+    FlsPredSet ps;
+    memset(&ps, 0, sizeof(ps));
+    ps.n = 1;
+    FlsPredDev &q = ps.p[0];
+    q.data = values; q.width = width; q.op = op; q.i64 = i64; q.f64 = f64;
+    if (type == FLS_T_FLOAT) q.kind = 2;
+    else if (type == FLS_T_DOUBLE) q.kind = 3;
+    else if (type == FLS_T_BOOLEAN || type == FLS_T_UINT8 || type == FLS_T_UINT16 || type == FLS_T_UINT32 || type == FLS_T_UINT64) q.kind = 1;
+    else q.kind = 0;
+    const uint32_t grid = (n_vec + 7) / 8;
+    noalloc_meta_kernel<<<(n_vec + 255) / 256, 256, 0, s>>>(n_rows, n_vec, d_valid, d_row0);
+    fls_filter::mask_kernel<<<grid, 256, 0, s>>>(ps, d_valid, n_vec, d_mask, d_cnt);
+    fls_filter::scan_kernel<<<1, 1024, 0, s>>>(d_cnt, n_vec, d_off, d_tot);
+    if (out_row_ids) fls_filter::compact_rowid_kernel<<<grid, 256, 0, s>>>(d_row0, d_mask, d_off, n_vec, out_row_ids);
+    if (out_values) switch (width) {
+      case 1: fls_filter::compact_fixed_kernel<uint8_t><<<grid, 256, 0, s>>>((const uint8_t *)values, d_mask, d_off, n_vec, (uint8_t *)out_values); break;
+      case 2: fls_filter::compact_fixed_kernel<uint16_t><<<grid, 256, 0, s>>>((const uint16_t *)values, d_mask, d_off, n_vec, (uint16_t *)out_values); break;
+      case 4: fls_filter::compact_fixed_kernel<uint32_t><<<grid, 256, 0, s>>>((const uint32_t *)values, d_mask, d_off, n_vec, (uint32_t *)out_values); break;
+      default: fls_filter::compact_fixed_kernel<uint64_t><<<grid, 256, 0, s>>>((const uint64_t *)values, d_mask, d_off, n_vec, (uint64_t *)out_values); break;
+    }
+  }
+  noalloc_count_kernel<<<1, 1, 0, s>>>(d_tot, out_count);
+  CKN(cudaGetLastError());
+  return FLSGPU_OK;
+#undef CKN
+}

@@ -115,6 +115,7 @@ def lib():
     L.flsgpu_reset_kernel_stats.argtypes = [vp]
     L.flsgpu_reset_kernel_stats.restype = None
     L.flsgpu_flush_l2.argtypes = [vp, u64]
+    L.flsgpu_select_fixed_noalloc.argtypes = [C.c_int32, vp, C.c_int32, u64, u32, C.c_int64, C.c_double, vp, vp, vp, vp]
     _lib = L
     return L
 
@@ -123,6 +124,22 @@ class FlsError(IOError):
     def __init__(self, code, msg):
         super().__init__(msg)
         self.code = code
+
+
+NOALLOC_MAX_ROWS = 4096 * 1024
+
+
+def select_fixed_noalloc(device, values, fls_type, n_rows, op, const, out_values, out_row_ids, out_count, stream=None):
+    """flsgpu_select_fixed_noalloc (include/flsgpu.h): every pointer is a raw device address the caller owns; the
+    kernels are launched on `stream` and not waited for.  Raises FlsError on a refused call."""
+    i64 = int(const) if not isinstance(const, float) else 0
+    f64 = float(const)
+    if i64 >= 1 << 63:
+        i64 -= 1 << 64
+    rc = lib().flsgpu_select_fixed_noalloc(device, values, fls_type, n_rows, CMP[op] if isinstance(op, str) else op, i64, f64,
+                                           out_values, out_row_ids, out_count, stream)
+    if rc:
+        raise FlsError(rc, (lib().flsgpu_last_error(None) or b"").decode("utf-8", "replace"))
 
 
 class Batch:

@@ -214,6 +214,32 @@ int flsgpu_decode_filtered(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t
  * batch's row count for an unfiltered batch. */
 int flsgpu_batch_selection(const flsgpu_batch_t *b, const uint64_t **ids, uint64_t *n);
 
+/* ---- selection without allocation ----------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * flsgpu_select_fixed_noalloc runs the selection kernels of flsgpu_decode_filtered (mask, scan, compaction) for ONE
+ * predicate `values[row] <op> constant` over a fixed-width column that is already decoded in HBM, with every scratch
+ * buffer (mask words, per-vector counts and offsets, the total) in a file-scope `static __device__` array of
+ * FLSGPU_NOALLOC_SCRATCH_BYTES that each GPU holds from the moment the library is loaded on it until exit.  It calls
+ * no cudaMalloc / cudaFree / allocating library routine; the caller passes every input and output:
+ *   device      CUDA device the pointers live on
+ *   values      device, n_rows values of `type` (enum fls_type: a fixed-width type, FLS_T_* of fls_format.h)
+ *   n_rows      at most FLSGPU_NOALLOC_MAX_ROWS, else FLSGPU_E_LIMIT and nothing is launched
+ *   op, i64, f64  the comparison, as in flsgpu_predicate (i64 for integer / BOOLEAN / DATE, f64 for FLOAT / DOUBLE)
+ *   out_values  device, room for n_rows values: receives the surviving values in row order (may be NULL)
+ *   out_row_ids device, room for n_rows uint64: receives the surviving rows' indices in row order (may be NULL)
+ *   out_count   device, one uint64: receives the number of surviving rows
+ *   stream      a cudaStream_t (NULL = the default stream); the kernels are launched on it and NOT waited for
+ * Every call on a device shares that device's scratch array, which keeps the previous call's contents (the entry
+ * point clears the one word that must start at zero): calls that overlap on the GPU — two streams, two threads —
+ * race; serialise them.  The first call on a device resolves the array's address (cudaGetSymbolAddress); call once
+ * with n_rows = 0 before a graph capture to get that out of the way.  Errors: flsgpu_last_error(NULL). */
+#define FLSGPU_NOALLOC_MAX_ROWS (4096u * 1024u)
+#define FLSGPU_NOALLOC_SCRATCH_BYTES (256u + 4096u * (4u + 4u + 8u + 8u + 128u))
+int flsgpu_select_fixed_noalloc(int32_t device, const void *values, int32_t type, uint64_t n_rows, uint32_t op,
+                                int64_t i64, double f64, void *out_values, uint64_t *out_row_ids,
+                                uint64_t *out_count, void *stream);
+
 /* ---- instrumentation ---------------------------------------------------------------------------------- */
 /* Per-kernel-family accumulators (needs FLSGPU_OPEN_TIME_KERNELS).  i in [0, flsgpu_num_kernel_stats). */
 uint32_t flsgpu_num_kernel_stats(const flsgpu_t *h);
