@@ -73,6 +73,10 @@ template <typename T> struct DecFFOR {
 };
 
 // ===================================================================== DELTA
+#ifndef FLS_DELTA_FASTW
+#define FLS_DELTA_FASTW 16u  /* widest delta the register-resident 64-bit path takes (0 = never) */
+#endif
+static_assert(FLS_DELTA_FASTW <= 16u, "narrow_deltas: 32 deltas must add up inside 32 bits, shift counts below 32");
 // payload: [lane bases 128 B][packed deltas 128*bw]; deltas are FFOR'd (wrapping + base).
 template <typename T> struct DecDELTA {
   static constexpr uint32_t TB = sizeof(T) * 8u, L = 1024u / TB;
@@ -109,6 +113,7 @@ template <typename T> struct DecDELTA {
   FLS_MEM static void run64(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
     w.stage(0, in, 128u + 128u * bw);
     w.wait();
+    if (bw >= 1u && bw <= FLS_DELTA_FASTW) { run64_narrow(w, bw, base, out); return; }
     const T *bases = (const T *)w.sm;
     const T *pk = (const T *)(w.sm + 128);
     {
@@ -141,6 +146,65 @@ template <typename T> struct DecDELTA {
       }
       FLS_LANES(t) { fls_tile_copy_out<T>(w.sm, out, t); }
     }
+  }
+  // T=64, deltas of W <= FLS_DELTA_FASTW bits (sorted keys: l_orderkey packs into 5-6 bits).  Thread (l, h) needs packed
+  // rows ORDER[4h + j/8] + 8 (j%8) = {0,4,2,6}[j/8] + 8 (j%8) + h of lane l: the even rows (h = 0) or the odd rows
+  // (h = 1) of the lane's bit stream.  The lane's W 64-bit words are loaded once into registers, shifted right by h W
+  // bits (so that both halves extract at the SAME, compile-time bit positions), and every delta is one funnel shift
+  // and one mask — against two shared loads, two 64-bit variable shifts and a 64-bit mask in fls_extract.
+  template <uint32_t W> FLS_MEM static void narrow_deltas(const uint8_t *lane_words, uint32_t h, uint32_t (&d)[32]) {
+    uint32_t wd[2u * W + 1u];
+#pragma unroll
+    for (uint32_t k = 0; k < W; ++k) {
+      const fls_u2 v = fls_lds64(lane_words + 128u * k);
+      wd[2u * k] = v.x; wd[2u * k + 1u] = v.y;
+    }
+    wd[2u * W] = 0u;
+    const uint32_t s0 = h * W;  // <= 16: a funnel shift's count
+#pragma unroll
+    for (uint32_t i = 0; i < 2u * W; ++i) wd[i] = fls_shf_r(wd[i], wd[i + 1u], s0);
+    constexpr uint32_t mask = (1u << W) - 1u;
+#pragma unroll
+    for (uint32_t j = 0; j < 32u; ++j) {
+      const uint32_t row = ((0x6240u >> (4u * (j >> 3))) & 0xFu) + 8u * (j & 7u);  // even rows, in chain order
+      const uint32_t bit = row * W, i = bit >> 5, s = bit & 31u;
+      d[j] = (s + W <= 32u ? wd[i] >> s : fls_shf_r(wd[i], wd[i + 1u], s)) & mask;
+    }
+  }
+  FLS_MEM static void run64_narrow(FlsWarp &w, uint32_t bw, uint64_t base, T *out) {
+    const T *bases = (const T *)w.sm;
+    uint64_t *xch = (uint64_t *)(w.sm + XCH);
+    T *tile = (T *)w.sm;  // overwrites the staged payload once every thread holds its deltas
+    FLS_VAR2(uint32_t, dl, 32);
+    FLS_VAR(uint64_t, lane_base);
+    FLS_LANES(t) {
+      const uint32_t l = t & 15u, h = t >> 4;
+      FLS_AT(lane_base) = (uint64_t)bases[l];
+      const uint8_t *lw = w.sm + 128u + 8u * l;
+      uint32_t d[32];
+      switch (bw) {  // warp-uniform
+#define FLS_DELTA_CASE(W) case W: narrow_deltas<W>(lw, h, d); break;
+        FLS_DELTA_CASE(1) FLS_DELTA_CASE(2) FLS_DELTA_CASE(3) FLS_DELTA_CASE(4) FLS_DELTA_CASE(5) FLS_DELTA_CASE(6)
+        FLS_DELTA_CASE(7) FLS_DELTA_CASE(8) FLS_DELTA_CASE(9) FLS_DELTA_CASE(10) FLS_DELTA_CASE(11) FLS_DELTA_CASE(12)
+        FLS_DELTA_CASE(13) FLS_DELTA_CASE(14) FLS_DELTA_CASE(15)
+#undef FLS_DELTA_CASE
+        default: narrow_deltas<16>(lw, h, d); break;
+      }
+      uint32_t tot = 0;  // 32 deltas of <= 16 bits
+#pragma unroll
+      for (uint32_t j = 0; j < 32u; ++j) { FLS_AT2(dl, j) = d[j]; tot += d[j]; }
+      xch[t] = (uint64_t)tot + 32ull * base;
+    }
+    FLS_LANES(t) {
+      const uint32_t l = t & 15u, h = t >> 4;
+      uint64_t acc = FLS_AT(lane_base) + (h ? xch[l] : 0ull);
+#pragma unroll
+      for (uint32_t j = 0; j < 32u; ++j) {
+        acc += (uint64_t)FLS_AT2(dl, j) + base;
+        tile[fls_tile_slot<T>(64u * l + 32u * h + j)] = (T)acc;
+      }
+    }
+    FLS_LANES(t) { fls_tile_copy_out<T>(w.sm, out, t); }
   }
   FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
     if constexpr (sizeof(T) == 8) {
@@ -249,22 +313,40 @@ FLS_DEV uint64_t fls_alp_value(uint64_t bits, double fact, double frac) {
 }
 
 struct DecALP {
-  static constexpr uint32_t SMEM = 8192u;
+  // The slot holds 32 packed word rows.  ALP integers are narrow (a vector that needs more than 32 bits is rare), and
+  // an 8 KB slot — what a 64-bit-wide vector would need — halves the resident warps of every launch.  Wider vectors
+  // are decoded in two passes of 32 output rows: the packed words of rows [32 p, 32 p + 32) are word rows
+  // [32 p W / 64, ((32 p + 32) W - 1) / 64], at most 32 of them.
+#ifndef FLS_ALP_SLOT
+#define FLS_ALP_SLOT 4096u
+#endif
+  static constexpr uint32_t SMEM = FLS_ALP_SLOT;
   FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint32_t e, uint32_t f, uint32_t n_exc,
                           uint64_t base, double *out) {
     const double fact = fls_alp_fact[f < 19u ? f : 18u], frac = fls_alp_frac[e < 21u ? e : 20u];
-    if (bw) { w.stage(0, in, 128u * bw); w.wait(); }
-    FLS_LANES(t) {
-      const uint32_t q = t & 7u, g = t >> 3;
+    const uint32_t passes = 128u * bw > SMEM ? 2u : 1u, rows = 64u / passes;
+    for (uint32_t ps = 0; ps < passes; ++ps) {
+      const uint32_t r0 = ps * rows;
+      uint32_t k0 = 0, k1 = 0;  // staged word rows [k0, k1]
+      if (bw) {
+        k0 = (r0 * bw) >> 6; k1 = ((r0 + rows) * bw - 1u) >> 6;
+        if (ps) w.fence_async();  // pass 0's reads of the slot before the next bulk copy lands in it
+        w.stage(0, in + 128u * k0, 128u * (k1 - k0 + 1u));
+        w.wait();
+      }
+      const uint8_t *sm0 = w.sm - 128u * k0;  // fls_unpack64_rows addresses word rows absolutely; it reads [k0, k1] only
+      FLS_LANES(t) {
+        const uint32_t q = t & 7u, g = t >> 3, per = rows / 4u;
 #pragma unroll 4
-      for (uint32_t j = 0; j < 16u; ++j) {
-        const uint32_t row = g * 16u + j;
-        fls_ul2 v;
-        if (bw) v = fls_unpack64_row(w.sm, bw, row, q, base);
-        else { v.x = base; v.y = base; }
-        v.x = fls_alp_value(v.x, fact, frac);
-        v.y = fls_alp_value(v.y, fact, frac);
-        fls_st128((uint8_t *)out + row * 128u + q * 16u, v);
+        for (uint32_t j = 0; j < per; ++j) {
+          const uint32_t row = r0 + g * per + j;
+          fls_ul2 v;
+          if (bw) v = fls_unpack64_rows(sm0, bw, row, q, base, k1);
+          else { v.x = base; v.y = base; }
+          v.x = fls_alp_value(v.x, fact, frac);
+          v.y = fls_alp_value(v.y, fact, frac);
+          fls_st128((uint8_t *)out + row * 128u + q * 16u, v);
+        }
       }
     }
     if (n_exc) {  // patches land after the region barrier above, so they win over the decoded values

@@ -258,6 +258,18 @@ FLS_DEV fls_ul2 fls_unpack64_row(const uint8_t *sm, uint32_t W, uint32_t row, ui
   return o;
 }
 
+// the same with the straddle row clamped to `klast` (the last word row the caller staged) instead of W - 1
+FLS_DEV fls_ul2 fls_unpack64_rows(const uint8_t *sm, uint32_t W, uint32_t row, uint32_t q, uint64_t base, uint32_t klast) {
+  const uint32_t bit = row * W, k = bit >> 6, s = bit & 63u;
+  const fls_ul2 a = fls_lds128<fls_ul2>(sm + k * 128u + q * 16u);
+  const fls_ul2 b = fls_lds128<fls_ul2>(sm + fls_min(k + 1u, klast) * 128u + q * 16u);
+  const uint64_t mask = W >= 64u ? ~0ull : ((1ull << W) - 1ull);
+  fls_ul2 o;
+  o.x = (((a.x >> s) | ((b.x << 1) << (63u - s))) & mask) + base;
+  o.y = (((a.y >> s) | ((b.y << 1) << (63u - s))) & mask) + base;
+  return o;
+}
+
 // two u16 lanes packed in each 32-bit word
 FLS_DEV uint32_t fls_unpack16_word(uint32_t a, uint32_t b, uint32_t s, uint32_t mask, uint32_t base) {
   const uint32_t lo = ((fls_prmt(a, b, 0x5410u) >> s) & mask) + base;

@@ -47,6 +47,15 @@ def delta_cases(n=70_000):
     out.append(("delta_i32_random_fullwidth", [v], None, [W.DELTA], None))
     v = np.full(n, 77, dtype=np.int32)
     out.append(("delta_i32_const_w0", [v], None, [W.DELTA], None))
+    # 64-bit keys, one delta width per vector: 1 .. 16 bits take the register-resident path of DecDELTA::run64_narrow,
+    # 17 .. 20 the generic one; the second column adds a negative frame of reference (descending runs)
+    width = 1 + (np.arange(n) // 1024) % 20
+    step = (r.integers(0, 2 ** 62, n) % (2 ** width.astype(np.int64))).astype(np.int64)
+    step[np.arange(n) % 1024 == 5] = 0
+    step[np.arange(n) % 1024 == 6] = 2 ** width[np.arange(n) % 1024 == 6].astype(np.int64) - 1
+    up = np.cumsum(step).astype(np.int64) + 10 ** 12
+    down = (2 ** 60 - np.cumsum(step + (np.arange(n) // 1024) * 3 - 1000)).astype(np.int64)
+    out.append(("delta_i64_width_sweep", [up, down, up.astype(np.uint64)], None, [W.DELTA, W.DELTA, W.DELTA], None))
     return out
 
 
@@ -154,6 +163,12 @@ def alp_cases(n=70_000):
     out.append(("alp_constant_w0", [v], None, [W.ALP], None))
     v = np.round(r.uniform(0, 9e15, n))
     out.append(("alp_huge_ints_wide", [v], None, [W.ALP], None))
+    # one integer width per vector, 30 .. 53 bits: 33 and up are decoded in two passes through the 4 KB slot
+    bits = 30 + (np.arange(n) // 1024) % 24
+    v = (r.integers(0, 2 ** 62, n) % (2 ** bits.astype(np.int64))).astype(np.float64)
+    v[np.arange(n) % 1024 == 3] = 0.0
+    v[np.arange(n) % 1024 == 4] = (2.0 ** bits[np.arange(n) % 1024 == 4]) - 1.0
+    out.append(("alp_width_sweep_30_53", [v, -v], None, [W.ALP, W.ALP], None))
     out.append(("alprd_entropy", [synth.alp_entropy(n)], None, [W.ALP_RD], None))
     v = r.uniform(0, 1, n) * 1000.0
     out.append(("alprd_uniform", [v], None, [W.ALP_RD], None))
