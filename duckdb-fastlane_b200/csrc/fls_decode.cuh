@@ -73,18 +73,12 @@ template <typename T> struct DecFFOR {
 };
 
 // ===================================================================== DELTA
-#ifndef FLS_DELTA_FASTW
-#define FLS_DELTA_FASTW 16u  /* widest delta the register-resident 64-bit path takes (0 = never) */
-#endif
-static_assert(FLS_DELTA_FASTW <= 16u, "narrow_deltas: 32 deltas must add up inside 32 bits, shift counts below 32");
 // payload: [lane bases 128 B][packed deltas 128*bw]; deltas are FFOR'd (wrapping + base).
 template <typename T> struct DecDELTA {
   static constexpr uint32_t TB = sizeof(T) * 8u, L = 1024u / TB;
   static constexpr uint32_t STAGE = 128u + 128u * TB;
-  // T=64: the deltas are unpacked into registers first, so the tile takes the place of the staged payload;
-  // XCH = half-lane totals
-  static constexpr uint32_t XCH = FLS_TILE_BYTES(T);
-  static constexpr uint32_t SMEM = sizeof(T) == 8 ? FLS_TILE_BYTES(T) + 256u : STAGE + FLS_TILE_BYTES(T);
+  // T=64: see run64 (half a vector per slot: 4224 bytes + the 16 half-lane totals)
+  static constexpr uint32_t SMEM = sizeof(T) == 8 ? 4224u + 128u : STAGE + FLS_TILE_BYTES(T);
 
   // Reconstruct into the warp's padded tile (original order).  `add` is added to every value (string offsets).
   FLS_MEM static void to_tile(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base) {
@@ -108,50 +102,22 @@ template <typename T> struct DecDELTA {
       }
     }
   }
-  // T=64: 16 lanes x 64 steps, thread (l = t&15, h = t>>4) owns steps [32h, 32h+32) = originals 64l+32h .. +31.
-  // Each half-lane unpacks its 32 deltas ONCE into registers; only the 16 half totals cross lanes.
-  FLS_MEM static void run64(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
-    w.stage(0, in, 128u + 128u * bw);
-    w.wait();
-    if (bw >= 1u && bw <= FLS_DELTA_FASTW) { run64_narrow(w, bw, base, out); return; }
-    const T *bases = (const T *)w.sm;
-    const T *pk = (const T *)(w.sm + 128);
-    {
-      // the upper half of a lane needs the lower half's total first
-      uint64_t *xch = (uint64_t *)(w.sm + XCH);
-      T *tile = (T *)w.sm;  // overwrites the staged payload: every packed word has been consumed by then
-      FLS_VAR2(uint64_t, dl, 32);
-      FLS_VAR(uint64_t, lane_base);
-      FLS_LANES(t) {
-        const uint32_t l = t & 15u, h = t >> 4;
-        FLS_AT(lane_base) = (uint64_t)bases[l];
-        uint64_t tot = 0;
-#pragma unroll
-        for (uint32_t j = 0; j < 32u; ++j) {
-          const uint32_t r = 32u * h + j;
-          const uint64_t dv = (bw ? (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(r), l) : 0ull) + base;
-          FLS_AT2(dl, j) = dv;
-          tot += dv;
-        }
-        xch[t] = tot;
-      }
-      FLS_LANES(t) {
-        const uint32_t l = t & 15u, h = t >> 4;
-        uint64_t acc = FLS_AT(lane_base) + (h ? xch[l] : 0ull);
-#pragma unroll
-        for (uint32_t j = 0; j < 32u; ++j) {
-          acc += FLS_AT2(dl, j);
-          tile[fls_tile_slot<T>(64u * l + 32u * h + j)] = (T)acc;
-        }
-      }
-      FLS_LANES(t) { fls_tile_copy_out<T>(w.sm, out, t); }
-    }
-  }
-  // T=64, deltas of W <= FLS_DELTA_FASTW bits (sorted keys: l_orderkey packs into 5-6 bits).  Thread (l, h) needs packed
-  // rows ORDER[4h + j/8] + 8 (j%8) = {0,4,2,6}[j/8] + 8 (j%8) + h of lane l: the even rows (h = 0) or the odd rows
-  // (h = 1) of the lane's bit stream.  The lane's W 64-bit words are loaded once into registers, shifted right by h W
-  // bits (so that both halves extract at the SAME, compile-time bit positions), and every delta is one funnel shift
-  // and one mask — against two shared loads, two 64-bit variable shifts and a 64-bit mask in fls_extract.
+  // ---- T=64: 16 lanes x 64 steps; thread (l = t&15, h = t>>4) owns steps [32h, 32h+32) = originals 64l+32h .. +31 and
+  // holds its 32 deltas in registers; only the 16 half totals cross lanes (xch).  The slot is HALF a vector wide: the
+  // staged payload (deltas of up to 16 bits: 128 + 128*16 bytes) and, once every thread holds its deltas, one half of
+  // the output at a time — the thread's values 16p .. 16p+15 (p = 0, 1) are the 128-byte output row 4l + 2h + p, so
+  // a half is every other output row; its 32 rows sit at 16 m + m/2 (m = 2l + h; the m/2 keeps the sixteen threads
+  // of a 64-bit store phase in sixteen different banks).  4.3 KB per warp instead of 8.4 KB: twice the resident warps.
+  // Deltas wider than 16 bits (rare: DELTA is picked for narrow deltas) are read from global memory, twice.
+  static constexpr uint32_t HALF_TILE = 4224u;  // >= 128 + 128*16 (payload) and >= 8 * (31*16 + 15 + 16) (half tile)
+  static constexpr uint32_t XCH = HALF_TILE;    // 16 x u64
+  FLS_MEM static uint32_t half_slot(uint32_t m, uint32_t jj) { return 16u * m + (m >> 1) + jj; }
+
+  // Thread (l, h) needs packed rows ORDER[4h + j/8] + 8 (j%8) = {0,4,2,6}[j/8] + 8 (j%8) + h of lane l: the even rows
+  // (h = 0) or the odd rows (h = 1) of the lane's bit stream.  W <= FLS_DELTA_FASTW (sorted keys: l_orderkey packs into
+  // 5-6 bits): the lane's W 64-bit words are loaded once into registers, shifted right by h W bits (so that both halves
+  // extract at the SAME, compile-time bit positions), and every delta is one funnel shift and one mask — against two
+  // shared loads, two 64-bit variable shifts and a 64-bit mask in fls_extract.
   template <uint32_t W> FLS_MEM static void narrow_deltas(const uint8_t *lane_words, uint32_t h, uint32_t (&d)[32]) {
     uint32_t wd[2u * W + 1u];
 #pragma unroll
@@ -164,47 +130,85 @@ template <typename T> struct DecDELTA {
 #pragma unroll
     for (uint32_t i = 0; i < 2u * W; ++i) wd[i] = fls_shf_r(wd[i], wd[i + 1u], s0);
     constexpr uint32_t mask = (1u << W) - 1u;
+    // ascending rows, so that the words die as the deltas appear (a thread never holds much more than 2W + 1 or 32
+    // registers of either); even row 2e is chain step j = 8 * {0,2,1,3}[e % 4] + e / 4
 #pragma unroll
-    for (uint32_t j = 0; j < 32u; ++j) {
-      const uint32_t row = ((0x6240u >> (4u * (j >> 3))) & 0xFu) + 8u * (j & 7u);  // even rows, in chain order
-      const uint32_t bit = row * W, i = bit >> 5, s = bit & 31u;
+    for (uint32_t e = 0; e < 32u; ++e) {
+      const uint32_t j = 8u * ((0x3120u >> (4u * (e & 3u))) & 0xFu) + (e >> 2);
+      const uint32_t bit = 2u * e * W, i = bit >> 5, s = bit & 31u;
       d[j] = (s + W <= 32u ? wd[i] >> s : fls_shf_r(wd[i], wd[i + 1u], s)) & mask;
     }
   }
-  FLS_MEM static void run64_narrow(FlsWarp &w, uint32_t bw, uint64_t base, T *out) {
+  FLS_MEM static void run64(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
+    const bool wide = bw > 16u;  // no register-resident deltas: two generic passes over the payload in global memory
+    w.stage(0, in, wide ? 128u : 128u + 128u * bw);
+    w.wait();
     const T *bases = (const T *)w.sm;
+    const T *pk = (const T *)(in + 128);  // wide only (the half tiles below overwrite the slot while deltas are still needed)
     uint64_t *xch = (uint64_t *)(w.sm + XCH);
     T *tile = (T *)w.sm;  // overwrites the staged payload once every thread holds its deltas
     FLS_VAR2(uint32_t, dl, 32);
-    FLS_VAR(uint64_t, lane_base);
+    FLS_VAR(uint64_t, accv);
     FLS_LANES(t) {
       const uint32_t l = t & 15u, h = t >> 4;
-      FLS_AT(lane_base) = (uint64_t)bases[l];
-      const uint8_t *lw = w.sm + 128u + 8u * l;
-      uint32_t d[32];
-      switch (bw) {  // warp-uniform
+      FLS_AT(accv) = (uint64_t)bases[l];
+      uint64_t tot = 0;
+      if (wide) {
+#pragma unroll 2
+        for (uint32_t j = 0; j < 32u; ++j) tot += (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(32u * h + j), l);
+      } else {
+        uint32_t d[32];
+        const uint8_t *lw = w.sm + 128u + 8u * l;
+        switch (bw) {  // warp-uniform
+          case 0:
+#pragma unroll
+            for (uint32_t j = 0; j < 32u; ++j) d[j] = 0u;
+            break;
 #define FLS_DELTA_CASE(W) case W: narrow_deltas<W>(lw, h, d); break;
-        FLS_DELTA_CASE(1) FLS_DELTA_CASE(2) FLS_DELTA_CASE(3) FLS_DELTA_CASE(4) FLS_DELTA_CASE(5) FLS_DELTA_CASE(6)
-        FLS_DELTA_CASE(7) FLS_DELTA_CASE(8) FLS_DELTA_CASE(9) FLS_DELTA_CASE(10) FLS_DELTA_CASE(11) FLS_DELTA_CASE(12)
-        FLS_DELTA_CASE(13) FLS_DELTA_CASE(14) FLS_DELTA_CASE(15)
+          FLS_DELTA_CASE(1) FLS_DELTA_CASE(2) FLS_DELTA_CASE(3) FLS_DELTA_CASE(4) FLS_DELTA_CASE(5) FLS_DELTA_CASE(6)
+          FLS_DELTA_CASE(7) FLS_DELTA_CASE(8) FLS_DELTA_CASE(9) FLS_DELTA_CASE(10) FLS_DELTA_CASE(11) FLS_DELTA_CASE(12)
+          FLS_DELTA_CASE(13) FLS_DELTA_CASE(14) FLS_DELTA_CASE(15)
 #undef FLS_DELTA_CASE
-        default: narrow_deltas<16>(lw, h, d); break;
-      }
-      uint32_t tot = 0;  // 32 deltas of <= 16 bits
+          default: narrow_deltas<16>(lw, h, d); break;
+        }
 #pragma unroll
-      for (uint32_t j = 0; j < 32u; ++j) { FLS_AT2(dl, j) = d[j]; tot += d[j]; }
-      xch[t] = (uint64_t)tot + 32ull * base;
+        for (uint32_t j = 0; j < 32u; ++j) { FLS_AT2(dl, j) = d[j]; tot += d[j]; }
+      }
+      if (h == 0u) xch[l] = tot + 32ull * base;  // the upper half of a lane starts where the lower half ends
     }
     FLS_LANES(t) {
       const uint32_t l = t & 15u, h = t >> 4;
-      uint64_t acc = FLS_AT(lane_base) + (h ? xch[l] : 0ull);
+      if (h) FLS_AT(accv) += xch[l];
+    }
 #pragma unroll
-      for (uint32_t j = 0; j < 32u; ++j) {
-        acc += (uint64_t)FLS_AT2(dl, j) + base;
-        tile[fls_tile_slot<T>(64u * l + 32u * h + j)] = (T)acc;
+    for (uint32_t p = 0; p < 2u; ++p) {
+      FLS_LANES(t) {
+        const uint32_t l = t & 15u, h = t >> 4, m = 2u * l + h;
+        uint64_t acc = FLS_AT(accv);
+        if (wide) {
+#pragma unroll 2
+          for (uint32_t jj = 0; jj < 16u; ++jj) {
+            acc += (uint64_t)fls_extract<T>(pk, bw, fls_chain_row<TB>(32u * h + 16u * p + jj), l) + base;
+            tile[half_slot(m, jj)] = (T)acc;
+          }
+        } else {
+#pragma unroll
+          for (uint32_t jj = 0; jj < 16u; ++jj) {
+            acc += (uint64_t)FLS_AT2(dl, 16u * p + jj) + base;
+            tile[half_slot(m, jj)] = (T)acc;
+          }
+        }
+        FLS_AT(accv) = acc;
+      }
+      FLS_LANES(t) {  // the half's 32 rows leave two at a time: threads 0..15 one 128-byte row, threads 16..31 the next
+        const uint32_t jj = t & 15u;
+#pragma unroll 8
+        for (uint32_t i = 0; i < 16u; ++i) {
+          const uint32_t m = 2u * i + (t >> 4);
+          out[16u * (2u * m + p) + jj] = tile[half_slot(m, jj)];
+        }
       }
     }
-    FLS_LANES(t) { fls_tile_copy_out<T>(w.sm, out, t); }
   }
   FLS_MEM static void run(FlsWarp &w, const uint8_t *in, uint32_t bw, uint64_t base, T *out) {
     if constexpr (sizeof(T) == 8) {

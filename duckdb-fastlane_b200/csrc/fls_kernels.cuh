@@ -35,8 +35,12 @@ template <typename T> struct VecFFOR {
                     (T *)k.out + (size_t)v * FLS_VEC);
   }
 };
+#ifndef FLS_DELTA64_MIN_BLOCKS
+#define FLS_DELTA64_MIN_BLOCKS 16 /* 64 registers: 16 blocks = 32 warps per SM (0.105 -> 0.091 ms on l_orderkey; 18 / 20 blocks spill: 0.096 / 0.105) */
+#endif
 template <typename T> struct VecDELTA {
   static constexpr uint32_t SMEM = DecDELTA<T>::SMEM, BLOCK_SMEM = 0;
+  static constexpr int MIN_BLOCKS = sizeof(T) == 8 ? FLS_DELTA64_MIN_BLOCKS : 1;
   FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
     const fls_vechdr h = fls_load_hdr(k, 0, v);
     const uint32_t bw = FLS_META_BW(h.meta);
@@ -150,8 +154,11 @@ template <class V> constexpr uint32_t fls_block_smem() {
   return FLS_WARPS_PER_BLOCK * V::SMEM + V::BLOCK_SMEM + FLS_WARPS_PER_BLOCK * 8u;
 }
 
+// V::MIN_BLOCKS (optional): resident blocks per SM the register allocation must allow
+template <class V, class = void> struct FlsMinBlocks { static constexpr int value = 1; };
+template <class V> struct FlsMinBlocks<V, decltype((void)V::MIN_BLOCKS)> { static constexpr int value = V::MIN_BLOCKS; };
 template <class V>
-__global__ void __launch_bounds__(FLS_WARPS_PER_BLOCK * 32) fls_vec_kernel(const FlsChunkDev *__restrict__ chunks) {
+__global__ void __launch_bounds__(FLS_WARPS_PER_BLOCK * 32, FlsMinBlocks<V>::value) fls_vec_kernel(const FlsChunkDev *__restrict__ chunks) {
   extern __shared__ __align__(128) uint8_t fls_smem[];
   const FlsChunkDev &k = chunks[blockIdx.x / FLS_BLOCKS_PER_CHUNK];
   const uint32_t warp = threadIdx.x >> 5, bx = blockIdx.x % FLS_BLOCKS_PER_CHUNK;

@@ -22,6 +22,7 @@ enum FlsKernelKind {
   FLS_K_STR_FSST_DICTPREP,  // decode an FSST-compressed dictionary into scratch
   FLS_K_VALIDITY,           // validity bitmap of a chunk (copied, or all ones) -> the column's bitmap
   FLS_K_FFOR_PATCH, FLS_K_CROSS_RLE, FLS_K_STR_FSST12,
+  FLS_K_STR_FLAGS,           // STR_DICT chunk with up to 8 one-byte entries, every vector full (flag columns)
   FLS_K_N
 };
 
@@ -106,6 +107,23 @@ static inline FlsColNeed fls_column_need(const FlsTable &t, uint32_t col, uint32
   return n;
 }
 
+// STR_DICT chunk `k` of a row group that starts at `rgp` in the host image: are its entries 1 .. 8 strings of one byte,
+// and does its payload hold exactly one byte per padded row?  *flags8 = the entries' bytes, entry e in byte e.
+static inline bool fls_dict_is_flags(const uint8_t *rgp, const fls_colchunk &k, uint32_t n_vec, uint64_t *flags8) {
+  const uint32_t n = k.aux32;
+  if (k.n_seg < 5 || n < 1u || n > 8u || k.aux64[0] != (uint64_t)n_vec * FLS_VEC) return false;
+  if (k.seg[2].size < 4ull * (n + 1u)) return false;
+  uint32_t off[9];
+  memcpy(off, rgp + k.seg[2].off, 4u * (n + 1u));
+  uint64_t v = 0;
+  for (uint32_t e = 0; e < n; ++e) {
+    if (off[e + 1u] != off[e] + 1u || (uint64_t)off[e] + 1u > k.seg[3].size) return false;
+    v |= (uint64_t)rgp[k.seg[3].off + off[e]] << (8u * e);
+  }
+  *flags8 = v;
+  return true;
+}
+
 // stage_base = address (device or host) of the byte at file offset t.rgs[g0].off
 static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint32_t g0, uint32_t g1,
                                           const uint8_t *stage_base, const uint8_t *host_image,
@@ -180,7 +198,20 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
           break;
         }
         case FLS_S_STR_CONSTANT: fls_launch_for(ls, FLS_K_STR_CONST, 0).add(d, rd, wr); break;
-        case FLS_S_STR_DICT: fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, rd, wr, g); break;
+        case FLS_S_STR_DICT: {
+          // Flag columns (l_returnflag, l_linestatus): a dictionary of up to 8 one-byte strings and no short vector.
+          // Nothing about them needs the table / staging machinery of the persistent DICT kernel — the offsets are
+          // arithmetic and 8 strings are two byte permutes — so they go to a plain warp-per-vector kernel that
+          // runs with the bandwidth-bound launches; the dictionary's bytes travel in the descriptor.
+          uint64_t flags8 = 0;
+          if (host_image && fls_dict_is_flags(host_image + rg.off, k, rg.n_vec, &flags8)) {
+            d.aux64[1] = flags8;
+            fls_launch_for(ls, FLS_K_STR_FLAGS, 0).add(d, rd, wr);
+          } else {
+            fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, rd, wr, g);
+          }
+          break;
+        }
         case FLS_S_STR_FSST: fls_launch_for(ls, FLS_K_STR_FSST, 0).add(d, rd, wr, g); break;
         case FLS_S_STR_FSST12: fls_launch_for(ls, FLS_K_STR_FSST12, 0).add(d, rd, wr); break;
         case FLS_S_STR_FSST_DICT: {

@@ -628,6 +628,46 @@ struct VecSTRDICT {
   }
 };
 
+// ===================================================================== flag columns
+// A STR_DICT chunk whose dictionary is up to 8 one-byte strings and whose vectors are all full (fls_dict_is_flags,
+// fls_plan.h): aux64[1] = the entries' bytes.  One warp per vector, no table: string i of the vector is byte i of its
+// 1024 payload bytes, offsets are arithmetic, a lane's 8 strings are two byte permutes of the dictionary.  The vector's
+// payload position is 1024 v by construction (every string is one byte), whatever seg[4] says.
+struct VecSTRFLAGS {
+  static constexpr uint32_t SMEM = 4096u, BLOCK_SMEM = 0;  // the staged index payload, widths up to 32 bits
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr h = fls_load_hdr(k, 0, v);
+    uint32_t bw = FLS_META_BW(h.meta);
+    if (bw > 32u) bw = 32u;
+    if (bw) { w.stage(0, k.seg[1] + 16ull * h.ep, 128u * bw); w.wait(); }
+    const uint32_t dlo = (uint32_t)k.aux64[1], dhi = (uint32_t)(k.aux64[1] >> 32);
+    const uint32_t lim = k.aux32 - 1u, first = k.pay_base + v * FLS_VEC;  // payload offset of the vector's first string
+    uint8_t *pay = k.pay + first;
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;
+    const bool aligned = ((uintptr_t)pay & 7u) == 0u;
+    for (uint32_t qt = 0; qt < 4u; ++qt) {
+      FLS_LANES(t) {
+        uint32_t d[8];
+        VecSTRDICT::unpack8(w.sm, bw, 8u * qt + (t >> 2), t, (uint32_t)h.base, lim, d);
+        const uint32_t s0 = 256u * qt + 8u * t, start = first + s0;
+        fls_u4 a, b;
+        a.x = start; a.y = start + 1u; a.z = start + 2u; a.w = start + 3u;
+        b.x = start + 4u; b.y = start + 5u; b.z = start + 6u; b.w = start + 7u;
+        fls_st128(offs + s0, a);
+        fls_st128(offs + s0 + 4u, b);
+        if (s0 == FLS_VEC - 8u) offs[FLS_VEC] = start + 8u;  // the vector's last end
+        const uint32_t lo = fls_prmt(dlo, dhi, d[0] | (d[1] << 4) | (d[2] << 8) | (d[3] << 12));
+        const uint32_t hi = fls_prmt(dlo, dhi, d[4] | (d[5] << 4) | (d[6] << 8) | (d[7] << 12));
+        if (aligned) fls_st64(pay + s0, lo, hi);
+        else {
+#pragma unroll
+          for (uint32_t i = 0; i < 4u; ++i) { pay[s0 + i] = (uint8_t)(lo >> (8u * i)); pay[s0 + 4u + i] = (uint8_t)(hi >> (8u * i)); }
+        }
+      }
+    }
+  }
+};
+
 // ===================================================================== FSST strings
 // chunk: seg[0]/[1] = decoded end-offset stream, seg[2]/[3] = compressed end-offset stream (both DELTA u32),
 //        seg[4] = symbol table (u64 symbol[256] | u8 len[256]), seg[5] = compressed bytes (+16 slack).

@@ -85,13 +85,14 @@ cudaError_t set_kernel_attrs() {
   if ((e = vec_attr<VecSTROFFS>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecSTRCONST>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecSTRFSST12>()) != cudaSuccess) return e;
+  if ((e = vec_attr<VecSTRFLAGS>()) != cudaSuccess) return e;
   if ((e = chunk_attr<VecSTRDICT>()) != cudaSuccess) return e;
   return chunk_attr<VecSTRFSST>();
 }
 
 const char *const kKindName[FLS_K_N] = {"ffor",     "delta",     "rle",      "dict",     "alp",  "alp_rd", "copy",
                                         "fill",     "str_offsets", "str_copy", "str_const", "str_dict", "str_fsst",
-                                        "fsst_dictprep", "validity", "ffor_patch", "cross_rle", "str_fsst12"};
+                                        "fsst_dictprep", "validity", "ffor_patch", "cross_rle", "str_fsst12", "str_flags"};
 
 struct LaunchRec {  // what is needed to (re)issue one launch once its descriptors are on the device
   int kind, width;
@@ -120,6 +121,7 @@ bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
     case FLS_K_STR_COPY: fls_str_copy_kernel<<<n * 32, 256, 0, s>>>(d, 32); return true;
     case FLS_K_STR_CONST: vec_launch<VecSTRCONST>(d, n, s); return true;
     case FLS_K_STR_FSST12: vec_launch<VecSTRFSST12>(d, n, s); return true;
+    case FLS_K_STR_FLAGS: vec_launch<VecSTRFLAGS>(d, n, s); return true;
     case FLS_K_STR_DICT: chunk_launch<VecSTRDICT>(d, n, s, l.cap); return true;
     case FLS_K_STR_FSST: chunk_launch<VecSTRFSST>(d, n, s, l.cap); return true;
     case FLS_K_STR_FSST_DICTPREP: fls_fsst_dictprep_kernel<<<n * 8, 128, 0, s>>>(d, 8); return true;

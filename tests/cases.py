@@ -231,6 +231,21 @@ def string_cases(n=70_000):
     strs = [mixed[i] for i in r.integers(0, 3, 65536)] + [(b"XY", b"ZW")[i] for i in r.integers(0, 2, n - 65536 + 4000)]
     out.append(("str_dict_mixed_then_uniform", [StrColumn.from_list(strs)], None, [W.STR_DICT], None))
     out.append(("str_dict_entries_17_bytes", [li[13]], None, [W.STR_DICT], None))
+    # flag columns (VecSTRFLAGS: up to 8 one-byte entries, full vectors): behind a row group with an odd payload size
+    # (unaligned stores), with 8 entries including the bytes 0x00 and 0xFF, with a wide index stream, and a 9-entry
+    # dictionary that must stay with the table kernel
+    flags5 = [b"\x00", b"\xff", b"N", b"R", b"A"]
+    strs = [mixed[i] for i in r.integers(0, 3, 65536)] + [flags5[i] for i in r.integers(0, 5, 65536 + 3000)]
+    out.append(("str_flags_after_odd_payload", [StrColumn.from_list(strs)], None, [W.STR_DICT], None))
+    flags8 = [bytes([c]) for c in b"ABCDEFG\x7f"]
+    out.append(("str_flags_8_entries", [StrColumn.from_list([flags8[i] for i in r.integers(0, 8, 2 * 65536)])], None,
+                [W.STR_DICT], None))
+    out.append(("str_flags_8_entries_index_bw17", [StrColumn.from_list([flags8[i] for i in r.integers(0, 8, 65536 + 1024)])],
+                None, [W.STR_DICT], [17]))
+    flags9 = flags8 + [b"z"]
+    out.append(("str_dict_9_one_byte_entries", [StrColumn.from_list([flags9[i] for i in r.integers(0, 9, 65536)])], None,
+                [W.STR_DICT], None))
+    out.append(("str_flags_one_entry", [StrColumn.from_list([b"F"] * 65536)], None, [W.STR_DICT], None))
     # index widths beyond the prefetch halves (<= 10 bits): whole-buffer staging (<= 20) and quarter-wise staging
     for bw in (11, 20, 21, 27, 32):
         out.append(("str_dict_shipmode_index_bw%d" % bw, [shipmode], None, [W.STR_DICT], [bw]))

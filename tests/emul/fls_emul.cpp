@@ -87,6 +87,7 @@ static bool run_launch(const FlsLaunch &l) {
       return true;
     case FLS_K_STR_CONST: run_vectors<VecSTRCONST>(l); return true;
     case FLS_K_STR_FSST12: run_vectors<VecSTRFSST12>(l); return true;
+    case FLS_K_STR_FLAGS: run_vectors<VecSTRFLAGS>(l); return true;
     case FLS_K_STR_DICT: run_vectors<VecSTRDICT>(l); return true;
     case FLS_K_STR_FSST: run_vectors<VecSTRFSST>(l); return true;
     case FLS_K_STR_FSST_DICTPREP:
