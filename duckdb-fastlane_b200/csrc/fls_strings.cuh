@@ -423,7 +423,12 @@ struct VecSTRDICT {
     const uint32_t bit = row * bw, kk = bit >> 5, s = bit & 31u;
     const uint8_t *pa = sm + kk * 128u + 32u * (t & 3u), *pb = sm + fls_min(kk + 1u, bw - 1u) * 128u + 32u * (t & 3u);
     const fls_u4 a0 = fls_lds128<fls_u4>(pa), a1 = fls_lds128<fls_u4>(pa + 16);
-    const fls_u4 b0 = fls_lds128<fls_u4>(pb), b1 = fls_lds128<fls_u4>(pb + 16);
+    // the next word row only where the row's values straddle it (never for widths that divide 32): a quarter-warp
+    // shares its row, so the skipped loads cost no shared-memory wavefronts
+    fls_u4 b0, b1;
+    b0.x = b0.y = b0.z = b0.w = 0u;
+    b1 = b0;
+    if (s + bw > 32u) { b0 = fls_lds128<fls_u4>(pb); b1 = fls_lds128<fls_u4>(pb + 16); }
     const uint32_t mask = bw >= 32u ? 0xFFFFFFFFu : ((1u << bw) - 1u);
     d[0] = fls_min((fls_shf_r(a0.x, b0.x, s) & mask) + base, lim);
     d[1] = fls_min((fls_shf_r(a0.y, b0.y, s) & mask) + base, lim);
