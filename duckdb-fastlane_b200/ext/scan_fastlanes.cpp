@@ -441,6 +441,9 @@ void ScanFastLanes::Register(DatabaseInstance &db) {
 		fn.named_parameters["file"] = LogicalType::VARCHAR;
 		fn.named_parameters["gpus"] = LogicalType::LIST(LogicalType::INTEGER);
 		fn.named_parameters["device"] = LogicalType::INTEGER;
+		// accepted and ignored, as in the reference (/root/reference/src/scanner/scan_fastlanes.cpp:34,156: stored, never
+		// read): the schema always comes from the file's footer
+		fn.named_parameters["auto_detect"] = LogicalType::BOOLEAN;
 		fn.projection_pushdown = true;
 		fn.cardinality = FastLanesCardinality;
 		fn.table_scan_progress = FastLanesProgress;

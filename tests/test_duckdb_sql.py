@@ -340,10 +340,13 @@ def test_gpus_and_device_named_parameters(tmp_path):
               "SELECT %s FROM scan_fastlanes('%s', device := 0)" % (agg, path),
               "SELECT id FROM read_fls('%s', gpus := %s) WHERE id %% 50000 = 1 ORDER BY id" % (path, gl),
               "SELECT count(*) FROM read_fls('%s', gpus := [0, 77])" % path,
-              "SELECT count(*) FROM read_fls('%s', device := -1)" % path)
+              "SELECT count(*) FROM read_fls('%s', device := -1)" % path,
+              # the reference's stream scan registers `auto_detect` (src/scanner/scan_fastlanes.cpp:156) and never reads it
+              "SELECT %s FROM scan_fastlanes('%s', auto_detect := true)" % (agg, path))
     assert "error" not in res[0] and same_rows(res[0]["rows"], res[1]["rows"]) and same_rows(res[0]["rows"], res[2]["rows"]), res[:3]
     assert [r[0] for r in res[3]["rows"]] == ["1", "50001", "100001", "150001"]
     assert "error" in res[4] and "error" in res[5]
+    assert "error" not in res[6] and same_rows(res[0]["rows"], res[6]["rows"]), res[6]
 
 
 # ------------------------------------------------------------------------------------------- the loadable extension
