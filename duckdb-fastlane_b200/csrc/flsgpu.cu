@@ -196,6 +196,38 @@ struct GlobalCache {
     dev[device].emplace(n, p); dev_bytes += n;
     return true;
   }
+  // a handle's six streams and its events outlive it too (a query = open + scan + close, on every scanning thread:
+  // creating and destroying them was a fixed cost per query and thread); at most 64 sets / 4096 events are kept
+  struct StreamSet { cudaStream_t s[6]; };
+  std::map<int, std::vector<StreamSet>> streams;
+  std::map<int, std::vector<cudaEvent_t>> events;
+  std::map<int, bool> attrs_set;  // cudaFuncSetAttribute of every kernel: once per device
+  bool take_streams(int device, StreamSet *out) {
+    std::lock_guard<std::mutex> g(mu);
+    auto &v = streams[device];
+    if (v.empty()) return false;
+    *out = v.back(); v.pop_back();
+    return true;
+  }
+  bool give_streams(int device, const StreamSet &ss) {
+    std::lock_guard<std::mutex> g(mu);
+    auto &v = streams[device];
+    if (v.size() >= 64) return false;
+    v.push_back(ss);
+    return true;
+  }
+  void take_events(int device, std::vector<cudaEvent_t> &into, size_t n) {
+    std::lock_guard<std::mutex> g(mu);
+    auto &v = events[device];
+    while (n-- && !v.empty()) { into.push_back(v.back()); v.pop_back(); }
+  }
+  bool give_event(int device, cudaEvent_t e) {
+    std::lock_guard<std::mutex> g(mu);
+    auto &v = events[device];
+    if (v.size() >= 4096) return false;
+    v.push_back(e);
+    return true;
+  }
 };
 GlobalCache g_cache;
 
@@ -410,11 +442,26 @@ void parallel_copy(void *dst, const void *src, uint64_t n) {
 int ensure_ready(flsgpu *h) {
   if (h->cuda_ready) { CK(cudaSetDevice(h->device)); return 0; }
   CK(cudaSetDevice(h->device));
-  CK(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
-  CK(cudaStreamCreateWithFlags(&h->s_k, cudaStreamNonBlocking));
-  CK(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
-  for (auto &sx : h->s_kx) CK(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
-  CK(set_kernel_attrs());
+  {
+    GlobalCache::StreamSet ss;
+    if (g_cache.take_streams(h->device, &ss)) {
+      h->s_h2d = ss.s[0]; h->s_k = ss.s[1]; h->s_d2h = ss.s[2];
+      for (int i = 0; i < 3; ++i) h->s_kx[i] = ss.s[3 + i];
+    } else {
+      CK(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
+      CK(cudaStreamCreateWithFlags(&h->s_k, cudaStreamNonBlocking));
+      CK(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+      for (auto &sx : h->s_kx) CK(cudaStreamCreateWithFlags(&sx, cudaStreamNonBlocking));
+    }
+    g_cache.take_events(h->device, h->ev_free, 64);
+    bool need_attrs;
+    { std::lock_guard<std::mutex> g(g_cache.mu); need_attrs = !g_cache.attrs_set[h->device]; }
+    if (need_attrs) {
+      CK(set_kernel_attrs());
+      std::lock_guard<std::mutex> g(g_cache.mu);
+      g_cache.attrs_set[h->device] = true;
+    }
+  }
   CK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, h->device));
   if (const char *e = getenv("FLSGPU_SM_SPLIT")) {  // "fsst,dict" SM counts; "0" = no partition
     g_split_fsst = g_split_dict = 0;
@@ -542,7 +589,8 @@ void flsgpu_close(flsgpu_t *h) {
   if (!h) return;
   if (h->cuda_ready) {
     cudaSetDevice(h->device);
-    cudaDeviceSynchronize();
+    // wait for this handle's own work only: other handles (the scan's other threads) keep the device busy
+    for (cudaStream_t st : {h->s_h2d, h->s_k, h->s_d2h, h->s_kx[0], h->s_kx[1], h->s_kx[2]}) if (st) cudaStreamSynchronize(st);
     // the pooled buffers go to the process-wide cache (up to its bounds) for the next handle
     for (auto &kv : h->pool.free_dev) { h->dev_size.erase(kv.second); if (!g_cache.give_dev(h->device, kv.second, kv.first)) cudaFree(kv.second); }
     for (auto &kv : h->pool.free_host) { h->host_size.erase(kv.second); if (!g_cache.give_host(kv.second, kv.first)) cudaFreeHost(kv.second); }
@@ -550,16 +598,15 @@ void flsgpu_close(flsgpu_t *h) {
     for (auto &kv : h->host_size) cudaFreeHost(kv.first);
     if (h->d_res) cudaFree(h->d_res);
     if (h->d_flush) cudaFree(h->d_flush);
-    for (auto e : h->ev_free) cudaEventDestroy(e);
+    for (auto e : h->ev_free) if (!g_cache.give_event(h->device, e)) cudaEventDestroy(e);
     if (h->image_registered) cudaHostUnregister((void *)h->image);
     gds_close(h);
     if (h->image_mapped) munmap((void *)h->image, h->size);
     if (h->fd >= 0) close(h->fd);
     if (h->image_owned) { if (h->flags & FLSGPU_OPEN_NO_PIN) free((void *)h->image); else cudaFreeHost((void *)h->image); }
-    cudaStreamDestroy(h->s_h2d);
-    cudaStreamDestroy(h->s_k);
-    cudaStreamDestroy(h->s_d2h);
-    for (auto sx : h->s_kx) cudaStreamDestroy(sx);
+    GlobalCache::StreamSet ss = {{h->s_h2d, h->s_k, h->s_d2h, h->s_kx[0], h->s_kx[1], h->s_kx[2]}};
+    if (!h->s_h2d || !h->s_k || !h->s_d2h || !h->s_kx[0] || !h->s_kx[1] || !h->s_kx[2] || !g_cache.give_streams(h->device, ss))
+      for (cudaStream_t st : ss.s) if (st) cudaStreamDestroy(st);
   }
   delete h;
 }
@@ -574,8 +621,18 @@ void flsgpu_trim_cache(void) {
     cudaSetDevice(d.first);
     for (auto &kv : d.second) cudaFree(kv.second);
   }
-  cudaSetDevice(cur);
   g_cache.dev.clear(); g_cache.dev_bytes = 0;
+  for (auto &d : g_cache.streams) {
+    cudaSetDevice(d.first);
+    for (auto &ss : d.second) for (cudaStream_t st : ss.s) cudaStreamDestroy(st);
+  }
+  g_cache.streams.clear();
+  for (auto &d : g_cache.events) {
+    cudaSetDevice(d.first);
+    for (cudaEvent_t e : d.second) cudaEventDestroy(e);
+  }
+  g_cache.events.clear();
+  cudaSetDevice(cur);
 }
 
 const char *flsgpu_last_error(const flsgpu_t *h) { return h ? h->err.c_str() : g_open_err.c_str(); }

@@ -56,6 +56,9 @@ public:
 	//! Projection and device filter stay; row-group pruning must be asked for again.
 	bool setRowGroupRange(idx_t g0, idx_t g1);
 	idx_t rowGroupCount() const;
+	//! A scan that needs no column (count(*)): readNextChunk serves the row counts of the current row-group range
+	//! from the footer and decodes nothing.
+	void setCountOnly(bool on);
 	//! Fills `result` with the next <= STANDARD_VECTOR_SIZE rows; false at the end of the file or on error.
 	bool readNextChunk(DataChunk &result);
 	void closeFile();

@@ -77,6 +77,7 @@ struct FastLanesScanState : public GlobalTableFunctionState {
 	vector<idx_t> projection; // file column id per output column
 	std::atomic<idx_t> rows_done {0};
 	bool initialized = false;
+	bool count_only = false; // no file column is projected (count(*))
 
 	idx_t MaxThreads() const override {
 		return max_threads;
@@ -116,6 +117,7 @@ static bool OpenFile(FastLanesLocalState &local, const FastLanesScanState &state
 		err = facade->lastError();
 		return false;
 	}
+	facade->setCountOnly(state.count_only);
 	if (!bind.zone_predicates.empty()) {
 		// late materialisation: the conjunction runs on the GPU, only the rows that pass come back
 		// (FLS_SCAN_NO_DEVICE_FILTER=1 keeps the row-group skipping alone, for A/B timing)
@@ -238,15 +240,17 @@ static unique_ptr<GlobalTableFunctionState> FastLanesInitGlobal(ClientContext &c
 	auto result = make_uniq<FastLanesScanState>();
 	auto &bind_data = input.bind_data->Cast<FastLanesBindData>();
 	// projection pushdown: output column i is file column column_ids[i]; a scan that needs no column at all
-	// (count(*)) gets the row-id pseudo column only -> decode the narrowest thing we can: column 0
+	// (count(*)) gets the row-id pseudo column only
 	for (auto col : input.column_ids) {
-		if (IsRowIdColumnId(col)) {
+		if (IsVirtualColumn(col)) { // the empty column of FastLanesVirtualColumns (or a row id): nothing of the file
 			continue;
 		}
 		result->projection.push_back(col);
 	}
 	if (result->projection.empty()) {
-		result->projection.push_back(0);
+		// nothing of the file is needed but its row counts: no decode at all (and never a column of another type
+		// copied into the row-id vector)
+		result->count_only = true;
 	}
 	// at most 16 scanning threads (every thread holds a handle with its page-locked buffers) and about four shards per
 	// thread, each of 8 to 64 row groups: long enough to keep a reader's H2D / decode / D2H pipeline full, short enough
@@ -309,6 +313,14 @@ static OperatorPartitionData FastLanesGetPartitionData(ClientContext &context, T
 		throw InternalException("scan_fastlanes: partition columns are not supported");
 	}
 	return OperatorPartitionData(input.local_state->Cast<FastLanesLocalState>().batch_index);
+}
+
+// The "empty" virtual column: a scan that needs no column (count(*)) asks for it instead of file column 0
+// (LogicalGet::GetAnyColumn, duckdb/src/planner/operator/logical_get.cpp:144-159) and gets row counts only.
+static virtual_column_map_t FastLanesVirtualColumns(ClientContext &context, optional_ptr<FunctionData> bind_data) {
+	virtual_column_map_t result;
+	result.insert(make_pair(COLUMN_IDENTIFIER_EMPTY, TableColumn("", LogicalType::BOOLEAN)));
+	return result;
 }
 
 static unique_ptr<NodeStatistics> FastLanesCardinality(ClientContext &context, const FunctionData *bind_data_p) {
@@ -438,6 +450,7 @@ void ScanFastLanes::Register(DatabaseInstance &db) {
 	for (auto name : {"scan_fastlanes", "read_fls"}) {
 		TableFunction fn(name, {LogicalType::VARCHAR}, FastLanesScan, FastLanesBind, FastLanesInitGlobal, FastLanesInitLocal);
 		fn.get_partition_data = FastLanesGetPartitionData;
+		fn.get_virtual_columns = FastLanesVirtualColumns;
 		fn.named_parameters["file"] = LogicalType::VARCHAR;
 		fn.named_parameters["gpus"] = LogicalType::LIST(LogicalType::INTEGER);
 		fn.named_parameters["device"] = LogicalType::INTEGER;

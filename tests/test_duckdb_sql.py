@@ -319,6 +319,28 @@ def test_nulls_round_trip_through_copy_and_read_fls(tmp_path):
     assert res[1]["rows"][0][1] != res[1]["rows"][0][0]       # there are NULLs
 
 
+def test_count_star_needs_no_decode_and_no_gpu(tmp_path):
+    """count(*) asks for the row-id pseudo column alone: the table function serves the row counts from the footer (no
+    CUDA device here) and never copies a file column of another type into the row-id vector — the first column of this
+    file is a VARCHAR of long strings."""
+    import fls_writer as W
+    n = 65536 * 2 + 4321
+    r = np.random.default_rng(3)
+    words = [b"x" * 40, b"yy" * 30, b"a somewhat longer comment string for the heap"]
+    col = W.StrColumn.from_list([words[i] for i in r.integers(0, 3, n)])
+    a, b = str(tmp_path / "a.fls"), str(tmp_path / "b.fls")
+    synth.encode([col, np.arange(n, dtype=np.int32)], ["s", "i"], path=a)
+    synth.encode([W.StrColumn.from_list([b"q"] * 1000), np.arange(1000, dtype=np.int32)], ["s", "i"], path=b)
+    res = sql("SELECT count(*) FROM read_fls('%s')" % a,
+              "SET threads = 1",
+              "SELECT count(*) FROM scan_fastlanes('%s')" % a,
+              "SELECT count(*) FROM read_fls(['%s', '%s', '%s'])" % (a, b, a),
+              "SELECT count(*) FROM (SELECT * FROM read_fls('%s') LIMIT 70000)" % a)
+    assert res[0]["rows"] == [[str(n)]] and res[2]["rows"] == [[str(n)]], res
+    assert res[3]["rows"] == [[str(2 * n + 1000)]], res[3]
+    assert res[4].get("rows") == [["70000"]] or "error" in res[4], res[4]   # needs no column either; a GPU only if DuckDB asks for one
+
+
 @pytest.mark.gpu
 def test_gpus_and_device_named_parameters(tmp_path):
     """`gpus := [..]` / `device := n` on read_fls / scan_fastlanes (the reference registers only `file`,
