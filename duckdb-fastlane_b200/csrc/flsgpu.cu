@@ -513,6 +513,43 @@ int ensure_ready(flsgpu *h) {
   return 0;
 }
 
+// Byte ranges (relative to the file offset of row group s0) that a decode of columns `cols` over row groups [s0, s1)
+// reads: the projected columns' chunks (and the chunk an EQUAL chunk names), each padded by 32 bytes for the kernels'
+// 16-byte-granular reads, merged where the gap between two is small — a copy call costs about as much as 128 KB on
+// the bus.  Every column projected = one range = the whole extent.
+struct StageRange { uint64_t off, len; };
+std::vector<StageRange> projected_ranges(const FlsTable &t, uint32_t s0, uint32_t s1, const std::vector<uint32_t> &cols, uint64_t ext) {
+  std::vector<StageRange> r;
+  std::vector<uint32_t> cs(cols);
+  std::sort(cs.begin(), cs.end());
+  cs.erase(std::unique(cs.begin(), cs.end()), cs.end());
+  if (cs.size() >= t.n_cols) { r.push_back({0, ext}); return r; }
+  auto add = [&](uint64_t a, uint64_t b) {
+    b = std::min(ext, b + 32);
+    a &= ~(uint64_t)15;
+    if (!r.empty() && a <= r.back().off + r.back().len + (128u << 10)) {
+      if (b > r.back().off + r.back().len) r.back().len = b - r.back().off;
+    } else if (b > a) r.push_back({a, b - a});
+  };
+  for (uint32_t g = s0; g < s1; ++g) {
+    const uint64_t base = t.rgs[g].off - t.rgs[s0].off;
+    std::vector<std::pair<uint64_t, uint64_t>> ch;
+    for (uint32_t c : cs) {
+      const fls_colchunk *k = &t.chunk(g, c);
+      if (k->scheme == FLS_S_EQUAL && k->aux32 < t.n_cols) k = &t.chunk(g, k->aux32);
+      uint64_t a = ~0ull, b = 0;
+      for (uint32_t sgi = 0; sgi < k->n_seg; ++sgi) {
+        a = std::min<uint64_t>(a, k->seg[sgi].off);
+        b = std::max<uint64_t>(b, k->seg[sgi].off + k->seg[sgi].size);
+      }
+      if (b > a) ch.emplace_back(base + a, base + b);
+    }
+    std::sort(ch.begin(), ch.end());
+    for (auto &x : ch) add(x.first, x.second);
+  }
+  return r;
+}
+
 uint64_t range_extent(const FlsTable &t, uint32_t g0, uint32_t g1) {
   return g1 > g0 ? t.rgs[g1 - 1].off + t.rgs[g1 - 1].size - t.rgs[g0].off : 0;
 }
@@ -1080,16 +1117,24 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     if (!resident) {
       if (h->gds) {  // GPUDirect Storage: file -> HBM, no host bounce (cuFileRead is synchronous)
         if (int rc = gds_read(h, d_stage + rel, t.rgs[s0].off, ext)) { const std::string m = h->err; return bail(rc, m); }
-      } else if (h->image_mapped) {  // mapped file: page cache -> page-locked bounce buffer -> HBM
-        void *bounce = h->host_alloc(ext);
-        if (!bounce) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
-        b->host_bufs.push_back(bounce);
-        parallel_copy(bounce, h->image + t.rgs[s0].off, ext);
-        CKB(cudaMemcpyAsync(d_stage + rel, bounce, ext, cudaMemcpyHostToDevice, h->s_h2d));
+        b->tm.h2d_bytes += ext;
       } else {
-        CKB(cudaMemcpyAsync(d_stage + rel, h->image + t.rgs[s0].off, ext, cudaMemcpyHostToDevice, h->s_h2d));
+        // only what the projected columns' chunks occupy crosses the bus (the staging buffer keeps the file's layout,
+        // so the planner's addresses do not change; the gaps are never read)
+        const std::vector<StageRange> ranges = projected_ranges(t, s0, s1, b->cols, ext);
+        uint8_t *bounce = nullptr;
+        if (h->image_mapped) {  // mapped file: page cache -> page-locked bounce buffer -> HBM
+          bounce = (uint8_t *)h->host_alloc(ext);
+          if (!bounce) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
+          b->host_bufs.push_back(bounce);
+        }
+        for (const StageRange &rg : ranges) {
+          const uint8_t *src = h->image + t.rgs[s0].off + rg.off;
+          if (bounce) { parallel_copy(bounce + rg.off, src, rg.len); src = bounce + rg.off; }
+          CKB(cudaMemcpyAsync(d_stage + rel + rg.off, src, rg.len, cudaMemcpyHostToDevice, h->s_h2d));
+          b->tm.h2d_bytes += rg.len;
+        }
       }
-      b->tm.h2d_bytes += ext;
     }
     if (!plan_hit)
       CKB(cudaMemcpyAsync(d_desc + desc0, h_desc + desc0, (desc_used - desc0) * sizeof(FlsChunkDev), cudaMemcpyHostToDevice,
