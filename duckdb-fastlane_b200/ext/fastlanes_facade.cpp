@@ -116,6 +116,21 @@ bool FastLanesFacade::setDeviceFilter(const std::vector<flsgpu_host::ZonePredica
 	return true;
 }
 
+// no byte of [p, p + n) has its top bit set: ASCII is valid UTF-8, and eight bytes at a time is an order of magnitude
+// faster than decoding code points
+static bool AllAscii(const uint8_t *p, uint64_t n) {
+	uint64_t acc = 0, i = 0;
+	for (; i + 32 <= n; i += 32) {
+		uint64_t w[4];
+		memcpy(w, p + i, 32);
+		acc |= w[0] | w[1] | w[2] | w[3];
+	}
+	for (; i < n; i++) {
+		acc |= (uint64_t)p[i] << 56;
+	}
+	return (acc & 0x8080808080808080ull) == 0;
+}
+
 template <class T>
 static void CopyFixed(Vector &out, const flsgpu_host::ColumnSlice &s, idx_t rows) {
 	memcpy(FlatVector::GetData<T>(out), s.data, rows * sizeof(T));
@@ -182,36 +197,33 @@ bool FastLanesFacade::readNextChunk(DataChunk &result) {
 			auto dst = FlatVector::GetData<string_t>(out);
 			const uint32_t first = s.offsets[0], last = s.offsets[rows];
 			bool ok = first <= last;
-			for (idx_t r = 0; ok && r < rows; r++) {
-				ok = s.offsets[r] <= s.offsets[r + 1];
+			idx_t long_bytes = 0;
+			for (idx_t r = 0; r < rows; r++) { // one pass: ascending offsets, bytes of the strings that are not inlined
+				const uint32_t a = s.offsets[r], b = s.offsets[r + 1];
+				ok = ok && a <= b;
+				const uint32_t len = b - a;
+				long_bytes += len > string_t::INLINE_LENGTH ? len : 0;
 			}
 			if (!ok) {
 				pImpl->error = "FastLanes file is damaged: string offsets of a chunk are not ascending";
 				return false;
 			}
-			if (s.type == FLSGPU_T_STR && last > first &&
+			if (s.type == FLSGPU_T_STR && last > first && !AllAscii(s.payload + first, last - first) &&
 			    Utf8Proc::Analyze(const_char_ptr_cast(s.payload + first), last - first) == UnicodeType::INVALID) {
 				pImpl->error = "FastLanes file holds a VARCHAR value that is not valid UTF-8";
 				return false;
 			}
-			idx_t long_bytes = 0;
-			for (idx_t r = 0; r < rows; r++) {
-				const uint32_t len = s.offsets[r + 1] - s.offsets[r];
-				long_bytes += len > string_t::INLINE_LENGTH ? len : 0;
-			}
-			char *heap = nullptr;
+			// the chunk's strings are one contiguous run of payload bytes: ONE copy into the vector's heap, then the
+			// long strings point into it (short ones are inlined by string_t's constructor)
+			const char *heap = nullptr;
 			if (long_bytes) {
-				heap = char_ptr_cast(StringVector::GetStringBuffer(out).AllocateShrinkableBuffer(long_bytes));
+				auto buf = StringVector::GetStringBuffer(out).AllocateShrinkableBuffer(last - first);
+				memcpy(buf, s.payload + first, last - first);
+				heap = const_char_ptr_cast(buf);
 			}
 			for (idx_t r = 0; r < rows; r++) {
 				const uint32_t a = s.offsets[r], len = s.offsets[r + 1] - a;
-				if (len <= string_t::INLINE_LENGTH) {
-					dst[r] = string_t(const_char_ptr_cast(s.payload + a), len);
-				} else {
-					memcpy(heap, s.payload + a, len);
-					dst[r] = string_t(heap, len);
-					heap += len;
-				}
+				dst[r] = len <= string_t::INLINE_LENGTH ? string_t(const_char_ptr_cast(s.payload + a), len) : string_t(heap + (a - first), len);
 			}
 			break;
 		}
