@@ -75,53 +75,6 @@ struct VecSTRCONST {
   }
 };
 
-// ===================================================================== FSST12 strings (12-bit codes, up to 4096 symbols)
-// chunk: seg[0]/[1] = decoded end-offset stream, seg[2]/[3] = compressed end-offset stream (both DELTA u32),
-//        seg[4] = symbol table (u64 symbol[aux32] | u8 len[aux32]; codes 0..255 = the bytes themselves, no escape),
-//        seg[5] = compressed bytes.  A string's codes are packed LSB first, two per three bytes.
-// The plain decoder: one warp per vector, both offset streams walked into the warp's tile one after the other, then
-// every lane decodes every 32nd string byte-wise with the 36 KB table read through L1 / L2.  (The 8-bit FSST kernel
-// keeps its table in shared memory; a 4096-entry table does not fit its replicated layout.  FSST12 chunks are written
-// only on request, the lineitem shape has none.)
-struct VecSTRFSST12 {
-  static constexpr uint32_t SMEM = DecDELTA<uint32_t>::SMEM, BLOCK_SMEM = 0;
-  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
-    const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
-    uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
-    if (bwd > 32u) bwd = 32u;
-    if (bwc > 32u) bwc = 32u;
-    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i, offs[i + 1] its end
-    const uint32_t *tile = (const uint32_t *)(w.sm + DecDELTA<uint32_t>::STAGE);
-    DecDELTA<uint32_t>::to_tile(w, k.seg[1] + 16ull * hd.ep, bwd, hd.base);
-    const uint32_t dv0 = ((const uint32_t *)w.sm)[0];  // lane 0's base = the vector's first decoded start
-    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + DecDELTA<uint32_t>::STAGE, offs + 1, t, k.pay_base); }
-    DecDELTA<uint32_t>::to_tile(w, k.seg[3] + 16ull * hc.ep, bwc, hc.base);
-    const uint32_t cv0 = ((const uint32_t *)w.sm)[0];
-    const uint64_t *sym = (const uint64_t *)k.seg[4];
-    const uint32_t n_sym = k.aux32 < 4096u ? k.aux32 : 4096u;
-    const uint8_t *len = k.seg[4] + 8ull * k.aux32, *comp = k.seg[5];
-    uint8_t *pay = k.pay + k.pay_base;
-    FLS_LANES(t) {
-      for (uint32_t i = t; i < FLS_VEC; i += 32u) {
-        const uint32_t c0 = i ? tile[fls_tile_slot<uint32_t>(i - 1u)] : cv0, c1 = tile[fls_tile_slot<uint32_t>(i)];
-        // decoded extent of the string: what phase 1 has just written (read back through L2), bounded by the row group's payload
-        uint64_t d0 = (i ? fls_ldcg(offs + i) - k.pay_base : dv0), d1 = fls_ldcg(offs + i + 1u) - k.pay_base;
-        if (c1 < c0 || c1 > k.aux64[1] || d1 < d0 || d1 > k.aux64[0]) continue;  // damaged offsets: nothing is written
-        const uint32_t n_codes = 2u * (c1 - c0) / 3u;
-        const uint8_t *in = comp + c0;
-        for (uint32_t q = 0; q < n_codes && d0 < d1; ++q) {
-          const uint8_t *p = in + 3u * (q >> 1);
-          uint32_t c = (q & 1u) ? ((uint32_t)fls_ldg(p + 1) >> 4) | ((uint32_t)fls_ldg(p + 2) << 4)
-                                : (uint32_t)fls_ldg(p) | (((uint32_t)fls_ldg(p + 1) & 15u) << 8);
-          if (c >= n_sym) c = 0;
-          uint64_t s = fls_ldg(sym + c);
-          for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(len + c)); b && d0 < d1; --b) { pay[d0++] = (uint8_t)s; s >>= 8; }
-        }
-      }
-    }
-  }
-};
-
 // ---- staged word writer.  A lane appends pieces of <= 8 bytes to ONE contiguous run inside the warp's shared
 // staging buffer.  State: `o` = 4-aligned address of the word being filled, `n8` = 8 * (bytes pending in that
 // word, 0..3), `prev` = a word whose TOP n8/8 bytes are the pending bytes.  A piece comes as a 16-byte table
@@ -228,6 +181,21 @@ FLS_DEV void fls_stage_store(FlsWarp &w, uint8_t *g, uint32_t h, uint32_t len) {
   const uint32_t tail_start = fls_max(16u * p1, head_end);
   uint8_t *gb = g - h;  // 16-byte aligned
   w.store_out(gb + 16u * p0, 16u * p0, p1 > p0 ? 16u * (p1 - p0) : 0u);
+  FLS_LANES(t) {
+    for (uint32_t i = h + t; i < head_end; i += 32u) gb[i] = stg[i];
+    for (uint32_t i = tail_start + t; i < end; i += 32u) gb[i] = stg[i];
+  }
+}
+
+// The same with the staging buffer at byte `off` (a multiple of 16) of the warp's slot.
+FLS_DEV void fls_stage_store_at(FlsWarp &w, uint32_t off, uint8_t *g, uint32_t h, uint32_t len) {
+  const uint8_t *stg = w.sm + off;
+  const uint32_t end = h + len;
+  const uint32_t p0 = h ? 1u : 0u, p1 = end >> 4;
+  const uint32_t head_end = fls_min(end, 16u * p0);
+  const uint32_t tail_start = fls_max(16u * p1, head_end);
+  uint8_t *gb = g - h;  // 16-byte aligned
+  w.store_out(gb + 16u * p0, off + 16u * p0, p1 > p0 ? 16u * (p1 - p0) : 0u);
   FLS_LANES(t) {
     for (uint32_t i = h + t; i < head_end; i += 32u) gb[i] = stg[i];
     for (uint32_t i = tail_start + t; i < end; i += 32u) gb[i] = stg[i];
@@ -670,6 +638,123 @@ struct VecSTRFLAGS {
         }
       }
     }
+  }
+};
+
+// ===================================================================== FSST12 strings (12-bit codes, up to 4096 symbols)
+// chunk: seg[0]/[1] = decoded end-offset stream, seg[2]/[3] = compressed end-offset stream (both DELTA u32),
+//        seg[4] = symbol table (u64 symbol[aux32] | u8 len[aux32]; codes 0..255 = the bytes themselves, no escape),
+//        seg[5] = compressed bytes.  A string's codes are packed LSB first, two per three bytes (an odd last code
+//        takes two bytes), so string boundaries matter: a lane decodes string by string.
+// One warp per vector.  Phase 1 walks both offset streams (decoded ends -> offsets[], compressed ends -> the warp's
+// tile).  Phase 2, per quarter of 256 strings: the quarter's compressed bytes are bulk-copied into the slot, lane t
+// owns the 8 consecutive strings 256q + 8t .. +7 = one contiguous run of output bytes, appended piece by piece
+// (FlsPush) to a staging buffer that leaves as one bulk copy.  The 36 KB symbol table is read through L1 (a
+// 4096-entry table does not fit the 8-bit kernel's replicated shared-memory layout).  A quarter whose compressed
+// bytes or output do not fit the slot, or whose offsets are damaged, takes the byte-wise path.
+// Slot: [0, 4224) offset-stream payload, later the compressed window | [4224, 8448) compressed ends (padded tile) |
+//       [8448, 8448 + STG) staging.
+struct VecSTRFSST12 {
+  static constexpr uint32_t CW = DecDELTA<uint32_t>::STAGE;   // 4224: compressed window
+  static constexpr uint32_t STG_OFF = DecDELTA<uint32_t>::SMEM, STG = 8448u;
+  static constexpr uint32_t SMEM = STG_OFF + STG, BLOCK_SMEM = 0;
+  static_assert(STG_OFF % 128u == 0 && SMEM % 128u == 0, "warp slots stay 128-byte aligned");
+  FLS_MEM static uint32_t code_at(const uint8_t *in, uint32_t q) {  // code q of a string whose codes start at `in`
+    const uint8_t *p = in + 3u * (q >> 1);
+    return (q & 1u) ? ((uint32_t)p[1] >> 4) | ((uint32_t)p[2] << 4) : (uint32_t)p[0] | (((uint32_t)p[1] & 15u) << 8);
+  }
+  // byte-wise, straight from / to global memory: strings i0, i0 + step, .. < i1 of the vector
+  FLS_MEM static void plain(const FlsChunkDev &k, const uint32_t *tile, const uint32_t *offs, uint32_t cv0, uint32_t dv0,
+                            uint32_t i0, uint32_t i1, uint32_t step) {
+    const uint64_t *sym = (const uint64_t *)k.seg[4];
+    const uint32_t n_sym = k.aux32 < 4096u ? k.aux32 : 4096u;
+    const uint8_t *len = k.seg[4] + 8ull * k.aux32, *comp = k.seg[5];
+    uint8_t *pay = k.pay + k.pay_base;
+    for (uint32_t i = i0; i < i1; i += step) {
+      const uint32_t c0 = i ? tile[fls_tile_slot<uint32_t>(i - 1u)] : cv0, c1 = tile[fls_tile_slot<uint32_t>(i)];
+      uint64_t d0 = (i ? fls_ldcg(offs + i) - k.pay_base : dv0), d1 = fls_ldcg(offs + i + 1u) - k.pay_base;
+      if (c1 < c0 || c1 > k.aux64[1] || d1 < d0 || d1 > k.aux64[0]) continue;  // damaged offsets: nothing is written
+      const uint32_t n_codes = 2u * (c1 - c0) / 3u;
+      const uint8_t *in = comp + c0;
+      for (uint32_t q = 0; q < n_codes && d0 < d1; ++q) {
+        const uint8_t *p = in + 3u * (q >> 1);
+        uint32_t c = (q & 1u) ? ((uint32_t)fls_ldg(p + 1) >> 4) | ((uint32_t)fls_ldg(p + 2) << 4)
+                              : (uint32_t)fls_ldg(p) | (((uint32_t)fls_ldg(p + 1) & 15u) << 8);
+        if (c >= n_sym) c = 0;
+        uint64_t sv = fls_ldg(sym + c);
+        for (uint32_t b = fls_min(8u, (uint32_t)fls_ldg(len + c)); b && d0 < d1; --b) { pay[d0++] = (uint8_t)sv; sv >>= 8; }
+      }
+    }
+  }
+  FLS_MEM static void run(const FlsChunkDev &k, uint32_t v, FlsWarp &w, const uint8_t *) {
+    const fls_vechdr hd = fls_load_hdr(k, 0, v), hc = fls_load_hdr(k, 2, v);
+    uint32_t bwd = FLS_META_BW(hd.meta), bwc = FLS_META_BW(hc.meta);
+    if (bwd > 32u) bwd = 32u;
+    if (bwc > 32u) bwc = 32u;
+    uint32_t *offs = (uint32_t *)k.out + (size_t)v * FLS_VEC;  // offs[i] = start of string i, offs[i + 1] its end
+    const uint32_t *tile = (const uint32_t *)(w.sm + CW);
+    DecDELTA<uint32_t>::to_tile(w, k.seg[1] + 16ull * hd.ep, bwd, hd.base);
+    const uint32_t dv0 = ((const uint32_t *)w.sm)[0];  // lane 0's base = the vector's first decoded start
+    FLS_LANES(t) { fls_tile_copy_out<uint32_t>(w.sm + CW, offs + 1, t, k.pay_base); }
+    DecDELTA<uint32_t>::to_tile(w, k.seg[3] + 16ull * hc.ep, bwc, hc.base);
+    const uint32_t cv0 = ((const uint32_t *)w.sm)[0];
+    const uint64_t *sym = (const uint64_t *)k.seg[4];
+    const uint32_t n_sym = k.aux32 < 4096u ? k.aux32 : 4096u;
+    const uint8_t *len = k.seg[4] + 8ull * k.aux32, *comp = k.seg[5];
+    uint8_t *pay = k.pay + k.pay_base;
+    for (uint32_t qt = 0; qt < 4u; ++qt) {
+      const uint32_t sq = 256u * qt;  // the quarter's first string
+      const uint32_t cq0 = sq ? tile[fls_tile_slot<uint32_t>(sq - 1u)] : cv0, cq1 = tile[fls_tile_slot<uint32_t>(sq + 255u)];
+      // decoded extent of the quarter: what phase 1 has just written (read back through L2)
+      const uint32_t dq0 = sq ? fls_ldcg(offs + sq) - k.pay_base : dv0, dq1 = fls_ldcg(offs + sq + 256u) - k.pay_base;
+      const uint32_t a0 = cq0 & ~15u, a1 = (cq1 + 15u) & ~15u;  // (the segment is padded to 16 bytes)
+      uint8_t *g = pay + dq0;
+      const uint32_t hh = (uint32_t)((uintptr_t)g & 15u), qlen = dq1 - dq0;
+      const bool fits = cq0 <= cq1 && cq1 <= k.aux64[1] && a1 - a0 <= CW && dq0 <= dq1 && dq1 <= k.aux64[0] && hh + qlen <= STG;
+      if (!fits) {
+        FLS_LANES(t) { plain(k, tile, offs, cv0, dv0, sq + t, sq + 256u, 32u); }
+        continue;
+      }
+      w.store_wait();  // the previous quarter's bulk copy has read the staging buffer
+      if (a1 > a0) { w.fence_async(); w.stage(0, comp + a0, a1 - a0); w.wait(); }
+      FLS_VAR(FlsPush, ps);
+      FLS_LANES(t) {
+        const uint32_t s0 = sq + 8u * t;
+        uint32_t dd[9];  // the decoded boundaries of the lane's 8 strings
+#pragma unroll
+        for (uint32_t j = 0; j < 9u; ++j) dd[j] = s0 + j ? fls_ldcg(offs + s0 + j) - k.pay_base : dv0;
+        bool ok = dd[0] >= dq0 && dd[8] <= dq1;
+#pragma unroll
+        for (uint32_t j = 0; j < 8u; ++j) ok = ok && dd[j] <= dd[j + 1u];
+        FlsPush p;
+        p.init(w.sm + STG_OFF, hh + (ok ? dd[0] - dq0 : 0u));
+        for (uint32_t j = 0; j < 8u; ++j) {
+          const uint32_t i = s0 + j;
+          const uint32_t c0 = i ? tile[fls_tile_slot<uint32_t>(i - 1u)] : cv0, c1 = tile[fls_tile_slot<uint32_t>(i)];
+          uint32_t left = ok ? dd[j + 1u] - dd[j] : 0u;  // damaged boundaries: the lane writes nothing
+          if (c0 <= c1 && c0 >= cq0 && c1 <= cq1) {
+            const uint8_t *in = w.sm + (c0 - a0);
+            const uint32_t n_codes = 2u * (c1 - c0) / 3u;
+            for (uint32_t q = 0; q < n_codes && left; ++q) {
+              uint32_t c = code_at(in, q);
+              if (c >= n_sym) c = 0;
+              const uint32_t L = fls_min(fls_min(8u, (uint32_t)fls_ldg(len + c)), left);
+              p.push(fls_piece_entry(fls_ldg(sym + c), L));
+              left -= L;
+            }
+          }
+          while (left) {  // codes that do not add up to the declared length: zeros, the run keeps its layout
+            const uint32_t L = fls_min(8u, left);
+            p.push(fls_piece_entry(0ull, L));
+            left -= L;
+          }
+        }
+        FLS_AT(ps) = p;
+      }
+      FLS_LANES(t) { FLS_AT(ps).finish(); }
+      fls_stage_store_at(w, STG_OFF, g, hh, qlen);
+    }
+    w.store_wait();
   }
 };
 
