@@ -735,7 +735,21 @@ struct VecSTRFSST12 {
           if (c0 <= c1 && c0 >= cq0 && c1 <= cq1) {
             const uint8_t *in = w.sm + (c0 - a0);
             const uint32_t n_codes = 2u * (c1 - c0) / 3u;
-            for (uint32_t q = 0; q < n_codes && left; ++q) {
+            uint32_t q = 0;
+            for (; q + 1u < n_codes && left; q += 2u) {  // two codes = three bytes; four table loads in flight
+              const uint8_t *pp = in + 3u * (q >> 1);
+              const uint32_t b1 = pp[1];
+              uint32_t ca = (uint32_t)pp[0] | ((b1 & 15u) << 8), cb = (b1 >> 4) | ((uint32_t)pp[2] << 4);
+              if (ca >= n_sym) ca = 0;
+              if (cb >= n_sym) cb = 0;
+              const uint64_t sa = fls_ldg(sym + ca), sb = fls_ldg(sym + cb);
+              const uint32_t la = fls_min(fls_min(8u, (uint32_t)fls_ldg(len + ca)), left);
+              const uint32_t lb = fls_min(fls_min(8u, (uint32_t)fls_ldg(len + cb)), left - la);
+              p.push(fls_piece_entry(sa, la));
+              p.push(fls_piece_entry(sb, lb));
+              left -= la + lb;
+            }
+            if (q < n_codes && left) {  // an odd last code
               uint32_t c = code_at(in, q);
               if (c >= n_sym) c = 0;
               const uint32_t L = fls_min(fls_min(8u, (uint32_t)fls_ldg(len + c)), left);
