@@ -16,6 +16,13 @@
 #define FLS_FOOTER_VERSION 1u
 
 #define FLS_VEC 1024u           /* values per FastLanes vector */
+/* dictionary-string kernel, short configuration (fls_strings.cuh): its staging buffer, and the longest entry of which any
+ * 256 fit it — what the planner routes by (fls_plan.h) */
+#ifndef FLS_DICT_SHORT_STG
+#define FLS_DICT_SHORT_STG 6656u
+#define FLS_DICT_SHORT_WARPS 20u
+#endif
+#define FLS_DICT_SHORT_MAXLEN ((FLS_DICT_SHORT_STG - 15u) / 256u) /* 25 */
 #define FLS_RG_VECS 64u         /* vectors per row group (65,536 rows;
                                    /root/reference/src/writer/write_fastlane_stream.cpp:21-24) */
 #define FLS_RG_ALIGN 256u       /* row groups start on 256-byte file offsets */

@@ -23,6 +23,7 @@ enum FlsKernelKind {
   FLS_K_VALIDITY,           // validity bitmap of a chunk (copied, or all ones) -> the column's bitmap
   FLS_K_FFOR_PATCH, FLS_K_CROSS_RLE, FLS_K_STR_FSST12,
   FLS_K_STR_FLAGS,           // STR_DICT chunk with up to 8 one-byte entries, every vector full (flag columns)
+  FLS_K_STR_DICT_LONG,       // STR_DICT chunk with an entry longer than FLS_DICT_SHORT_MAXLEN bytes (or unknown lengths)
   FLS_K_N
 };
 
@@ -105,6 +106,21 @@ static inline FlsColNeed fls_column_need(const FlsTable &t, uint32_t col, uint32
     n.payload_bytes += 16;
   }
   return n;
+}
+
+// Dictionary offsets u32[n + 1] (in the host image): is every entry at most FLS_DICT_SHORT_MAXLEN bytes long, so that any
+// 256 of them fit the staging buffer of the 20-warp configuration of the DICT kernel?
+static inline bool fls_dict_is_short(const uint8_t *offsets, uint64_t seg_size, uint32_t n) {
+  if (seg_size < 4ull * ((uint64_t)n + 1u)) return false;
+  uint32_t prev;
+  memcpy(&prev, offsets, 4);
+  for (uint32_t e = 0; e < n; ++e) {
+    uint32_t next;
+    memcpy(&next, offsets + 4ull * (e + 1u), 4);
+    if (next < prev || next - prev > FLS_DICT_SHORT_MAXLEN) return false;
+    prev = next;
+  }
+  return true;
 }
 
 // STR_DICT chunk `k` of a row group that starts at `rgp` in the host image: are its entries 1 .. 8 strings of one byte,
@@ -208,7 +224,8 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
             d.aux64[1] = flags8;
             fls_launch_for(ls, FLS_K_STR_FLAGS, 0).add(d, rd, wr);
           } else {
-            fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, rd, wr, g);
+            const bool sh = host_image && fls_dict_is_short(host_image + rg.off + k.seg[2].off, k.seg[2].size, k.aux32);
+            fls_launch_for(ls, sh ? FLS_K_STR_DICT : FLS_K_STR_DICT_LONG, 0).add(d, rd, wr, g);
           }
           break;
         }
@@ -225,7 +242,9 @@ static inline std::string fls_plan_column(const FlsTable &t, uint32_t col, uint3
           d.seg[2] = d.seg[6];
           d.seg[3] = out.scratch + scratch_off;
           scratch_off += ((uint64_t)sz + 31) & ~15ull;
-          fls_launch_for(ls, FLS_K_STR_DICT, 0).add(d, k.seg[0].size + k.seg[1].size + k.seg[4].size + k.seg[6].size, wr, g);
+          const bool sh = fls_dict_is_short(host_image + rg.off + k.seg[6].off, k.seg[6].size, k.aux32);
+          fls_launch_for(ls, sh ? FLS_K_STR_DICT : FLS_K_STR_DICT_LONG, 0)
+              .add(d, k.seg[0].size + k.seg[1].size + k.seg[4].size + k.seg[6].size, wr, g);
           break;
         }
         default: return "scheme not valid for a string column";

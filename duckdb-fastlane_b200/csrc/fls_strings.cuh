@@ -222,13 +222,14 @@ FLS_DEV void fls_walk32(const uint8_t *stage, uint32_t bw, uint32_t base, uint32
 // unpacks them straight from the staged payload with 128-bit loads; its strings form one contiguous run of
 // output bytes, appended piece by piece (FlsPush) to the warp's staging buffer, and its 8 end offsets leave as
 // two aligned 128-bit stores {run start, end 0 .. end 6} (end 7 is the next lane's run start).
-struct VecSTRDICT {
-#ifndef FLS_DICT_WARPS
-#define FLS_DICT_WARPS 16  /* the most that fit.  With the LDS/STG copy-out 14 was best (12 / 14 / 16 warps: 0.697 / 0.668 /
-                              0.683 ms on the SF10 launch); with the bulk-copy copy-out 16 is (see profiles/r01_SUMMARY.md) */
-#endif
-  static constexpr uint32_t WARPS = FLS_DICT_WARPS;
-  static constexpr uint32_t STG = 8448u;     // staging of one quarter's payload (33 bytes per string on average)
+// Two configurations of the same kernel: short entries (the planner routes a chunk here when 256 of its longest entry
+// fit the staging buffer) run 20 warps with a 6.5 KB staging buffer; every other dictionary the round-1 configuration,
+// 16 warps and 8.25 KB (quarters that still do not fit go byte-wise).  More warps keep paying on this kernel: 12 / 14 /
+// 16 / 18 / 20 warps = 0.508 / 0.468 / 0.437 / 0.420 / 0.403 ms on the two dictionary columns of the SF10 launch
+// (profiles/r02_dict_warps.log); at 20 the compiler is held to 96 registers.
+template <uint32_t WARPS_, uint32_t STG_> struct VecSTRDICTT {
+  static constexpr uint32_t WARPS = WARPS_;
+  static constexpr uint32_t STG = STG_;      // staging of one quarter's payload
   // staged index payload: two halves of HALF bytes (this vector's and the prefetched next one's, widths <= 10 bits),
   // or one vector's payload up to 20 bits wide, or — wider still — the packed rows of one quarter at a time
   static constexpr uint32_t IDX = STG, HALF = 1280u;
@@ -600,6 +601,8 @@ struct VecSTRDICT {
     }
   }
 };
+typedef VecSTRDICTT<FLS_DICT_SHORT_WARPS, FLS_DICT_SHORT_STG> VecSTRDICT;  // entries of up to FLS_DICT_SHORT_MAXLEN bytes
+typedef VecSTRDICTT<16u, 8448u> VecSTRDICTL;              // everything else
 
 // ===================================================================== flag columns
 // A STR_DICT chunk whose dictionary is up to 8 one-byte strings and whose vectors are all full (fls_dict_is_flags,

@@ -87,12 +87,13 @@ cudaError_t set_kernel_attrs() {
   if ((e = vec_attr<VecSTRFSST12>()) != cudaSuccess) return e;
   if ((e = vec_attr<VecSTRFLAGS>()) != cudaSuccess) return e;
   if ((e = chunk_attr<VecSTRDICT>()) != cudaSuccess) return e;
+  if ((e = chunk_attr<VecSTRDICTL>()) != cudaSuccess) return e;
   return chunk_attr<VecSTRFSST>();
 }
 
 const char *const kKindName[FLS_K_N] = {"ffor",     "delta",     "rle",      "dict",     "alp",  "alp_rd", "copy",
                                         "fill",     "str_offsets", "str_copy", "str_const", "str_dict", "str_fsst",
-                                        "fsst_dictprep", "validity", "ffor_patch", "cross_rle", "str_fsst12", "str_flags"};
+                                        "fsst_dictprep", "validity", "ffor_patch", "cross_rle", "str_fsst12", "str_flags", "str_dict_long"};
 
 struct LaunchRec {  // what is needed to (re)issue one launch once its descriptors are on the device
   int kind, width;
@@ -123,6 +124,7 @@ bool launch_kind(const LaunchRec &l, const FlsChunkDev *d, cudaStream_t s) {
     case FLS_K_STR_FSST12: vec_launch<VecSTRFSST12>(d, n, s); return true;
     case FLS_K_STR_FLAGS: vec_launch<VecSTRFLAGS>(d, n, s); return true;
     case FLS_K_STR_DICT: chunk_launch<VecSTRDICT>(d, n, s, l.cap); return true;
+    case FLS_K_STR_DICT_LONG: chunk_launch<VecSTRDICTL>(d, n, s, l.cap); return true;
     case FLS_K_STR_FSST: chunk_launch<VecSTRFSST>(d, n, s, l.cap); return true;
     case FLS_K_STR_FSST_DICTPREP: fls_fsst_dictprep_kernel<<<n * 8, 128, 0, s>>>(d, 8); return true;
     case FLS_K_VALIDITY: fls_validity_kernel<<<n, 256, 0, s>>>(d); return true;
@@ -1095,11 +1097,11 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     if (!perr.empty()) break;
     // dictionary preparation must run before the gathers that read it
     // ... and the longest kernels go first
-    auto rank_of = [](int kind) { return kind == FLS_K_STR_FSST_DICTPREP ? 0 : kind == FLS_K_STR_FSST ? 1 : kind == FLS_K_STR_DICT ? 2 : 3; };
+    auto rank_of = [](int kind) { return kind == FLS_K_STR_FSST_DICTPREP ? 0 : kind == FLS_K_STR_FSST ? 1 : (kind == FLS_K_STR_DICT || kind == FLS_K_STR_DICT_LONG) ? 2 : 3; };
     std::stable_sort(ls.begin(), ls.end(), [&](const FlsLaunch &a, const FlsLaunch &b2) { return rank_of(a.kind) < rank_of(b2.kind); });
     const size_t desc0 = desc_used;
     for (auto &l : ls) {
-      if (l.kind == FLS_K_STR_DICT || l.kind == FLS_K_STR_FSST) fls_sort_by_key(l);
+      if (l.kind == FLS_K_STR_DICT || l.kind == FLS_K_STR_DICT_LONG || l.kind == FLS_K_STR_FSST) fls_sort_by_key(l);
       if (desc_used + l.chunks.size() > desc_cap) { perr = "internal: descriptor overflow"; break; }
       memcpy(h_desc + desc_used, l.chunks.data(), l.chunks.size() * sizeof(FlsChunkDev));
       recs.push_back(LaunchRec{l.kind, l.width, (uint32_t)l.chunks.size(), l.bytes_read, l.bytes_written, l.vectors, 0u, desc_used});
@@ -1156,7 +1158,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     for (auto &l : recs) { if (l.kind == FLS_K_STR_FSST) has_fsst = true; else if (l.kind != FLS_K_STR_FSST_DICTPREP) has_other = true; }
     const bool split = !time_kernels && g_split_fsst > 0 && has_fsst && has_other;
     if (split) std::stable_sort(recs.begin(), recs.end(), [](const LaunchRec &a, const LaunchRec &b2) {
-      auto rk = [](int kind) { return kind == FLS_K_STR_FSST ? 0 : kind == FLS_K_STR_FSST_DICTPREP ? 1 : kind == FLS_K_STR_DICT ? 3 : 2; };
+      auto rk = [](int kind) { return kind == FLS_K_STR_FSST ? 0 : kind == FLS_K_STR_FSST_DICTPREP ? 1 : (kind == FLS_K_STR_DICT || kind == FLS_K_STR_DICT_LONG) ? 3 : 2; };
       return rk(a.kind) < rk(b2.kind); });
     for (auto &l : recs) {
       KEv ke = {nullptr, nullptr, l.kind * 5 + width_slot(l.width), l.rd, l.wr, l.vec};
@@ -1167,9 +1169,9 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
           l.cap = (uint32_t)g_split_fsst;
           ks = h->s_kx[0];
           if (!side_used[0]) { CKB(cudaStreamWaitEvent(ks, ek.a, 0)); side_used[0] = true; }
-        } else if (l.kind == FLS_K_STR_DICT) l.cap = (uint32_t)g_split_dict;
+        } else if (l.kind == FLS_K_STR_DICT || l.kind == FLS_K_STR_DICT_LONG) l.cap = (uint32_t)g_split_dict;
       } else
-      if (!time_kernels && recs.size() > 1 && l.kind != FLS_K_STR_FSST_DICTPREP && l.kind != FLS_K_STR_DICT) {
+      if (!time_kernels && recs.size() > 1 && l.kind != FLS_K_STR_FSST_DICTPREP && l.kind != FLS_K_STR_DICT && l.kind != FLS_K_STR_DICT_LONG) {
         const uint32_t si = l.kind == FLS_K_STR_FSST ? 0u : 1u + (rr++ & 1u);
         ks = h->s_kx[si];
         if (!side_used[si]) { CKB(cudaStreamWaitEvent(ks, ek.a, 0)); side_used[si] = true; }

@@ -231,6 +231,11 @@ def string_cases(n=70_000):
     strs = [mixed[i] for i in r.integers(0, 3, 65536)] + [(b"XY", b"ZW")[i] for i in r.integers(0, 2, n - 65536 + 4000)]
     out.append(("str_dict_mixed_then_uniform", [StrColumn.from_list(strs)], None, [W.STR_DICT], None))
     out.append(("str_dict_entries_17_bytes", [li[13]], None, [W.STR_DICT], None))
+    # quarters larger than the staging buffer: staged in 2 / 4 / 8 groups of lanes, byte-wise beyond
+    for lo, hi in ((20, 40), (40, 90), (90, 190), (300, 700)):
+        pool = _rand_strings(r, 40, lo, hi).to_list()
+        out.append(("str_dict_40_entries_len_%d_%d" % (lo, hi), [StrColumn.from_list([pool[i] for i in r.integers(0, 40, 9000)])],
+                    None, [W.STR_DICT], None))
     # flag columns (VecSTRFLAGS: up to 8 one-byte entries, full vectors): behind a row group with an odd payload size
     # (unaligned stores), with 8 entries including the bytes 0x00 and 0xFF, with a wide index stream, and a 9-entry
     # dictionary that must stay with the table kernel

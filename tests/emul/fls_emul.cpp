@@ -89,6 +89,7 @@ static bool run_launch(const FlsLaunch &l) {
     case FLS_K_STR_FSST12: run_vectors<VecSTRFSST12>(l); return true;
     case FLS_K_STR_FLAGS: run_vectors<VecSTRFLAGS>(l); return true;
     case FLS_K_STR_DICT: run_vectors<VecSTRDICT>(l); return true;
+    case FLS_K_STR_DICT_LONG: run_vectors<VecSTRDICTL>(l); return true;
     case FLS_K_STR_FSST: run_vectors<VecSTRFSST>(l); return true;
     case FLS_K_STR_FSST_DICTPREP:
       for (auto &k : l.chunks) fls_fsst_dictprep_chunk_host(k);
