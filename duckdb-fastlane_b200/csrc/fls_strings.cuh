@@ -809,7 +809,10 @@ struct VecSTRFSST {
   // symbols and literals 13 % of the warps' time was the spin on ready[], profiles/r02_SUMMARY.md).
   static constexpr uint32_t COPIES = FLS_FSST_COPIES, SH = 7u;
   static constexpr uint32_t BLOCK_SMEM = 256u * 16u * COPIES;  // one array
-  static constexpr uint32_t NBUF = 2, CONST_SMEM = 0, TABLES_SMEM = 3u * BLOCK_SMEM;
+#ifndef FLS_FSST_NBUF
+#define FLS_FSST_NBUF 2  /* 1: one symbol table per block (64 KB with the literals), warps spin at chunk boundaries */
+#endif
+  static constexpr uint32_t NBUF = FLS_FSST_NBUF, CONST_SMEM = 0, TABLES_SMEM = (NBUF + 1u) * BLOCK_SMEM;
   FLS_MEM static constexpr uint32_t tab_off(uint32_t b) { return 2u * b * BLOCK_SMEM; }
   static constexpr bool PIPELINED = true;
   static_assert(COPIES == 8u, "the entry stride is 128 bytes");
