@@ -293,9 +293,14 @@ struct flsgpu {
     if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); return nullptr; }
     return e;
   }
-  void *dev_alloc(size_t n) {
+  // `prefer`: the buffer a cached plan of the same decode was built for — taken when it is free and fits, so that a
+  // scan that walks a table batch by batch, again and again, finds each batch's descriptors still valid
+  void *dev_alloc(size_t n, const void *prefer = nullptr) {
     n = (n + 255) & ~(size_t)255;
     if (!n) n = 256;
+    if (prefer)
+      for (auto it = pool.free_dev.lower_bound(n); it != pool.free_dev.end() && it->first <= n + n / 4 + 4096; ++it)
+        if (it->second == prefer) { void *q = it->second; pool.free_dev.erase(it); return q; }
     void *p = pool.get(pool.free_dev, n);
     if (p) return p;
     size_t got = 0;
@@ -910,6 +915,14 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
 
   // ---- output buffers
   b->out.resize(nc); b->dev.resize(nc); b->need.resize(nc); b->parts.resize(nc); b->off64_dev.assign(nc, nullptr);
+  // a cached plan of this very decode (range, columns) names the buffers its descriptors point at: ask the pool for them
+  const flsgpu::PlanCache *hint = nullptr;
+  if (!to_host && !(h->flags & FLSGPU_OPEN_NO_PLAN_CACHE))
+    for (auto &pc : h->plans)
+      if (pc.valid && pc.g0 == g0 && pc.g1 == g1 && pc.cols == b->cols && pc.ptrs.size() == 2 + 4 * (size_t)nc &&
+          (!hint || pc.stamp > hint->stamp))
+        hint = &pc;  // (the most recently used one)
+  auto hinted = [&](size_t k) -> const void * { return hint ? hint->ptrs[k] : nullptr; };
   const uint64_t rows = t.rows(g0, g1), prow = t.padded_rows(g0, g1);
   uint64_t scratch_total = 0;
   for (uint32_t i = 0; i < nc; ++i) {
@@ -924,10 +937,10 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
     o.compressed_bytes = n.compressed_bytes; o.decoded_bytes = n.decoded_bytes;
     b->tm.compressed_bytes += n.compressed_bytes; b->tm.decoded_bytes += n.decoded_bytes;
     FlsColOut &d = b->dev[i];
-    auto dalloc = [&](size_t sz) { void *p = h->dev_alloc(sz); b->dev_bufs.push_back(p); return p; };
+    auto dalloc = [&](size_t sz, const void *prefer = nullptr) { void *p = h->dev_alloc(sz, prefer); b->dev_bufs.push_back(p); return p; };
     auto halloc = [&](size_t sz) { void *p = h->host_alloc(sz); b->host_bufs.push_back(p); return p; };
     if (o.width) {
-      if (!(d.data = dalloc(n.data_bytes))) return bail(FLSGPU_E_NOMEM, "out of device memory");
+      if (!(d.data = dalloc(n.data_bytes, hinted(2 + 4 * (size_t)i)))) return bail(FLSGPU_E_NOMEM, "out of device memory");
       o.data = d.data;
       if (to_host && !(o.data = halloc(n.data_bytes))) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
     } else {
@@ -942,8 +955,8 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
           row += (uint64_t)t.rgs[g].n_vec * FLS_VEC;
         }
       }
-      d.offsets = (uint32_t *)dalloc(n.offsets_bytes + 16 * parts.size());
-      d.payload = (uint8_t *)dalloc(n.payload_bytes);
+      d.offsets = (uint32_t *)dalloc(n.offsets_bytes + 16 * parts.size(), hinted(3 + 4 * (size_t)i));
+      d.payload = (uint8_t *)dalloc(n.payload_bytes, hinted(4 + 4 * (size_t)i));
       if (!d.offsets || !d.payload) return bail(FLSGPU_E_NOMEM, "out of device memory");
       o.offsets = d.offsets; o.payload = d.payload;
       o.payload_bytes = n.payload_bytes - 16;
@@ -960,7 +973,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
       scratch_total += n.scratch_bytes;
     }
     if (n.validity_bytes) {
-      if (!(d.validity = (uint8_t *)dalloc(n.validity_bytes + 16))) return bail(FLSGPU_E_NOMEM, "out of device memory");
+      if (!(d.validity = (uint8_t *)dalloc(n.validity_bytes + 16, hinted(5 + 4 * (size_t)i)))) return bail(FLSGPU_E_NOMEM, "out of device memory");
       o.validity = (uint64_t *)d.validity;
       if (to_host && !(o.validity = (uint64_t *)halloc(n.validity_bytes + 16))) return bail(FLSGPU_E_NOMEM, "out of pinned host memory");
     }
@@ -986,7 +999,7 @@ int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, u
   }
   uint8_t *d_scratch = nullptr;
   if (scratch_total) {
-    d_scratch = (uint8_t *)h->dev_alloc(scratch_total + 16);
+    d_scratch = (uint8_t *)h->dev_alloc(scratch_total + 16, hinted(1));
     b->dev_bufs.push_back(d_scratch);
     if (!d_scratch) return bail(FLSGPU_E_NOMEM, "out of device memory");
   }
