@@ -163,7 +163,9 @@ int flsgpu_rowgroup_dict_contains(flsgpu_t *h, uint32_t rg, uint32_t col, const 
 /* ---- decode ------------------------------------------------------------------------------------------- */
 /* Stage the compressed bytes of row groups [g0,g1) into HBM and keep them until close / the next call. */
 int flsgpu_make_resident(flsgpu_t *h, uint32_t g0, uint32_t g1);
-/* Decode columns cols[0..n_cols) (NULL = all) of row groups [g0,g1).  Returns when the batch is complete. */
+/* Decode columns cols[0..n_cols) (NULL = all) of row groups [g0,g1).  Returns when the batch is complete.
+ * Unless the range is resident, only the byte ranges of the listed columns' chunks are copied to the device
+ * (flsgpu_timing.h2d_bytes says how many). */
 int flsgpu_decode(flsgpu_t *h, uint32_t g0, uint32_t g1, const uint32_t *cols, uint32_t n_cols, uint32_t flags,
                   flsgpu_batch_t **out);
 uint32_t flsgpu_batch_num_columns(const flsgpu_batch_t *b);
